@@ -38,6 +38,7 @@ struct GemmEpilogue {
     const float* snake_invbeta = nullptr;  // [N] 1/exp(beta)
     int          snake_period  = 0;        // channel index = n % snake_period (0 = n)
     int          atomic        = 0;        // out_f32 += v via red.add (split-K); bias only from split 0
+    int          silu_f16      = 0;        // out_f16 = silu(v) (time-embedding MLP), out_f32 keeps v
 };
 
 struct GemmProblem {

@@ -1,0 +1,648 @@
+// Tap-GEMM for sm_100a (see gemm.h): warp-specialised, persistent, tcgen05 + TMEM + TMA.
+//
+// CTA = 10 warps:
+//   warps 0-3  weight decoders: packed codes (smem, landed by cp.async.bulk) -> fp16 UMMA tile (smem)
+//   warps 4-7  epilogue: TMEM -> registers -> fused element-wise -> global
+//   warp  8    TMA producer (activation boxes through a tensor map, weight tiles as 1-D bulk copies)
+//   warp  9    TMEM allocator + single-thread tcgen05.mma issuer
+// Tile = 128 (rows of A) x BN (rows of W) x 64 (K) per pipeline stage; accumulators are double-buffered
+// in TMEM (2 x BN columns) so the epilogue of tile i overlaps the MMAs of tile i+1.
+#include "gemm.h"
+#include "ptx.cuh"
+
+#include <cuda.h>
+#include <cstdio>
+#include <cstdlib>
+#include <mutex>
+
+namespace ace {
+
+namespace {
+
+constexpr int BM = 128;
+constexpr int BK = 64;
+constexpr int A_STAGE_BYTES = BM * BK * 2;     // 16 KB
+constexpr int W_SUB_BYTES   = TILE_N * BK * 2; // 16 KB per 128-row sub-tile
+constexpr int RAW_MAX_BYTES = 8704;            // largest packed tile (Q8_0)
+constexpr int NUM_THREADS   = 320;
+
+struct KParams {
+    const uint8_t* W;
+    int  wtype, tile_bytes;
+    int  N, n_tiles128;          // n_tiles128: number of 128-row weight tiles
+    int  kb_per_tap, taps, kb_total;
+    int  tap_stride, tap_offset;
+    int  B, l_out, m_tiles_per_b;
+    int  split_k;
+    GemmEpilogue epi;
+};
+
+template <int BN, bool QUANT>
+struct SmemLayout {
+    static constexpr int SUBS       = BN / 128;
+    static constexpr int B_STAGE    = SUBS * W_SUB_BYTES;
+    static constexpr int RAW_STAGE  = QUANT ? SUBS * RAW_MAX_BYTES : 0;
+    static constexpr int STAGE      = A_STAGE_BYTES + B_STAGE;
+    static constexpr int BUDGET     = 225 * 1024 - 1024 /*align slack*/ - 256 /*barriers*/;
+    static constexpr int STAGES_RAW = BUDGET / (STAGE + RAW_STAGE);
+    static constexpr int STAGES     = STAGES_RAW > 6 ? 6 : STAGES_RAW;
+    static constexpr int BYTES      = STAGES * (STAGE + RAW_STAGE) + 256 + 1024;
+};
+
+// ---------------------------------------------------------------- weight decoders (one thread = one tile row)
+__device__ __forceinline__ void st_chunk(uint8_t* btile, int row, int chunk, uint4 v) {
+    *reinterpret_cast<uint4*>(btile + row * 128 + ((chunk ^ (row & 7)) << 4)) = v;
+}
+__device__ __forceinline__ uint32_t h2u(__half2 h) { return *reinterpret_cast<uint32_t*>(&h); }
+__device__ __forceinline__ __half2 u2h(uint32_t u) { return *reinterpret_cast<__half2*>(&u); }
+
+// Q8_0 tile: codes [4][128][16] int8, scales [128][2] fp16 at +8192
+__device__ __forceinline__ void decode_q8_0(const uint8_t* raw, uint8_t* btile, int row) {
+    const __half2 sc2 = *reinterpret_cast<const __half2*>(raw + 8192 + row * 4);
+    const __half2 kOff = __floats2half2_rn(1152.f, 1152.f);
+#pragma unroll
+    for (int j = 0; j < 4; ++j) {
+        const uint4 q = *reinterpret_cast<const uint4*>(raw + j * 2048 + row * 16);
+        const __half s = (j < 2) ? __low2half(sc2) : __high2half(sc2);
+        const __half2 s2 = __half2half2(s);
+        const uint32_t w[4] = {q.x ^ 0x80808080u, q.y ^ 0x80808080u, q.z ^ 0x80808080u, q.w ^ 0x80808080u};
+        uint32_t o[8];
+#pragma unroll
+        for (int i = 0; i < 4; ++i) {
+            // bytes -> fp16 (1024 + u): 0x64 in the high byte of each half
+            const uint32_t lo = __byte_perm(w[i], 0x64646464u, 0x4140);
+            const uint32_t hi = __byte_perm(w[i], 0x64646464u, 0x4342);
+            o[2 * i]     = h2u(__hmul2(__hsub2(u2h(lo), kOff), s2));
+            o[2 * i + 1] = h2u(__hmul2(__hsub2(u2h(hi), kOff), s2));
+        }
+        st_chunk(btile, row, 2 * j, make_uint4(o[0], o[1], o[2], o[3]));
+        st_chunk(btile, row, 2 * j + 1, make_uint4(o[4], o[5], o[6], o[7]));
+    }
+}
+
+// Q4_K tile: nibble words [2][128][16], (d*sc, dmin*m) fp16 pairs [128][2] at +4096
+__device__ __forceinline__ void decode_q4_k(const uint8_t* raw, uint8_t* btile, int row) {
+    const uint2 sm = *reinterpret_cast<const uint2*>(raw + 4096 + row * 8);
+    const __half2 k1024 = __floats2half2_rn(1024.f, 1024.f);
+#pragma unroll
+    for (int j = 0; j < 2; ++j) {
+        const uint4 q = *reinterpret_cast<const uint4*>(raw + j * 2048 + row * 16);
+        const __half2 pr = u2h(j == 0 ? sm.x : sm.y);
+        const __half2 ds = __half2half2(__low2half(pr));
+        const __half2 dm = __hneg2(__half2half2(__high2half(pr)));
+        const uint32_t w[4] = {q.x, q.y, q.z, q.w};
+#pragma unroll
+        for (int wi = 0; wi < 4; ++wi) {
+            uint32_t o[4];
+#pragma unroll
+            for (int i = 0; i < 4; ++i) {
+                const uint32_t t = ((w[wi] >> (4 * i)) & 0x000F000Fu) | 0x64006400u;
+                o[i] = h2u(__hfma2(__hsub2(u2h(t), k1024), ds, dm));
+            }
+            st_chunk(btile, row, 4 * j + wi, make_uint4(o[0], o[1], o[2], o[3]));
+        }
+    }
+}
+
+// Q6_K tile: low nibble words [2][128][16], 2-bit plane [128][16] at +4096, fp16 d*sc [128][4] at +6144
+__device__ __forceinline__ void decode_q6_k(const uint8_t* raw, uint8_t* btile, int row) {
+    const uint4 hp = *reinterpret_cast<const uint4*>(raw + 4096 + row * 16);
+    const uint2 sc = *reinterpret_cast<const uint2*>(raw + 6144 + row * 8);
+    const uint32_t P[4] = {hp.x, hp.y, hp.z, hp.w};
+    const __half2 k1056 = __floats2half2_rn(1056.f, 1056.f);
+#pragma unroll
+    for (int j = 0; j < 2; ++j) {
+        const uint4 q = *reinterpret_cast<const uint4*>(raw + j * 2048 + row * 16);
+        const uint32_t w[4] = {q.x, q.y, q.z, q.w};
+#pragma unroll
+        for (int wi = 0; wi < 4; ++wi) {
+            const int g = 4 * j + wi;
+            const uint32_t Hs = (g & 1) ? (P[g >> 1] >> 4) : (P[g >> 1] << 4);
+            const uint32_t scw = (g >> 1) < 2 ? sc.x : sc.y;
+            const __half sh = ((g >> 1) & 1) ? __high2half(u2h(scw)) : __low2half(u2h(scw));
+            const __half2 s2 = __half2half2(sh);
+            uint32_t o[4];
+#pragma unroll
+            for (int i = 0; i < 4; ++i) {
+                const uint32_t t = ((w[wi] >> (4 * i)) & 0x000F000Fu) | ((Hs >> (2 * i)) & 0x00300030u) | 0x64006400u;
+                o[i] = h2u(__hmul2(__hsub2(u2h(t), k1056), s2));
+            }
+            st_chunk(btile, row, g, make_uint4(o[0], o[1], o[2], o[3]));
+        }
+    }
+}
+
+__device__ __forceinline__ void decode_tile(int wtype, const uint8_t* raw, uint8_t* btile, int row) {
+    if (wtype == W_Q8_0) decode_q8_0(raw, btile, row);
+    else if (wtype == W_Q4_K) decode_q4_k(raw, btile, row);
+    else decode_q6_k(raw, btile, row);
+}
+
+// ---------------------------------------------------------------- fused epilogue for 32 consecutive columns of one row
+// Snake: v + sin^2(a v) / b.  sin^2 has period pi: reduce with a two-term Cody-Waite split so the
+// MUFU sine only ever sees |r| <= pi/2 (abs error ~1e-6, independent of |a v|).
+__device__ __forceinline__ float snake_f(float v, float a, float inv_b) {
+    const float t = a * v;
+    const float k = rintf(t * 0.318309886183790672f);
+    float r = fmaf(-k, 3.140625f, t);
+    r = fmaf(-k, 9.67653589793e-4f, r);
+    const float s = __sinf(r);
+    return fmaf(s * s, inv_b, v);
+}
+
+__device__ __forceinline__ void epilogue_row32(const KParams& p, const float (&acc)[32], int b, int l, int n0,
+                                               bool add_bias) {
+    const GemmEpilogue& e = p.epi;
+    if (l >= p.l_out) return;
+    if (e.mode == EPI_SWIGLU) {
+        // columns (2j, 2j+1) = (gate_j, up_j)
+        const int nout = p.N >> 1;
+        const int j0 = n0 >> 1;
+        __half* o = e.out_f16 + (long)b * e.out_bstride + (long)l * e.ld_out + j0;
+        __align__(16) __half h[16];
+#pragma unroll
+        for (int i = 0; i < 16; ++i) {
+            const float g = acc[2 * i], u = acc[2 * i + 1];
+            h[i] = __float2half_rn(g / (1.0f + __expf(-g)) * u);
+        }
+        if (j0 + 16 <= nout) {
+            *reinterpret_cast<uint4*>(o) = *reinterpret_cast<const uint4*>(h);
+            *reinterpret_cast<uint4*>(o + 8) = *reinterpret_cast<const uint4*>(h + 8);
+        } else {
+            for (int i = 0; i < 16 && j0 + i < nout; ++i) o[i] = h[i];
+        }
+        return;
+    }
+    const long flat0 = (long)l * e.ld_out + n0 + e.out_shift;  // position inside the sample
+    const long base = (long)b * e.out_bstride + flat0;
+    const int ncols = min(32, p.N - n0);
+    if (ncols <= 0) return;
+    const bool interior = (ncols == 32) && flat0 >= 0 && flat0 + 32 <= e.out_valid;
+    float v[32];
+#pragma unroll
+    for (int i = 0; i < 32; ++i) v[i] = acc[i];
+    if (e.bias && add_bias) {
+#pragma unroll
+        for (int i = 0; i < 32; ++i) if (i < ncols) v[i] += __ldg(e.bias + n0 + i);
+    }
+    if (e.gate) {
+        const float* g = e.gate + (long)b * e.gate_bstride + n0;
+#pragma unroll
+        for (int i = 0; i < 32; ++i) if (i < ncols) v[i] *= __ldg(g + i);
+    }
+    if (e.atomic) {
+        for (int i = 0; i < ncols; ++i) {
+            const long f = flat0 + i;
+            if (f >= 0 && f < e.out_valid) atomicAdd(e.out_f32 + base + i, v[i]);
+        }
+        return;
+    }
+    if (interior && ((base & 3) == 0)) {
+        if (e.resid) {
+            const float4* r = reinterpret_cast<const float4*>(e.resid + base);
+#pragma unroll
+            for (int i = 0; i < 8; ++i) {
+                const float4 t = r[i];
+                v[4 * i] += t.x; v[4 * i + 1] += t.y; v[4 * i + 2] += t.z; v[4 * i + 3] += t.w;
+            }
+        }
+        if (e.out_f32) {
+            float4* o = reinterpret_cast<float4*>(e.out_f32 + base);
+#pragma unroll
+            for (int i = 0; i < 8; ++i) o[i] = make_float4(v[4 * i], v[4 * i + 1], v[4 * i + 2], v[4 * i + 3]);
+        }
+        if (e.out_f16) {
+            if (e.snake_alpha) {
+                const int c0 = e.snake_period ? (n0 % e.snake_period) : n0;  // period is a multiple of 32 or N<=period
+#pragma unroll
+                for (int i = 0; i < 32; ++i) v[i] = snake_f(v[i], __ldg(e.snake_alpha + c0 + i), __ldg(e.snake_invbeta + c0 + i));
+            } else if (e.silu_f16) {
+#pragma unroll
+                for (int i = 0; i < 32; ++i) v[i] = v[i] / (1.0f + __expf(-v[i]));
+            }
+            __align__(16) __half h[32];
+#pragma unroll
+            for (int i = 0; i < 32; ++i) h[i] = __float2half_rn(v[i]);
+            if ((base & 7) == 0) {
+                uint4* o = reinterpret_cast<uint4*>(e.out_f16 + base);
+#pragma unroll
+                for (int i = 0; i < 4; ++i) o[i] = reinterpret_cast<const uint4*>(h)[i];
+            } else {
+                uint2* o = reinterpret_cast<uint2*>(e.out_f16 + base);
+#pragma unroll
+                for (int i = 0; i < 8; ++i) o[i] = reinterpret_cast<const uint2*>(h)[i];
+            }
+        }
+        return;
+    }
+    // edge path: element-wise with bounds checks
+    for (int i = 0; i < ncols; ++i) {
+        const long f = flat0 + i;
+        if (f < 0 || f >= e.out_valid) continue;
+        float x = v[i];
+        if (e.resid) x += e.resid[base + i];
+        if (e.out_f32) e.out_f32[base + i] = x;
+        if (e.out_f16) {
+            if (e.snake_alpha) {
+                const int c = e.snake_period ? ((n0 + i) % e.snake_period) : (n0 + i);
+                x = snake_f(x, __ldg(e.snake_alpha + c), __ldg(e.snake_invbeta + c));
+            } else if (e.silu_f16) {
+                x = x / (1.0f + __expf(-x));
+            }
+            e.out_f16[base + i] = __float2half_rn(x);
+        }
+    }
+}
+
+}  // namespace
+
+namespace {
+
+// ---------------------------------------------------------------- the tensor-core kernel
+template <int BN, bool QUANT>
+__global__ void __launch_bounds__(NUM_THREADS, 1)
+gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const KParams p) {
+    using SL = SmemLayout<BN, QUANT>;
+    constexpr int STAGES = SL::STAGES;
+    constexpr int SUBS = SL::SUBS;
+    constexpr int TMEM_COLS = 2 * BN;  // two accumulators
+
+    extern __shared__ uint8_t smem_raw[];
+    uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
+    uint8_t* sA = smem;                                  // [STAGES][16 KB]
+    uint8_t* sB = sA + STAGES * A_STAGE_BYTES;           // [STAGES][SUBS*16 KB]
+    uint8_t* sR = sB + STAGES * SL::B_STAGE;             // [STAGES][SUBS*RAW_MAX] (QUANT only)
+    uint64_t* bars = reinterpret_cast<uint64_t*>(sR + STAGES * SL::RAW_STAGE);
+    uint64_t* full = bars;                  // [STAGES] operands of stage s are in smem
+    uint64_t* empty = bars + STAGES;        // [STAGES] MMAs reading stage s have completed
+    uint64_t* raw_full = bars + 2 * STAGES; // [STAGES] packed codes landed
+    uint64_t* raw_empty = bars + 3 * STAGES;// [STAGES] decoders done with the packed codes
+    uint64_t* acc_full = bars + 4 * STAGES; // [2]
+    uint64_t* acc_empty = acc_full + 2;     // [2]
+    uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(acc_empty + 2);
+
+    const int warp = threadIdx.x >> 5;
+    const int lane = threadIdx.x & 31;
+
+    const int m_tiles = p.B * p.m_tiles_per_b;
+    const int n_tiles = (p.n_tiles128 + SUBS - 1) / SUBS;
+    const int total_tiles = n_tiles * p.split_k * m_tiles;
+
+    if (threadIdx.x == 0) {
+        for (int s = 0; s < STAGES; ++s) {
+            ptx::mbar_init(&full[s], QUANT ? 1 + 4 : 1);
+            ptx::mbar_init(&empty[s], 1);
+            ptx::mbar_init(&raw_full[s], 1);
+            ptx::mbar_init(&raw_empty[s], 4);
+        }
+        for (int a = 0; a < 2; ++a) {
+            ptx::mbar_init(&acc_full[a], 1);
+            ptx::mbar_init(&acc_empty[a], 4);
+        }
+        ptx::fence_mbar_init();
+    }
+    if (warp == 9) {
+        ptx::tmem_alloc<TMEM_COLS>(tmem_slot);
+    }
+    if (warp == 8 && lane == 0) ptx::prefetch_tmap(&tmA);
+    ptx::tc_fence_before();
+    __syncthreads();
+    ptx::tc_fence_after();
+    const uint32_t tmem_base = *tmem_slot;
+
+    auto decode_tile_index = [&](int t, int& nt, int& sp, int& b, int& l0) {
+        const int mt = t % m_tiles;
+        const int rest = t / m_tiles;
+        sp = rest % p.split_k;
+        nt = rest / p.split_k;
+        b = mt / p.m_tiles_per_b;
+        l0 = (mt % p.m_tiles_per_b) * BM;
+    };
+    auto k_range = [&](int sp, int& kb0, int& kb1) {
+        kb0 = (int)((long)p.kb_total * sp / p.split_k);
+        kb1 = (int)((long)p.kb_total * (sp + 1) / p.split_k);
+    };
+
+    if (warp == 8) {
+        // ===================== TMA producer =====================
+        if (lane == 0) {
+            uint32_t g = 0;
+            for (int t = blockIdx.x; t < total_tiles; t += gridDim.x) {
+                int nt, sp, b, l0, kb0, kb1;
+                decode_tile_index(t, nt, sp, b, l0);
+                k_range(sp, kb0, kb1);
+                const int subs_valid = min(SUBS, p.n_tiles128 - nt * SUBS);
+                for (int kb = kb0; kb < kb1; ++kb, ++g) {
+                    const int s = g % STAGES;
+                    const uint32_t ph = (g / STAGES) & 1;
+                    const int tap = kb / p.kb_per_tap;
+                    const int c0 = (kb - tap * p.kb_per_tap) * BK;
+                    const int row = l0 + tap * p.tap_stride + p.tap_offset;
+                    ptx::mbar_wait(&empty[s], ph ^ 1);
+                    if (QUANT) {
+                        ptx::mbar_expect_tx(&full[s], A_STAGE_BYTES);
+                        ptx::tma_load_3d(sA + s * A_STAGE_BYTES, &tmA, &full[s], c0, row, b);
+                        ptx::mbar_wait(&raw_empty[s], ph ^ 1);
+                        ptx::mbar_expect_tx(&raw_full[s], (uint32_t)(subs_valid * p.tile_bytes));
+                        for (int sub = 0; sub < subs_valid; ++sub) {
+                            const size_t off = ((size_t)(nt * SUBS + sub) * p.kb_total + kb) * p.tile_bytes;
+                            ptx::bulk_load(sR + s * SL::RAW_STAGE + sub * RAW_MAX_BYTES, p.W + off, p.tile_bytes, &raw_full[s]);
+                        }
+                    } else {
+                        ptx::mbar_expect_tx(&full[s], A_STAGE_BYTES + subs_valid * W_SUB_BYTES);
+                        ptx::tma_load_3d(sA + s * A_STAGE_BYTES, &tmA, &full[s], c0, row, b);
+                        for (int sub = 0; sub < subs_valid; ++sub) {
+                            const size_t off = ((size_t)(nt * SUBS + sub) * p.kb_total + kb) * W_SUB_BYTES;
+                            ptx::bulk_load(sB + s * SL::B_STAGE + sub * W_SUB_BYTES, p.W + off, W_SUB_BYTES, &full[s]);
+                        }
+                    }
+                }
+            }
+        }
+    } else if (warp == 9) {
+        // ===================== MMA issuer =====================
+        constexpr uint32_t idesc = ptx::umma_idesc_f16(BM, BN);
+        uint32_t g = 0;
+        int it = 0;
+        for (int t = blockIdx.x; t < total_tiles; t += gridDim.x, ++it) {
+            int nt, sp, b, l0, kb0, kb1;
+            decode_tile_index(t, nt, sp, b, l0);
+            k_range(sp, kb0, kb1);
+            const int a = it & 1;
+            const uint32_t aph = (it >> 1) & 1;
+            ptx::mbar_wait(&acc_empty[a], aph ^ 1);
+            ptx::tc_fence_after();
+            const uint32_t d_tmem = tmem_base + (uint32_t)(a * BN);
+            for (int kb = kb0; kb < kb1; ++kb, ++g) {
+                const int s = g % STAGES;
+                const uint32_t ph = (g / STAGES) & 1;
+                ptx::mbar_wait(&full[s], ph);
+                ptx::tc_fence_after();
+                if (lane == 0) {
+                    const uint32_t a_addr = ptx::smem_u32(sA + s * A_STAGE_BYTES);
+                    const uint32_t b_addr = ptx::smem_u32(sB + s * SL::B_STAGE);
+#pragma unroll
+                    for (int k = 0; k < BK / 16; ++k) {
+                        const uint64_t da = ptx::umma_desc_sw128(a_addr + k * 32);
+                        const uint64_t db = ptx::umma_desc_sw128(b_addr + k * 32);
+                        ptx::umma_f16(d_tmem, da, db, idesc, (kb > kb0 || k > 0) ? 1u : 0u);
+                    }
+                    ptx::umma_commit(&empty[s]);
+                    if (kb == kb1 - 1) ptx::umma_commit(&acc_full[a]);
+                }
+                __syncwarp();
+            }
+        }
+    } else if (warp < 4) {
+        // ===================== weight decoders =====================
+        if (QUANT) {
+            const int row = threadIdx.x;  // 0..127
+            uint32_t g = 0;
+            for (int t = blockIdx.x; t < total_tiles; t += gridDim.x) {
+                int nt, sp, b, l0, kb0, kb1;
+                decode_tile_index(t, nt, sp, b, l0);
+                k_range(sp, kb0, kb1);
+                const int subs_valid = min(SUBS, p.n_tiles128 - nt * SUBS);
+                for (int kb = kb0; kb < kb1; ++kb, ++g) {
+                    const int s = g % STAGES;
+                    const uint32_t ph = (g / STAGES) & 1;
+                    ptx::mbar_wait(&raw_full[s], ph);
+                    ptx::mbar_wait(&empty[s], ph ^ 1);
+                    for (int sub = 0; sub < subs_valid; ++sub)
+                        decode_tile(p.wtype, sR + s * SL::RAW_STAGE + sub * RAW_MAX_BYTES,
+                                    sB + s * SL::B_STAGE + sub * W_SUB_BYTES, row);
+                    ptx::fence_proxy_async_smem();
+                    __syncwarp();
+                    if (lane == 0) {
+                        ptx::mbar_arrive(&full[s]);
+                        ptx::mbar_arrive(&raw_empty[s]);
+                    }
+                }
+            }
+        }
+    } else {
+        // ===================== epilogue (warps 4..7 -> TMEM lanes 32*(warp-4)) =====================
+        const int q = warp - 4;
+        int it = 0;
+        for (int t = blockIdx.x; t < total_tiles; t += gridDim.x, ++it) {
+            int nt, sp, b, l0, kb0, kb1;
+            decode_tile_index(t, nt, sp, b, l0);
+            k_range(sp, kb0, kb1);
+            const int a = it & 1;
+            const uint32_t aph = (it >> 1) & 1;
+            ptx::mbar_wait(&acc_full[a], aph);
+            ptx::tc_fence_after();
+            const int l = l0 + q * 32 + lane;
+            const uint32_t taddr = tmem_base + ((uint32_t)(q * 32) << 16) + (uint32_t)(a * BN);
+#pragma unroll 1
+            for (int c = 0; c < BN / 32; ++c) {
+                const int n0 = nt * BN + c * 32;
+                if (n0 >= p.N) break;  // warp-uniform
+                uint32_t r[32];
+                ptx::tmem_ld32(taddr + c * 32, r);
+                ptx::tmem_ld_wait();
+                float acc[32];
+#pragma unroll
+                for (int i = 0; i < 32; ++i) acc[i] = __uint_as_float(r[i]);
+                if (kb1 > kb0) epilogue_row32(p, acc, b, l, n0, sp == 0);
+            }
+            ptx::tc_fence_before();
+            __syncwarp();
+            if (lane == 0) ptx::mbar_arrive(&acc_empty[a]);
+        }
+    }
+
+    ptx::tc_fence_before();
+    __syncthreads();
+    if (warp == 9) {
+        ptx::tc_fence_after();
+        ptx::tmem_dealloc<TMEM_COLS>(tmem_base);
+    }
+}
+
+// ---------------------------------------------------------------- plain-FMA debug kernel (same operands, same epilogue)
+// One thread per (row, 32-column group); decodes the packed weight element-wise. Slow by construction; it exists so
+// the tcgen05 kernel can be bisected against an independent implementation on the GPU.
+__device__ float packed_weight_at(const KParams& p, int n, int kbt, int k) {
+    const int nt = n >> 7, r = n & 127;
+    const uint8_t* tile = p.W + ((size_t)nt * p.kb_total + kbt) * p.tile_bytes;
+    if (p.wtype == W_F16) {
+        const __half h = *reinterpret_cast<const __half*>(tile + r * 128 + (((k >> 3) ^ (r & 7)) << 4) + (k & 7) * 2);
+        return __half2float(h);
+    }
+    if (p.wtype == W_Q8_0) {
+        const int8_t c = (int8_t)tile[(k >> 4) * 2048 + r * 16 + (k & 15)];
+        const __half s = *reinterpret_cast<const __half*>(tile + 8192 + r * 4 + (k >> 5) * 2);
+        return __half2float(__hmul(__int2half_rn(c), s));
+    }
+    if (p.wtype == W_Q4_K) {
+        const int j = k >> 5, wi = (k >> 3) & 3, i = k & 7;
+        const uint32_t w = *reinterpret_cast<const uint32_t*>(tile + j * 2048 + r * 16 + wi * 4);
+        const int nib = (i >> 1) + ((i & 1) ? 4 : 0);
+        const int c = (w >> (4 * nib)) & 0xF;
+        const __half ds = *reinterpret_cast<const __half*>(tile + 4096 + r * 8 + j * 4);
+        const __half dm = *reinterpret_cast<const __half*>(tile + 4096 + r * 8 + j * 4 + 2);
+        return __half2float(__hfma(__int2half_rn(c), ds, __hneg(dm)));
+    }
+    const int g = k >> 3, i = k & 7;
+    const uint32_t w = *reinterpret_cast<const uint32_t*>(tile + (g >> 2) * 2048 + r * 16 + (g & 3) * 4);
+    const uint32_t P = *reinterpret_cast<const uint32_t*>(tile + 4096 + r * 16 + (g >> 1) * 4);
+    const int nib = (i >> 1) + ((i & 1) ? 4 : 0);
+    const int lo = (w >> (4 * nib)) & 0xF;
+    const int bit = ((g & 1) ? 8 : 0) + ((i & 1) ? 16 : 0) + 2 * (i >> 1);
+    const int hi = (P >> bit) & 3;
+    const __half s = *reinterpret_cast<const __half*>(tile + 6144 + r * 8 + (g >> 1) * 2);
+    return __half2float(__hmul(__int2half_rn((lo | (hi << 4)) - 32), s));
+}
+
+__global__ void gemm_simt_kernel(const __half* A, long a_lstride, long a_bstride, int L, int C, const KParams p) {
+    const int groups = (p.N + 31) / 32;
+    const long idx = (long)blockIdx.x * blockDim.x + threadIdx.x;
+    const long total = (long)p.B * p.l_out * groups;
+    if (idx >= total) return;
+    const int gq = (int)(idx % groups);
+    const long rest = idx / groups;
+    const int l = (int)(rest % p.l_out);
+    const int b = (int)(rest / p.l_out);
+    const int n0 = gq * 32;
+    float acc[32];
+#pragma unroll
+    for (int i = 0; i < 32; ++i) acc[i] = 0.f;
+    for (int kbt = 0; kbt < p.kb_total; ++kbt) {
+        const int tap = kbt / p.kb_per_tap;
+        const int c0 = (kbt - tap * p.kb_per_tap) * BK;
+        const int row = l + tap * p.tap_stride + p.tap_offset;
+        if (row < 0 || row >= L) continue;
+        const __half* a = A + (long)b * a_bstride + (long)row * a_lstride;
+        for (int k = 0; k < BK && c0 + k < C; ++k) {
+            const float av = __half2float(a[c0 + k]);
+            for (int i = 0; i < 32; ++i)
+                if (n0 + i < p.N) acc[i] = fmaf(av, packed_weight_at(p, n0 + i, kbt, k), acc[i]);
+        }
+    }
+    KParams q = p;
+    q.epi.atomic = 0;  // debug kernel never splits K: plain read-modify-write
+    if (p.epi.atomic) q.epi.resid = p.epi.out_f32;
+    epilogue_row32(q, acc, b, l, n0, true);
+}
+
+}  // namespace
+
+// ---------------------------------------------------------------- host side
+namespace {
+
+typedef CUresult (*PFN_encodeTiled)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*,
+                                    const cuuint64_t*, const cuuint32_t*, const cuuint32_t*, CUtensorMapInterleave,
+                                    CUtensorMapSwizzle, CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
+
+PFN_encodeTiled get_encode_fn() {
+    static PFN_encodeTiled fn = nullptr;
+    static std::once_flag once;
+    std::call_once(once, [] {
+        void* sym = nullptr;
+        cudaDriverEntryPointQueryResult qres;
+        if (cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &sym, cudaEnableDefault, &qres) == cudaSuccess &&
+            qres == cudaDriverEntryPointSuccess)
+            fn = reinterpret_cast<PFN_encodeTiled>(sym);
+    });
+    return fn;
+}
+
+bool make_tmap_a(const GemmProblem& g, CUtensorMap* tm) {
+    PFN_encodeTiled enc = get_encode_fn();
+    if (!enc) return false;
+    const long bstride = g.B > 1 ? g.a_bstride : (long)g.L * g.a_lstride;
+    cuuint64_t dims[3] = {(cuuint64_t)g.C, (cuuint64_t)g.L, (cuuint64_t)g.B};
+    cuuint64_t strides[2] = {(cuuint64_t)g.a_lstride * 2, (cuuint64_t)bstride * 2};
+    cuuint32_t box[3] = {(cuuint32_t)BK, (cuuint32_t)BM, 1};
+    cuuint32_t estr[3] = {1, 1, 1};
+    const CUresult r = enc(tm, CU_TENSOR_MAP_DATA_TYPE_FLOAT16, 3, const_cast<__half*>(g.A), dims, strides, box, estr,
+                           CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_128B,
+                           CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+    return r == CUDA_SUCCESS;
+}
+
+template <int BN, bool QUANT>
+cudaError_t launch_tc(const CUtensorMap& tm, const KParams& kp, int grid, cudaStream_t stream) {
+    using SL = SmemLayout<BN, QUANT>;
+    static bool attr_set = false;
+    if (!attr_set) {
+        cudaError_t e = cudaFuncSetAttribute(gemm_tc_kernel<BN, QUANT>, cudaFuncAttributeMaxDynamicSharedMemorySize, SL::BYTES);
+        if (e != cudaSuccess) return e;
+        attr_set = true;
+    }
+    gemm_tc_kernel<BN, QUANT><<<grid, NUM_THREADS, SL::BYTES, stream>>>(tm, kp);
+    return cudaGetLastError();
+}
+
+}  // namespace
+
+int device_sm_count() {
+    static int sms = 0;
+    if (sms == 0) {
+        int dev = 0;
+        cudaGetDevice(&dev);
+        cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
+        if (sms <= 0) sms = 148;
+    }
+    return sms;
+}
+
+bool gemm_force_simt() {
+    static int v = -1;
+    if (v < 0) {
+        const char* e = std::getenv("ACE_B200_GEMM");
+        v = (e && std::string(e) == "simt") ? 1 : 0;
+    }
+    return v == 1;
+}
+
+cudaError_t gemm_launch(const GemmProblem& g, cudaStream_t stream, bool simt) {
+    const PackedWeight& w = *g.W;
+    KParams kp;
+    kp.W = static_cast<const uint8_t*>(w.dev);
+    kp.wtype = w.wtype;
+    kp.tile_bytes = w.tile_bytes;
+    kp.N = w.N;
+    kp.n_tiles128 = w.n_tiles;
+    kp.kb_per_tap = w.kb_per_tap;
+    kp.taps = w.taps;
+    kp.kb_total = w.taps * w.kb_per_tap;
+    kp.tap_stride = g.tap_stride;
+    kp.tap_offset = g.tap_offset;
+    kp.B = g.B;
+    kp.l_out = g.l_out;
+    kp.m_tiles_per_b = (g.l_out + BM - 1) / BM;
+    kp.split_k = g.split_k < 1 ? 1 : g.split_k;
+    if (kp.split_k > kp.kb_total) kp.split_k = kp.kb_total;
+    kp.epi = g.epi;
+    if (kp.split_k > 1) kp.epi.atomic = 1;
+    if (kp.epi.out_valid == 0) kp.epi.out_valid = (long)g.l_out * kp.epi.ld_out;
+    if (g.C != w.K) return cudaErrorInvalidValue;
+
+    if (simt || gemm_force_simt()) {
+        kp.split_k = 1;
+        const long total = (long)g.B * g.l_out * ((w.N + 31) / 32);
+        const int threads = 128;
+        gemm_simt_kernel<<<(unsigned)((total + threads - 1) / threads), threads, 0, stream>>>(g.A, g.a_lstride, g.a_bstride,
+                                                                                            g.L, g.C, kp);
+        return cudaGetLastError();
+    }
+
+    CUtensorMap tm;
+    if (!make_tmap_a(g, &tm)) return cudaErrorInvalidValue;
+    const int sms = device_sm_count();
+    const int m_tiles = kp.B * kp.m_tiles_per_b;
+    const long tiles256 = (long)((kp.n_tiles128 + 1) / 2) * m_tiles * kp.split_k;
+    const long tiles128 = (long)kp.n_tiles128 * m_tiles * kp.split_k;
+    static const char* force_bn = std::getenv("ACE_B200_GEMM_BN");
+    bool bn256 = kp.n_tiles128 >= 2 && tiles256 >= 2L * sms;
+    if (force_bn) bn256 = (std::atoi(force_bn) == 256) && kp.n_tiles128 >= 2;
+    const long tiles = bn256 ? tiles256 : tiles128;
+    const int grid = (int)(tiles < sms ? tiles : sms);
+    const bool quant = w.wtype != W_F16;
+    if (bn256) return quant ? launch_tc<256, true>(tm, kp, grid, stream) : launch_tc<256, false>(tm, kp, grid, stream);
+    return quant ? launch_tc<128, true>(tm, kp, grid, stream) : launch_tc<128, false>(tm, kp, grid, stream);
+}
+
+}  // namespace ace

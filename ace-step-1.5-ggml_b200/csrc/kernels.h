@@ -1,0 +1,60 @@
+// Launchers of the non-GEMM kernels of the path (element-wise / normalisation / attention / VAE tail).
+// Every function enqueues on `st` and returns; errors surface through cudaGetLastError() at the call site.
+#pragma once
+#include <cstdint>
+#include <cuda_fp16.h>
+#include <cuda_runtime.h>
+
+namespace ace {
+
+// ---- DiT input side ------------------------------------------------------------------------------
+// x0[b, p, k*in_ch + c] = (c < ctx_dim ? context[b, 2p+k, c] : hidden[b, 2p+k, c-ctx_dim]), zero past T
+// reference: acestep_dit_model.cpp:1343-1377 (pack + zero pad to a patch multiple)
+void launch_pack_dit_input(const float* hidden, const float* context, __half* x0, int B, int T, int S, int patch,
+                           int ctx_dim, int audio_dim, cudaStream_t st);
+void launch_f32_to_f16(const float* src, __half* dst, long n, cudaStream_t st);
+// patch_mask[b, p] = any(mask[b, p*patch + k] != 0); mask == nullptr -> all ones  (acestep_dit_model.cpp:1433-1449)
+void launch_patch_mask(const int32_t* mask, int32_t* patch_mask, int B, int T, int S, int patch, cudaStream_t st);
+// 256-d sinusoidal features of 1000*t: [cos(0..127) | sin(0..127)], freqs exp(-ln(1e4) i/128)
+// reference: acestep_dit_model.cpp:1261-1284.  t: [n] device floats -> out fp16 [n, 256]
+void launch_timestep_features(const float* t, __half* out, int n, cudaStream_t st);
+// mod[b, layer, j, :] = table[layer][j, :] + proj[b, j, :]   with +1 folded into the scale rows (j = 1, 4)
+// out_mod[b, j, :]    = out_table[j, :] + temb_a[b, :] + temb_b[b, :]        (+1 on j = 1)
+// reference: acestep_dit_model.cpp:1469-1481, 1522-1526, 1537-1549
+void launch_build_modulation(const float* tables /*[layers,6,H]*/, const float* proj /*[B,6,H]*/, float* mod,
+                             const float* out_table /*[2,H]*/, const float* temb_a, const float* temb_b,
+                             float* out_mod /*[B,2,H]*/, int B, int layers, int H, cudaStream_t st);
+
+// ---- normalisation -------------------------------------------------------------------------------
+// y = fp16( x / sqrt(mean(x^2)+eps) * w * scale1[b] + shift[b] );  scale1/shift may be null (plain RMSNorm)
+// reference: ggml_rms_norm (ggml-cpu/ops.cpp:3646-3697) + acestep_dit_model.cpp:1097-1106, 1477-1481
+void launch_rmsnorm_mod(const float* x, const float* w, const float* scale1, const float* shift, long mod_bstride,
+                        __half* y, int B, int rows_per_b, int H, float eps, cudaStream_t st);
+// in place on a token-major fp16 buffer: per (token, head) RMSNorm over head_dim=128 with weight w, then NEOX RoPE
+// (pairs (i, i+64), angle pos * theta^(-2i/128)) when rope_tab != null.  rope_tab: [S, 64] (cos, sin) float2.
+// reference: acestep_dit_model.cpp:1202-1210, ggml_rope_ext NEOX (ggml-cpu/ops.cpp:5637-5777)
+void launch_headnorm_rope(__half* buf, long row_stride, int col0, int n_heads, const float* w, const float2* rope_tab,
+                          int B, int rows_per_b, float eps, cudaStream_t st);
+void launch_build_rope_table(float2* tab, int S, int half_dim, float theta, cudaStream_t st);
+
+// ---- attention -----------------------------------------------------------------------------------
+// O[b, q, h, :] = softmax_k( Q[b,q,h,:].K[b,k,h/rep,:] / sqrt(128) + mask ) V      (head_dim = 128)
+// Q/K/V/O are token-major fp16 with independent row strides; key k is visible to query q iff
+// (window < 0 or |q-k| <= window) and (key_mask == null or key_mask[b,k] != 0).
+// reference: acestep_dit_model.cpp:1132-1173 (mask), 1212-1256 (GQA repeat, scale, softmax, PV)
+void launch_attention(const __half* Q, long q_stride, const __half* K, long k_stride, const __half* V, long v_stride,
+                      __half* O, long o_stride, const int32_t* key_mask, int B, int q_len, int k_len, int n_heads,
+                      int n_kv_heads, int window, cudaStream_t st);
+
+// ---- sampler -------------------------------------------------------------------------------------
+// x -= v * dt   (acestep_ggml.cpp:2075-2085);  with CFG: v = v_u + g (v_c - v_u)
+void launch_euler_step(float* x, const float* v_cond, const float* v_uncond, float guidance, float dt, long n,
+                       cudaStream_t st);
+
+// ---- VAE tail ------------------------------------------------------------------------------------
+// final conv: out[b, l, co] = sum_{tap, c} xs[b, l + tap - pad, c] * w[co, tap, c]  (+bias) for tiny C_out (audio channels)
+// reference: acestep_vae_model.cpp:999-1000 (conv2 k7, no bias)
+void launch_conv_small_out(const __half* xs, const __half* w /*[Cout, taps, C]*/, const float* bias, float* out, int B,
+                           long L, int C, int Cout, int taps, int pad, cudaStream_t st);
+
+}  // namespace ace

@@ -1,0 +1,324 @@
+"""ctypes bridge to ``libacestep_b200.so`` — the host-side mirror of the reference's plugin seam.
+
+The acestep pipeline reaches the ggml library through ``GGMLCAPIBridge`` and two monkey-patch installers
+(reference: ``scripts/run_non_ggml_real_case.py:135-354`` bridge, ``:445-538`` DiT hook, ``:541-661`` VAE hook).
+``B200Bridge`` keeps that class's method names, argument meaning and error behaviour (``RuntimeError`` carrying
+``ace_ggml_last_error``) so the same hooks work when handed this object, and adds the batched / device-resident
+entry points of ``include/acestep_b200.h``.
+
+There is no CPU fallback: if the shared library is missing, or no sm_100 device is present, construction raises.
+"""
+from __future__ import annotations
+
+import ctypes
+import os
+from pathlib import Path
+from typing import Optional, Sequence
+
+import numpy as np
+
+_HERE = Path(__file__).resolve().parent
+DEFAULT_LIB = _HERE / "lib" / "libacestep_b200.so"
+
+_F = ctypes.POINTER(ctypes.c_float)
+_I = ctypes.POINTER(ctypes.c_int32)
+_P = ctypes.c_void_p
+
+STATUS_NAMES = {0: "OK", 1: "ERR", 2: "ERR_INVALID_ARG", 3: "ERR_IO", 4: "ERR_UNSUPPORTED"}
+
+
+class AceInitParams(ctypes.Structure):
+    """``ace_ggml_init_params`` (acestep_ggml.h:31-35)."""
+    _fields_ = [("n_threads", ctypes.c_int32), ("use_metal", ctypes.c_int32),
+                ("compute_buffer_bytes", ctypes.c_size_t)]
+
+
+# every symbol include/acestep_ggml.h and include/acestep_b200.h declare: (restype, argtypes)
+SIGNATURES = {
+    "ace_ggml_create": (ctypes.c_int, [ctypes.POINTER(AceInitParams), ctypes.POINTER(_P)]),
+    "ace_ggml_destroy": (None, [_P]),
+    "ace_ggml_last_error": (ctypes.c_char_p, [_P]),
+    "ace_ggml_load_lm": (ctypes.c_int, [_P, ctypes.c_char_p]),
+    "ace_ggml_load_text_encoder": (ctypes.c_int, [_P, ctypes.c_char_p]),
+    "ace_ggml_load_dit": (ctypes.c_int, [_P, ctypes.c_char_p]),
+    "ace_ggml_load_vae": (ctypes.c_int, [_P, ctypes.c_char_p]),
+    "ace_ggml_vae_get_info": (ctypes.c_int, [_P, _I, _I, _I]),
+    "ace_ggml_vae_decode": (ctypes.c_int, [_P, _F, ctypes.c_int32, _F, ctypes.c_size_t]),
+    "ace_ggml_vae_encode": (ctypes.c_int, [_P, _F, ctypes.c_int32, _F, ctypes.c_size_t]),
+    "ace_ggml_text_encoder_forward": (ctypes.c_int, [_P, _I, ctypes.c_int32, _F, ctypes.c_size_t]),
+    "ace_ggml_text_encoder_forward_masked": (ctypes.c_int, [_P, _I, _I, ctypes.c_int32, _F, ctypes.c_size_t]),
+    "ace_ggml_text_encoder_forward_embeddings": (ctypes.c_int, [_P, _I, ctypes.c_int32, _F, ctypes.c_size_t]),
+    "ace_ggml_text_encoder_forward_layers": (ctypes.c_int, [_P, _I, _I, ctypes.c_int32, ctypes.c_int32,
+                                                            ctypes.c_int32, _F, ctypes.c_size_t]),
+    "ace_ggml_dit_forward": (ctypes.c_int, [_P, _F, _F, _F, _I, _I, ctypes.c_int32, ctypes.c_int32,
+                                            ctypes.c_float, ctypes.c_float, _F, ctypes.c_size_t]),
+    "ace_ggml_generate_audio_simple": (ctypes.c_int, [_P, _I, ctypes.c_int32, ctypes.c_int32, ctypes.c_float,
+                                                      ctypes.c_int32, _F, ctypes.c_size_t, _I, _I]),
+    "ace_ggml_generate_audio_style_lyric_simple": (ctypes.c_int, [_P, _I, ctypes.c_int32, _I, ctypes.c_int32,
+                                                                  ctypes.c_int32, ctypes.c_float, ctypes.c_int32,
+                                                                  _F, ctypes.c_size_t, _I, _I]),
+    "ace_ggml_generate_audio_style_lyric_timbre_simple": (ctypes.c_int, [_P, _I, ctypes.c_int32, _I, ctypes.c_int32,
+                                                                         _F, _I, ctypes.c_int32, ctypes.c_int32,
+                                                                         ctypes.c_int32, ctypes.c_float,
+                                                                         ctypes.c_int32, _F, ctypes.c_size_t, _I, _I]),
+    "ace_b200_dit_forward_batched": (ctypes.c_int, [_P, _F, _F, _F, _I, _I, ctypes.c_int32, ctypes.c_int32,
+                                                    ctypes.c_int32, _F, _F, _F, ctypes.c_size_t]),
+    "ace_b200_generate_latents": (ctypes.c_int, [_P, _F, _F, _F, _F, _I, _I, ctypes.c_int32, ctypes.c_int32,
+                                                 ctypes.c_int32, _F, ctypes.c_int32, ctypes.c_float, _F,
+                                                 ctypes.c_size_t]),
+    "ace_b200_vae_decode_batched": (ctypes.c_int, [_P, _F, ctypes.c_int32, ctypes.c_int32, _F, ctypes.c_size_t]),
+    "ace_b200_generate_audio": (ctypes.c_int, [_P, _F, _F, _F, _F, _I, _I, ctypes.c_int32, ctypes.c_int32,
+                                               ctypes.c_int32, _F, ctypes.c_int32, ctypes.c_float, _F, _F,
+                                               ctypes.c_size_t]),
+    "ace_b200_shift_schedule": (ctypes.c_int, [ctypes.c_float, ctypes.c_int32, _F]),
+    "ace_b200_last_device_ms": (ctypes.c_double, [_P]),
+    "ace_b200_kernel_launches": (ctypes.c_uint64, []),
+    "ace_b200_model_info": (ctypes.c_char_p, [_P]),
+    "ace_b200_debug_gemm": (ctypes.c_int, [_P, _F, ctypes.c_int32, ctypes.c_int32, ctypes.c_int32, _P, ctypes.c_int32,
+                                           ctypes.c_int32, ctypes.c_int32, ctypes.c_int32, ctypes.c_int32,
+                                           ctypes.c_int32, _F, _F, ctypes.c_int32, ctypes.c_int32, _F,
+                                           ctypes.c_size_t]),
+    "ace_b200_debug_attention": (ctypes.c_int, [_P, _F, _F, _F, _I, ctypes.c_int32, ctypes.c_int32, ctypes.c_int32,
+                                                ctypes.c_int32, ctypes.c_int32, ctypes.c_int32, _F, ctypes.c_size_t]),
+    "ace_b200_debug_pack_roundtrip": (ctypes.c_int, [_P, ctypes.c_int32, ctypes.c_int32, ctypes.c_int32, _F, _F]),
+}
+
+
+def load_library(lib_path: Optional[os.PathLike] = None) -> ctypes.CDLL:
+    """dlopen the library and bind every declared symbol (raises if the library or a symbol is missing)."""
+    path = Path(lib_path) if lib_path else Path(os.environ.get("ACE_B200_LIB", DEFAULT_LIB))
+    if not path.exists():
+        raise RuntimeError(f"{path} not found: build it with `make -C ace-step-1.5-ggml_b200/csrc` "
+                           "(there is no CPU fallback)")
+    lib = ctypes.CDLL(str(path))
+    for name, (res, args) in SIGNATURES.items():
+        fn = getattr(lib, name)  # AttributeError if the export is missing
+        fn.restype = res
+        fn.argtypes = args
+    return lib
+
+
+def _f(a: Optional[np.ndarray]):
+    return a.ctypes.data_as(_F) if a is not None else None
+
+
+def _i(a: Optional[np.ndarray]):
+    return a.ctypes.data_as(_I) if a is not None else None
+
+
+def _f32(a, ndim=None) -> Optional[np.ndarray]:
+    if a is None:
+        return None
+    a = np.ascontiguousarray(a, dtype=np.float32)
+    if ndim is not None and a.ndim != ndim:
+        raise ValueError(f"expected a {ndim}-D array, got shape {a.shape}")
+    return a
+
+
+def _i32(a) -> Optional[np.ndarray]:
+    return None if a is None else np.ascontiguousarray(a, dtype=np.int32)
+
+
+class B200Bridge:
+    """Same surface as the reference ``GGMLCAPIBridge`` (run_non_ggml_real_case.py:135-354)."""
+
+    def __init__(self, lib_path: Optional[os.PathLike] = None, n_threads: int = 1, compute_buffer_mb: int = 0,
+                 use_metal: bool = False):
+        self.lib = load_library(lib_path)
+        self.ctx = _P()
+        prm = AceInitParams(int(n_threads), 1 if use_metal else 0, int(compute_buffer_mb) * 1024 * 1024)
+        st = self.lib.ace_ggml_create(ctypes.byref(prm), ctypes.byref(self.ctx))
+        if st != 0 or not self.ctx:
+            self.ctx = _P()
+            raise RuntimeError(f"ace_ggml_create failed with status {st} ({STATUS_NAMES.get(st, '?')}): "
+                               "an sm_100 CUDA device is required")
+        self.latent_channels = 0
+        self.audio_channels = 0
+        self.hop_length = 0
+        self.dit_dims = None
+
+    # ------------------------------------------------------------------ plumbing
+    def _last_error(self) -> str:
+        msg = self.lib.ace_ggml_last_error(self.ctx)
+        return msg.decode("utf-8", "replace") if msg else ""
+
+    def _ensure_ok(self, status: int, where: str) -> None:
+        if status != 0:
+            raise RuntimeError(f"{where} failed: status={status} ({STATUS_NAMES.get(status, '?')}) {self._last_error()}")
+
+    def close(self) -> None:
+        if getattr(self, "ctx", None):
+            self.lib.ace_ggml_destroy(self.ctx)
+            self.ctx = _P()
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+    def __enter__(self):
+        return self
+
+    def __exit__(self, *exc):
+        self.close()
+
+    # ------------------------------------------------------------------ loads
+    def load_text_encoder(self, model_dir) -> None:
+        self._ensure_ok(self.lib.ace_ggml_load_text_encoder(self.ctx, str(model_dir).encode()), "ace_ggml_load_text_encoder")
+
+    def load_dit(self, model_dir) -> None:
+        self._ensure_ok(self.lib.ace_ggml_load_dit(self.ctx, str(model_dir).encode()), "ace_ggml_load_dit")
+
+    def load_vae(self, model_dir) -> None:
+        self._ensure_ok(self.lib.ace_ggml_load_vae(self.ctx, str(model_dir).encode()), "ace_ggml_load_vae")
+        a, b, c = ctypes.c_int32(), ctypes.c_int32(), ctypes.c_int32()
+        self._ensure_ok(self.lib.ace_ggml_vae_get_info(self.ctx, ctypes.byref(a), ctypes.byref(b), ctypes.byref(c)),
+                        "ace_ggml_vae_get_info")
+        self.latent_channels, self.audio_channels, self.hop_length = a.value, b.value, c.value
+
+    # ------------------------------------------------------------------ reference-shaped calls (one sample)
+    def vae_decode_tfirst(self, latents_tfirst: np.ndarray) -> np.ndarray:
+        """latents [T, C] -> audio [T*hop, channels]."""
+        if self.audio_channels <= 0 or self.hop_length <= 0:
+            raise RuntimeError("VAE not initialized in bridge")
+        lat = _f32(latents_tfirst, 2)
+        n = int(lat.shape[0])
+        out = np.empty((n * self.hop_length, self.audio_channels), dtype=np.float32)
+        self._ensure_ok(self.lib.ace_ggml_vae_decode(self.ctx, _f(lat), n, _f(out), out.nbytes), "ace_ggml_vae_decode")
+        return out
+
+    def dit_forward_tfirst(self, hidden_states_tfirst, context_latents_tfirst, encoder_hidden_states_tfirst,
+                           attention_mask, encoder_attention_mask, timestep: float, timestep_r: float) -> np.ndarray:
+        """hidden [T, D], context [T, Ctx], encoder states [L, H], masks [T] / [L] (or None) -> v [T, D]."""
+        hs = _f32(hidden_states_tfirst, 2)
+        cx = _f32(context_latents_tfirst, 2)
+        enc = _f32(encoder_hidden_states_tfirst, 2) if encoder_hidden_states_tfirst is not None else None
+        am, eam = _i32(attention_mask), _i32(encoder_attention_mask)
+        T = int(hs.shape[0])
+        E = int(enc.shape[0]) if enc is not None else 0
+        out = np.empty_like(hs)
+        st = self.lib.ace_ggml_dit_forward(self.ctx, _f(hs), _f(cx), _f(enc) if E else None, _i(am), _i(eam), T, E,
+                                           float(timestep), float(timestep_r), _f(out), out.nbytes)
+        self._ensure_ok(st, "ace_ggml_dit_forward")
+        return out
+
+    # ------------------------------------------------------------------ batched / device-resident extensions
+    def dit_forward_batched(self, hidden, context, enc, attention_mask, encoder_attention_mask,
+                            timesteps: Sequence[float], timesteps_r: Sequence[float]) -> np.ndarray:
+        hs, cx = _f32(hidden, 3), _f32(context, 3)
+        en = _f32(enc, 3) if enc is not None else None
+        am, eam = _i32(attention_mask), _i32(encoder_attention_mask)
+        B, T = int(hs.shape[0]), int(hs.shape[1])
+        E = int(en.shape[1]) if en is not None else 0
+        t = _f32(np.broadcast_to(np.asarray(timesteps, dtype=np.float32), (B,)))
+        tr = _f32(np.broadcast_to(np.asarray(timesteps_r, dtype=np.float32), (B,)))
+        out = np.empty_like(hs)
+        st = self.lib.ace_b200_dit_forward_batched(self.ctx, _f(hs), _f(cx), _f(en) if E else None, _i(am), _i(eam),
+                                                   B, T, E, _f(t), _f(tr), _f(out), out.nbytes)
+        self._ensure_ok(st, "ace_b200_dit_forward_batched")
+        return out
+
+    def shift_schedule(self, shift: float, n_steps: int) -> np.ndarray:
+        out = np.empty((n_steps,), dtype=np.float32)
+        self._ensure_ok(self.lib.ace_b200_shift_schedule(float(shift), int(n_steps), _f(out)), "ace_b200_shift_schedule")
+        return out
+
+    def generate_latents(self, noise, context, enc, uncond_enc=None, attention_mask=None, encoder_attention_mask=None,
+                         schedule=None, guidance: float = 1.0) -> np.ndarray:
+        x, cx = _f32(noise, 3), _f32(context, 3)
+        en = _f32(enc, 3) if enc is not None else None
+        un = _f32(uncond_enc, 3) if uncond_enc is not None else None
+        am, eam = _i32(attention_mask), _i32(encoder_attention_mask)
+        sch = _f32(schedule, 1)
+        B, T = int(x.shape[0]), int(x.shape[1])
+        E = int(en.shape[1]) if en is not None else 0
+        out = np.empty_like(x)
+        st = self.lib.ace_b200_generate_latents(self.ctx, _f(x), _f(cx), _f(en) if E else None, _f(un), _i(am), _i(eam),
+                                                B, T, E, _f(sch), int(sch.shape[0]), float(guidance), _f(out), out.nbytes)
+        self._ensure_ok(st, "ace_b200_generate_latents")
+        return out
+
+    def vae_decode_batched(self, latents) -> np.ndarray:
+        lat = _f32(latents, 3)
+        B, T = int(lat.shape[0]), int(lat.shape[1])
+        out = np.empty((B, T * self.hop_length, self.audio_channels), dtype=np.float32)
+        self._ensure_ok(self.lib.ace_b200_vae_decode_batched(self.ctx, _f(lat), B, T, _f(out), out.nbytes),
+                        "ace_b200_vae_decode_batched")
+        return out
+
+    def generate_audio(self, noise, context, enc, uncond_enc=None, attention_mask=None, encoder_attention_mask=None,
+                       schedule=None, guidance: float = 1.0, out_audio: Optional[np.ndarray] = None,
+                       return_latents: bool = False):
+        x, cx = _f32(noise, 3), _f32(context, 3)
+        en = _f32(enc, 3) if enc is not None else None
+        un = _f32(uncond_enc, 3) if uncond_enc is not None else None
+        am, eam = _i32(attention_mask), _i32(encoder_attention_mask)
+        sch = _f32(schedule, 1)
+        B, T = int(x.shape[0]), int(x.shape[1])
+        E = int(en.shape[1]) if en is not None else 0
+        audio = out_audio if out_audio is not None else np.empty((B, T * self.hop_length, self.audio_channels), np.float32)
+        lat = np.empty_like(x) if return_latents else None
+        st = self.lib.ace_b200_generate_audio(self.ctx, _f(x), _f(cx), _f(en) if E else None, _f(un), _i(am), _i(eam),
+                                              B, T, E, _f(sch), int(sch.shape[0]), float(guidance), _f(lat), _f(audio),
+                                              audio.nbytes)
+        self._ensure_ok(st, "ace_b200_generate_audio")
+        return (audio, lat) if return_latents else audio
+
+    # ------------------------------------------------------------------ measurement
+    def last_device_ms(self) -> float:
+        return float(self.lib.ace_b200_last_device_ms(self.ctx))
+
+    def kernel_launches(self) -> int:
+        return int(self.lib.ace_b200_kernel_launches())
+
+    def model_info(self) -> str:
+        return self.lib.ace_b200_model_info(self.ctx).decode()
+
+    # ------------------------------------------------------------------ unit-test hooks
+    def debug_gemm(self, A, W, *, w_type: int = 0, N: int, taps: int = 1, tap_stride: int = 0, tap_offset: int = 0,
+                   l_out: Optional[int] = None, bias=None, resid=None, swiglu=False, split_k=False, simt=False):
+        A = _f32(A, 3)
+        B, L, C = (int(v) for v in A.shape)
+        l_out = L if l_out is None else int(l_out)
+        if w_type in (0, -8):
+            Wb = _f32(W)
+            wp = Wb.ctypes.data_as(_P)
+        else:
+            Wb = np.ascontiguousarray(W, dtype=np.uint8)
+            wp = Wb.ctypes.data_as(_P)
+        bias = _f32(bias)
+        resid = _f32(resid)
+        epi = (1 if bias is not None else 0) | (2 if swiglu else 0) | (4 if resid is not None else 0) | (8 if split_k else 0)
+        n_out = N // 2 if swiglu else N
+        out = np.empty((B, l_out, n_out), dtype=np.float32)
+        st = self.lib.ace_b200_debug_gemm(self.ctx, _f(A), B, L, C, wp, int(w_type), int(N), int(taps), int(tap_stride),
+                                          int(tap_offset), l_out, _f(bias), _f(resid), epi, 1 if simt else 0, _f(out),
+                                          out.nbytes)
+        self._ensure_ok(st, "ace_b200_debug_gemm")
+        return out
+
+    def debug_attention(self, Q, K, V, key_mask=None, n_heads: int = 1, n_kv: int = 1, window: int = -1):
+        Q, K, V = _f32(Q, 3), _f32(K, 3), _f32(V, 3)
+        km = _i32(key_mask)
+        B, ql, kl = int(Q.shape[0]), int(Q.shape[1]), int(K.shape[1])
+        out = np.empty_like(Q)
+        st = self.lib.ace_b200_debug_attention(self.ctx, _f(Q), _f(K), _f(V), _i(km), B, ql, kl, int(n_heads), int(n_kv),
+                                               int(window), _f(out), out.nbytes)
+        self._ensure_ok(st, "ace_b200_debug_attention")
+        return out
+
+
+def pack_roundtrip(W, w_type: int, N: int, K: int, lib: Optional[ctypes.CDLL] = None):
+    """CPU-only: (kernel-decoder emulation of the packed tiles, ggml dequantisation) of the same rows."""
+    lib = lib or load_library()
+    if w_type == 0:
+        Wb = _f32(W)
+    else:
+        Wb = np.ascontiguousarray(W, dtype=np.uint8)
+    un = np.empty((N, K), dtype=np.float32)
+    ref = np.empty((N, K), dtype=np.float32)
+    st = lib.ace_b200_debug_pack_roundtrip(Wb.ctypes.data_as(_P), int(w_type), int(N), int(K), _f(un), _f(ref))
+    if st != 0:
+        raise RuntimeError(f"ace_b200_debug_pack_roundtrip failed: {st}")
+    return un, ref

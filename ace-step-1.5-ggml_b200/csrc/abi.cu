@@ -1,0 +1,369 @@
+// C ABI of libacestep_b200.so: the reference's ace_ggml_* entry points (include/acestep_ggml.h) plus the
+// ace_b200_* extensions (include/acestep_b200.h).  Host pointers in, host pointers out; no exception crosses.
+// reference behaviour mirrored: acestep_ggml.cpp:65-70, 192-236 (context, errors), 260-357 / 529-632 (load),
+// 634-657 (get_info), 659-682 (vae_decode checks), 1304-1329 (dit_forward checks), 2056-2086 (Euler loop)
+#include "abi_internal.h"
+
+#include <atomic>
+#include <chrono>
+#include <cmath>
+#include <cstdio>
+#include <cstdlib>
+#include <cstring>
+#include <string>
+#include <vector>
+
+namespace ace {
+std::atomic<uint64_t> g_kernel_launches{0};
+}
+
+namespace ace_abi {
+
+// H2D copies of one batched forward's inputs into the workspace
+ace_ggml_status stage_dit_inputs(ace_ggml_context* ctx, const float* hidden, const float* context, const float* enc,
+                                 const int32_t* mask, const int32_t* enc_mask, int B, int T, int E) {
+    const DitConfig& c = ctx->dit.cfg;
+    const int A = c.audio_acoustic_hidden_dim, cd = c.in_channels - A, H = c.hidden_size;
+    DitWorkspace& ws = ctx->dws;
+    cudaStream_t st = ctx->stream;
+    cudaError_t e = cudaSuccess;
+    auto h2d = [&](void* dst, const void* src, size_t bytes) {
+        if (e == cudaSuccess && bytes) e = cudaMemcpyAsync(dst, src, bytes, cudaMemcpyHostToDevice, st);
+    };
+    if (hidden) h2d(ws.d_hidden, hidden, (size_t)B * T * A * 4);
+    else if (e == cudaSuccess) e = cudaMemsetAsync(ws.d_hidden, 0, (size_t)B * T * A * 4, st);
+    if (context) h2d(ws.d_context, context, (size_t)B * T * cd * 4);
+    else if (e == cudaSuccess) e = cudaMemsetAsync(ws.d_context, 0, (size_t)B * T * cd * 4, st);
+    if (E > 0) {
+        if (enc) h2d(ws.d_enc, enc, (size_t)B * E * H * 4);
+        else if (e == cudaSuccess) e = cudaMemsetAsync(ws.d_enc, 0, (size_t)B * E * H * 4, st);
+    }
+    if (mask) h2d(ws.d_mask, mask, (size_t)B * T * 4);
+    if (enc_mask && E > 0) h2d(ws.d_enc_mask, enc_mask, (size_t)B * E * 4);
+    if (e != cudaSuccess) return cuda_fail(ctx, "input upload failed", e);
+    return ACE_GGML_OK;
+}
+
+int env_max_layers() {
+    const char* v = std::getenv("ACE_GGML_DIT_MAX_LAYERS");
+    if (!v) return 0;
+    char* endp = nullptr;
+    const long long x = std::strtoll(v, &endp, 10);
+    return (endp && endp != v && x > 0) ? (int)std::min<long long>(x, 1 << 20) : 0;
+}
+
+ace_ggml_status dit_forward_impl(ace_ggml_context* ctx, const float* hidden, const float* context, const float* enc,
+                                 const int32_t* mask, const int32_t* enc_mask, int B, int T, int E, const float* t,
+                                 const float* t_r, float* out, size_t out_size, const char* profile_name) {
+    const auto t0 = Clock::now();
+    DeviceGuard guard(ctx->device);
+    const DitConfig& c = ctx->dit.cfg;
+    const size_t needed = (size_t)B * T * c.audio_acoustic_hidden_dim * sizeof(float);
+    if (out_size < needed) return set_error(ctx, ACE_GGML_ERR_INVALID_ARG, "output buffer too small");
+    std::string err;
+    if (!dit_workspace_reserve(ctx->dit, ctx->dws, B, T, E, err)) return set_error(ctx, ACE_GGML_ERR, err);
+    const auto t_init = Clock::now();
+    ace_ggml_status s = stage_dit_inputs(ctx, hidden, context, enc, mask, enc_mask, B, T, E);
+    if (s != ACE_GGML_OK) return s;
+    std::vector<float> tt((size_t)2 * B);
+    for (int b = 0; b < B; ++b) {
+        tt[(size_t)b] = t[b];
+        tt[(size_t)B + b] = t[b] - t_r[b];  // second embedder sees t - t_r (acestep_dit_model.cpp:1423)
+    }
+    cudaError_t e = cudaMemcpyAsync(ctx->dws.d_t, tt.data(), tt.size() * 4, cudaMemcpyHostToDevice, ctx->stream);
+    if (e != cudaSuccess) return cuda_fail(ctx, "timestep upload failed", e);
+    DitForwardOpts o;
+    o.max_layers = env_max_layers();
+    o.has_mask = mask != nullptr;
+    o.has_enc_mask = enc_mask != nullptr && E > 0;
+    cudaEventRecord(ctx->ev0, ctx->stream);
+    e = dit_forward_device(ctx->dit, ctx->dws, B, T, E, ctx->dws.d_out, o, ctx->stream);
+    cudaEventRecord(ctx->ev1, ctx->stream);
+    if (e != cudaSuccess) return cuda_fail(ctx, "dit forward launch failed", e);
+    e = cudaStreamSynchronize(ctx->stream);  // also makes the pageable `tt` upload safe to drop
+    if (e != cudaSuccess) return cuda_fail(ctx, "dit forward failed", e);
+    const auto t_done = Clock::now();
+    e = cudaMemcpy(out, ctx->dws.d_out, needed, cudaMemcpyDeviceToHost);
+    if (e != cudaSuccess) return cuda_fail(ctx, "output download failed", e);
+    float ms = 0.f;
+    cudaEventElapsedTime(&ms, ctx->ev0, ctx->ev1);
+    ctx->last_device_ms = ms;
+    if (env_on("ACE_GGML_DIT_PROFILE")) {
+        const auto t_end = Clock::now();
+        std::fprintf(stderr,
+                     "%s profile: backend=%s seq=%d enc=%d threads=%d init_ms=%lld build_ms=%lld graph_ms=%lld compute_ms=%lld "
+                     "copy_ms=%lld total_ms=%lld device_ms=%.3f batch=%d\n",
+                     profile_name, "b200", T, E, ctx->n_threads, ms_between(t0, t_init), 0LL, 0LL, ms_between(t_init, t_done),
+                     ms_between(t_done, t_end), ms_between(t0, t_end), ms, B);
+    }
+    return ACE_GGML_OK;
+}
+
+ace_ggml_status vae_decode_impl(ace_ggml_context* ctx, const float* latents, int B, int n_frames, float* out, size_t out_size) {
+    const auto t0 = Clock::now();
+    DeviceGuard guard(ctx->device);
+    const VaeConfig& c = ctx->vae.cfg;
+    const size_t expected = (size_t)B * n_frames * c.hop_length * c.audio_channels * sizeof(float);
+    if (out_size < expected) return set_error(ctx, ACE_GGML_ERR_INVALID_ARG, "output buffer too small");
+    std::string err;
+    if (!vae_workspace_reserve(ctx->vae, ctx->vws, B, n_frames, err)) return set_error(ctx, ACE_GGML_ERR, err);
+    const auto t_init = Clock::now();
+    cudaError_t e = cudaMemcpyAsync(ctx->vws.d_lat, latents, (size_t)B * n_frames * c.decoder_input_channels * 4,
+                                    cudaMemcpyHostToDevice, ctx->stream);
+    if (e != cudaSuccess) return cuda_fail(ctx, "latent upload failed", e);
+    cudaEventRecord(ctx->ev0, ctx->stream);
+    e = vae_decode_device(ctx->vae, ctx->vws, B, n_frames, ctx->vws.d_audio, ctx->stream);
+    cudaEventRecord(ctx->ev1, ctx->stream);
+    if (e != cudaSuccess) return cuda_fail(ctx, "vae decode launch failed", e);
+    e = cudaStreamSynchronize(ctx->stream);
+    if (e != cudaSuccess) return cuda_fail(ctx, "vae decode failed", e);
+    const auto t_done = Clock::now();
+    e = cudaMemcpy(out, ctx->vws.d_audio, expected, cudaMemcpyDeviceToHost);
+    if (e != cudaSuccess) return cuda_fail(ctx, "audio download failed", e);
+    float ms = 0.f;
+    cudaEventElapsedTime(&ms, ctx->ev0, ctx->ev1);
+    ctx->last_device_ms = ms;
+    if (env_on("ACE_GGML_VAE_PROFILE")) {
+        const auto t_end = Clock::now();
+        std::fprintf(stderr,
+                     "ace_ggml_vae_decode profile: backend=%s frames=%d out_len=%d threads=%d init_ms=%lld build_ms=%lld graph_ms=%lld "
+                     "compute_ms=%lld copy_ms=%lld total_ms=%lld device_ms=%.3f batch=%d\n",
+                     "b200", n_frames, n_frames * c.hop_length, ctx->n_threads, ms_between(t0, t_init), 0LL, 0LL,
+                     ms_between(t_init, t_done), ms_between(t_done, t_end), ms_between(t0, t_end), ms, B);
+    }
+    return ACE_GGML_OK;
+}
+
+// Device-resident Euler sampler (+ optional CFG as one 2B-sample batch). Leaves the final latents in ctx->d_x.
+ace_ggml_status sample_latents_device(ace_ggml_context* ctx, const float* noise, const float* context, const float* enc,
+                                      const float* uncond_enc, const int32_t* mask, const int32_t* enc_mask, int B, int T,
+                                      int E, const float* schedule, int n_steps, float guidance) {
+    const DitConfig& c = ctx->dit.cfg;
+    const int A = c.audio_acoustic_hidden_dim, cd = c.in_channels - A, H = c.hidden_size;
+    const bool cfg = uncond_enc != nullptr && E > 0;
+    const int EB = cfg ? 2 * B : B;  // evaluations per step
+    std::string err;
+    if (!dit_workspace_reserve(ctx->dit, ctx->dws, EB, T, E, err)) return set_error(ctx, ACE_GGML_ERR, err);
+    DitWorkspace& ws = ctx->dws;
+    const size_t n_lat = (size_t)B * T * A;
+    if (ctx->sampler_cap < n_lat) {
+        if (ctx->d_x) cudaFree(ctx->d_x);
+        if (ctx->d_v) cudaFree(ctx->d_v);
+        ctx->d_x = ctx->d_v = nullptr;
+        ctx->sampler_cap = 0;
+        if (cudaMalloc(&ctx->d_x, n_lat * 4) != cudaSuccess || cudaMalloc(&ctx->d_v, 2 * n_lat * 4) != cudaSuccess)
+            return cuda_fail(ctx, "sampler cudaMalloc failed", cudaGetLastError());
+        ctx->sampler_cap = n_lat;
+    }
+    cudaStream_t st = ctx->stream;
+    cudaError_t e = cudaSuccess;
+    auto chk = [&](cudaError_t r) { if (e == cudaSuccess) e = r; };
+    chk(cudaMemcpyAsync(ctx->d_x, noise, n_lat * 4, cudaMemcpyHostToDevice, st));
+    // step-invariant inputs: context, encoder states (cond | uncond), masks
+    for (int rep = 0; rep < (cfg ? 2 : 1); ++rep) {
+        float* dctx = ws.d_context + (size_t)rep * B * T * cd;
+        if (context) chk(cudaMemcpyAsync(dctx, context, (size_t)B * T * cd * 4, cudaMemcpyHostToDevice, st));
+        else chk(cudaMemsetAsync(dctx, 0, (size_t)B * T * cd * 4, st));
+        if (E > 0) {
+            const float* src = rep == 0 ? enc : uncond_enc;
+            float* denc = ws.d_enc + (size_t)rep * B * E * H;
+            if (src) chk(cudaMemcpyAsync(denc, src, (size_t)B * E * H * 4, cudaMemcpyHostToDevice, st));
+            else chk(cudaMemsetAsync(denc, 0, (size_t)B * E * H * 4, st));
+            if (enc_mask) chk(cudaMemcpyAsync(ws.d_enc_mask + (size_t)rep * B * E, enc_mask, (size_t)B * E * 4, cudaMemcpyHostToDevice, st));
+        }
+        if (mask) chk(cudaMemcpyAsync(ws.d_mask + (size_t)rep * B * T, mask, (size_t)B * T * 4, cudaMemcpyHostToDevice, st));
+    }
+    if (e != cudaSuccess) return cuda_fail(ctx, "sampler input upload failed", e);
+
+    DitForwardOpts o;
+    o.max_layers = env_max_layers();
+    o.has_mask = mask != nullptr;
+    o.has_enc_mask = enc_mask != nullptr && E > 0;
+    ws.cross_kv_valid = false;
+    std::vector<float> tt((size_t)2 * EB);
+    cudaEventRecord(ctx->ev0, st);
+    for (int i = 0; i < n_steps; ++i) {
+        const float t = schedule[i];
+        for (int b = 0; b < EB; ++b) {
+            tt[(size_t)b] = t;
+            tt[(size_t)EB + b] = 0.f;  // timestep_r == timestep in every caller (acestep_ggml.cpp:2062-2071)
+        }
+        chk(cudaMemcpyAsync(ws.d_t, tt.data(), tt.size() * 4, cudaMemcpyHostToDevice, st));
+        // current latents are the hidden_states of both CFG branches
+        chk(cudaMemcpyAsync(ws.d_hidden, ctx->d_x, n_lat * 4, cudaMemcpyDeviceToDevice, st));
+        if (cfg) chk(cudaMemcpyAsync(ws.d_hidden + n_lat, ctx->d_x, n_lat * 4, cudaMemcpyDeviceToDevice, st));
+        o.reuse_cross_kv = i > 0;  // condition_embedder output and cross K/V do not depend on the step
+        chk(dit_forward_device(ctx->dit, ws, EB, T, E, ctx->d_v, o, st));
+        const float dt = (i == n_steps - 1) ? t : (t - schedule[i + 1]);
+        launch_euler_step(ctx->d_x, ctx->d_v, cfg ? ctx->d_v + n_lat : nullptr, guidance, dt, (long)n_lat, st);
+        if (e != cudaSuccess) break;
+    }
+    cudaEventRecord(ctx->ev1, st);
+    ws.cross_kv_valid = false;
+    if (e != cudaSuccess) return cuda_fail(ctx, "sampler launch failed", e);
+    return ACE_GGML_OK;
+}
+
+}  // namespace ace_abi
+
+using namespace ace_abi;
+
+namespace {
+ace_ggml_status unsupported(ace_ggml_context* ctx, const char* what) {
+    if (!ctx) return ACE_GGML_ERR_INVALID_ARG;
+    return set_error(ctx, ACE_GGML_ERR_UNSUPPORTED,
+                     std::string(what) + " is not part of the B200 hot path (DiT forward + VAE decode); see INTEGRATION.md");
+}
+
+}  // namespace
+
+extern "C" {
+
+ace_ggml_status ace_ggml_create(const ace_ggml_init_params* params, ace_ggml_context** out_ctx) {
+    if (!out_ctx) return ACE_GGML_ERR_INVALID_ARG;
+    *out_ctx = nullptr;
+    int n_dev = 0;
+    if (cudaGetDeviceCount(&n_dev) != cudaSuccess || n_dev <= 0) {
+        std::fprintf(stderr, "ace_ggml_create: no CUDA device available (%s); this library has no CPU path\n",
+                     cudaGetErrorString(cudaGetLastError()));
+        return ACE_GGML_ERR;
+    }
+    int dev = 0;
+    if (const char* v = std::getenv("ACE_B200_DEVICE")) dev = std::atoi(v);
+    else cudaGetDevice(&dev);
+    if (dev < 0 || dev >= n_dev) return ACE_GGML_ERR_INVALID_ARG;
+    cudaDeviceProp prop;
+    if (cudaGetDeviceProperties(&prop, dev) != cudaSuccess) return ACE_GGML_ERR;
+    if (prop.major != 10) {
+        std::fprintf(stderr, "ace_ggml_create: device %d is sm_%d%d; this library is built for sm_100a only\n", dev, prop.major, prop.minor);
+        return ACE_GGML_ERR_UNSUPPORTED;
+    }
+    ace_ggml_context* ctx = new (std::nothrow) ace_ggml_context();
+    if (!ctx) return ACE_GGML_ERR;
+    ctx->device = dev;
+    ctx->n_threads = (params && params->n_threads > 0) ? params->n_threads : 1;
+    DeviceGuard guard(dev);
+    if (cudaStreamCreateWithFlags(&ctx->stream, cudaStreamNonBlocking) != cudaSuccess || cudaEventCreate(&ctx->ev0) != cudaSuccess ||
+        cudaEventCreate(&ctx->ev1) != cudaSuccess) {
+        delete ctx;
+        return ACE_GGML_ERR;
+    }
+    *out_ctx = ctx;
+    return ACE_GGML_OK;
+}
+
+void ace_ggml_destroy(ace_ggml_context* ctx) {
+    if (!ctx) return;
+    {
+        DeviceGuard guard(ctx->device);
+        cudaStreamSynchronize(ctx->stream);
+        ctx->dit.release();
+        ctx->dws.release();
+        ctx->vae.release();
+        ctx->vws.release();
+        if (ctx->d_x) cudaFree(ctx->d_x);
+        if (ctx->d_v) cudaFree(ctx->d_v);
+        for (void* p : ctx->dbg_allocs) cudaFree(p);
+        if (ctx->ev0) cudaEventDestroy(ctx->ev0);
+        if (ctx->ev1) cudaEventDestroy(ctx->ev1);
+        if (ctx->stream) cudaStreamDestroy(ctx->stream);
+    }
+    delete ctx;
+}
+
+const char* ace_ggml_last_error(const ace_ggml_context* ctx) {
+    if (!ctx) return "ace_ggml_last_error: null context";
+    return ctx->last_error.c_str();
+}
+
+ace_ggml_status ace_ggml_load_lm(ace_ggml_context* ctx, const char* model_dir) {
+    if (!ctx || !model_dir) return ACE_GGML_ERR_INVALID_ARG;
+    return unsupported(ctx, "ace_ggml_load_lm");
+}
+ace_ggml_status ace_ggml_load_text_encoder(ace_ggml_context* ctx, const char* model_dir) {
+    if (!ctx || !model_dir) return ACE_GGML_ERR_INVALID_ARG;
+    return unsupported(ctx, "ace_ggml_load_text_encoder");
+}
+
+ace_ggml_status ace_ggml_load_dit(ace_ggml_context* ctx, const char* model_dir) {
+    if (!ctx || !model_dir) return ACE_GGML_ERR_INVALID_ARG;
+    DeviceGuard guard(ctx->device);
+    cudaStreamSynchronize(ctx->stream);
+    ctx->dit_loaded = false;
+    ctx->dws.release();
+    std::string err;
+    const int st = dit_load(model_dir, ctx->dit, err);
+    if (st != 0) return set_error(ctx, map_load_status(st), err);
+    ctx->dit_loaded = true;
+    return ACE_GGML_OK;
+}
+
+ace_ggml_status ace_ggml_load_vae(ace_ggml_context* ctx, const char* model_dir) {
+    if (!ctx || !model_dir) return ACE_GGML_ERR_INVALID_ARG;
+    DeviceGuard guard(ctx->device);
+    cudaStreamSynchronize(ctx->stream);
+    ctx->vae_loaded = false;
+    ctx->vws.release();
+    std::string err;
+    const int st = vae_load(model_dir, ctx->vae, err);
+    if (st != 0) return set_error(ctx, map_load_status(st), err);
+    ctx->vae_loaded = true;
+    return ACE_GGML_OK;
+}
+
+ace_ggml_status ace_ggml_vae_get_info(ace_ggml_context* ctx, int32_t* latent_channels, int32_t* audio_channels, int32_t* hop_length) {
+    if (!ctx) return ACE_GGML_ERR_INVALID_ARG;
+    if (!ctx->vae_loaded) return set_error(ctx, ACE_GGML_ERR, "vae not loaded");
+    if (latent_channels) *latent_channels = ctx->vae.cfg.decoder_input_channels;
+    if (audio_channels) *audio_channels = ctx->vae.cfg.audio_channels;
+    if (hop_length) *hop_length = ctx->vae.cfg.hop_length;
+    return ACE_GGML_OK;
+}
+
+ace_ggml_status ace_ggml_vae_decode(ace_ggml_context* ctx, const float* latents, int32_t n_frames, float* out, size_t out_size) {
+    if (!ctx || !latents || !out || n_frames <= 0) return ACE_GGML_ERR_INVALID_ARG;
+    if (!ctx->vae_loaded) return set_error(ctx, ACE_GGML_ERR, "vae not loaded");
+    return vae_decode_impl(ctx, latents, 1, n_frames, out, out_size);
+}
+
+ace_ggml_status ace_ggml_vae_encode(ace_ggml_context* ctx, const float*, int32_t, float*, size_t) {
+    return unsupported(ctx, "ace_ggml_vae_encode");
+}
+ace_ggml_status ace_ggml_text_encoder_forward(ace_ggml_context* ctx, const int32_t*, int32_t, float*, size_t) {
+    return unsupported(ctx, "ace_ggml_text_encoder_forward");
+}
+ace_ggml_status ace_ggml_text_encoder_forward_masked(ace_ggml_context* ctx, const int32_t*, const int32_t*, int32_t, float*, size_t) {
+    return unsupported(ctx, "ace_ggml_text_encoder_forward_masked");
+}
+ace_ggml_status ace_ggml_text_encoder_forward_embeddings(ace_ggml_context* ctx, const int32_t*, int32_t, float*, size_t) {
+    return unsupported(ctx, "ace_ggml_text_encoder_forward_embeddings");
+}
+ace_ggml_status ace_ggml_text_encoder_forward_layers(ace_ggml_context* ctx, const int32_t*, const int32_t*, int32_t, int32_t, int32_t, float*, size_t) {
+    return unsupported(ctx, "ace_ggml_text_encoder_forward_layers");
+}
+
+ace_ggml_status ace_ggml_dit_forward(ace_ggml_context* ctx, const float* hidden_states, const float* context_latents,
+                                     const float* encoder_hidden_states, const int32_t* attention_mask,
+                                     const int32_t* encoder_attention_mask, int32_t seq_len, int32_t enc_len, float timestep,
+                                     float timestep_r, float* out, size_t out_size) {
+    if (!ctx || !out || seq_len <= 0) return ACE_GGML_ERR_INVALID_ARG;
+    if (!ctx->dit_loaded) return set_error(ctx, ACE_GGML_ERR, "dit not loaded");
+    if (enc_len < 0) enc_len = 0;
+    return dit_forward_impl(ctx, hidden_states, context_latents, encoder_hidden_states, attention_mask, encoder_attention_mask, 1,
+                            seq_len, enc_len, &timestep, &timestep_r, out, out_size, "ace_ggml_dit_forward");
+}
+
+ace_ggml_status ace_ggml_generate_audio_simple(ace_ggml_context* ctx, const int32_t*, int32_t, int32_t, float, int32_t, float*, size_t, int32_t*, int32_t*) {
+    return unsupported(ctx, "ace_ggml_generate_audio_simple (needs the text encoder)");
+}
+ace_ggml_status ace_ggml_generate_audio_style_lyric_simple(ace_ggml_context* ctx, const int32_t*, int32_t, const int32_t*, int32_t, int32_t, float, int32_t,
+                                                           float*, size_t, int32_t*, int32_t*) {
+    return unsupported(ctx, "ace_ggml_generate_audio_style_lyric_simple (needs the text / lyric encoders)");
+}
+ace_ggml_status ace_ggml_generate_audio_style_lyric_timbre_simple(ace_ggml_context* ctx, const int32_t*, int32_t, const int32_t*, int32_t, const float*,
+                                                                  const int32_t*, int32_t, int32_t, int32_t, float, int32_t, float*, size_t, int32_t*,
+                                                                  int32_t*) {
+    return unsupported(ctx, "ace_ggml_generate_audio_style_lyric_timbre_simple (needs the text / lyric / timbre encoders)");
+}
+
+}  // extern "C"

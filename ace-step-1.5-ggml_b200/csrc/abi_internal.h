@@ -1,0 +1,85 @@
+// Internal: the context behind the opaque ace_ggml_context handle and helpers shared by abi.cu / abi_ext.cu.
+#pragma once
+#include "../../include/acestep_b200.h"
+
+#include "dit.h"
+#include "gemm.h"
+#include "kernels.h"
+#include "vae.h"
+
+#include <algorithm>
+#include <chrono>
+#include <cstdlib>
+#include <cstring>
+#include <string>
+#include <vector>
+
+struct ace_ggml_context {
+    int device = 0;
+    int n_threads = 1;
+    cudaStream_t stream = nullptr;
+    cudaEvent_t ev0 = nullptr, ev1 = nullptr;
+    bool dit_loaded = false, vae_loaded = false;
+    ace::DitModel dit;
+    ace::DitWorkspace dws;
+    ace::VaeModel vae;
+    ace::VaeWorkspace vws;
+    std::string last_error;
+    std::string info;
+    double last_device_ms = 0.0;
+    // sampler scratch
+    float* d_x = nullptr;   // [B, T, A] latents being integrated
+    float* d_v = nullptr;   // [2B, T, A] velocities
+    size_t sampler_cap = 0;
+    // debug scratch (unit-test hooks)
+    std::vector<void*> dbg_allocs;
+};
+
+namespace ace_abi {
+
+using namespace ace;
+
+inline ace_ggml_status set_error(ace_ggml_context* ctx, ace_ggml_status st, const std::string& msg) {
+    if (ctx) ctx->last_error = msg;
+    return st;
+}
+inline ace_ggml_status cuda_fail(ace_ggml_context* ctx, const char* what, cudaError_t e) {
+    return set_error(ctx, ACE_GGML_ERR, std::string(what) + ": " + cudaGetErrorString(e));
+}
+inline bool env_on(const char* k) {
+    const char* v = std::getenv(k);
+    return v && v[0] && std::strcmp(v, "0") != 0;
+}
+inline ace_ggml_status map_load_status(int st) {
+    switch (st) {
+        case 0: return ACE_GGML_OK;
+        case 3: return ACE_GGML_ERR_IO;
+        case 4: return ACE_GGML_ERR_UNSUPPORTED;
+    }
+    return ACE_GGML_ERR;
+}
+struct DeviceGuard {
+    int prev = 0;
+    explicit DeviceGuard(int dev) {
+        cudaGetDevice(&prev);
+        if (prev != dev) cudaSetDevice(dev);
+    }
+    ~DeviceGuard() { cudaSetDevice(prev); }
+};
+using Clock = std::chrono::steady_clock;
+inline long long ms_between(Clock::time_point a, Clock::time_point b) {
+    return std::chrono::duration_cast<std::chrono::milliseconds>(b - a).count();
+}
+
+
+// implemented in abi.cu
+ace_ggml_status dit_forward_impl(ace_ggml_context* ctx, const float* hidden, const float* context, const float* enc,
+                                 const int32_t* mask, const int32_t* enc_mask, int B, int T, int E, const float* t,
+                                 const float* t_r, float* out, size_t out_size, const char* profile_name);
+ace_ggml_status vae_decode_impl(ace_ggml_context* ctx, const float* latents, int B, int n_frames, float* out, size_t out_size);
+ace_ggml_status sample_latents_device(ace_ggml_context* ctx, const float* noise, const float* context, const float* enc,
+                                      const float* uncond_enc, const int32_t* mask, const int32_t* enc_mask, int B, int T,
+                                      int E, const float* schedule, int n_steps, float guidance);
+int env_max_layers();
+
+}  // namespace ace_abi

@@ -245,6 +245,7 @@ attention_kernel(const __half* __restrict__ Q, long q_stride, const __half* __re
 void launch_attention(const __half* Q, long q_stride, const __half* K, long k_stride, const __half* V, long v_stride,
                       __half* O, long o_stride, const int32_t* key_mask, int B, int q_len, int k_len, int n_heads,
                       int n_kv_heads, int window, cudaStream_t st) {
+    note_launch();
     static bool attr = false;
     if (!attr) {
         cudaFuncSetAttribute(attention_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, ATT_SMEM);

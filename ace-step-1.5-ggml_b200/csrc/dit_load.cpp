@@ -1,0 +1,347 @@
+// DiT weight ingest: config.json + (model.gguf | model.safetensors) -> packed tiles in HBM.
+// reference: acestep_dit_config.cpp:19-93 (keys), acestep_dit_model.cpp:47-70 (file choice),
+//            156-192 (on-the-fly quantisation), 334-490 / 640-715 (conv -> linear relayout), 753-1088 (tensor names)
+#include "dit.h"
+#include "tensor_file.h"
+
+#include <algorithm>
+#include <cstdlib>
+#include <cstring>
+
+namespace ace {
+
+namespace {
+
+struct Loader {
+    const TensorFile* tf;
+    DitModel* m;
+    std::string err;
+    int status = 0;
+    int online_q = -1;  // W_Q8_0 when ACE_GGML_*_WEIGHT_QTYPE asks for it (safetensors only)
+
+    bool fail(int st, const std::string& e) {
+        if (status == 0) {
+            status = st;
+            err = e;
+        }
+        return false;
+    }
+    void* dev_alloc(size_t bytes) {
+        void* p = nullptr;
+        if (cudaMalloc(&p, bytes ? bytes : 16) != cudaSuccess) {
+            fail(1, "cudaMalloc failed (" + std::to_string(bytes) + " bytes): " + cudaGetErrorString(cudaGetLastError()));
+            return nullptr;
+        }
+        m->allocs.push_back(p);
+        m->weight_bytes += bytes;
+        return p;
+    }
+    bool upload(PackedWeight& w, const std::vector<uint8_t>& img) {
+        w.dev = dev_alloc(img.size());
+        if (!w.dev) return false;
+        if (cudaMemcpy(w.dev, img.data(), img.size(), cudaMemcpyHostToDevice) != cudaSuccess)
+            return fail(1, std::string("cudaMemcpy failed: ") + cudaGetErrorString(cudaGetLastError()));
+        return true;
+    }
+    float* upload_f32(const std::vector<float>& v) {
+        float* d = static_cast<float*>(dev_alloc(v.size() * 4));
+        if (!d) return nullptr;
+        if (cudaMemcpy(d, v.data(), v.size() * 4, cudaMemcpyHostToDevice) != cudaSuccess) {
+            fail(1, std::string("cudaMemcpy failed: ") + cudaGetErrorString(cudaGetLastError()));
+            return nullptr;
+        }
+        return d;
+    }
+    bool vec(const std::string& name, int64_t expect, float*& out) {
+        std::vector<float> v;
+        std::string e;
+        if (!tf->read_f32(name, v, nullptr, e)) return fail(3, e);
+        if ((int64_t)v.size() != expect) return fail(3, "unexpected size for " + name);
+        out = upload_f32(v);
+        return out != nullptr;
+    }
+
+    // Row-concatenation (or pairwise interleave) of 2-D weights [N_i, K] -> one packed matrix.
+    bool linear(const std::vector<std::string>& names, bool interleave, int K, PackedWeight& out) {
+        std::vector<const TensorInfo*> ti;
+        int N = 0;
+        for (const auto& n : names) {
+            const TensorInfo* t = tf->find(n);
+            if (!t) return fail(3, "missing tensor: " + n);
+            if (t->shape.size() != 2 || t->shape[1] != K) return fail(3, "invalid tensor shape for " + n);
+            ti.push_back(t);
+            N += (int)t->shape[0];
+        }
+        if (interleave && (ti.size() != 2 || ti[0]->shape[0] != ti[1]->shape[0])) return fail(1, "bad interleave request");
+        const int gt = ti[0]->ggml_type;
+        bool same = true;
+        for (auto* t : ti) same = same && t->ggml_type == gt;
+        const bool quant_file = same && (gt == GGML_Q8_0 || gt == GGML_Q4_K || gt == GGML_Q6_K) && K % TILE_K == 0;
+        std::vector<uint8_t> img;
+        std::string e;
+        if (quant_file) {
+            const size_t rb = ggml_row_bytes(gt, K);
+            std::vector<uint8_t> rows((size_t)N * rb);
+            if (interleave) {
+                const int half = (int)ti[0]->shape[0];
+                for (int j = 0; j < half; ++j) {
+                    std::memcpy(rows.data() + (size_t)(2 * j) * rb, ti[0]->data + (size_t)j * rb, rb);
+                    std::memcpy(rows.data() + (size_t)(2 * j + 1) * rb, ti[1]->data + (size_t)j * rb, rb);
+                }
+            } else {
+                size_t off = 0;
+                for (auto* t : ti) {
+                    std::memcpy(rows.data() + off, t->data, (size_t)t->shape[0] * rb);
+                    off += (size_t)t->shape[0] * rb;
+                }
+            }
+            if (!pack_tiles_ggml(rows.data(), gt, N, K, img, out, e)) return fail(1, e);
+        } else {
+            std::vector<float> w((size_t)N * K);
+            if (interleave) {
+                std::vector<float> a, b;
+                if (!tf->read_f32(names[0], a, nullptr, e) || !tf->read_f32(names[1], b, nullptr, e)) return fail(3, e);
+                const int half = (int)ti[0]->shape[0];
+                for (int j = 0; j < half; ++j) {
+                    std::memcpy(w.data() + (size_t)(2 * j) * K, a.data() + (size_t)j * K, (size_t)K * 4);
+                    std::memcpy(w.data() + (size_t)(2 * j + 1) * K, b.data() + (size_t)j * K, (size_t)K * 4);
+                }
+            } else {
+                size_t off = 0;
+                for (const auto& n : names) {
+                    std::vector<float> a;
+                    if (!tf->read_f32(n, a, nullptr, e)) return fail(3, e);
+                    std::memcpy(w.data() + off, a.data(), a.size() * 4);
+                    off += a.size();
+                }
+            }
+            if (!pack_f32(w, N, K, img, out)) return false;
+        }
+        return upload(out, img);
+    }
+    bool pack_f32(const std::vector<float>& w, int N, int K, std::vector<uint8_t>& img, PackedWeight& out) {
+        std::string e;
+        const int wt = (online_q == W_Q8_0 && !tf->is_gguf() && K % 32 == 0 && K % TILE_K == 0) ? W_Q8_0 : W_F16;
+        if (!pack_tiles_f32(w.data(), N, 1, K, wt, img, out, e)) return fail(1, e);
+        return true;
+    }
+};
+
+bool parse_config(const std::string& path, DitConfig& c, std::string& err) {
+    JsonValue root;
+    if (!json_parse_file(path, root, err)) return false;
+    if (root.kind != JsonValue::Object) {
+        err = "config is not object";
+        return false;
+    }
+    auto need_int = [&](const char* k, int& dst) {
+        int64_t v;
+        if (!root.get_int(k, v)) {
+            if (err.empty()) err = std::string("config.json: missing key ") + k;
+            return false;
+        }
+        dst = (int)v;
+        return true;
+    };
+    double d;
+    int64_t iv;
+    if (!need_int("hidden_size", c.hidden_size) || !need_int("intermediate_size", c.intermediate_size) ||
+        !need_int("num_hidden_layers", c.num_hidden_layers) || !need_int("num_attention_heads", c.num_attention_heads) ||
+        !need_int("num_key_value_heads", c.num_key_value_heads) || !need_int("head_dim", c.head_dim) ||
+        !need_int("max_position_embeddings", c.max_position_embeddings))
+        return false;
+    if (!root.get_num("rms_norm_eps", d)) {
+        err = "config.json: missing key rms_norm_eps";
+        return false;
+    }
+    c.rms_norm_eps = (float)d;
+    if (!need_int("patch_size", c.patch_size) || !need_int("in_channels", c.in_channels) ||
+        !need_int("audio_acoustic_hidden_dim", c.audio_acoustic_hidden_dim))
+        return false;
+    (void)root.get_bool("use_sliding_window", c.use_sliding_window);
+    if (root.get_int("sliding_window", iv)) c.sliding_window = (int)iv;
+    if (root.get_num("rope_theta", d)) c.rope_theta = (float)d;
+    const JsonValue* lt = root.get("layer_types");
+    if (!lt || lt->kind != JsonValue::Array) {
+        err = "missing layer_types";
+        return false;
+    }
+    for (const auto& v : lt->arr) c.layer_types.push_back(v.str);
+    return true;
+}
+
+std::string resolve_gguf(const std::string& dir) {
+    for (const char* key : {"ACE_GGML_DIT_GGUF", "ACE_GGML_DIT_GGUF_PATH"}) {
+        const char* v = std::getenv(key);
+        if (v && v[0] && file_exists(v)) return v;
+    }
+    if (dir.size() > 5 && dir.substr(dir.size() - 5) == ".gguf" && file_exists(dir)) return dir;
+    const std::string cand = dir + "/model.gguf";
+    if (file_exists(cand)) return cand;
+    return "";
+}
+
+int parse_online_qtype(std::string& unsupported) {
+    for (const char* key : {"ACE_GGML_DIT_WEIGHT_QTYPE", "ACE_GGML_WEIGHT_QTYPE"}) {
+        const char* v = std::getenv(key);
+        if (!v || !v[0]) continue;
+        std::string s(v);
+        std::transform(s.begin(), s.end(), s.begin(), [](unsigned char ch) { return (char)std::toupper(ch); });
+        if (s == "Q8" || s == "Q8_0") return W_Q8_0;
+        if (s == "Q6" || s == "Q6_K" || s == "Q4" || s == "Q4_K" || s == "Q4_K_M") {
+            unsupported = s;
+            return -2;
+        }
+        return -1;  // unknown strings are ignored by the reference too
+    }
+    return -1;
+}
+
+}  // namespace
+
+void DitModel::release() {
+    for (void* p : allocs) cudaFree(p);
+    allocs.clear();
+    layers.clear();
+    weight_bytes = 0;
+}
+
+int dit_load(const std::string& model_dir, DitModel& m, std::string& err) {
+    m.release();
+    m.cfg = DitConfig();
+    std::string cfg_dir = model_dir;
+    if (cfg_dir.size() > 5 && cfg_dir.substr(cfg_dir.size() - 5) == ".gguf") {
+        const size_t slash = cfg_dir.find_last_of('/');
+        cfg_dir = slash == std::string::npos ? "." : cfg_dir.substr(0, slash);
+    }
+    if (!parse_config(cfg_dir + "/config.json", m.cfg, err)) return 3;
+    const DitConfig& c = m.cfg;
+    if (c.head_dim != 128) {
+        err = "unsupported head_dim (the attention kernel is specialised on 128)";
+        return 4;
+    }
+    if ((int)c.layer_types.size() < c.num_hidden_layers) {
+        err = "layer_types shorter than num_hidden_layers";
+        return 3;
+    }
+    if (c.hidden_size % 64 != 0 || c.intermediate_size % 64 != 0 || c.num_attention_heads % c.num_key_value_heads != 0) {
+        err = "unsupported DiT dimensions";
+        return 4;
+    }
+
+    std::unique_ptr<TensorFile> tf;
+    const std::string gguf = resolve_gguf(model_dir);
+    if (!gguf.empty()) tf = TensorFile::open_gguf(gguf, err);
+    else tf = TensorFile::open_safetensors(model_dir + "/model.safetensors", err);
+    if (!tf) return 3;
+
+    Loader L{tf.get(), &m, {}, 0, -1};
+    std::string unsup;
+    L.online_q = parse_online_qtype(unsup);
+    if (L.online_q == -2 && !tf->is_gguf()) {
+        err = "on-the-fly " + unsup + " quantisation of safetensors weights is not provided; export a pre-quantised GGUF "
+              "(tools/export_safetensors_to_gguf.py) and point ACE_GGML_DIT_GGUF at it";
+        m.release();
+        return 4;
+    }
+
+    const int H = c.hidden_size, I = c.intermediate_size, hd = c.head_dim;
+    const int nq = c.num_attention_heads * hd, nkv = c.num_key_value_heads * hd;
+    const int P = c.patch_size, C = c.in_channels, A = c.audio_acoustic_hidden_dim;
+    bool ok = true;
+    std::string e;
+
+    // proj_in: conv1d weight [H, C, P] -> linear [H, P*C] with column index k*C + c   (acestep_dit_model.cpp:366-375)
+    {
+        std::vector<float> w;
+        std::vector<int64_t> sh;
+        if (!tf->read_f32("decoder.proj_in.1.weight", w, &sh, e)) ok = L.fail(3, e);
+        else if (sh.size() != 3 || sh[0] != H || sh[1] != C || sh[2] != P) ok = L.fail(3, "invalid tensor shape for decoder.proj_in.1.weight");
+        else {
+            std::vector<float> lin((size_t)H * P * C);
+            for (int o = 0; o < H; ++o)
+                for (int ci = 0; ci < C; ++ci)
+                    for (int k = 0; k < P; ++k) lin[(size_t)o * P * C + (size_t)k * C + ci] = w[((size_t)o * C + ci) * P + k];
+            std::vector<uint8_t> img;
+            ok = ok && L.pack_f32(lin, H, P * C, img, m.proj_in) && L.upload(m.proj_in, img);
+        }
+        ok = ok && L.vec("decoder.proj_in.1.bias", H, m.proj_in_b);
+    }
+    // proj_out: conv-transpose weight [H, A, P] -> linear [P*A, H] with row index k*A + a   (acestep_dit_model.cpp:445-454)
+    if (ok) {
+        std::vector<float> w, b;
+        std::vector<int64_t> sh;
+        if (!tf->read_f32("decoder.proj_out.1.weight", w, &sh, e)) ok = L.fail(3, e);
+        else if (sh.size() != 3 || sh[0] != H || sh[1] != A || sh[2] != P) ok = L.fail(3, "invalid tensor shape for decoder.proj_out.1.weight");
+        else {
+            std::vector<float> lin((size_t)P * A * H);
+            for (int i = 0; i < H; ++i)
+                for (int a = 0; a < A; ++a)
+                    for (int k = 0; k < P; ++k) lin[((size_t)k * A + a) * H + i] = w[((size_t)i * A + a) * P + k];
+            std::vector<uint8_t> img;
+            ok = ok && L.pack_f32(lin, P * A, H, img, m.proj_out) && L.upload(m.proj_out, img);
+        }
+        if (ok && !tf->read_f32("decoder.proj_out.1.bias", b, nullptr, e)) ok = L.fail(3, e);
+        if (ok && (int)b.size() != A) ok = L.fail(3, "unexpected size for decoder.proj_out.1.bias");
+        if (ok) {
+            std::vector<float> be((size_t)P * A);
+            for (int k = 0; k < P; ++k)
+                for (int a = 0; a < A; ++a) be[(size_t)k * A + a] = b[(size_t)a];
+            m.proj_out_b = L.upload_f32(be);
+            ok = m.proj_out_b != nullptr;
+        }
+    }
+    ok = ok && L.linear({"decoder.condition_embedder.weight"}, false, H, m.condition);
+    ok = ok && L.vec("decoder.condition_embedder.bias", H, m.condition_b);
+    ok = ok && L.vec("decoder.norm_out.weight", H, m.norm_out);
+    ok = ok && L.vec("decoder.scale_shift_table", 2L * H, m.out_table);
+    auto load_te = [&](const std::string& p, DitTimeEmbed& te) {
+        return L.linear({p + ".linear_1.weight"}, false, 256, te.w1) && L.vec(p + ".linear_1.bias", H, te.b1) &&
+               L.linear({p + ".linear_2.weight"}, false, H, te.w2) && L.vec(p + ".linear_2.bias", H, te.b2) &&
+               L.linear({p + ".time_proj.weight"}, false, H, te.w_proj) && L.vec(p + ".time_proj.bias", 6L * H, te.b_proj);
+    };
+    ok = ok && load_te("decoder.time_embed", m.te) && load_te("decoder.time_embed_r", m.te_r);
+
+    std::vector<float> tables((size_t)c.num_hidden_layers * 6 * H);
+    m.layers.resize((size_t)c.num_hidden_layers);
+    for (int i = 0; ok && i < c.num_hidden_layers; ++i) {
+        DitLayer& ly = m.layers[(size_t)i];
+        const std::string p = "decoder.layers." + std::to_string(i) + ".";
+        ly.sliding = c.layer_types[(size_t)i] == "sliding_attention";
+        ok = ok && L.vec(p + "self_attn_norm.weight", H, ly.self_norm) && L.vec(p + "cross_attn_norm.weight", H, ly.cross_norm) &&
+             L.vec(p + "mlp_norm.weight", H, ly.mlp_norm);
+        ok = ok && L.linear({p + "self_attn.q_proj.weight", p + "self_attn.k_proj.weight", p + "self_attn.v_proj.weight"}, false, H, ly.self_qkv);
+        ok = ok && L.linear({p + "self_attn.o_proj.weight"}, false, nq, ly.self_o);
+        ok = ok && L.vec(p + "self_attn.q_norm.weight", hd, ly.self_qn) && L.vec(p + "self_attn.k_norm.weight", hd, ly.self_kn);
+        ok = ok && L.linear({p + "cross_attn.q_proj.weight"}, false, H, ly.cross_q);
+        ok = ok && L.linear({p + "cross_attn.k_proj.weight", p + "cross_attn.v_proj.weight"}, false, H, ly.cross_kv);
+        ok = ok && L.linear({p + "cross_attn.o_proj.weight"}, false, nq, ly.cross_o);
+        ok = ok && L.vec(p + "cross_attn.q_norm.weight", hd, ly.cross_qn) && L.vec(p + "cross_attn.k_norm.weight", hd, ly.cross_kn);
+        ok = ok && L.linear({p + "mlp.gate_proj.weight", p + "mlp.up_proj.weight"}, true, H, ly.mlp_gate_up);
+        ok = ok && L.linear({p + "mlp.down_proj.weight"}, false, I, ly.mlp_down);
+        if (ok) {
+            std::vector<float> t;
+            if (!tf->read_f32(p + "scale_shift_table", t, nullptr, e)) ok = L.fail(3, e);
+            else if ((int64_t)t.size() != 6L * H) ok = L.fail(3, "unexpected size for " + p + "scale_shift_table");
+            else std::memcpy(tables.data() + (size_t)i * 6 * H, t.data(), t.size() * 4);
+        }
+        if (ok && (ly.self_qkv.N != nq + 2 * nkv || ly.self_o.N != H || ly.cross_q.N != nq || ly.cross_kv.N != 2 * nkv ||
+                   ly.mlp_gate_up.N != 2 * I || ly.mlp_down.N != H))
+            ok = L.fail(3, "unexpected projection shape in layer " + std::to_string(i));
+    }
+    if (ok) {
+        m.layer_tables = L.upload_f32(tables);
+        ok = m.layer_tables != nullptr;
+    }
+    if (!ok) {
+        err = L.err;
+        m.release();
+        return L.status ? L.status : 1;
+    }
+    m.weight_desc = std::string(tf->is_gguf() ? "gguf:" : "safetensors:") +
+                    (m.layers.empty() ? "?" : (m.layers[0].self_qkv.wtype == W_F16 ? "F16" : m.layers[0].self_qkv.wtype == W_Q8_0 ? "Q8_0"
+                                               : m.layers[0].self_qkv.wtype == W_Q4_K ? "Q4_K" : "Q6_K"));
+    return 0;
+}
+
+}  // namespace ace

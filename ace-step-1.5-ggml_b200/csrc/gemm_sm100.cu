@@ -9,6 +9,7 @@
 // in TMEM (2 x BN columns) so the epilogue of tile i overlaps the MMAs of tile i+1.
 #include "gemm.h"
 #include "ptx.cuh"
+#include "kernels.h"
 
 #include <cuda.h>
 #include <cstdio>
@@ -599,6 +600,7 @@ bool gemm_force_simt() {
 
 cudaError_t gemm_launch(const GemmProblem& g, cudaStream_t stream, bool simt) {
     const PackedWeight& w = *g.W;
+    note_launch();
     KParams kp;
     kp.W = static_cast<const uint8_t*>(w.dev);
     kp.wtype = w.wtype;

@@ -5,7 +5,12 @@
 #include <cuda_fp16.h>
 #include <cuda_runtime.h>
 
+#include <atomic>
+
 namespace ace {
+
+extern std::atomic<uint64_t> g_kernel_launches;
+inline void note_launch() { g_kernel_launches.fetch_add(1, std::memory_order_relaxed); }
 
 // ---- DiT input side ------------------------------------------------------------------------------
 // x0[b, p, k*in_ch + c] = (c < ctx_dim ? context[b, 2p+k, c] : hidden[b, 2p+k, c-ctx_dim]), zero past T

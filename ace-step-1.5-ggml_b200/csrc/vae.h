@@ -1,0 +1,76 @@
+// Oobleck VAE decoder: weight-norm folded conv weights as packed F16 tiles + the fused decode schedule.
+// reference: acestep_vae_model.h:13-78 (Config / handles), acestep_vae_model.cpp:56-126 (config),
+//            503-641 (snake / conv / residual-unit / decoder-block loaders), 761-955 (names), 957-1002 (forward_decode)
+#pragma once
+#include <string>
+#include <vector>
+
+#include <cuda_fp16.h>
+#include <cuda_runtime.h>
+
+#include "wpack.h"
+
+namespace ace {
+
+struct VaeConfig {
+    int audio_channels = 0, encoder_hidden_size = 0, decoder_channels = 0, decoder_input_channels = 0;
+    int sampling_rate = 0;
+    std::vector<int> downsampling_ratios, channel_multiples, upsampling_ratios;
+    int hop_length = 1;
+};
+
+struct VaeSnake {
+    float* alpha = nullptr;     // exp(alpha) [C]
+    float* inv_beta = nullptr;  // 1 / exp(beta) [C]
+};
+
+struct VaeConv {
+    PackedWeight w;
+    float* bias = nullptr;  // [N of the GEMM] (conv-transpose: tiled over the stride phases)
+    int c_in = 0, c_out = 0, k = 1, dilation = 1, stride = 1, pad = 0;
+};
+
+struct VaeResUnit {
+    VaeSnake snake1, snake2;
+    VaeConv conv1, conv2;
+};
+
+struct VaeBlock {
+    VaeSnake snake1;
+    VaeConv conv_t;
+    VaeResUnit res[3];
+};
+
+struct VaeModel {
+    VaeConfig cfg;
+    VaeConv conv1;
+    std::vector<VaeBlock> blocks;
+    VaeSnake snake_out;
+    __half* conv2_w = nullptr;  // [audio_channels, 7, C] fp16 (tiny-N tail conv)
+    int conv2_cin = 0;
+    std::vector<void*> allocs;
+    size_t weight_bytes = 0;
+    void release();
+};
+
+int vae_load(const std::string& model_dir, VaeModel& m, std::string& err);
+
+struct VaeWorkspace {
+    size_t cap_frames = 0;
+    int capB = 0;
+    float* d_lat = nullptr;   // [B, T, 64] f32
+    __half* lat16 = nullptr;
+    float* x = nullptr;       // fp32 residual stream (largest level)
+    __half* xs = nullptr;     // snake'd fp16 copy feeding the next conv
+    __half* h = nullptr;      // fp16 intermediate inside a residual unit / conv-transpose input
+    float* d_audio = nullptr; // [B, T*hop, audio_channels]
+    std::vector<void*> allocs;
+    void release();
+};
+
+bool vae_workspace_reserve(const VaeModel& m, VaeWorkspace& ws, int B, int n_frames, std::string& err);
+
+// latents in ws.d_lat [B, n_frames, latent_ch] -> audio [B, n_frames*hop, audio_ch] (device pointer `audio`)
+cudaError_t vae_decode_device(const VaeModel& m, VaeWorkspace& ws, int B, int n_frames, float* audio, cudaStream_t st);
+
+}  // namespace ace

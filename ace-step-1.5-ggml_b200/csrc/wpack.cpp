@@ -1,8 +1,11 @@
 // Host side of the weight formats: ggml block decoders, Q8_0 quantiser and the tile packer (see wpack.h).
 #include "wpack.h"
 
+#include <algorithm>
+#include <atomic>
 #include <cmath>
 #include <cstring>
+#include <thread>
 
 namespace ace {
 
@@ -246,6 +249,25 @@ void quantize_row_q8_0(const float* x, void* dst_v, int64_t n) {
 }
 
 // ------------------------------------------------------------------ tile packer
+// n-tiles are independent: pack them on all host cores (load time of a 1.6 G-parameter model is dominated by this)
+template <typename F>
+static void parallel_for(int n, F&& fn) {
+    unsigned hw = std::thread::hardware_concurrency();
+    if (hw == 0) hw = 4;
+    const int nthreads = (int)std::min<unsigned>(hw, (unsigned)std::max(1, n));
+    if (nthreads <= 1) {
+        for (int i = 0; i < n; ++i) fn(i);
+        return;
+    }
+    std::atomic<int> next{0};
+    std::vector<std::thread> th;
+    for (int t = 0; t < nthreads; ++t)
+        th.emplace_back([&] {
+            for (int i = next.fetch_add(1); i < n; i = next.fetch_add(1)) fn(i);
+        });
+    for (auto& t : th) t.join();
+}
+
 static inline void put16(uint8_t* p, uint16_t v) {
     p[0] = (uint8_t)(v & 0xFF);
     p[1] = (uint8_t)(v >> 8);
@@ -348,14 +370,14 @@ bool pack_tiles_ggml(const void* rows_v, int ggml_type, int N, int K, std::vecto
     const uint8_t* rows = static_cast<const uint8_t*>(rows_v);
     init_meta(meta, wtype, N, 1, K);
     out.assign(meta.bytes, 0);
-    std::vector<RowCodes> rc((size_t)TILE_N);
-    for (int nt = 0; nt < meta.n_tiles; ++nt) {
+    parallel_for(meta.n_tiles, [&](int nt) {
+        std::vector<RowCodes> rc((size_t)TILE_N);
         const int r0 = nt * TILE_N;
         const int nr = std::min(TILE_N, N - r0);
         for (int r = 0; r < nr; ++r) decode_row_codes(ggml_type, rows + (size_t)(r0 + r) * rb, K, rc[(size_t)r]);
         for (int kb = 0; kb < meta.kb_per_tap; ++kb)
             pack_quant_tile(out.data() + meta.tile_offset(nt, kb), wtype, rc, 0, nr, kb * TILE_K);
-    }
+    });
     return true;
 }
 
@@ -368,7 +390,10 @@ bool pack_tiles_f32(const float* w, int N, int taps, int K, int wtype, std::vect
         }
         const size_t rb = ggml_row_bytes(GGML_Q8_0, K);
         std::vector<uint8_t> q((size_t)N * rb);
-        for (int r = 0; r < N; ++r) quantize_row_q8_0(w + (size_t)r * K, q.data() + (size_t)r * rb, K);
+        parallel_for((N + 63) / 64, [&](int blk) {
+            for (int r = blk * 64; r < std::min(N, blk * 64 + 64); ++r)
+                quantize_row_q8_0(w + (size_t)r * K, q.data() + (size_t)r * rb, K);
+        });
         return pack_tiles_ggml(q.data(), GGML_Q8_0, N, K, out, meta, err);
     }
     if (wtype != W_F16) {
@@ -378,7 +403,7 @@ bool pack_tiles_f32(const float* w, int N, int taps, int K, int wtype, std::vect
     init_meta(meta, W_F16, N, taps, K);
     out.assign(meta.bytes, 0);
     const long row_stride = (long)taps * K;
-    for (int nt = 0; nt < meta.n_tiles; ++nt) {
+    parallel_for(meta.n_tiles, [&](int nt) {
         const int r0 = nt * TILE_N;
         const int nr = std::min(TILE_N, N - r0);
         for (int tap = 0; tap < taps; ++tap) {
@@ -389,7 +414,7 @@ bool pack_tiles_f32(const float* w, int N, int taps, int K, int wtype, std::vect
                               w + (size_t)r0 * row_stride + (size_t)tap * K + k0, row_stride, nr, nc);
             }
         }
-    }
+    });
     return true;
 }
 

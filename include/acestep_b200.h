@@ -1,0 +1,90 @@
+/* acestep_b200.h — additive extensions to the acestep_ggml C ABI (new symbols only; the reference symbols in
+ * acestep_ggml.h keep their exact meaning).  They exist because the reference ABI evaluates one sample per call
+ * from host buffers (acestep_ggml.h:96-108; the Python hook loops `for b in range(bsz)`,
+ * scripts/run_non_ggml_real_case.py:516-527), which on a GPU would spend the step in PCIe copies:
+ *
+ *   ace_b200_dit_forward_batched   B samples per call (what the hook's loop becomes)
+ *   ace_b200_generate_latents      device-resident Euler sampler: N steps, optional CFG, one H2D + one D2H
+ *                                  (same update rule as acestep_ggml.cpp:2056-2086)
+ *   ace_b200_vae_decode_batched    B clips per call, un-tiled (exact) decode
+ *   ace_b200_generate_audio        sampler + VAE decode without leaving the device
+ *   ace_b200_*_stats / debug_*     measurement + unit-test hooks (device time of the last call, launch count,
+ *                                  direct access to the GEMM / attention kernels for parity tests)
+ */
+#ifndef ACESTEP_B200_H
+#define ACESTEP_B200_H
+
+#include "acestep_ggml.h"
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+/* hidden_states [B, seq_len, 64], context_latents [B, seq_len, 128], encoder_hidden_states [B, enc_len, hidden],
+ * attention_mask [B, seq_len] / encoder_attention_mask [B, enc_len] (nullable), timesteps / timesteps_r [B],
+ * out [B, seq_len, 64]; out_size in bytes. */
+ACE_GGML_API ace_ggml_status ace_b200_dit_forward_batched(
+    ace_ggml_context * ctx, const float * hidden_states, const float * context_latents,
+    const float * encoder_hidden_states, const int32_t * attention_mask, const int32_t * encoder_attention_mask,
+    int32_t batch, int32_t seq_len, int32_t enc_len, const float * timesteps, const float * timesteps_r,
+    float * out, size_t out_size);
+
+/* Euler sampler on the device.  noise [B, seq_len, 64] is the initial x_T (the caller draws it, so any RNG —
+ * including the reference's std::mt19937 sequence — can be reproduced); schedule [n_steps] are the t_i
+ * (x -= v*(t_i - t_{i+1}); last step x -= v*t_i).  uncond_encoder_hidden_states == NULL disables CFG; otherwise
+ * v = v_u + guidance*(v_c - v_u) with both branches evaluated in ONE batched forward of 2B samples.
+ * out_latents [B, seq_len, 64]. */
+ACE_GGML_API ace_ggml_status ace_b200_generate_latents(
+    ace_ggml_context * ctx, const float * noise, const float * context_latents,
+    const float * encoder_hidden_states, const float * uncond_encoder_hidden_states,
+    const int32_t * attention_mask, const int32_t * encoder_attention_mask, int32_t batch, int32_t seq_len,
+    int32_t enc_len, const float * schedule, int32_t n_steps, float guidance, float * out_latents, size_t out_size);
+
+/* latents [B, n_frames, latent_ch] -> out [B, n_frames*hop, audio_ch] */
+ACE_GGML_API ace_ggml_status ace_b200_vae_decode_batched(ace_ggml_context * ctx, const float * latents, int32_t batch,
+                                                         int32_t n_frames, float * out, size_t out_size);
+
+/* ace_b200_generate_latents followed by the VAE decode, latents never leave HBM. out_audio [B, seq_len*hop, audio_ch];
+ * out_latents may be NULL. */
+ACE_GGML_API ace_ggml_status ace_b200_generate_audio(
+    ace_ggml_context * ctx, const float * noise, const float * context_latents,
+    const float * encoder_hidden_states, const float * uncond_encoder_hidden_states,
+    const int32_t * attention_mask, const int32_t * encoder_attention_mask, int32_t batch, int32_t seq_len,
+    int32_t enc_len, const float * schedule, int32_t n_steps, float guidance, float * out_latents,
+    float * out_audio, size_t out_audio_size);
+
+/* the reference's shift schedules (acestep_ggml.cpp:1484-1500): t_i = s*u/(1+(s-1)*u), u = 1 - i/n_steps.
+ * For n_steps == 8 and shift in {1,2,3} this reproduces the three hard-coded tables. */
+ACE_GGML_API ace_ggml_status ace_b200_shift_schedule(float shift, int32_t n_steps, float * out_schedule);
+
+/* measurement: device time (CUDA events on the context's stream) of the kernels of the last successful call on this
+ * context, excluding host<->device copies; and the number of kernels this library launched since process start. */
+ACE_GGML_API double   ace_b200_last_device_ms(const ace_ggml_context * ctx);
+ACE_GGML_API uint64_t ace_b200_kernel_launches(void);
+ACE_GGML_API const char * ace_b200_model_info(const ace_ggml_context * ctx);
+
+/* ---- unit-test hooks (tests/ only) -------------------------------------------------------------------------
+ * debug_gemm: D[B, l_out, N] = tapGEMM(A fp32 [B, L, C] rounded to fp16, W) through the tensor-core kernel (simt = 0)
+ * or the plain-FMA debug kernel (simt = 1).  W is given either as fp32 [N, taps, C] (w_ggml_type = 0 -> F16 tiles,
+ * 8 -> quantised to Q8_0 on the fly) or as raw ggml rows of w_ggml_type (8 Q8_0 / 12 Q4_K / 14 Q6_K), taps = 1.
+ * epilogue: bit 0 bias[N], bit 1 SwiGLU over interleaved rows (out [.., N/2]), bit 2 residual add of `resid`,
+ * bit 3 split-K = 4.  Output is fp32 (SwiGLU: the fp16 result widened). */
+ACE_GGML_API ace_ggml_status ace_b200_debug_gemm(ace_ggml_context * ctx, const float * A, int32_t B, int32_t L,
+                                                 int32_t C, const void * W, int32_t w_ggml_type, int32_t N,
+                                                 int32_t taps, int32_t tap_stride, int32_t tap_offset, int32_t l_out,
+                                                 const float * bias, const float * resid, int32_t epilogue,
+                                                 int32_t simt, float * out, size_t out_size);
+/* debug_attention: Q [B, q_len, n_heads*128], K/V [B, k_len, n_kv*128] fp32 (rounded to fp16 inside), window < 0 = full */
+ACE_GGML_API ace_ggml_status ace_b200_debug_attention(ace_ggml_context * ctx, const float * Q, const float * K,
+                                                      const float * V, const int32_t * key_mask, int32_t B,
+                                                      int32_t q_len, int32_t k_len, int32_t n_heads, int32_t n_kv,
+                                                      int32_t window, float * out, size_t out_size);
+/* CPU-only: pack raw ggml rows (or fp32 when w_ggml_type == 0) into device tiles and decode them back with the host
+ * emulation of the kernel's decoder; `ref` receives the ggml dequantisation of the same rows. No GPU needed. */
+ACE_GGML_API ace_ggml_status ace_b200_debug_pack_roundtrip(const void * W, int32_t w_ggml_type, int32_t N, int32_t K,
+                                                           float * unpacked, float * ref);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* ACESTEP_B200_H */

@@ -91,7 +91,8 @@ class VaeDims:
 
 
 VAE_FULL = VaeDims()
-VAE_TOY = VaeDims(decoder_channels=16, encoder_hidden_size=16,
+# toy VAE: channels 128 -> 64 -> 32 (every level a multiple of 32, like the real 2048..128 plan)
+VAE_TOY = VaeDims(decoder_channels=32, encoder_hidden_size=16,
                   downsampling_ratios=[2, 4, 6], channel_multiples=[1, 2, 4])
 
 

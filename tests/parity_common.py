@@ -1,0 +1,60 @@
+"""Shared helpers for the parity tests: seeded fixtures on disk, reference (oracle/_ref) runs, distance metrics.
+Metrics follow the reference's own compare tools (tools/compare_dit.py:576-627: MAE / max-abs / cosine;
+tools/eval_quant_prompt_pipeline.py:197-225: SNR)."""
+import os
+
+import numpy as np
+
+from acestep_b200 import fixtures as fx
+from oracle import refbridge
+
+
+def metrics(a: np.ndarray, ref: np.ndarray) -> dict:
+    a = np.asarray(a, dtype=np.float64).ravel()
+    r = np.asarray(ref, dtype=np.float64).ravel()
+    d = a - r
+    return {
+        "rel_l2": float(np.linalg.norm(d) / (np.linalg.norm(r) + 1e-30)),
+        "cos": float(a @ r / (np.linalg.norm(a) * np.linalg.norm(r) + 1e-30)),
+        "mae": float(np.abs(d).mean()),
+        "max_abs": float(np.abs(d).max()),
+        "snr_db": float(10 * np.log10((r @ r + 1e-30) / (d @ d + 1e-30))),
+    }
+
+
+def make_dit_dir(root: str, dims=fx.TOY, seed: int = 0, quant: str = None) -> str:
+    """safetensors fixture, or (quant in F16/Q8_0/Q4_K/Q6_K) a GGUF-only directory."""
+    name = f"dit_{dims.hidden_size}_{dims.num_hidden_layers}_{quant or 'st'}"
+    d = os.path.join(root, name)
+    if os.path.exists(os.path.join(d, "config.json")):
+        return d
+    if quant:
+        fx.make_dit_fixture(d, dims, seed, safetensors=False, gguf_quant=quant,
+                            ggml_lib=refbridge.ref_lib() if refbridge.ref_available() else None)
+    else:
+        fx.make_dit_fixture(d, dims, seed)
+    return d
+
+
+def make_vae_dir(root: str, dims=fx.VAE_TOY, seed: int = 0) -> str:
+    d = os.path.join(root, f"vae_{dims.decoder_channels}")
+    if not os.path.exists(os.path.join(d, "config.json")):
+        fx.make_vae_fixture(d, dims, seed)
+    return d
+
+
+def ref_dit_forward(dit_dir, inputs, t, t_r, max_layers=None, threads=4, buffer_bytes=1 << 30, masks=None):
+    env = {}
+    if max_layers:
+        env["ACE_GGML_DIT_MAX_LAYERS"] = str(max_layers)
+    call = {"op": "dit_forward", "t": t, "t_r": t_r, "out": "v"}
+    inp = dict(inputs)
+    if masks:
+        if masks.get("mask") is not None:
+            inp["attention_mask"] = masks["mask"]
+            call["mask"] = "attention_mask"
+        if masks.get("enc_mask") is not None:
+            inp["encoder_attention_mask"] = masks["enc_mask"]
+            call["enc_mask"] = "encoder_attention_mask"
+    outs, tim = refbridge.run_ref([call], inp, dit_dir=dit_dir, threads=threads, compute_buffer_bytes=buffer_bytes, env=env)
+    return outs["v"], tim

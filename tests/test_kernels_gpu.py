@@ -1,0 +1,211 @@
+"""GPU: the tap-GEMM (tcgen05) and attention kernels against numpy restatements, through the C ABI test hooks.
+
+GEMM oracle: operands rounded to fp16 exactly as the kernel sees them (activations: cvt.rn; weights: the ggml
+dequantisation of the same blocks, third_party/ggml/src/ggml-quants.c), products accumulated in float64.
+Tolerance: fp32 accumulation order + (for quantised weights) the fp16 rounding of the decoded weight: 2e-3 relative
+to the output RMS, stated per test.
+"""
+import numpy as np
+import pytest
+
+from blocks import random_rows
+
+pytestmark = pytest.mark.gpu
+
+
+@pytest.fixture(scope="module")
+def br():
+    from acestep_b200.bridge import B200Bridge
+    b = B200Bridge()
+    yield b
+    b.close()
+
+
+def h16(x):
+    return np.asarray(x, dtype=np.float32).astype(np.float16).astype(np.float64)
+
+
+def tap_gemm_ref(A, W, taps, tap_stride, tap_offset, l_out):
+    """A [B, L, C] fp64, W [N, taps, C] fp64 -> [B, l_out, N]"""
+    B, L, C = A.shape
+    N = W.shape[0]
+    out = np.zeros((B, l_out, N))
+    for t in range(taps):
+        sh = t * tap_stride + tap_offset
+        rows = np.arange(l_out) + sh
+        ok = (rows >= 0) & (rows < L)
+        At = np.zeros((B, l_out, C))
+        At[:, ok] = A[:, rows[ok]]
+        out += At @ W[:, t].T
+    return out
+
+
+def rel_err(a, b):
+    return float(np.sqrt(np.mean((a - b) ** 2)) / (np.sqrt(np.mean(b ** 2)) + 1e-30))
+
+
+def dequant_ref(rows, gt, N, K):
+    from acestep_b200.bridge import pack_roundtrip
+    _, ref = pack_roundtrip(rows, gt, N, K)
+    return ref
+
+
+@pytest.mark.parametrize("B,L,C,N", [(1, 128, 64, 128), (1, 200, 256, 384), (2, 130, 384, 200), (1, 1, 256, 512),
+                                       (1, 700, 2048, 1024)])
+@pytest.mark.parametrize("simt", [False, True])
+def test_gemm_f16_linear(br, B, L, C, N, simt):
+    g = np.random.default_rng(B * 7 + L + C + N)
+    A = g.standard_normal((B, L, C), dtype=np.float32)
+    W = (g.standard_normal((N, C), dtype=np.float32) * C ** -0.5).astype(np.float32)
+    bias = g.standard_normal((N,), dtype=np.float32)
+    out = br.debug_gemm(A, W, w_type=0, N=N, bias=bias, simt=simt)
+    ref = tap_gemm_ref(h16(A), h16(W)[:, None, :], 1, 0, 0, L) + bias
+    assert rel_err(out, ref) < 1e-4, rel_err(out, ref)
+
+
+@pytest.mark.parametrize("gt", [8, 12, 14])
+@pytest.mark.parametrize("L,K,N", [(128, 256, 128), (300, 512, 384), (64, 2048, 256)])
+def test_gemm_quant_linear(br, gt, L, K, N):
+    g = np.random.default_rng(gt * 31 + L + K + N)
+    A = g.standard_normal((1, L, K), dtype=np.float32)
+    rows = random_rows(gt, N, K, seed=gt + L)
+    Wd = dequant_ref(rows, gt, N, K).astype(np.float64)
+    ref = tap_gemm_ref(h16(A), Wd[:, None, :], 1, 0, 0, L)
+    for simt in (True, False):
+        out = br.debug_gemm(A, rows, w_type=gt, N=N, simt=simt)
+        # decoded weights are rounded to fp16 in shared memory: <= 2^-11 relative per weight
+        assert rel_err(out, ref) < 2e-3, (simt, rel_err(out, ref))
+
+
+def test_gemm_q8_online(br):
+    g = np.random.default_rng(5)
+    A = g.standard_normal((1, 96, 384), dtype=np.float32)
+    W = (g.standard_normal((256, 384), dtype=np.float32) * 0.05).astype(np.float32)
+    out = br.debug_gemm(A, W, w_type=-8, N=256)
+    ref = tap_gemm_ref(h16(A), W.astype(np.float64)[:, None, :], 1, 0, 0, 96)
+    assert rel_err(out, ref) < 1e-2  # Q8_0 quantisation noise of the weights themselves
+
+
+@pytest.mark.parametrize("dil", [1, 3, 9])
+def test_gemm_conv7(br, dil):
+    """k=7 dilated conv with zero padding = 7 taps, stride = dilation, offset = -3*dilation (acestep_vae_model.cpp:709)."""
+    g = np.random.default_rng(dil)
+    B, L, C, N = 2, 333, 64, 96
+    A = g.standard_normal((B, L, C), dtype=np.float32)
+    W = (g.standard_normal((N, 7, C), dtype=np.float32) * (7 * C) ** -0.5).astype(np.float32)
+    out = br.debug_gemm(A, W, w_type=0, N=N, taps=7, tap_stride=dil, tap_offset=-3 * dil)
+    ref = tap_gemm_ref(h16(A), h16(W), 7, dil, -3 * dil, L)
+    assert rel_err(out, ref) < 1e-4
+
+
+def test_gemm_conv_transpose_phases(br):
+    """conv-transpose k=2s as 2 taps (rows i, i-1) x s phase columns (acestep_vae_model.cpp:696-707)."""
+    g = np.random.default_rng(11)
+    B, L, Cin, Cout, s = 1, 150, 64, 32, 4
+    x = g.standard_normal((B, L, Cin), dtype=np.float32)
+    w = (g.standard_normal((Cin, Cout, 2 * s), dtype=np.float32) * Cin ** -0.5).astype(np.float32)
+    Wp = np.zeros((s * Cout, 2, Cin), dtype=np.float32)
+    for r in range(s):
+        for tap in range(2):
+            Wp[r * Cout:(r + 1) * Cout, tap] = w[:, :, r + tap * s].T
+    out = br.debug_gemm(x, Wp, w_type=0, N=s * Cout, taps=2, tap_stride=-1, tap_offset=0, l_out=L + 1)
+    full = out.reshape(B, (L + 1) * s, Cout)
+    xr, wr = h16(x), h16(w)
+    ref = np.zeros((B, (L - 1) * s + 2 * s, Cout))
+    for i in range(L):
+        for k in range(2 * s):
+            ref[:, i * s + k] += xr[:, i] @ wr[:, :, k]
+    assert rel_err(full[:, : ref.shape[1]], ref) < 1e-4
+
+
+def test_gemm_swiglu_and_residual_and_splitk(br):
+    g = np.random.default_rng(2)
+    L, K, I = 260, 512, 384
+    A = g.standard_normal((1, L, K), dtype=np.float32)
+    Wg = (g.standard_normal((I, K), dtype=np.float32) * K ** -0.5).astype(np.float32)
+    Wu = (g.standard_normal((I, K), dtype=np.float32) * K ** -0.5).astype(np.float32)
+    Wi = np.empty((2 * I, K), dtype=np.float32)
+    Wi[0::2], Wi[1::2] = Wg, Wu
+    out = br.debug_gemm(A, Wi, w_type=0, N=2 * I, swiglu=True)
+    gg = h16(A)[0] @ h16(Wg).T
+    uu = h16(A)[0] @ h16(Wu).T
+    ref = gg / (1 + np.exp(-gg)) * uu
+    assert rel_err(out[0], ref) < 2e-3  # fp16 output rounding
+    # residual add, plain and split-K (atomics)
+    W = (g.standard_normal((256, K), dtype=np.float32) * K ** -0.5).astype(np.float32)
+    R = g.standard_normal((1, L, 256), dtype=np.float32)
+    ref2 = h16(A)[0] @ h16(W).T + R[0]
+    for sk in (False, True):
+        o = br.debug_gemm(A, W, w_type=0, N=256, resid=R, split_k=sk)
+        assert rel_err(o[0], ref2) < 1e-4, sk
+
+
+def test_gemm_ragged_n_quant(br):
+    """N = 640 = 5 tiles of 128 (odd count: the 128x256 variant must cope with a missing second sub-tile)."""
+    g = np.random.default_rng(9)
+    A = g.standard_normal((1, 512, 256), dtype=np.float32)
+    rows = random_rows(12, 640, 256, seed=4)
+    out = br.debug_gemm(A, rows, w_type=12, N=640)
+    ref = tap_gemm_ref(h16(A), dequant_ref(rows, 12, 640, 256).astype(np.float64)[:, None, :], 1, 0, 0, 512)
+    assert rel_err(out, ref) < 2e-3
+
+
+def test_gemm_large_tiles(br):
+    """enough tiles (>= 2 waves of 128x256) that the launcher picks BN=256 by itself, quantised + F16."""
+    g = np.random.default_rng(10)
+    L, K, N = 128 * 40, 256, 2048
+    A = g.standard_normal((1, L, K), dtype=np.float32)
+    rows = random_rows(8, N, K, seed=6)
+    ref = tap_gemm_ref(h16(A), dequant_ref(rows, 8, N, K).astype(np.float64)[:, None, :], 1, 0, 0, L)
+    out = br.debug_gemm(A, rows, w_type=8, N=N)
+    assert rel_err(out, ref) < 2e-3
+    W = (g.standard_normal((N, K), dtype=np.float32) * K ** -0.5).astype(np.float32)
+    out = br.debug_gemm(A, W, w_type=0, N=N)
+    assert rel_err(out, tap_gemm_ref(h16(A), h16(W)[:, None, :], 1, 0, 0, L)) < 1e-4
+
+
+def attention_ref(Q, K, V, key_mask, n_heads, n_kv, window):
+    B, ql, _ = Q.shape
+    kl = K.shape[1]
+    q = h16(Q).reshape(B, ql, n_heads, 128)
+    k = h16(K).reshape(B, kl, n_kv, 128)
+    v = h16(V).reshape(B, kl, n_kv, 128)
+    rep = n_heads // n_kv
+    out = np.zeros((B, ql, n_heads, 128))
+    for b in range(B):
+        for h in range(n_heads):
+            s = q[b, :, h] @ k[b, :, h // rep].T / np.sqrt(128.0)
+            allow = np.ones((ql, kl), dtype=bool)
+            if window >= 0:
+                d = np.arange(ql)[:, None] - np.arange(kl)[None, :]
+                allow &= np.abs(d) <= window
+            if key_mask is not None:
+                allow &= (key_mask[b] != 0)[None, :]
+            s = np.where(allow, s, -np.inf)
+            s = s - s.max(axis=1, keepdims=True)
+            p = np.exp(s)
+            p /= p.sum(axis=1, keepdims=True)
+            out[b, :, h] = p @ v[b, :, h // rep]
+    return out.reshape(B, ql, n_heads * 128)
+
+
+@pytest.mark.parametrize("ql,kl,window,masked", [(64, 64, -1, False), (200, 200, -1, False), (375, 375, 128, False),
+                                                   (130, 77, -1, True), (300, 300, 16, True), (1, 5, -1, False)])
+def test_attention(br, ql, kl, window, masked):
+    g = np.random.default_rng(ql + kl)
+    B, nh, nkv = 2, 4, 2
+    Q = g.standard_normal((B, ql, nh * 128), dtype=np.float32)
+    K = g.standard_normal((B, kl, nkv * 128), dtype=np.float32)
+    V = g.standard_normal((B, kl, nkv * 128), dtype=np.float32)
+    km = None
+    if masked:
+        km = (g.random((B, kl)) > 0.3).astype(np.int32)
+        km[:, :: 7] = 1
+        if window >= 0:  # keep every query's own key visible so no row is fully masked
+            km[:] = 1
+            km[:, 5:40] = 0
+            window = max(window, 40)
+    out = br.debug_attention(Q, K, V, km, nh, nkv, window)
+    ref = attention_ref(Q, K, V, km, nh, nkv, window)
+    # P and O are rounded to fp16 inside the kernel: ~1e-3 relative
+    assert rel_err(out, ref) < 3e-3, rel_err(out, ref)

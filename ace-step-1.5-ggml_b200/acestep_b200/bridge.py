@@ -74,6 +74,9 @@ SIGNATURES = {
     "ace_b200_last_device_ms": (ctypes.c_double, [_P]),
     "ace_b200_kernel_launches": (ctypes.c_uint64, []),
     "ace_b200_model_info": (ctypes.c_char_p, [_P]),
+    "ace_b200_profile_enable": (None, [ctypes.c_int32]),
+    "ace_b200_profile_collect": (None, [ctypes.POINTER(ctypes.c_double), ctypes.POINTER(ctypes.c_double),
+                                        ctypes.POINTER(ctypes.c_double), ctypes.POINTER(ctypes.c_int64)]),
     "ace_b200_debug_gemm": (ctypes.c_int, [_P, _F, ctypes.c_int32, ctypes.c_int32, ctypes.c_int32, _P, ctypes.c_int32,
                                            ctypes.c_int32, ctypes.c_int32, ctypes.c_int32, ctypes.c_int32,
                                            ctypes.c_int32, _F, _F, ctypes.c_int32, ctypes.c_int32, _F,
@@ -274,6 +277,17 @@ class B200Bridge:
 
     def model_info(self) -> str:
         return self.lib.ace_b200_model_info(self.ctx).decode()
+
+    def profile_enable(self, on: bool) -> None:
+        self.lib.ace_b200_profile_enable(1 if on else 0)
+
+    def profile_collect(self) -> dict:
+        """per-family totals since profile_enable(True): {family: {ms, flops, bytes, launches}}"""
+        ms, fl, by = (ctypes.c_double * 4)(), (ctypes.c_double * 4)(), (ctypes.c_double * 4)()
+        n = (ctypes.c_int64 * 4)()
+        self.lib.ace_b200_profile_collect(ms, fl, by, n)
+        names = ("gemm", "attention", "elementwise", "vae_tail")
+        return {k: {"ms": ms[i], "flops": fl[i], "bytes": by[i], "launches": int(n[i])} for i, k in enumerate(names)}
 
     # ------------------------------------------------------------------ unit-test hooks
     def debug_gemm(self, A, W, *, w_type: int = 0, N: int, taps: int = 1, tap_stride: int = 0, tap_offset: int = 0,

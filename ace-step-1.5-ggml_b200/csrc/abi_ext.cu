@@ -108,4 +108,16 @@ const char* ace_b200_model_info(const ace_ggml_context* ctx_c) {
     return ctx->info.c_str();
 }
 
+void ace_b200_profile_enable(int32_t on) { ace::prof_enable(on != 0); }
+void ace_b200_profile_collect(double* ms, double* flops, double* bytes, int64_t* launches) {
+    ace::ProfTotals t;
+    ace::prof_collect(t);
+    for (int c = 0; c < ace::PROF_NCAT; ++c) {
+        if (ms) ms[c] = t.ms[c];
+        if (flops) flops[c] = t.flops[c];
+        if (bytes) bytes[c] = t.bytes[c];
+        if (launches) launches[c] = t.launches[c];
+    }
+}
+
 }  // extern "C"

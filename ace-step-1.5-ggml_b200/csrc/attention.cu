@@ -246,6 +246,8 @@ void launch_attention(const __half* Q, long q_stride, const __half* K, long k_st
                       __half* O, long o_stride, const int32_t* key_mask, int B, int q_len, int k_len, int n_heads,
                       int n_kv_heads, int window, cudaStream_t st) {
     note_launch();
+    const double k_eff = window >= 0 ? (double)(2 * window + 1 < k_len ? 2 * window + 1 : k_len) : (double)k_len;
+    ProfScope prof_scope(PROF_ATTN, 4.0 * B * n_heads * (double)q_len * k_eff * 128.0, 0.0, st);
     static bool attr = false;
     if (!attr) {
         cudaFuncSetAttribute(attention_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, ATT_SMEM);

@@ -601,6 +601,8 @@ bool gemm_force_simt() {
 cudaError_t gemm_launch(const GemmProblem& g, cudaStream_t stream, bool simt) {
     const PackedWeight& w = *g.W;
     note_launch();
+    ProfScope prof_scope(PROF_GEMM, 2.0 * g.B * (double)g.l_out * w.N * (double)w.K * w.taps,
+                         (double)w.bytes + (double)g.B * g.L * g.C * 2.0, stream);
     KParams kp;
     kp.W = static_cast<const uint8_t*>(w.dev);
     kp.wtype = w.wtype;

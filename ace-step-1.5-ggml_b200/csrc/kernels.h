@@ -12,6 +12,31 @@ namespace ace {
 extern std::atomic<uint64_t> g_kernel_launches;
 inline void note_launch() { g_kernel_launches.fetch_add(1, std::memory_order_relaxed); }
 
+// Optional per-kernel-family device timing (off by default; bench.py turns it on for ONE extra pass so the timed
+// pass carries no event overhead): every launcher brackets its kernel with a CUDA event pair on the launching stream.
+enum ProfCat : int { PROF_GEMM = 0, PROF_ATTN = 1, PROF_ELEM = 2, PROF_VAE_TAIL = 3, PROF_NCAT = 4 };
+struct ProfTotals {
+    double ms[PROF_NCAT];
+    double flops[PROF_NCAT];   // algorithmic FLOPs
+    double bytes[PROF_NCAT];   // algorithmic HBM bytes (where the launcher knows them)
+    long launches[PROF_NCAT];
+};
+bool prof_enabled();
+void prof_enable(bool on);                     // clears previous records
+void prof_begin(int cat, double flops, double bytes, cudaStream_t st);
+void prof_end(cudaStream_t st);
+void prof_collect(ProfTotals& out);            // synchronises on the recorded events
+struct ProfScope {
+    cudaStream_t st;
+    bool on;
+    ProfScope(int cat, double flops, double bytes, cudaStream_t s) : st(s), on(prof_enabled()) {
+        if (on) prof_begin(cat, flops, bytes, st);
+    }
+    ~ProfScope() {
+        if (on) prof_end(st);
+    }
+};
+
 // ---- DiT input side ------------------------------------------------------------------------------
 // x0[b, p, k*in_ch + c] = (c < ctx_dim ? context[b, 2p+k, c] : hidden[b, 2p+k, c-ctx_dim]), zero past T
 // reference: acestep_dit_model.cpp:1343-1377 (pack + zero pad to a patch multiple)

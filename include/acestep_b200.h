@@ -62,6 +62,10 @@ ACE_GGML_API ace_ggml_status ace_b200_shift_schedule(float shift, int32_t n_step
 ACE_GGML_API double   ace_b200_last_device_ms(const ace_ggml_context * ctx);
 ACE_GGML_API uint64_t ace_b200_kernel_launches(void);
 ACE_GGML_API const char * ace_b200_model_info(const ace_ggml_context * ctx);
+/* per-kernel-family device timing: enable(1) before a call, collect after it (then enable(0)).
+ * families: 0 tap-GEMM, 1 attention, 2 element-wise / norm, 3 VAE output conv.  out arrays have 4 entries each. */
+ACE_GGML_API void ace_b200_profile_enable(int32_t on);
+ACE_GGML_API void ace_b200_profile_collect(double * ms, double * flops, double * bytes, int64_t * launches);
 
 /* ---- unit-test hooks (tests/ only) -------------------------------------------------------------------------
  * debug_gemm: D[B, l_out, N] = tapGEMM(A fp32 [B, L, C] rounded to fp16, W) through the tensor-core kernel (simt = 0)

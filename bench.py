@@ -161,7 +161,7 @@ def run_reference_arm(a, world, rank):
     sched = shift_schedule(3.0, max(a.steps + a.warmup, 1))
     calls = [{"op": "dit_forward", "t": float(sched[i]), "t_r": float(sched[i]), "out": f"v{i}"} for i in range(a.warmup + a.steps)]
     inp = {"hidden_states": noise[0], "context_latents": ctx[0], "encoder_hidden_states": enc[0]}
-    buf = int(float(os.environ.get("ACE_REF_BUFFER_GB", "12")) * (1 << 30))
+    buf = int(float(os.environ.get("ACE_REF_BUFFER_GB", "20")) * (1 << 30))
     outs, tim = refbridge.run_ref(calls, inp, dit_dir=d, threads=cores, compute_buffer_bytes=buf, env={"ACE_GGML_DIT_PROFILE": "1"}, timeout=6000)
     per = [tim[f"dit_forward_v{i}_s"] for i in range(a.warmup, a.warmup + a.steps)]
     total = float(sum(per))
@@ -317,7 +317,7 @@ def cpu_baseline(d, noise, ctx, enc):
     if not refbridge.ref_available():
         return {"value": None, "unit": UNIT, "cores": 0, "kind": "reference", "sample": "oracle/_ref not built"}
     cores = os.cpu_count() or 1
-    buf = int(float(os.environ.get("ACE_REF_BUFFER_GB", "12")) * (1 << 30))
+    buf = int(float(os.environ.get("ACE_REF_BUFFER_GB", "20")) * (1 << 30))
     inp = {"hidden_states": noise[0], "context_latents": ctx[0], "encoder_hidden_states": enc[0]}
     calls = [{"op": "dit_forward", "t": 1.0, "t_r": 1.0, "out": "v0"}, {"op": "dit_forward", "t": 0.9, "t_r": 0.9, "out": "v1"}]
     outs, tim = refbridge.run_ref(calls, inp, dit_dir=d, threads=cores, compute_buffer_bytes=buf, env={"ACE_GGML_DIT_PROFILE": "1"}, timeout=3000)

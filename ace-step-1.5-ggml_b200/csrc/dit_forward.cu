@@ -100,14 +100,7 @@ struct Fwd {
         g.W = &W;
         g.epi = epi;
         if (g.epi.out_bstride == 0) g.epi.out_bstride = (long)rows_per_b * g.epi.ld_out;
-        g.split_k = 1;
-        if (allow_split) {
-            const long tiles = (long)W.n_tiles * B * ((rows_per_b + 127) / 128);
-            const int kb = W.kb_per_tap * W.taps;
-            int sk = 1;
-            while (tiles * sk < sms && sk < 8 && kb / (sk * 2) >= 8) sk *= 2;
-            g.split_k = sk;
-        }
+        g.split_k = allow_split ? 0 : 1;  // 0 = let the launcher split K when one wave of tiles would not fill the SMs
         rc = gemm_launch(g, st);
     }
 };
@@ -155,11 +148,14 @@ cudaError_t dit_forward_device(const DitModel& m, DitWorkspace& ws, int B, int T
         for (int i = 0; i < n_layers; ++i) {
             const DitLayer& ly = m.layers[(size_t)i];
             __half* kv = ws.cross_kv + (size_t)i * B * E * 2 * nkv;
-            GemmEpilogue ek;
+            GemmEpilogue ek;  // K heads normed in the epilogue (no RoPE on the cross path), V stored as is
+            ek.mode = EPI_HEADNORM;
+            ek.hn_wa = ly.cross_kn;
+            ek.hn_na = nkv;
+            ek.hn_eps = eps;
             ek.out_f16 = kv;
             ek.ld_out = 2 * nkv;
             f.gemm(ws.encp, H, 1, B * E, ly.cross_kv, ek, false);
-            launch_headnorm_rope(kv, 2 * nkv, 0, NKV, ly.cross_kn, nullptr, 1, B * E, eps, st);
         }
     }
     // ---- timestep embeddings -> AdaLN tables   (M = B rows; HBM-bound GEMVs through the same kernel)
@@ -204,13 +200,18 @@ cudaError_t dit_forward_device(const DitModel& m, DitWorkspace& ws, int B, int T
         // self-attention
         launch_rmsnorm_mod(ws.x, ly.self_norm, scale_msa, shift_msa, mod_bs, ws.xn, B, S, H, eps, st);
         {
-            GemmEpilogue e;
+            GemmEpilogue e;  // fused: per-head RMSNorm(q, k) + NEOX RoPE at position l; V stored as is
+            e.mode = EPI_HEADNORM;
+            e.hn_wa = ly.self_qn;
+            e.hn_na = nq;
+            e.hn_wb = ly.self_kn;
+            e.hn_nb = nkv;
+            e.rope = ws.rope;
+            e.hn_eps = eps;
             e.out_f16 = ws.qkv;
             e.ld_out = qkv_w;
-            f.gemm(ws.xn, H, 1, B * S, ly.self_qkv, e, false);
+            f.gemm(ws.xn, H, B, S, ly.self_qkv, e, false);
         }
-        launch_headnorm_rope(ws.qkv, qkv_w, 0, NQ, ly.self_qn, ws.rope, B, S, eps, st);
-        launch_headnorm_rope(ws.qkv, qkv_w, nq, NKV, ly.self_kn, ws.rope, B, S, eps, st);
         launch_attention(ws.qkv, qkv_w, ws.qkv + nq, qkv_w, ws.qkv + nq + nkv, qkv_w, ws.att, nq, ws.d_pmask, B, S, S, NQ,
                          NKV, ly.sliding ? c.sliding_window : -1, st);
         {
@@ -227,11 +228,14 @@ cudaError_t dit_forward_device(const DitModel& m, DitWorkspace& ws, int B, int T
             launch_rmsnorm_mod(ws.x, ly.cross_norm, nullptr, nullptr, 0, ws.xn, B, S, H, eps, st);
             {
                 GemmEpilogue e;
+                e.mode = EPI_HEADNORM;
+                e.hn_wa = ly.cross_qn;
+                e.hn_na = nq;
+                e.hn_eps = eps;
                 e.out_f16 = ws.qkv;
                 e.ld_out = nq;
                 f.gemm(ws.xn, H, 1, B * S, ly.cross_q, e, false);
             }
-            launch_headnorm_rope(ws.qkv, nq, 0, NQ, ly.cross_qn, nullptr, 1, B * S, eps, st);
             const __half* kv = ws.cross_kv + (size_t)i * B * E * 2 * nkv;
             launch_attention(ws.qkv, nq, kv, 2 * nkv, kv + nkv, 2 * nkv, ws.att, nq, opts.has_enc_mask ? ws.d_enc_mask : nullptr, B,
                              S, E, NQ, NKV, -1, st);

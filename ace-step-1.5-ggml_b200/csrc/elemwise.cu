@@ -107,29 +107,43 @@ __global__ void build_modulation_kernel(const float* __restrict__ tables, const 
     }
 }
 
-// ---------------------------------------------------------------- RMSNorm (+ AdaLN modulate): one warp per row
-__global__ void rmsnorm_mod_kernel(const float* __restrict__ x, const float* __restrict__ w,
-                                   const float* __restrict__ scale1, const float* __restrict__ shift, long mod_bstride,
-                                   __half* __restrict__ y, long rows, int rows_per_b, int H, float eps) {
-    const long row = (long)blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);
-    if (row >= rows) return;
-    const int lane = threadIdx.x & 31;
+// ---------------------------------------------------------------- RMSNorm (+ AdaLN modulate): one 128-thread CTA per row
+// (rows x 4 warps keeps every SM busy at S = 375..3000; the row stays in registers between the two passes)
+__global__ void __launch_bounds__(128)
+rmsnorm_mod_kernel(const float* __restrict__ x, const float* __restrict__ w, const float* __restrict__ scale1,
+                   const float* __restrict__ shift, long mod_bstride, __half* __restrict__ y, long rows, int rows_per_b,
+                   int H, float eps) {
+    __shared__ float red[4];
+    const long row = blockIdx.x;
+    const int tid = threadIdx.x;
     const float* xr = x + row * H;
     const int b = (int)(row / rows_per_b);
+    constexpr int MAXV = 4;  // up to H = 2048 held in registers; wider rows re-read from L1/L2
+    float4 v[MAXV];
     float ss = 0.f;
-    for (int c = lane * 4; c < H; c += 128) {
-        const float4 v = *reinterpret_cast<const float4*>(xr + c);
-        ss += v.x * v.x + v.y * v.y + v.z * v.z + v.w * v.w;
+#pragma unroll
+    for (int i = 0; i < MAXV; ++i) {
+        const int c = (i * 128 + tid) * 4;
+        if (c < H) {
+            v[i] = *reinterpret_cast<const float4*>(xr + c);
+            ss += v[i].x * v[i].x + v[i].y * v[i].y + v[i].z * v[i].z + v[i].w * v[i].w;
+        }
+    }
+    for (int c = (MAXV * 128 + tid) * 4; c < H; c += 512) {
+        const float4 t = *reinterpret_cast<const float4*>(xr + c);
+        ss += t.x * t.x + t.y * t.y + t.z * t.z + t.w * t.w;
     }
     ss = warp_sum(ss);
+    if ((tid & 31) == 0) red[tid >> 5] = ss;
+    __syncthreads();
+    ss = red[0] + red[1] + red[2] + red[3];
     const float inv = 1.0f / sqrtf(ss / (float)H + eps);
     const float* s1 = scale1 ? scale1 + (long)b * mod_bstride : nullptr;
     const float* sh = shift ? shift + (long)b * mod_bstride : nullptr;
     __half* yr = y + row * H;
-    for (int c = lane * 4; c < H; c += 128) {
-        const float4 v = *reinterpret_cast<const float4*>(xr + c);  // second read hits L1/L2
+    auto emit = [&](int c, float4 t) {
         const float4 ww = *reinterpret_cast<const float4*>(w + c);
-        float o0 = v.x * inv * ww.x, o1 = v.y * inv * ww.y, o2 = v.z * inv * ww.z, o3 = v.w * inv * ww.w;
+        float o0 = t.x * inv * ww.x, o1 = t.y * inv * ww.y, o2 = t.z * inv * ww.z, o3 = t.w * inv * ww.w;
         if (s1) {
             const float4 a = *reinterpret_cast<const float4*>(s1 + c);
             o0 *= a.x; o1 *= a.y; o2 *= a.z; o3 *= a.w;
@@ -143,7 +157,13 @@ __global__ void rmsnorm_mod_kernel(const float* __restrict__ x, const float* __r
         o.x = *reinterpret_cast<uint32_t*>(&h0);
         o.y = *reinterpret_cast<uint32_t*>(&h1);
         *reinterpret_cast<uint2*>(yr + c) = o;
+    };
+#pragma unroll
+    for (int i = 0; i < MAXV; ++i) {
+        const int c = (i * 128 + tid) * 4;
+        if (c < H) emit(c, v[i]);
     }
+    for (int c = (MAXV * 128 + tid) * 4; c < H; c += 512) emit(c, *reinterpret_cast<const float4*>(xr + c));
 }
 
 // ---------------------------------------------------------------- per-head RMSNorm + NEOX RoPE, in place (head_dim 128)
@@ -277,7 +297,7 @@ void launch_rmsnorm_mod(const float* x, const float* w, const float* scale1, con
     note_launch();
     ProfScope prof_scope(PROF_ELEM, 0.0, 0.0, st);
     const long rows = (long)B * rows_per_b;
-    rmsnorm_mod_kernel<<<blocks_for(rows, 8), 256, 0, st>>>(x, w, scale1, shift, mod_bstride, y, rows, rows_per_b, H, eps);
+    rmsnorm_mod_kernel<<<(unsigned)rows, 128, 0, st>>>(x, w, scale1, shift, mod_bstride, y, rows, rows_per_b, H, eps);
 }
 void launch_headnorm_rope(__half* buf, long row_stride, int col0, int n_heads, const float* w, const float2* rope_tab,
                           int B, int rows_per_b, float eps, cudaStream_t st) {

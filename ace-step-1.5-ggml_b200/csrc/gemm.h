@@ -20,6 +20,11 @@ namespace ace {
 enum EpiMode : int {
     EPI_STORE  = 0,  // v = acc (+bias) (*gate) (+resid) -> out_f32 / out_f16 (optionally snake'd)
     EPI_SWIGLU = 1,  // packed rows interleave (gate_j, up_j): out_f16[m, j] = silu(acc[2j]) * acc[2j+1]
+    // Q/K/V projections: columns are heads of 128; the first hn_na columns get per-head RMSNorm with weight hn_wa,
+    // the next hn_nb columns with hn_wb, the rest are stored as they are; normed heads are then rotated (NEOX RoPE,
+    // pairs (i, i+64), angle table `rope`[l]) when rope != null.  out_f16 only.
+    // reference: acestep_dit_model.cpp:1202-1210 (rms_norm(q/k) + ggml_rope_ext)
+    EPI_HEADNORM = 2,
 };
 
 struct GemmEpilogue {
@@ -39,6 +44,11 @@ struct GemmEpilogue {
     int          snake_period  = 0;        // channel index = n % snake_period (0 = n)
     int          atomic        = 0;        // out_f32 += v via red.add (split-K); bias only from split 0
     int          silu_f16      = 0;        // out_f16 = silu(v) (time-embedding MLP), out_f32 keeps v
+    const float* hn_wa         = nullptr;  // EPI_HEADNORM: [128] norm weight of the first hn_na columns
+    const float* hn_wb         = nullptr;  //               [128] norm weight of the next hn_nb columns
+    int          hn_na = 0, hn_nb = 0;
+    const float2* rope         = nullptr;  // [rows_per_sample, 64] (cos, sin)
+    float        hn_eps        = 1e-6f;
 };
 
 struct GemmProblem {
@@ -49,7 +59,7 @@ struct GemmProblem {
     int  l_out = 0;                // rows of D per sample (L for linear/conv, L+1 for conv-transpose)
     int  tap_stride = 0, tap_offset = 0;
     const PackedWeight* W = nullptr;
-    int  split_k = 1;
+    int  split_k = 1;              // 1 = never split K, 0 = automatic (only in-place accumulating epilogues), n = force
     GemmEpilogue epi;
 };
 

@@ -14,6 +14,7 @@
 #include <cuda.h>
 #include <cstdio>
 #include <cstdlib>
+#include <algorithm>
 #include <mutex>
 
 namespace ace {
@@ -192,6 +193,15 @@ __device__ __forceinline__ void epilogue_row32(const KParams& p, const float (&a
         for (int i = 0; i < 32; ++i) if (i < ncols) v[i] *= __ldg(g + i);
     }
     if (e.atomic) {
+        if (interior && ((base & 3) == 0)) {  // vector reduction: 8 x red.v4.f32 instead of 32 scalar atomics
+            float* o = e.out_f32 + base;
+#pragma unroll
+            for (int i = 0; i < 8; ++i)
+                asm volatile("red.global.add.v4.f32 [%0], {%1, %2, %3, %4};" ::"l"(o + 4 * i), "f"(v[4 * i]), "f"(v[4 * i + 1]),
+                             "f"(v[4 * i + 2]), "f"(v[4 * i + 3])
+                             : "memory");
+            return;
+        }
         for (int i = 0; i < ncols; ++i) {
             const long f = flat0 + i;
             if (f >= 0 && f < e.out_valid) atomicAdd(e.out_f32 + base + i, v[i]);
@@ -251,6 +261,64 @@ __device__ __forceinline__ void epilogue_row32(const KParams& p, const float (&a
                 x = x / (1.0f + __expf(-x));
             }
             e.out_f16[base + i] = __float2half_rn(x);
+        }
+    }
+}
+
+// EPI_HEADNORM: one head (128 accumulator columns) of one row.  Pass 1 reads the four 32-column chunks from TMEM for
+// the sum of squares, pass 2 re-reads them as rotate-half pairs (chunk c with chunk c+2), normalises, rotates, stores.
+__device__ __forceinline__ void epilogue_head128(const KParams& p, uint32_t taddr, int b, int l, int n0) {
+    const GemmEpilogue& e = p.epi;
+    const float* w = n0 < e.hn_na ? e.hn_wa : (n0 < e.hn_na + e.hn_nb ? e.hn_wb : nullptr);
+    __half* o = e.out_f16 + (long)b * e.out_bstride + (long)l * e.ld_out + n0;
+    const bool row_ok = l < p.l_out;
+    uint32_t r0[32], r1[32];
+    float inv = 1.f;
+    if (w) {
+        float ss = 0.f;
+#pragma unroll 1
+        for (int c = 0; c < 4; ++c) {
+            ptx::tmem_ld32(taddr + c * 32, r0);
+            ptx::tmem_ld_wait();
+#pragma unroll
+            for (int i = 0; i < 32; ++i) {
+                const float v = __uint_as_float(r0[i]);
+                ss = fmaf(v, v, ss);
+            }
+        }
+        inv = 1.0f / sqrtf(ss * (1.0f / 128.0f) + e.hn_eps);
+    }
+    const float2* rt = (w && e.rope) ? e.rope + (long)(row_ok ? l : 0) * 64 : nullptr;
+#pragma unroll 1
+    for (int c = 0; c < 2; ++c) {
+        ptx::tmem_ld32(taddr + c * 32, r0);
+        ptx::tmem_ld32(taddr + (c + 2) * 32, r1);
+        ptx::tmem_ld_wait();
+        __align__(16) __half h0[32], h1[32];
+#pragma unroll
+        for (int i = 0; i < 32; ++i) {
+            float a = __uint_as_float(r0[i]), bb = __uint_as_float(r1[i]);
+            if (w) {
+                a *= inv * __ldg(w + c * 32 + i);
+                bb *= inv * __ldg(w + 64 + c * 32 + i);
+                if (rt) {
+                    const float2 cs = __ldg(rt + c * 32 + i);
+                    const float ra = a * cs.x - bb * cs.y;
+                    bb = a * cs.y + bb * cs.x;
+                    a = ra;
+                }
+            }
+            h0[i] = __float2half_rn(a);
+            h1[i] = __float2half_rn(bb);
+        }
+        if (row_ok) {
+            uint4* o0 = reinterpret_cast<uint4*>(o + c * 32);
+            uint4* o1 = reinterpret_cast<uint4*>(o + 64 + c * 32);
+#pragma unroll
+            for (int i = 0; i < 4; ++i) {
+                o0[i] = reinterpret_cast<const uint4*>(h0)[i];
+                o1[i] = reinterpret_cast<const uint4*>(h1)[i];
+            }
         }
     }
 }
@@ -435,6 +503,14 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const KParams p) {
             ptx::tc_fence_after();
             const int l = l0 + q * 32 + lane;
             const uint32_t taddr = tmem_base + ((uint32_t)(q * 32) << 16) + (uint32_t)(a * BN);
+            if (p.epi.mode == EPI_HEADNORM) {
+#pragma unroll 1
+                for (int hh = 0; hh < BN / 128; ++hh) {
+                    const int n0 = nt * BN + hh * 128;
+                    if (n0 >= p.N) break;  // warp-uniform
+                    if (kb1 > kb0) epilogue_head128(p, taddr + hh * 128, b, l, n0);
+                }
+            } else
 #pragma unroll 1
             for (int c = 0; c < BN / 32; ++c) {
                 const int n0 = nt * BN + c * 32;
@@ -617,32 +693,54 @@ cudaError_t gemm_launch(const GemmProblem& g, cudaStream_t stream, bool simt) {
     kp.B = g.B;
     kp.l_out = g.l_out;
     kp.m_tiles_per_b = (g.l_out + BM - 1) / BM;
-    kp.split_k = g.split_k < 1 ? 1 : g.split_k;
-    if (kp.split_k > kp.kb_total) kp.split_k = kp.kb_total;
     kp.epi = g.epi;
-    if (kp.split_k > 1) kp.epi.atomic = 1;
     if (kp.epi.out_valid == 0) kp.epi.out_valid = (long)g.l_out * kp.epi.ld_out;
+    // In-place accumulation (out += gate*acc + bias, the DiT residual updates) goes through red.global.add: no
+    // read-modify-write latency in the epilogue, and it is what makes a K split legal.
+    const bool accumulate = g.epi.mode == EPI_STORE && g.epi.out_f32 && g.epi.resid == g.epi.out_f32 && !g.epi.out_f16;
+    if (accumulate) kp.epi.atomic = 1;
+    const int sms = device_sm_count();
+    const int m_tiles = kp.B * kp.m_tiles_per_b;
+    // tile shape: 128x256 halves the operand traffic per FLOP (L2 -> SM bandwidth is the limiter of the 128x128 tile);
+    // keep 128x128 only where the wider tile would leave most SMs without work
+    const long tiles256 = (long)((kp.n_tiles128 + 1) / 2) * m_tiles;
+    const long tiles128 = (long)kp.n_tiles128 * m_tiles;
+    bool bn256 = kp.n_tiles128 >= 2 && (tiles256 >= sms / 2 || accumulate);
+    if (const char* fb = std::getenv("ACE_B200_GEMM_BN")) bn256 = (std::atoi(fb) == 256) && kp.n_tiles128 >= 2;  // tuning knob
+    const long tiles_nosplit = bn256 ? tiles256 : tiles128;
+    // split-K (g.split_k == 0: automatic): fill the SMs when one wave of tiles does not, >= 8 k-blocks per split
+    int sk = g.split_k > 0 ? g.split_k : 1;
+    if (g.split_k == 0 && accumulate) {
+        sk = (int)((sms + tiles_nosplit / 2) / tiles_nosplit);
+        sk = std::max(1, std::min(sk, 4));
+        while (sk > 1 && kp.kb_total / sk < 8) --sk;
+    }
+    if (const char* fs = std::getenv("ACE_B200_GEMM_SPLITK")) {  // tuning knob: only honoured where a split is legal
+        if (accumulate) sk = std::max(1, std::atoi(fs));
+    }
+    if (sk > 1 && !accumulate) return cudaErrorInvalidValue;
+    kp.split_k = std::min(sk, kp.kb_total);
     if (g.C != w.K) return cudaErrorInvalidValue;
 
     if (simt || gemm_force_simt()) {
         kp.split_k = 1;
         const long total = (long)g.B * g.l_out * ((w.N + 31) / 32);
         const int threads = 128;
+        const bool headnorm = kp.epi.mode == EPI_HEADNORM;
+        if (headnorm) kp.epi.mode = EPI_STORE;  // raw projection, then the stand-alone norm/RoPE kernel (independent path)
         gemm_simt_kernel<<<(unsigned)((total + threads - 1) / threads), threads, 0, stream>>>(g.A, g.a_lstride, g.a_bstride,
                                                                                             g.L, g.C, kp);
+        if (headnorm) {
+            const GemmEpilogue& e = g.epi;
+            if (e.hn_na > 0) launch_headnorm_rope(e.out_f16, e.ld_out, 0, e.hn_na / 128, e.hn_wa, e.rope, g.B, g.l_out, e.hn_eps, stream);
+            if (e.hn_nb > 0) launch_headnorm_rope(e.out_f16, e.ld_out, e.hn_na, e.hn_nb / 128, e.hn_wb, e.rope, g.B, g.l_out, e.hn_eps, stream);
+        }
         return cudaGetLastError();
     }
 
     CUtensorMap tm;
     if (!make_tmap_a(g, &tm)) return cudaErrorInvalidValue;
-    const int sms = device_sm_count();
-    const int m_tiles = kp.B * kp.m_tiles_per_b;
-    const long tiles256 = (long)((kp.n_tiles128 + 1) / 2) * m_tiles * kp.split_k;
-    const long tiles128 = (long)kp.n_tiles128 * m_tiles * kp.split_k;
-    static const char* force_bn = std::getenv("ACE_B200_GEMM_BN");
-    bool bn256 = kp.n_tiles128 >= 2 && tiles256 >= 2L * sms;
-    if (force_bn) bn256 = (std::atoi(force_bn) == 256) && kp.n_tiles128 >= 2;
-    const long tiles = bn256 ? tiles256 : tiles128;
+    const long tiles = tiles_nosplit * kp.split_k;
     const int grid = (int)(tiles < sms ? tiles : sms);
     const bool quant = w.wtype != W_F16;
     if (bn256) return quant ? launch_tc<256, true>(tm, kp, grid, stream) : launch_tc<256, false>(tm, kp, grid, stream);

@@ -58,3 +58,18 @@ def ref_dit_forward(dit_dir, inputs, t, t_r, max_layers=None, threads=4, buffer_
             call["enc_mask"] = "encoder_attention_mask"
     outs, tim = refbridge.run_ref([call], inp, dit_dir=dit_dir, threads=threads, compute_buffer_bytes=buffer_bytes, env=env)
     return outs["v"], tim
+
+
+def dequantised_gguf_tensors(path: str) -> dict:
+    """name -> float32 array (PyTorch shapes) of a GGUF file, quantised tensors dequantised with gguf.quants.dequantize
+    (the numpy port of ggml-quants.c).  Used as the "truth for the same quantised weights" calibrator."""
+    import gguf
+    from gguf import quants as gq
+    out = {}
+    for t in gguf.GGUFReader(path).tensors:
+        shape = [int(x) for x in reversed(t.shape)]
+        if t.tensor_type in (gguf.GGMLQuantizationType.F32, gguf.GGMLQuantizationType.F16):
+            out[t.name] = np.asarray(t.data, dtype=np.float32).reshape(shape)
+        else:
+            out[t.name] = gq.dequantize(np.asarray(t.data), t.tensor_type).astype(np.float32).reshape(shape)
+    return out

@@ -75,6 +75,12 @@ ace_ggml_status ace_b200_debug_gemm(ace_ggml_context* ctx, const float* A, int32
     if ((epilogue & 4) && resid) cudaMemcpyAsync(dOut, resid, out_elems * 4, cudaMemcpyHostToDevice, st);
     else cudaMemsetAsync(dOut, 0, out_elems * 4, st);
     launch_f32_to_f16(dA32, dA, (long)a_elems, st);
+    if (pw.wtype != W_F16 && predecode_enabled()) {  // decoded twin, as the loaders build it (gemm.h policy picks the route)
+        pw.dev_f16 = tmp.get(gemm_predecode_bytes(pw));
+        if (!pw.dev_f16) return cuda_fail(ctx, "debug_gemm cudaMalloc failed", cudaGetLastError());
+        cudaError_t pe = gemm_predecode(pw, pw.dev_f16, st);
+        if (pe != cudaSuccess) return cuda_fail(ctx, "debug_gemm predecode failed", pe);
+    }
     GemmProblem g;
     g.A = dA;
     g.B = B;

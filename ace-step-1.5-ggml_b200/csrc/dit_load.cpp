@@ -2,6 +2,7 @@
 // reference: acestep_dit_config.cpp:19-93 (keys), acestep_dit_model.cpp:47-70 (file choice),
 //            156-192 (on-the-fly quantisation), 334-490 / 640-715 (conv -> linear relayout), 753-1088 (tensor names)
 #include "dit.h"
+#include "gemm.h"
 #include "tensor_file.h"
 
 #include <algorithm>
@@ -41,6 +42,12 @@ struct Loader {
         if (!w.dev) return false;
         if (cudaMemcpy(w.dev, img.data(), img.size(), cudaMemcpyHostToDevice) != cudaSuccess)
             return fail(1, std::string("cudaMemcpy failed: ") + cudaGetErrorString(cudaGetLastError()));
+        if (w.wtype != W_F16 && predecode_enabled()) {  // decoded F16 twin for the compute-bound regime (gemm.h)
+            w.dev_f16 = dev_alloc(gemm_predecode_bytes(w));
+            if (!w.dev_f16) return false;
+            const cudaError_t e = gemm_predecode(w, w.dev_f16, nullptr);
+            if (e != cudaSuccess) return fail(1, std::string("weight predecode failed: ") + cudaGetErrorString(e));
+        }
         return true;
     }
     float* upload_f32(const std::vector<float>& v) {
@@ -341,6 +348,12 @@ int dit_load(const std::string& model_dir, DitModel& m, std::string& err) {
     m.weight_desc = std::string(tf->is_gguf() ? "gguf:" : "safetensors:") +
                     (m.layers.empty() ? "?" : (m.layers[0].self_qkv.wtype == W_F16 ? "F16" : m.layers[0].self_qkv.wtype == W_Q8_0 ? "Q8_0"
                                                : m.layers[0].self_qkv.wtype == W_Q4_K ? "Q4_K" : "Q6_K"));
+    if (!m.layers.empty() && m.layers[0].self_qkv.dev_f16) m.weight_desc += "+f16twin";
+    if (cudaDeviceSynchronize() != cudaSuccess) {  // predecode kernels ran on the default stream
+        err = std::string("weight predecode failed: ") + cudaGetErrorString(cudaGetLastError());
+        m.release();
+        return 1;
+    }
     return 0;
 }
 

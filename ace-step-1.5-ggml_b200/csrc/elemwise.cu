@@ -217,44 +217,88 @@ __global__ void euler_step_kernel(float* __restrict__ x, const float* __restrict
 }
 
 // ---------------------------------------------------------------- tiny-C_out conv (VAE output conv)
-// one warp per output position: lanes split the input channels, 16-byte loads, shuffle reduction
-template <int COUT>
-__global__ void conv_small_out_kernel(const __half* __restrict__ xs, const __half* __restrict__ w,
-                                      const float* __restrict__ bias, float* __restrict__ out, int B, long L, int C,
-                                      int taps, int pad) {
-    const long wid = (long)blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);
-    if (wid >= (long)B * L) return;
-    const int lane = threadIdx.x & 31;
-    const int b = (int)(wid / L);
-    const long l = wid % L;
-    float acc[COUT];
+// HBM-bound: 2 B of input per (position, channel), read ONCE.  A CTA stages TL + taps - 1 channels-last rows in
+// shared memory (coalesced 16-byte cp.async, zero fill past the clip ends), then every warp runs m16n8k16 MMAs over
+// its 32 positions with the taps*C reduction as K and the (<= 8) output channels as N; only the first C_out columns
+// of the n8 tile are real.  Row stride C + 8 halves keeps ldmatrix conflict-free.
+constexpr int CSO_TL = 128;       // output positions per CTA
+constexpr int CSO_THREADS = 128;  // 4 warps x 32 positions
+
+__global__ void __launch_bounds__(CSO_THREADS)
+conv_small_out_kernel(const __half* __restrict__ xs, const __half* __restrict__ w, const float* __restrict__ bias,
+                      float* __restrict__ out, long L, int C, int Cout, int taps, int pad) {
+    extern __shared__ __align__(16) uint8_t cso_smem[];
+    const int rs = C + 8;                       // padded row stride (halves)
+    const int rows = CSO_TL + taps - 1;
+    __half* sx = reinterpret_cast<__half*>(cso_smem);            // [rows][rs]
+    __half* sw = sx + (size_t)rows * rs;                         // [8][taps*C] (rows >= Cout are zero)
+    const int K = taps * C;
+    const long l0 = (long)blockIdx.x * CSO_TL;
+    const int b = blockIdx.y;
+    const __half* xb = xs + (long)b * L * C;
+    const int cpr = C / 8;                      // 16-byte chunks per row
+    for (int i = threadIdx.x; i < rows * cpr; i += CSO_THREADS) {
+        const int r = i / cpr, ch = i - r * cpr;
+        const long ls = l0 + r - pad;
+        const bool ok = ls >= 0 && ls < L;
+        const uint32_t dst = (uint32_t)__cvta_generic_to_shared(sx + (size_t)r * rs + ch * 8);
+        const __half* src = xb + (ok ? ls : 0) * C + ch * 8;
+        const int sz = ok ? 16 : 0;
+        asm volatile("cp.async.cg.shared.global [%0], [%1], 16, %2;" ::"r"(dst), "l"(src), "r"(sz) : "memory");
+    }
+    for (int i = threadIdx.x; i < 8 * K / 2; i += CSO_THREADS) {
+        const int n = (2 * i) / K;
+        reinterpret_cast<uint32_t*>(sw)[i] = n < Cout ? reinterpret_cast<const uint32_t*>(w)[i] : 0u;
+    }
+    asm volatile("cp.async.commit_group;" ::: "memory");
+    asm volatile("cp.async.wait_group 0;" ::: "memory");
+    __syncthreads();
+
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    const int g = lane >> 2, t4 = lane & 3;
+    float acc[2][4];
 #pragma unroll
-    for (int o = 0; o < COUT; ++o) acc[o] = 0.f;
+    for (int m = 0; m < 2; ++m) acc[m][0] = acc[m][1] = acc[m][2] = acc[m][3] = 0.f;
+    const int ksteps_per_tap = C / 16;
     for (int tap = 0; tap < taps; ++tap) {
-        const long ls = l + tap - pad;
-        if (ls < 0 || ls >= L) continue;
-        const __half* xr = xs + ((long)b * L + ls) * C;
-        for (int c = lane * 8; c < C; c += 256) {
-            const uint4 xv = *reinterpret_cast<const uint4*>(xr + c);
-            const __half2* xh = reinterpret_cast<const __half2*>(&xv);
+        for (int kc = 0; kc < ksteps_per_tap; ++kc) {
+            const int k0 = tap * C + kc * 16;
+            const uint32_t b0 = *reinterpret_cast<const uint32_t*>(sw + (size_t)g * K + k0 + 2 * t4);
+            const uint32_t b1 = *reinterpret_cast<const uint32_t*>(sw + (size_t)g * K + k0 + 2 * t4 + 8);
 #pragma unroll
-            for (int o = 0; o < COUT; ++o) {
-                const uint4 wv = *reinterpret_cast<const uint4*>(w + ((long)o * taps + tap) * C + c);
-                const __half2* wh = reinterpret_cast<const __half2*>(&wv);
-#pragma unroll
-                for (int i = 0; i < 4; ++i) {
-                    const float2 xf = __half22float2(xh[i]), wf = __half22float2(wh[i]);
-                    acc[o] = fmaf(xf.x, wf.x, acc[o]);
-                    acc[o] = fmaf(xf.y, wf.y, acc[o]);
-                }
+            for (int m = 0; m < 2; ++m) {
+                // A tile: positions warp*32 + m*16 + (0..15), columns kc*16 + (0..15) of row (position + tap)
+                const int r = warp * 32 + m * 16 + (lane & 15) + tap;
+                const uint32_t addr = (uint32_t)__cvta_generic_to_shared(sx + (size_t)r * rs + kc * 16 + (lane >> 4) * 8);
+                uint32_t a0, a1, a2, a3;
+                asm volatile("ldmatrix.sync.aligned.m8n8.x4.shared.b16 {%0,%1,%2,%3}, [%4];"
+                             : "=r"(a0), "=r"(a1), "=r"(a2), "=r"(a3) : "r"(addr));
+                asm volatile("mma.sync.aligned.m16n8k16.row.col.f32.f16.f16.f32 {%0,%1,%2,%3}, {%4,%5,%6,%7}, {%8,%9}, {%0,%1,%2,%3};"
+                             : "+f"(acc[m][0]), "+f"(acc[m][1]), "+f"(acc[m][2]), "+f"(acc[m][3])
+                             : "r"(a0), "r"(a1), "r"(a2), "r"(a3), "r"(b0), "r"(b1));
             }
         }
     }
+    // accumulator layout: (row g, cols 2*t4, 2*t4+1) and (row g+8, same cols)
+    const int c0 = 2 * t4;
+    if (c0 < Cout) {
+        const float bz0 = bias ? bias[c0] : 0.f;
+        const float bz1 = (bias && c0 + 1 < Cout) ? bias[c0 + 1] : 0.f;
 #pragma unroll
-    for (int o = 0; o < COUT; ++o) acc[o] = warp_sum(acc[o]);
-    if (lane == 0) {
+        for (int m = 0; m < 2; ++m) {
 #pragma unroll
-        for (int o = 0; o < COUT; ++o) out[((long)b * L + l) * COUT + o] = acc[o] + (bias ? bias[o] : 0.f);
+            for (int hrow = 0; hrow < 2; ++hrow) {
+                const long l = l0 + warp * 32 + m * 16 + g + hrow * 8;
+                if (l >= L) continue;
+                float* o = out + ((long)b * L + l) * Cout + c0;
+                const float v0 = acc[m][2 * hrow] + bz0, v1 = acc[m][2 * hrow + 1] + bz1;
+                if (c0 + 1 < Cout && (Cout & 1) == 0) *reinterpret_cast<float2*>(o) = make_float2(v0, v1);
+                else {
+                    o[0] = v0;
+                    if (c0 + 1 < Cout) o[1] = v1;
+                }
+            }
+        }
     }
 }
 
@@ -321,9 +365,15 @@ void launch_conv_small_out(const __half* xs, const __half* w, const float* bias,
                            int Cout, int taps, int pad, cudaStream_t st) {
     note_launch();
     ProfScope prof_scope(PROF_VAE_TAIL, 2.0 * B * L * C * Cout * taps, (double)B * L * (C * 2.0 + Cout * 4.0), st);
-    const long warps = (long)B * L;
-    if (Cout == 1) conv_small_out_kernel<1><<<blocks_for(warps, 8), 256, 0, st>>>(xs, w, bias, out, B, L, C, taps, pad);
-    else if (Cout == 2) conv_small_out_kernel<2><<<blocks_for(warps, 8), 256, 0, st>>>(xs, w, bias, out, B, L, C, taps, pad);
+    // loaders guarantee C % 16 == 0 (vae.cu: channel levels are multiples of 32) and Cout <= 8
+    const size_t smem = ((size_t)(CSO_TL + taps - 1) * (C + 8) + (size_t)8 * taps * C) * sizeof(__half);
+    static size_t attr = 0;
+    if (smem > attr) {
+        cudaFuncSetAttribute(conv_small_out_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+        attr = smem;
+    }
+    dim3 grid((unsigned)((L + CSO_TL - 1) / CSO_TL), (unsigned)B);
+    conv_small_out_kernel<<<grid, CSO_THREADS, smem, st>>>(xs, w, bias, out, L, C, Cout, taps, pad);
 }
 
 }  // namespace ace

@@ -67,6 +67,18 @@ struct GemmProblem {
 // (same operands, same epilogue) that the tensor-core kernel is unit-tested against.
 cudaError_t gemm_launch(const GemmProblem& p, cudaStream_t stream, bool simt = false);
 
+// Decode a quantised packed weight ONCE into the F16 tile image (n_tiles * taps*kb_per_tap * 16 KB at `dst`), with the
+// same device decoders the GEMM runs in shared memory, so both routes feed the tensor cores bit-identical operands.
+// Policy (gemm_launch): a quantised weight with a decoded twin (PackedWeight::dev_f16) uses the twin when the problem
+// has >= predecode_min_rows() activation rows: there the GEMM is compute-bound, every weight tile would be re-decoded
+// by each of the M/128 row tiles, and 3 GB of HBM (of 180) for the twin buys F16-kernel speed.  Below the threshold
+// (time-embedding GEMVs, short clips) the GEMM is HBM-bound on the weight stream and decodes the 4.5-8.5 bit codes
+// in shared memory.  ACE_B200_PREDECODE=0 disables the twins, ACE_B200_PREDECODE_MIN_M moves the threshold.
+size_t      gemm_predecode_bytes(const PackedWeight& w);
+cudaError_t gemm_predecode(const PackedWeight& w, void* dst, cudaStream_t stream);
+bool        predecode_enabled();
+int         predecode_min_rows();
+
 // true when ACE_B200_GEMM=simt is set (debug bisecting aid; never the default)
 bool gemm_force_simt();
 

@@ -366,7 +366,7 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const KParams p) {
         }
         for (int a = 0; a < 2; ++a) {
             ptx::mbar_init(&acc_full[a], 1);
-            ptx::mbar_init(&acc_empty[a], 4);
+            ptx::mbar_init(&acc_empty[a], QUANT ? 4 : 8);
         }
         ptx::fence_mbar_init();
     }
@@ -462,9 +462,9 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const KParams p) {
                 __syncwarp();
             }
         }
-    } else if (warp < 4) {
+    } else if (QUANT && warp < 4) {
         // ===================== weight decoders =====================
-        if (QUANT) {
+        {
             const int row = threadIdx.x;  // 0..127
             uint32_t g = 0;
             for (int t = blockIdx.x; t < total_tiles; t += gridDim.x) {
@@ -490,8 +490,12 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const KParams p) {
             }
         }
     } else {
-        // ===================== epilogue (warps 4..7 -> TMEM lanes 32*(warp-4)) =====================
-        const int q = warp - 4;
+        // ===================== epilogue =====================
+        // warp w may touch TMEM lanes 32*(w%4)..+31.  QUANT: warps 4..7, one group.  F16 weights: warps 0..3 have no
+        // decoding to do and form a second group; the two groups take alternate column chunks / heads of a tile.
+        const int q = warp & 3;
+        const int part = QUANT ? 0 : (warp >> 2);
+        constexpr int NPARTS = QUANT ? 1 : 2;
         int it = 0;
         for (int t = blockIdx.x; t < total_tiles; t += gridDim.x, ++it) {
             int nt, sp, b, l0, kb0, kb1;
@@ -505,14 +509,14 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const KParams p) {
             const uint32_t taddr = tmem_base + ((uint32_t)(q * 32) << 16) + (uint32_t)(a * BN);
             if (p.epi.mode == EPI_HEADNORM) {
 #pragma unroll 1
-                for (int hh = 0; hh < BN / 128; ++hh) {
+                for (int hh = part; hh < BN / 128; hh += NPARTS) {
                     const int n0 = nt * BN + hh * 128;
                     if (n0 >= p.N) break;  // warp-uniform
                     if (kb1 > kb0) epilogue_head128(p, taddr + hh * 128, b, l, n0);
                 }
             } else
 #pragma unroll 1
-            for (int c = 0; c < BN / 32; ++c) {
+            for (int c = part; c < BN / 32; c += NPARTS) {
                 const int n0 = nt * BN + c * 32;
                 if (n0 >= p.N) break;  // warp-uniform
                 uint32_t r[32];
@@ -603,7 +607,52 @@ __global__ void gemm_simt_kernel(const __half* A, long a_lstride, long a_bstride
     epilogue_row32(q, acc, b, l, n0, true);
 }
 
+// ---------------------------------------------------------------- one-off decode of a packed tile to its F16 image
+__global__ void __launch_bounds__(128) predecode_kernel(const uint8_t* __restrict__ W, int wtype, int tile_bytes, uint8_t* __restrict__ dst,
+                                                        long n_tiles) {
+    __shared__ __align__(16) uint8_t raw[RAW_MAX_BYTES];
+    __shared__ __align__(16) uint8_t out[W_SUB_BYTES];
+    for (long t = blockIdx.x; t < n_tiles; t += gridDim.x) {
+        const uint4* src = reinterpret_cast<const uint4*>(W + (size_t)t * tile_bytes);
+        for (int i = threadIdx.x; i < tile_bytes / 16; i += 128) reinterpret_cast<uint4*>(raw)[i] = src[i];
+        __syncthreads();
+        decode_tile(wtype, raw, out, threadIdx.x);
+        __syncthreads();
+        uint4* d = reinterpret_cast<uint4*>(dst + (size_t)t * W_SUB_BYTES);
+        for (int i = threadIdx.x; i < W_SUB_BYTES / 16; i += 128) d[i] = reinterpret_cast<const uint4*>(out)[i];
+        __syncthreads();
+    }
+}
+
 }  // namespace
+
+size_t gemm_predecode_bytes(const PackedWeight& w) {
+    return (size_t)w.n_tiles * w.taps * w.kb_per_tap * W_SUB_BYTES;
+}
+
+cudaError_t gemm_predecode(const PackedWeight& w, void* dst, cudaStream_t stream) {
+    if (w.wtype == W_F16 || !w.dev || !dst) return cudaErrorInvalidValue;
+    const long n_tiles = (long)w.n_tiles * w.taps * w.kb_per_tap;
+    note_launch();
+    const int grid = (int)std::min<long>(n_tiles, 148L * 16);
+    predecode_kernel<<<grid, 128, 0, stream>>>(static_cast<const uint8_t*>(w.dev), w.wtype, w.tile_bytes, static_cast<uint8_t*>(dst), n_tiles);
+    return cudaGetLastError();
+}
+
+bool predecode_enabled() {
+    static int v = -1;
+    if (v < 0) {
+        const char* e = std::getenv("ACE_B200_PREDECODE");
+        v = (e && e[0] == '0') ? 0 : 1;
+    }
+    return v == 1;
+}
+
+int predecode_min_rows() {
+    const char* e = std::getenv("ACE_B200_PREDECODE_MIN_M");  // read per call: tests flip it between launches
+    if (e && e[0]) return std::max(1, std::atoi(e));
+    return 256;
+}
 
 // ---------------------------------------------------------------- host side
 namespace {
@@ -683,6 +732,11 @@ cudaError_t gemm_launch(const GemmProblem& g, cudaStream_t stream, bool simt) {
     kp.W = static_cast<const uint8_t*>(w.dev);
     kp.wtype = w.wtype;
     kp.tile_bytes = w.tile_bytes;
+    if (w.wtype != W_F16 && w.dev_f16 && !simt && !gemm_force_simt() && (long)g.B * g.l_out >= predecode_min_rows()) {
+        kp.W = static_cast<const uint8_t*>(w.dev_f16);  // compute-bound: decoded twin through the F16 kernel
+        kp.wtype = W_F16;
+        kp.tile_bytes = W_SUB_BYTES;
+    }
     kp.N = w.N;
     kp.n_tiles128 = w.n_tiles;
     kp.kb_per_tap = w.kb_per_tap;
@@ -742,7 +796,7 @@ cudaError_t gemm_launch(const GemmProblem& g, cudaStream_t stream, bool simt) {
     if (!make_tmap_a(g, &tm)) return cudaErrorInvalidValue;
     const long tiles = tiles_nosplit * kp.split_k;
     const int grid = (int)(tiles < sms ? tiles : sms);
-    const bool quant = w.wtype != W_F16;
+    const bool quant = kp.wtype != W_F16;
     if (bn256) return quant ? launch_tc<256, true>(tm, kp, grid, stream) : launch_tc<256, false>(tm, kp, grid, stream);
     return quant ? launch_tc<128, true>(tm, kp, grid, stream) : launch_tc<128, false>(tm, kp, grid, stream);
 }

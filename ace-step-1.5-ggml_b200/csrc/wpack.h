@@ -59,6 +59,8 @@ float    bf16_to_f32(uint16_t h);
 
 struct PackedWeight {
     void*   dev = nullptr;   // device tiles
+    void*   dev_f16 = nullptr; // quantised weights only: the same tiles decoded once to the F16 image (gemm_predecode);
+                               // used when the GEMM has enough rows to be compute-bound (gemm.h: predecode_min_rows)
     int     wtype = W_F16;
     int     N = 0;           // output features (rows of W)
     int     K = 0;           // input features per tap

@@ -209,3 +209,20 @@ def test_attention(br, ql, kl, window, masked):
     ref = attention_ref(Q, K, V, km, nh, nkv, window)
     # P and O are rounded to fp16 inside the kernel: ~1e-3 relative
     assert rel_err(out, ref) < 3e-3, rel_err(out, ref)
+
+
+@pytest.mark.parametrize("gt", [8, 12, 14])
+def test_gemm_predecoded_twin_is_bit_identical(br, gt, monkeypatch):
+    """quantised weight, two routes (gemm.h policy): decoded in shared memory inside the GEMM vs decoded once to the F16
+    twin and run through the F16 kernel.  Same decoder arithmetic, same MMA order -> identical fp32 results."""
+    g = np.random.default_rng(gt)
+    L, K, N = 640, 512, 384
+    A = g.standard_normal((1, L, K), dtype=np.float32)
+    rows = random_rows(gt, N, K, seed=gt + 1)
+    monkeypatch.setenv("ACE_B200_PREDECODE_MIN_M", "1000000")
+    in_kernel = br.debug_gemm(A, rows, w_type=gt, N=N)
+    monkeypatch.setenv("ACE_B200_PREDECODE_MIN_M", "1")
+    twin = br.debug_gemm(A, rows, w_type=gt, N=N)
+    assert np.array_equal(in_kernel, twin)
+    ref = tap_gemm_ref(h16(A), dequant_ref(rows, gt, N, K).astype(np.float64)[:, None, :], 1, 0, 0, L)
+    assert rel_err(twin, ref) < 2e-3

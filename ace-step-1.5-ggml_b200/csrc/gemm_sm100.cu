@@ -541,6 +541,203 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const KParams p) {
     }
 }
 
+// ---------------------------------------------------------------- CTA-pair kernel (cta_group::2), F16 weight tiles
+// A cluster of two CTAs (one TPC) computes a 256 x 256 tile with M = 256 MMAs: CTA r owns rows [l0 + 128 r, +128) of A and
+// of the accumulator (its own TMEM) and stages only HALF of the weight tile (rows n0 + 128 r ..) — the tensor core reads
+// the other half from the peer's shared memory.  Per k-block a CTA pulls 16 KB (A) + 16 KB (W) from L2 instead of 16 + 32,
+// which is what bounds the single-CTA 128 x 256 tile (L2 -> SM operand delivery, profiles/r1_gemm_ncu_big1.md).
+// Synchronisation: every CTA has local full/empty/acc_full barriers; CTA 1 forwards "my stage landed" to the leader with
+// a remote mbarrier arrive (peer_full), the leader's tcgen05.commit multicasts "stage consumed" / "accumulator ready" to
+// both CTAs, and both CTAs' epilogue warps arrive on the leader's acc_empty.
+constexpr int STAGES2 = 6;
+constexpr int STAGE2_BYTES = A_STAGE_BYTES + W_SUB_BYTES;  // 32 KB
+constexpr int SMEM2_BYTES = STAGES2 * STAGE2_BYTES + 512 + 1024;
+
+__global__ void __launch_bounds__(NUM_THREADS, 1)
+gemm_tc2_kernel(const __grid_constant__ CUtensorMap tmA, const KParams p) {
+    constexpr int BN = 256;
+    constexpr int TMEM_COLS = 2 * BN;
+    extern __shared__ uint8_t smem_raw[];
+    uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
+    uint8_t* sA = smem;                            // [STAGES2][16 KB]
+    uint8_t* sB = sA + STAGES2 * A_STAGE_BYTES;    // [STAGES2][16 KB]  this CTA's half of the weight tile
+    uint64_t* bars = reinterpret_cast<uint64_t*>(sB + STAGES2 * W_SUB_BYTES);
+    uint64_t* full = bars;                    // [S] local operands landed
+    uint64_t* empty = bars + STAGES2;         // [S] MMAs reading this CTA's stage completed (multicast commit)
+    uint64_t* peer_full = bars + 2 * STAGES2; // [S] leader only: CTA 1's stage landed
+    uint64_t* acc_full = bars + 3 * STAGES2;  // [2] local (multicast commit)
+    uint64_t* acc_empty = acc_full + 2;       // [2] leader only: 16 epilogue warps of the pair
+    uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(acc_empty + 2);
+
+    const int warp = threadIdx.x >> 5;
+    const int lane = threadIdx.x & 31;
+    const uint32_t rank = ptx::cluster_ctarank();
+    const int cluster_id = blockIdx.x >> 1;
+    const int n_clusters = gridDim.x >> 1;
+
+    const int m_pairs_per_b = (p.l_out + 2 * BM - 1) / (2 * BM);
+    const int m_tiles = p.B * m_pairs_per_b;
+    const int n_tiles = p.n_tiles128 >> 1;  // launcher guarantees an even count
+    const int total_tiles = n_tiles * p.split_k * m_tiles;
+
+    if (threadIdx.x == 0) {
+        for (int s = 0; s < STAGES2; ++s) {
+            ptx::mbar_init(&full[s], 1);
+            ptx::mbar_init(&empty[s], 1);
+            ptx::mbar_init(&peer_full[s], 1);
+        }
+        for (int a = 0; a < 2; ++a) {
+            ptx::mbar_init(&acc_full[a], 1);
+            ptx::mbar_init(&acc_empty[a], 16);
+        }
+        ptx::fence_mbar_init();
+    }
+    if (warp == 9) ptx::tmem_alloc_2cta<TMEM_COLS>(tmem_slot);
+    if (warp == 8 && lane == 0) ptx::prefetch_tmap(&tmA);
+    ptx::tc_fence_before();
+    __syncthreads();
+    ptx::cluster_sync();
+    ptx::tc_fence_after();
+    const uint32_t tmem_base = *tmem_slot;
+
+    auto decode_tile_index = [&](int t, int& nt, int& sp, int& b, int& l0) {
+        const int mt = t % m_tiles;
+        const int rest = t / m_tiles;
+        sp = rest % p.split_k;
+        nt = rest / p.split_k;
+        b = mt / m_pairs_per_b;
+        l0 = (mt % m_pairs_per_b) * (2 * BM) + (int)rank * BM;  // this CTA's 128 rows
+    };
+    auto k_range = [&](int sp, int& kb0, int& kb1) {
+        kb0 = (int)((long)p.kb_total * sp / p.split_k);
+        kb1 = (int)((long)p.kb_total * (sp + 1) / p.split_k);
+    };
+
+    if (warp == 8) {
+        // ===================== TMA producer (both CTAs) =====================
+        if (lane == 0) {
+            uint32_t g = 0;
+            for (int t = cluster_id; t < total_tiles; t += n_clusters) {
+                int nt, sp, b, l0, kb0, kb1;
+                decode_tile_index(t, nt, sp, b, l0);
+                k_range(sp, kb0, kb1);
+                for (int kb = kb0; kb < kb1; ++kb, ++g) {
+                    const int s = g % STAGES2;
+                    const uint32_t ph = (g / STAGES2) & 1;
+                    const int tap = kb / p.kb_per_tap;
+                    const int c0 = (kb - tap * p.kb_per_tap) * BK;
+                    const int row = l0 + tap * p.tap_stride + p.tap_offset;
+                    ptx::mbar_wait(&empty[s], ph ^ 1);
+                    ptx::mbar_expect_tx(&full[s], STAGE2_BYTES);
+                    ptx::tma_load_3d(sA + s * A_STAGE_BYTES, &tmA, &full[s], c0, row, b);
+                    const size_t off = ((size_t)(nt * 2 + (int)rank) * p.kb_total + kb) * W_SUB_BYTES;
+                    ptx::bulk_load(sB + s * W_SUB_BYTES, p.W + off, W_SUB_BYTES, &full[s]);
+                }
+            }
+        }
+    } else if (warp == 9) {
+        if (rank == 0) {
+            // ===================== MMA issuer (leader CTA) =====================
+            constexpr uint32_t idesc = ptx::umma_idesc_f16(2 * BM, BN);
+            uint32_t g = 0;
+            int it = 0;
+            for (int t = cluster_id; t < total_tiles; t += n_clusters, ++it) {
+                int nt, sp, b, l0, kb0, kb1;
+                decode_tile_index(t, nt, sp, b, l0);
+                k_range(sp, kb0, kb1);
+                const int a = it & 1;
+                const uint32_t aph = (it >> 1) & 1;
+                ptx::mbar_wait(&acc_empty[a], aph ^ 1);
+                ptx::tc_fence_after();
+                const uint32_t d_tmem = tmem_base + (uint32_t)(a * BN);
+                for (int kb = kb0; kb < kb1; ++kb, ++g) {
+                    const int s = g % STAGES2;
+                    const uint32_t ph = (g / STAGES2) & 1;
+                    ptx::mbar_wait(&full[s], ph);
+                    ptx::mbar_wait(&peer_full[s], ph);
+                    ptx::tc_fence_after();
+                    if (lane == 0) {
+                        const uint32_t a_addr = ptx::smem_u32(sA + s * A_STAGE_BYTES);
+                        const uint32_t b_addr = ptx::smem_u32(sB + s * W_SUB_BYTES);
+#pragma unroll
+                        for (int k = 0; k < BK / 16; ++k) {
+                            const uint64_t da = ptx::umma_desc_sw128(a_addr + k * 32);
+                            const uint64_t db = ptx::umma_desc_sw128(b_addr + k * 32);
+                            ptx::umma_f16_2cta(d_tmem, da, db, idesc, (kb > kb0 || k > 0) ? 1u : 0u);
+                        }
+                        ptx::umma_commit_2cta(&empty[s], 3);
+                        if (kb == kb1 - 1) ptx::umma_commit_2cta(&acc_full[a], 3);
+                    }
+                    __syncwarp();
+                }
+            }
+        } else {
+            // ===================== relay (CTA 1): local "stage landed" -> leader's peer_full =====================
+            if (lane == 0) {
+                uint32_t g = 0;
+                for (int t = cluster_id; t < total_tiles; t += n_clusters) {
+                    int nt, sp, b, l0, kb0, kb1;
+                    decode_tile_index(t, nt, sp, b, l0);
+                    k_range(sp, kb0, kb1);
+                    for (int kb = kb0; kb < kb1; ++kb, ++g) {
+                        const int s = g % STAGES2;
+                        const uint32_t ph = (g / STAGES2) & 1;
+                        ptx::mbar_wait(&full[s], ph);
+                        ptx::mbar_arrive_cluster(ptx::mapa(&peer_full[s], 0));
+                    }
+                }
+            }
+        }
+    } else {
+        // ===================== epilogue: warps 0..7 of both CTAs, two groups on alternate column chunks =====================
+        const int q = warp & 3;
+        const int part = warp >> 2;
+        int it = 0;
+        for (int t = cluster_id; t < total_tiles; t += n_clusters, ++it) {
+            int nt, sp, b, l0, kb0, kb1;
+            decode_tile_index(t, nt, sp, b, l0);
+            k_range(sp, kb0, kb1);
+            const int a = it & 1;
+            const uint32_t aph = (it >> 1) & 1;
+            ptx::mbar_wait(&acc_full[a], aph);
+            ptx::tc_fence_after();
+            const int l = l0 + q * 32 + lane;
+            const uint32_t taddr = tmem_base + ((uint32_t)(q * 32) << 16) + (uint32_t)(a * BN);
+            if (p.epi.mode == EPI_HEADNORM) {
+#pragma unroll 1
+                for (int hh = part; hh < BN / 128; hh += 2) {
+                    const int n0 = nt * BN + hh * 128;
+                    if (n0 >= p.N) break;
+                    if (kb1 > kb0) epilogue_head128(p, taddr + hh * 128, b, l, n0);
+                }
+            } else
+#pragma unroll 1
+            for (int c = part; c < BN / 32; c += 2) {
+                const int n0 = nt * BN + c * 32;
+                if (n0 >= p.N) break;
+                uint32_t r[32];
+                ptx::tmem_ld32(taddr + c * 32, r);
+                ptx::tmem_ld_wait();
+                float acc[32];
+#pragma unroll
+                for (int i = 0; i < 32; ++i) acc[i] = __uint_as_float(r[i]);
+                if (kb1 > kb0) epilogue_row32(p, acc, b, l, n0, sp == 0);
+            }
+            ptx::tc_fence_before();
+            __syncwarp();
+            if (lane == 0) ptx::mbar_arrive_cluster(ptx::mapa(&acc_empty[a], 0));
+        }
+    }
+
+    ptx::tc_fence_before();
+    __syncthreads();
+    ptx::cluster_sync();  // the peer's smem / barriers stay alive until every MMA and remote arrive has landed
+    if (warp == 9) {
+        ptx::tc_fence_after();
+        ptx::tmem_dealloc_2cta<TMEM_COLS>(tmem_base);
+    }
+}
+
 // ---------------------------------------------------------------- plain-FMA debug kernel (same operands, same epilogue)
 // One thread per (row, 32-column group); decodes the packed weight element-wise. Slow by construction; it exists so
 // the tcgen05 kernel can be bisected against an independent implementation on the GPU.
@@ -688,6 +885,48 @@ bool make_tmap_a(const GemmProblem& g, CUtensorMap* tm) {
     return r == CUDA_SUCCESS;
 }
 
+// co-resident CTA pairs on this device (a GPC with an odd SM count cannot pair its last SM); 0 = pairs unavailable
+int max_active_pairs() {
+    static int n = -1;
+    if (n < 0) {
+        n = 0;
+        if (cudaFuncSetAttribute(gemm_tc2_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, SMEM2_BYTES) == cudaSuccess) {
+            cudaLaunchConfig_t cfg = {};
+            cfg.gridDim = dim3(2 * 148);
+            cfg.blockDim = dim3(NUM_THREADS);
+            cfg.dynamicSmemBytes = SMEM2_BYTES;
+            cudaLaunchAttribute at[1];
+            at[0].id = cudaLaunchAttributeClusterDimension;
+            at[0].val.clusterDim.x = 2;
+            at[0].val.clusterDim.y = 1;
+            at[0].val.clusterDim.z = 1;
+            cfg.attrs = at;
+            cfg.numAttrs = 1;
+            int c = 0;
+            if (cudaOccupancyMaxActiveClusters(&c, gemm_tc2_kernel, &cfg) == cudaSuccess) n = c;
+            else cudaGetLastError();
+            if (std::getenv("ACE_B200_DEBUG")) std::fprintf(stderr, "[ace_b200] max active CTA pairs: %d\n", n);
+        } else cudaGetLastError();
+    }
+    return n;
+}
+
+cudaError_t launch_tc2(const CUtensorMap& tm, const KParams& kp, int clusters, cudaStream_t stream) {
+    cudaLaunchConfig_t cfg = {};
+    cfg.gridDim = dim3((unsigned)(2 * clusters));
+    cfg.blockDim = dim3(NUM_THREADS);
+    cfg.dynamicSmemBytes = SMEM2_BYTES;
+    cfg.stream = stream;
+    cudaLaunchAttribute at[1];
+    at[0].id = cudaLaunchAttributeClusterDimension;
+    at[0].val.clusterDim.x = 2;
+    at[0].val.clusterDim.y = 1;
+    at[0].val.clusterDim.z = 1;
+    cfg.attrs = at;
+    cfg.numAttrs = 1;
+    return cudaLaunchKernelEx(&cfg, gemm_tc2_kernel, tm, kp);
+}
+
 template <int BN, bool QUANT>
 cudaError_t launch_tc(const CUtensorMap& tm, const KParams& kp, int grid, cudaStream_t stream) {
     using SL = SmemLayout<BN, QUANT>;
@@ -761,11 +1000,21 @@ cudaError_t gemm_launch(const GemmProblem& g, cudaStream_t stream, bool simt) {
     const long tiles128 = (long)kp.n_tiles128 * m_tiles;
     bool bn256 = kp.n_tiles128 >= 2 && (tiles256 >= sms / 2 || accumulate);
     if (const char* fb = std::getenv("ACE_B200_GEMM_BN")) bn256 = (std::atoi(fb) == 256) && kp.n_tiles128 >= 2;  // tuning knob
-    const long tiles_nosplit = bn256 ? tiles256 : tiles128;
+    // CTA pair (256 x 256 per cluster): F16 tiles, whole 256-column tiles only; ACE_B200_GEMM_2CTA=0/1 overrides
+    const int m_pairs = kp.B * ((g.l_out + 2 * BM - 1) / (2 * BM));
+    // Measured (profiles/r1_gemm_sweep_pair2.log): the pair wins once a cluster runs several tiles (M = 6000: +6..17 %),
+    // and loses at M = 750 where its longer per-tile ramp (relay hop, cluster syncs) is not amortised -> rows >= 2048.
+    const bool pair_ok = kp.wtype == W_F16 && (kp.n_tiles128 & 1) == 0 && kp.n_tiles128 >= 2;
+    bool pair = pair_ok && (long)g.B * g.l_out >= 2048;
+    if (const char* fp = std::getenv("ACE_B200_GEMM_2CTA")) pair = pair_ok && std::atoi(fp) != 0;
+    const long tiles_pair = (long)(kp.n_tiles128 / 2) * m_pairs;
+    if (pair && max_active_pairs() < 8) pair = false;
+    const int units = pair ? max_active_pairs() : sms;  // schedulable units: clusters or CTAs
+    const long tiles_nosplit = pair ? tiles_pair : (bn256 ? tiles256 : tiles128);
     // split-K (g.split_k == 0: automatic): fill the SMs when one wave of tiles does not, >= 8 k-blocks per split
     int sk = g.split_k > 0 ? g.split_k : 1;
     if (g.split_k == 0 && accumulate) {
-        sk = (int)((sms + tiles_nosplit / 2) / tiles_nosplit);
+        sk = (int)((units + tiles_nosplit / 2) / tiles_nosplit);
         sk = std::max(1, std::min(sk, 4));
         while (sk > 1 && kp.kb_total / sk < 8) --sk;
     }
@@ -795,6 +1044,7 @@ cudaError_t gemm_launch(const GemmProblem& g, cudaStream_t stream, bool simt) {
     CUtensorMap tm;
     if (!make_tmap_a(g, &tm)) return cudaErrorInvalidValue;
     const long tiles = tiles_nosplit * kp.split_k;
+    if (pair) return launch_tc2(tm, kp, (int)(tiles < units ? tiles : units), stream);
     const int grid = (int)(tiles < sms ? tiles : sms);
     const bool quant = kp.wtype != W_F16;
     if (bn256) return quant ? launch_tc<256, true>(tm, kp, grid, stream) : launch_tc<256, false>(tm, kp, grid, stream);

@@ -26,9 +26,10 @@ def main():
             R = np.zeros((1, M, N), dtype=np.float32)
             fl = 2.0 * M * N * K
             res = []
-            for bn in (128, 256):
+            for bn in (128, 256, 512):  # 512 = the CTA-pair kernel (256 x 256 per cluster)
                 for sk in (1, 2, 3, 4):
-                    os.environ["ACE_B200_GEMM_BN"] = str(bn)
+                    os.environ["ACE_B200_GEMM_2CTA"] = "1" if bn == 512 else "0"
+                    os.environ["ACE_B200_GEMM_BN"] = str(min(bn, 256))
                     os.environ["ACE_B200_GEMM_SPLITK"] = str(sk)
                     best = 1e9
                     for rep in range(3):

@@ -226,3 +226,36 @@ def test_gemm_predecoded_twin_is_bit_identical(br, gt, monkeypatch):
     assert np.array_equal(in_kernel, twin)
     ref = tap_gemm_ref(h16(A), dequant_ref(rows, gt, N, K).astype(np.float64)[:, None, :], 1, 0, 0, L)
     assert rel_err(twin, ref) < 2e-3
+
+
+@pytest.mark.parametrize("shape", [(1, 700, 2048, 1024, 1), (2, 333, 128, 256, 7), (1, 128 * 20, 256, 2048, 1), (1, 100, 512, 512, 1)])
+def test_gemm_cta_pair_matches_single_cta(br, shape, monkeypatch):
+    """cta_group::2 route (256 x 256 per CTA pair) vs the single-CTA kernel on the same operands: same K order per
+    output element, so results must agree to fp32 rounding; both against the float64 restatement."""
+    B, L, C, N, taps = shape
+    g = np.random.default_rng(L + N)
+    A = g.standard_normal((B, L, C), dtype=np.float32)
+    W = (g.standard_normal((N, taps, C), dtype=np.float32) * (taps * C) ** -0.5).astype(np.float32)
+    bias = g.standard_normal((N,), dtype=np.float32)
+    kw = dict(w_type=0, N=N, bias=bias, taps=taps, tap_stride=1 if taps > 1 else 0, tap_offset=-(taps // 2))
+    monkeypatch.setenv("ACE_B200_GEMM_2CTA", "0")
+    single = br.debug_gemm(A, W if taps > 1 else W[:, 0], **kw)
+    monkeypatch.setenv("ACE_B200_GEMM_2CTA", "1")
+    pair = br.debug_gemm(A, W if taps > 1 else W[:, 0], **kw)
+    ref = tap_gemm_ref(h16(A), h16(W), taps, 1 if taps > 1 else 0, -(taps // 2), L) + bias
+    assert rel_err(single, ref) < 1e-4
+    assert rel_err(pair, ref) < 1e-4, rel_err(pair, ref)
+    assert np.abs(pair - single).max() <= 1e-5 * np.abs(ref).max()
+
+
+def test_gemm_cta_pair_splitk_residual(br, monkeypatch):
+    g = np.random.default_rng(21)
+    L, K, N = 260, 1024, 512
+    A = g.standard_normal((1, L, K), dtype=np.float32)
+    W = (g.standard_normal((N, K), dtype=np.float32) * K ** -0.5).astype(np.float32)
+    R = g.standard_normal((1, L, N), dtype=np.float32)
+    ref = h16(A)[0] @ h16(W).T + R[0]
+    monkeypatch.setenv("ACE_B200_GEMM_2CTA", "1")
+    for sk in (False, True):
+        o = br.debug_gemm(A, W, w_type=0, N=N, resid=R, split_k=sk)
+        assert rel_err(o[0], ref) < 1e-4, sk

@@ -7,6 +7,7 @@
 #include "kernels.h"
 
 #include <cstdint>
+#include <cstdio>
 
 namespace ace {
 
@@ -248,6 +249,12 @@ void launch_attention(const __half* Q, long q_stride, const __half* K, long k_st
     note_launch();
     const double k_eff = window >= 0 ? (double)(2 * window + 1 < k_len ? 2 * window + 1 : k_len) : (double)k_len;
     ProfScope prof_scope(PROF_ATTN, 4.0 * B * n_heads * (double)q_len * k_eff * 128.0, 0.0, st);
+    if (attention_use_tc()) {
+        const cudaError_t e = launch_attention_tc(Q, q_stride, K, k_stride, V, v_stride, O, o_stride, key_mask, B, q_len, k_len, n_heads,
+                                                  n_kv_heads, window, st);
+        if (e == cudaSuccess) return;
+        std::fprintf(stderr, "[ace_b200] tcgen05 attention launch failed (%s); using the mma.sync kernel\n", cudaGetErrorString(e));
+    }
     static bool attr = false;
     if (!attr) {
         cudaFuncSetAttribute(attention_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, ATT_SMEM);

@@ -10,12 +10,14 @@
 #include "gemm.h"
 #include "ptx.cuh"
 #include "kernels.h"
+#include "tmap.h"
 
 #include <cuda.h>
 #include <cstdio>
 #include <cstdlib>
 #include <algorithm>
 #include <mutex>
+#include <vector>
 
 namespace ace {
 
@@ -37,7 +39,14 @@ struct KParams {
     int  B, l_out, m_tiles_per_b;
     int  split_k;
     GemmEpilogue epi;
+    long long* trace;            // debug (ACE_B200_GEMM_TRACE=1): per-CTA clock64 stamps of the pipeline phases, else null
 };
+
+// trace slots per CTA
+enum { TR_START = 0, TR_SETUP = 1, TR_FIRST_FULL = 2, TR_LAST_MMA = 3, TR_ACC_READY = 4, TR_EPI_DONE = 5, TR_END = 6, TR_N = 8 };
+__device__ __forceinline__ void trace_stamp(const KParams& p, int slot) {
+    if (p.trace) p.trace[(size_t)blockIdx.x * TR_N + slot] = clock64();
+}
 
 template <int BN, bool QUANT>
 struct SmemLayout {
@@ -336,6 +345,7 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const KParams p) {
     constexpr int SUBS = SL::SUBS;
     constexpr int TMEM_COLS = 2 * BN;  // two accumulators
 
+    if (threadIdx.x == 0) trace_stamp(p, TR_START);
     extern __shared__ uint8_t smem_raw[];
     uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
     uint8_t* sA = smem;                                  // [STAGES][16 KB]
@@ -378,6 +388,7 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const KParams p) {
     __syncthreads();
     ptx::tc_fence_after();
     const uint32_t tmem_base = *tmem_slot;
+    if (threadIdx.x == 0) trace_stamp(p, TR_SETUP);
 
     auto decode_tile_index = [&](int t, int& nt, int& sp, int& b, int& l0) {
         const int mt = t % m_tiles;
@@ -448,6 +459,7 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const KParams p) {
                 ptx::mbar_wait(&full[s], ph);
                 ptx::tc_fence_after();
                 if (lane == 0) {
+                    if (g == 0) trace_stamp(p, TR_FIRST_FULL);
                     const uint32_t a_addr = ptx::smem_u32(sA + s * A_STAGE_BYTES);
                     const uint32_t b_addr = ptx::smem_u32(sB + s * SL::B_STAGE);
 #pragma unroll
@@ -457,7 +469,10 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const KParams p) {
                         ptx::umma_f16(d_tmem, da, db, idesc, (kb > kb0 || k > 0) ? 1u : 0u);
                     }
                     ptx::umma_commit(&empty[s]);
-                    if (kb == kb1 - 1) ptx::umma_commit(&acc_full[a]);
+                    if (kb == kb1 - 1) {
+                        ptx::umma_commit(&acc_full[a]);
+                        trace_stamp(p, TR_LAST_MMA);
+                    }
                 }
                 __syncwarp();
             }
@@ -505,6 +520,7 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const KParams p) {
             const uint32_t aph = (it >> 1) & 1;
             ptx::mbar_wait(&acc_full[a], aph);
             ptx::tc_fence_after();
+            if (warp == 4 && lane == 0) trace_stamp(p, TR_ACC_READY);
             const int l = l0 + q * 32 + lane;
             const uint32_t taddr = tmem_base + ((uint32_t)(q * 32) << 16) + (uint32_t)(a * BN);
             if (p.epi.mode == EPI_HEADNORM) {
@@ -530,6 +546,7 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const KParams p) {
             ptx::tc_fence_before();
             __syncwarp();
             if (lane == 0) ptx::mbar_arrive(&acc_empty[a]);
+            if (warp == 4 && lane == 0) trace_stamp(p, TR_EPI_DONE);
         }
     }
 
@@ -539,6 +556,7 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const KParams p) {
         ptx::tc_fence_after();
         ptx::tmem_dealloc<TMEM_COLS>(tmem_base);
     }
+    if (threadIdx.x == 0) trace_stamp(p, TR_END);
 }
 
 // ---------------------------------------------------------------- CTA-pair kernel (cta_group::2), F16 weight tiles
@@ -927,6 +945,26 @@ cudaError_t launch_tc2(const CUtensorMap& tm, const KParams& kp, int clusters, c
     return cudaLaunchKernelEx(&cfg, gemm_tc2_kernel, tm, kp);
 }
 
+}  // namespace
+
+bool make_tmap_f16_sw128(CUtensorMap* tm, const void* base, int rank, const uint64_t* dims, const uint64_t* strides_bytes,
+                         const uint32_t* box) {
+    PFN_encodeTiled enc = get_encode_fn();
+    if (!enc || rank < 1 || rank > 5) return false;
+    cuuint64_t d[5], s[4];
+    cuuint32_t bx[5], es[5];
+    for (int i = 0; i < rank; ++i) {
+        d[i] = dims[i];
+        bx[i] = box[i];
+        es[i] = 1;
+        if (i > 0) s[i - 1] = strides_bytes[i - 1];
+    }
+    return enc(tm, CU_TENSOR_MAP_DATA_TYPE_FLOAT16, (cuuint32_t)rank, const_cast<void*>(base), d, s, bx, es, CU_TENSOR_MAP_INTERLEAVE_NONE,
+               CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_128B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE) == CUDA_SUCCESS;
+}
+
+namespace {
+
 template <int BN, bool QUANT>
 cudaError_t launch_tc(const CUtensorMap& tm, const KParams& kp, int grid, cudaStream_t stream) {
     using SL = SmemLayout<BN, QUANT>;
@@ -1044,6 +1082,29 @@ cudaError_t gemm_launch(const GemmProblem& g, cudaStream_t stream, bool simt) {
     CUtensorMap tm;
     if (!make_tmap_a(g, &tm)) return cudaErrorInvalidValue;
     const long tiles = tiles_nosplit * kp.split_k;
+    kp.trace = nullptr;
+    static long long* trace_buf = nullptr;
+    const bool tracing = std::getenv("ACE_B200_GEMM_TRACE") != nullptr && !pair;
+    if (tracing) {
+        if (!trace_buf) cudaMalloc(&trace_buf, (size_t)sms * TR_N * sizeof(long long));
+        cudaMemsetAsync(trace_buf, 0, (size_t)sms * TR_N * sizeof(long long), stream);
+        kp.trace = trace_buf;
+    }
+    struct TraceDump {
+        bool on; long long* buf; int ctas; cudaStream_t st; int M, N, K, bn, sk;
+        ~TraceDump() {
+            if (!on) return;
+            cudaStreamSynchronize(st);
+            std::vector<long long> h((size_t)ctas * TR_N);
+            cudaMemcpy(h.data(), buf, h.size() * sizeof(long long), cudaMemcpyDeviceToHost);
+            double acc[TR_N] = {0};
+            for (int c = 0; c < ctas; ++c)
+                for (int i = 0; i < TR_N; ++i) acc[i] += (double)(h[(size_t)c * TR_N + i] - h[(size_t)c * TR_N + TR_START]);
+            std::fprintf(stderr, "[gemm trace] M=%d N=%d K=%d bn=%d sk=%d ctas=%d | cycles from CTA start (mean): setup %.0f first_full %.0f last_mma_issued %.0f "
+                                 "acc_ready(last tile) %.0f epi_done(last tile) %.0f end %.0f\n", M, N, K, bn, sk, ctas, acc[TR_SETUP] / ctas,
+                         acc[TR_FIRST_FULL] / ctas, acc[TR_LAST_MMA] / ctas, acc[TR_ACC_READY] / ctas, acc[TR_EPI_DONE] / ctas, acc[TR_END] / ctas);
+        }
+    } trace_dump{tracing, trace_buf, (int)(tiles < sms ? tiles : sms), stream, g.B * g.l_out, w.N, w.K * w.taps, bn256 ? 256 : 128, kp.split_k};
     if (pair) return launch_tc2(tm, kp, (int)(tiles < units ? tiles : units), stream);
     const int grid = (int)(tiles < sms ? tiles : sms);
     const bool quant = kp.wtype != W_F16;

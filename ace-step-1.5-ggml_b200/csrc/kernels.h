@@ -76,6 +76,13 @@ void launch_attention(const __half* Q, long q_stride, const __half* K, long k_st
                       __half* O, long o_stride, const int32_t* key_mask, int B, int q_len, int k_len, int n_heads,
                       int n_kv_heads, int window, cudaStream_t st);
 
+// tcgen05 / TMEM / TMA implementation (attention_tc.cu), the default; ACE_B200_ATTN=mma selects the mma.sync kernel of
+// attention.cu (kept as the independent implementation the tensor-memory kernel is unit-tested against)
+bool attention_use_tc();
+cudaError_t launch_attention_tc(const __half* Q, long q_stride, const __half* K, long k_stride, const __half* V, long v_stride,
+                                __half* O, long o_stride, const int32_t* key_mask, int B, int q_len, int k_len, int n_heads,
+                                int n_kv_heads, int window, cudaStream_t st);
+
 // ---- sampler -------------------------------------------------------------------------------------
 // x -= v * dt   (acestep_ggml.cpp:2075-2085);  with CFG: v = v_u + g (v_c - v_u)
 void launch_euler_step(float* x, const float* v_cond, const float* v_uncond, float guidance, float dt, long n,

@@ -189,9 +189,12 @@ def attention_ref(Q, K, V, key_mask, n_heads, n_kv, window):
     return out.reshape(B, ql, n_heads * 128)
 
 
+@pytest.mark.parametrize("impl", ["tcgen05", "mma"])
 @pytest.mark.parametrize("ql,kl,window,masked", [(64, 64, -1, False), (200, 200, -1, False), (375, 375, 128, False),
-                                                   (130, 77, -1, True), (300, 300, 16, True), (1, 5, -1, False)])
-def test_attention(br, ql, kl, window, masked):
+                                                   (130, 77, -1, True), (300, 300, 16, True), (1, 5, -1, False),
+                                                   (700, 700, -1, False), (1000, 1000, 128, False), (300, 512, -1, True)])
+def test_attention(br, ql, kl, window, masked, impl, monkeypatch):
+    monkeypatch.setenv("ACE_B200_ATTN", "mma" if impl == "mma" else "tc")
     g = np.random.default_rng(ql + kl)
     B, nh, nkv = 2, 4, 2
     Q = g.standard_normal((B, ql, nh * 128), dtype=np.float32)
@@ -259,3 +262,18 @@ def test_gemm_cta_pair_splitk_residual(br, monkeypatch):
     for sk in (False, True):
         o = br.debug_gemm(A, W, w_type=0, N=N, resid=R, split_k=sk)
         assert rel_err(o[0], ref) < 1e-4, sk
+
+
+def test_attention_lazy_rescale(br, monkeypatch):
+    """scores that grow by far more than 2^8 along the key axis force the tcgen05 kernel through its O / l rescale path
+    (stale reference max) several times; the result must not depend on it"""
+    monkeypatch.setenv("ACE_B200_ATTN", "tc")
+    g = np.random.default_rng(3)
+    B, nh, nkv, ql, kl = 1, 2, 1, 256, 640
+    Q = g.standard_normal((B, ql, nh * 128), dtype=np.float32)
+    K = g.standard_normal((B, kl, nkv * 128), dtype=np.float32)
+    K *= np.linspace(0.2, 6.0, kl, dtype=np.float32)[None, :, None]  # later keys score much higher in magnitude
+    V = g.standard_normal((B, kl, nkv * 128), dtype=np.float32)
+    out = br.debug_attention(Q, K, V, None, nh, nkv, -1)
+    ref = attention_ref(Q, K, V, None, nh, nkv, -1)
+    assert rel_err(out, ref) < 3e-3, rel_err(out, ref)

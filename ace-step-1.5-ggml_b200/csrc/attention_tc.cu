@@ -295,6 +295,284 @@ attention_tc_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_consta
     }
 }
 
+// ---------------------------------------------------------------- 8 softmax warps: two threads per query row
+// Same pipeline as attention_tc_kernel, but the 64 score columns of a row are split between two threads (warp w and w + 4
+// share a TMEM lane quadrant; w < 4 takes keys 0..31 of the tile, w >= 4 keys 32..63), halving the serial exp / pack chain
+// that bounded the 4-warp version (ncu: tensor pipe 30 %, issue 31 %, MUFU 33 % — a latency chain, nothing saturated).
+// Both threads of a row must exponentiate against the SAME reference max.  It only moves in the lazy-rescale events, so the
+// common path needs one OR-reduction barrier per tile ("does any row need to move its max?") and no data exchange; the rare
+// path swaps the two half-row maxima through the (idle) P buffer, and each thread rescales its half of the O columns.
+constexpr int ATT8_THREADS = 320;
+
+__global__ void __launch_bounds__(ATT8_THREADS, 2)
+attention_tc8_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__ CUtensorMap tmK,
+                     const __grid_constant__ CUtensorMap tmV, const AttnParams p) {
+    extern __shared__ __align__(1024) uint8_t smem[];
+    uint8_t* sQ = smem;
+    uint8_t* sK = smem + OFF_K;
+    uint8_t* sV = smem + OFF_V;
+    uint8_t* sP = smem + OFF_P;
+    uint64_t* bars = reinterpret_cast<uint64_t*>(smem + OFF_BAR);
+    uint64_t* q_full = bars;
+    uint64_t* kv_full = bars + 1;
+    uint64_t* kv_empty = bars + 3;
+    uint64_t* s_ready = bars + 5;
+    uint64_t* s_free = bars + 7;
+    uint64_t* p_ready = bars + 9;
+    uint64_t* pv_done = bars + 10;
+    uint64_t* kmask = bars + 12;
+    uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + 14);
+
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    const int q0 = blockIdx.x * BQ;
+    const int h = blockIdx.y, b = blockIdx.z;
+    const int hk = h / p.n_rep;
+
+    int kb_lo = 0, kb_hi = (p.k_len + BKV - 1) / BKV - 1;
+    if (p.window >= 0) {
+        kb_lo = max(0, (q0 - p.window) / BKV);
+        kb_hi = min(kb_hi, (min(q0 + BQ - 1, p.q_len - 1) + p.window) / BKV);
+    }
+    const int n_tiles = kb_hi - kb_lo + 1;
+
+    if (threadIdx.x == 0) {
+        if ((ptx::smem_u32(smem) & 1023u) != 0) __trap();
+        ptx::mbar_init(q_full, 1);
+        for (int s = 0; s < 2; ++s) {
+            ptx::mbar_init(&kv_full[s], 1);
+            ptx::mbar_init(&kv_empty[s], 1);
+            ptx::mbar_init(&s_ready[s], 1);
+            ptx::mbar_init(&s_free[s], 8);
+        }
+        ptx::mbar_init(p_ready, 8);
+        ptx::mbar_init(pv_done, 1);
+        ptx::fence_mbar_init();
+    }
+    if (warp == 9) ptx::tmem_alloc<TMEM_COLS>(tmem_slot);
+    if (warp == 8 && lane == 0) {
+        ptx::prefetch_tmap(&tmQ);
+        ptx::prefetch_tmap(&tmK);
+        ptx::prefetch_tmap(&tmV);
+    }
+    ptx::tc_fence_before();
+    __syncthreads();
+    ptx::tc_fence_after();
+    const uint32_t tmem_base = *tmem_slot;
+
+    if (warp == 8) {
+        // ===================== producer =====================
+        if (lane == 0) {
+            ptx::mbar_expect_tx(q_full, Q_BYTES);
+            ptx::tma_load_4d(sQ, &tmQ, q_full, 0, h, q0, b);
+            ptx::tma_load_4d(sQ + Q_BYTES / 2, &tmQ, q_full, 64, h, q0, b);
+        }
+        const int32_t* mb = p.key_mask ? p.key_mask + (long)b * p.k_len : nullptr;
+        for (int j = 0; j < n_tiles; ++j) {
+            const int s = j & 1;
+            const uint32_t ph = (j >> 1) & 1;
+            const int k0 = (kb_lo + j) * BKV;
+            ptx::mbar_wait(&kv_empty[s], ph ^ 1);
+            const int ka = k0 + lane, kb2 = k0 + 32 + lane;
+            const bool ok_a = ka < p.k_len && (!mb || mb[ka] != 0);
+            const bool ok_b = kb2 < p.k_len && (!mb || mb[kb2] != 0);
+            const uint32_t lo = __ballot_sync(0xffffffffu, ok_a), hi = __ballot_sync(0xffffffffu, ok_b);
+            if (lane == 0) {
+                kmask[s] = (uint64_t)lo | ((uint64_t)hi << 32);
+                ptx::mbar_expect_tx(&kv_full[s], 2 * KV_TILE);
+                ptx::tma_load_4d(sK + s * KV_TILE, &tmK, &kv_full[s], 0, hk, k0, b);
+                ptx::tma_load_4d(sK + s * KV_TILE + KV_TILE / 2, &tmK, &kv_full[s], 64, hk, k0, b);
+                ptx::tma_load_4d(sV + s * KV_TILE, &tmV, &kv_full[s], 0, hk, k0, b);
+                ptx::tma_load_4d(sV + s * KV_TILE + KV_TILE / 2, &tmV, &kv_full[s], 64, hk, k0, b);
+            }
+            __syncwarp();
+        }
+    } else if (warp == 9) {
+        // ===================== MMA issuer (identical to the 4-warp kernel) =====================
+        constexpr uint32_t idesc_s = ptx::umma_idesc_f16(BQ, BKV);
+        constexpr uint32_t idesc_o = ptx::umma_idesc_f16_bmn(BQ, HD);
+        const uint32_t q_addr = ptx::smem_u32(sQ), p_addr = ptx::smem_u32(sP);
+        auto issue_s = [&](int j) {
+            const int s = j & 1;
+            const uint32_t k_addr = ptx::smem_u32(sK + s * KV_TILE);
+#pragma unroll
+            for (int kk = 0; kk < HD / 16; ++kk) {
+                const uint64_t da = ptx::umma_desc_sw128(q_addr + (kk >> 2) * (Q_BYTES / 2) + (kk & 3) * 32);
+                const uint64_t db = ptx::umma_desc_sw128(k_addr + (kk >> 2) * (KV_TILE / 2) + (kk & 3) * 32);
+                ptx::umma_f16(tmem_base + (uint32_t)(s * BKV), da, db, idesc_s, kk > 0 ? 1u : 0u);
+            }
+            ptx::umma_commit(&s_ready[s]);
+        };
+        ptx::mbar_wait(q_full, 0);
+        ptx::mbar_wait(&kv_full[0], 0);
+        ptx::tc_fence_after();
+        if (lane == 0) issue_s(0);
+        __syncwarp();
+        for (int j = 0; j < n_tiles; ++j) {
+            if (j + 1 < n_tiles) {
+                const int s1 = (j + 1) & 1;
+                const uint32_t u = (uint32_t)((j + 1) >> 1);
+                ptx::mbar_wait(&kv_full[s1], u & 1);
+                ptx::mbar_wait(&s_free[s1], (u & 1) ^ 1);
+                ptx::tc_fence_after();
+                if (lane == 0) issue_s(j + 1);
+                __syncwarp();
+            }
+            ptx::mbar_wait(p_ready, j & 1);
+            ptx::tc_fence_after();
+            if (lane == 0) {
+                const uint32_t v_addr = ptx::smem_u32(sV + (j & 1) * KV_TILE);
+#pragma unroll
+                for (int kk = 0; kk < BKV / 16; ++kk) {
+                    const uint64_t da = ptx::umma_desc_sw128(p_addr + kk * 32);
+                    const uint64_t db = ptx::umma_desc_mn_sw128(v_addr + kk * 2048, KV_TILE / 2, 1024);
+                    ptx::umma_f16(tmem_base + 128u, da, db, idesc_o, (j > 0 || kk > 0) ? 1u : 0u);
+                }
+                ptx::umma_commit(&kv_empty[j & 1]);
+                ptx::umma_commit(pv_done);
+            }
+            __syncwarp();
+        }
+    } else {
+        // ===================== softmax: warps 0..7, thread = (query row, half of the tile's keys) =====================
+        const int quad = warp & 3, hf = warp >> 2;
+        const int r = quad * 32 + lane;
+        const int q = q0 + r;
+        const uint32_t lane_addr = tmem_base + ((uint32_t)(quad * 32) << 16);
+        const float sc = 0.08838834764831845f * 1.4426950408889634f;
+        float* xch = reinterpret_cast<float*>(sP);  // [2][128] scratch inside the idle P buffer (rare path / final sum)
+        float m_used = -INFINITY, l = 0.f;
+        for (int j = 0; j < n_tiles; ++j) {
+            const int s = j & 1;
+            const int k0 = (kb_lo + j) * BKV + hf * 32;   // first key of this thread's 32 columns
+            ptx::mbar_wait(&s_ready[s], (j >> 1) & 1);
+            ptx::tc_fence_after();
+            uint32_t r0[32];
+            ptx::tmem_ld32(lane_addr + (uint32_t)(s * BKV + hf * 32), r0);
+            ptx::tmem_ld_wait();
+            const uint32_t km = (uint32_t)(kmask[s] >> (hf * 32));
+            ptx::tc_fence_before();
+            __syncwarp();
+            if (lane == 0) ptx::mbar_arrive(&s_free[s]);
+
+            float v[32];
+#pragma unroll
+            for (int i = 0; i < 32; ++i) v[i] = __uint_as_float(r0[i]) * sc;
+            if (km != ~0u) {
+#pragma unroll
+                for (int i = 0; i < 32; ++i)
+                    if (!((km >> i) & 1u)) v[i] = -INFINITY;
+            }
+            const bool band_edge = p.window >= 0 && ((q0 + BQ - 1) - k0 > p.window || (k0 + 31) - q0 > p.window);
+            if (band_edge) {
+#pragma unroll
+                for (int i = 0; i < 32; ++i) {
+                    const int d = q - (k0 + i);
+                    if (d > p.window || d < -p.window) v[i] = -INFINITY;
+                }
+            }
+            float mx = v[0];
+#pragma unroll
+            for (int i = 1; i < 32; ++i) mx = fmaxf(mx, v[i]);
+            // does ANY row of the CTA have to move its reference max at this tile?  (OR-reduction barrier, 256 threads)
+            const int need_local = mx > m_used + RESCALE_THRESHOLD ? 1 : 0;
+            int any;
+            asm volatile(
+                "{\n\t.reg .pred p, q;\n\t"
+                "setp.ne.b32 p, %1, 0;\n\t"
+                "barrier.red.or.pred q, 1, 256, p;\n\t"
+                "selp.b32 %0, 1, 0, q;\n\t}"
+                : "=r"(any)
+                : "r"(need_local)
+                : "memory");
+            float alpha = 1.0f;
+            if (any) {  // rare (always at j = 0): agree on the row max across the two halves, rescale O
+                if (j > 0) {
+                    ptx::mbar_wait(pv_done, (j - 1) & 1);  // P buffer idle, O quiescent
+                    ptx::tc_fence_after();
+                }
+                xch[hf * 128 + r] = mx;
+                asm volatile("bar.sync 1, 256;" ::: "memory");
+                const float m_row = fmaxf(mx, xch[(hf ^ 1) * 128 + r]);
+                const bool need = m_row > m_used + RESCALE_THRESHOLD;
+                if (need) {
+                    alpha = ptx::ex2(m_used - m_row);
+                    m_used = m_row;
+                }
+                if (j > 0 && __any_sync(0xffffffffu, need)) {
+#pragma unroll 1
+                    for (int c = 0; c < 2; ++c) {  // this thread's half of the O columns
+                        uint32_t o[32];
+                        const uint32_t oa = lane_addr + 128u + (uint32_t)(hf * 64 + c * 32);
+                        ptx::tmem_ld32(oa, o);
+                        ptx::tmem_ld_wait();
+#pragma unroll
+                        for (int i = 0; i < 32; ++i) o[i] = __float_as_uint(__uint_as_float(o[i]) * alpha);
+                        ptx::tmem_st32(oa, o);
+                    }
+                    ptx::tmem_st_wait();
+                }
+                asm volatile("bar.sync 1, 256;" ::: "memory");  // scratch read by everyone before P overwrites it
+            }
+            const float msafe = (m_used == -INFINITY) ? 0.f : m_used;
+            uint32_t ph[16];
+            float psum = 0.f;
+#pragma unroll
+            for (int i = 0; i < 16; ++i) {
+                const float p0 = ptx::ex2(v[2 * i] - msafe), p1 = ptx::ex2(v[2 * i + 1] - msafe);
+                psum += p0 + p1;
+                const __half2 hh = __floats2half2_rn(p0, p1);
+                ph[i] = *reinterpret_cast<const uint32_t*>(&hh);
+            }
+            l = l * alpha + psum;
+            if (j > 0 && !any) {
+                ptx::mbar_wait(pv_done, (j - 1) & 1);
+                ptx::tc_fence_after();
+            }
+#pragma unroll
+            for (int c = 0; c < 4; ++c) {
+                const int cc = hf * 4 + c;
+                *reinterpret_cast<uint4*>(sP + r * 128 + ((cc ^ (r & 7)) << 4)) = make_uint4(ph[4 * c], ph[4 * c + 1], ph[4 * c + 2], ph[4 * c + 3]);
+            }
+            ptx::fence_proxy_async_smem();
+            ptx::tc_fence_before();
+            __syncwarp();
+            if (lane == 0) ptx::mbar_arrive(p_ready);
+        }
+        // ---- finalise: total row sum across the two halves, O / l -> fp16 (each thread writes 64 of the 128 columns)
+        ptx::mbar_wait(pv_done, (n_tiles - 1) & 1);
+        ptx::tc_fence_after();
+        xch[hf * 128 + r] = l;
+        asm volatile("bar.sync 1, 256;" ::: "memory");
+        const float lt = l + xch[(hf ^ 1) * 128 + r];
+        const float inv = lt > 0.f ? 1.0f / lt : 0.f;
+        __half* op = p.O + ((long)b * p.q_len + q) * p.o_stride + (long)h * HD + hf * 64;
+#pragma unroll 1
+        for (int c = 0; c < 2; ++c) {
+            uint32_t o[32];
+            ptx::tmem_ld32(lane_addr + 128u + (uint32_t)(hf * 64 + c * 32), o);
+            ptx::tmem_ld_wait();
+            if (q < p.q_len) {
+                uint32_t w[16];
+#pragma unroll
+                for (int i = 0; i < 16; ++i) {
+                    const __half2 hh = __floats2half2_rn(__uint_as_float(o[2 * i]) * inv, __uint_as_float(o[2 * i + 1]) * inv);
+                    w[i] = *reinterpret_cast<const uint32_t*>(&hh);
+                }
+#pragma unroll
+                for (int i = 0; i < 4; ++i)
+                    *reinterpret_cast<uint4*>(op + c * 32 + i * 8) = make_uint4(w[4 * i], w[4 * i + 1], w[4 * i + 2], w[4 * i + 3]);
+            }
+        }
+    }
+
+    ptx::tc_fence_before();
+    __syncthreads();
+    if (warp == 9) {
+        ptx::tc_fence_after();
+        ptx::tmem_dealloc<TMEM_COLS>(tmem_base);
+    }
+}
+
 bool make_qkv_tmap(CUtensorMap* tm, const __half* base, long row_stride, int rows, int heads, int B, int box_rows) {
     const uint64_t dims[4] = {(uint64_t)HD, (uint64_t)heads, (uint64_t)rows, (uint64_t)B};
     const uint64_t strides[3] = {(uint64_t)HD * 2, (uint64_t)row_stride * 2, (uint64_t)rows * (uint64_t)row_stride * 2};
@@ -319,12 +597,15 @@ cudaError_t launch_attention_tc(const __half* Q, long q_stride, const __half* K,
     static bool attr = false;
     if (!attr) {
         cudaError_t e = cudaFuncSetAttribute(attention_tc_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, ATT_TC_SMEM);
+        if (e == cudaSuccess) e = cudaFuncSetAttribute(attention_tc8_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, ATT_TC_SMEM);
         if (e != cudaSuccess) return e;
         attr = true;
     }
     AttnParams p{O, o_stride, key_mask, q_len, k_len, n_heads / n_kv_heads, window};
     dim3 grid((q_len + BQ - 1) / BQ, n_heads, B);
-    attention_tc_kernel<<<grid, ATT_TC_THREADS, ATT_TC_SMEM, st>>>(tq, tk, tv, p);
+    const char* env = std::getenv("ACE_B200_ATTN");
+    if (env && std::string(env) == "tc4") attention_tc_kernel<<<grid, ATT_TC_THREADS, ATT_TC_SMEM, st>>>(tq, tk, tv, p);
+    else attention_tc8_kernel<<<grid, ATT8_THREADS, ATT_TC_SMEM, st>>>(tq, tk, tv, p);
     return cudaGetLastError();
 }
 

@@ -29,6 +29,7 @@ constexpr int A_STAGE_BYTES = BM * BK * 2;     // 16 KB
 constexpr int W_SUB_BYTES   = TILE_N * BK * 2; // 16 KB per 128-row sub-tile
 constexpr int RAW_MAX_BYTES = 8704;            // largest packed tile (Q8_0)
 constexpr int NUM_THREADS   = 320;
+constexpr int STG_WARP_BYTES = 32 * 32 * 4;    // one epilogue warp's transpose buffer: 32 rows x 32 fp32 columns
 
 struct KParams {
     const uint8_t* W;
@@ -43,7 +44,7 @@ struct KParams {
 };
 
 // trace slots per CTA
-enum { TR_START = 0, TR_SETUP = 1, TR_FIRST_FULL = 2, TR_LAST_MMA = 3, TR_ACC_READY = 4, TR_EPI_DONE = 5, TR_END = 6, TR_N = 8 };
+enum { TR_START = 0, TR_SETUP = 1, TR_FIRST_FULL = 2, TR_LAST_MMA = 3, TR_ACC_READY = 4, TR_EPI_DONE = 5, TR_END = 6, TR_EPI_LD0 = 7, TR_EPI_CHUNK0 = 8, TR_N = 12 };
 __device__ __forceinline__ void trace_stamp(const KParams& p, int slot) {
     if (p.trace) p.trace[(size_t)blockIdx.x * TR_N + slot] = clock64();
 }
@@ -54,10 +55,13 @@ struct SmemLayout {
     static constexpr int B_STAGE    = SUBS * W_SUB_BYTES;
     static constexpr int RAW_STAGE  = QUANT ? SUBS * RAW_MAX_BYTES : 0;
     static constexpr int STAGE      = A_STAGE_BYTES + B_STAGE;
-    static constexpr int BUDGET     = 225 * 1024 - 1024 /*align slack*/ - 256 /*barriers*/;
+    static constexpr int EPI_WARPS  = QUANT ? 4 : 8;
+    static constexpr int STG_BYTES  = EPI_WARPS * STG_WARP_BYTES;  // epilogue transpose buffers
+    static constexpr int COL_BYTES  = 2 * BN * 4;                  // staged bias + gate of one tile
+    static constexpr int BUDGET     = 227 * 1024 - 256 /*barriers*/ - STG_BYTES - COL_BYTES;
     static constexpr int STAGES_RAW = BUDGET / (STAGE + RAW_STAGE);
     static constexpr int STAGES     = STAGES_RAW > 6 ? 6 : STAGES_RAW;
-    static constexpr int BYTES      = STAGES * (STAGE + RAW_STAGE) + 256 + 1024;
+    static constexpr int BYTES      = STAGES * (STAGE + RAW_STAGE) + STG_BYTES + COL_BYTES + 256;
 };
 
 // ---------------------------------------------------------------- weight decoders (one thread = one tile row)
@@ -174,7 +178,7 @@ __device__ __forceinline__ void epilogue_row32(const KParams& p, const float (&a
 #pragma unroll
         for (int i = 0; i < 16; ++i) {
             const float g = acc[2 * i], u = acc[2 * i + 1];
-            h[i] = __float2half_rn(g / (1.0f + __expf(-g)) * u);
+            h[i] = __float2half_rn(__fdividef(g, 1.0f + __expf(-g)) * u);  // fast divide: the result is rounded to fp16
         }
         if (j0 + 16 <= nout) {
             *reinterpret_cast<uint4*>(o) = *reinterpret_cast<const uint4*>(h);
@@ -238,7 +242,7 @@ __device__ __forceinline__ void epilogue_row32(const KParams& p, const float (&a
                 for (int i = 0; i < 32; ++i) v[i] = snake_f(v[i], __ldg(e.snake_alpha + c0 + i), __ldg(e.snake_invbeta + c0 + i));
             } else if (e.silu_f16) {
 #pragma unroll
-                for (int i = 0; i < 32; ++i) v[i] = v[i] / (1.0f + __expf(-v[i]));
+                for (int i = 0; i < 32; ++i) v[i] = __fdividef(v[i], 1.0f + __expf(-v[i]));
             }
             __align__(16) __half h[32];
 #pragma unroll
@@ -267,11 +271,104 @@ __device__ __forceinline__ void epilogue_row32(const KParams& p, const float (&a
                 const int c = e.snake_period ? ((n0 + i) % e.snake_period) : (n0 + i);
                 x = snake_f(x, __ldg(e.snake_alpha + c), __ldg(e.snake_invbeta + c));
             } else if (e.silu_f16) {
-                x = x / (1.0f + __expf(-x));
+                x = __fdividef(x, 1.0f + __expf(-x));
             }
             e.out_f16[base + i] = __float2half_rn(x);
         }
     }
+}
+
+// EPI_STORE for a full 32-column chunk, through the warp's shared-memory transpose buffer.
+// Phase 1 (thread = accumulator row, as tcgen05.ld delivers it) applies the per-column terms (bias, AdaLN gate) and parks
+// the row in smem; phase 2 re-reads it so that 8 lanes cover one row's 128 contiguous bytes and one warp instruction
+// touches 4 full 128-byte lines — instead of 32 rows x 16 bytes, which made every epilogue cost ~12 k cycles per 128x256
+// tile (profiles/r1_gemm_trace_tr1.log) because each 16-byte piece was its own L2 transaction.  The residual read, the fp32
+// store / red.add and the fp16 (Snake / SiLU) store all happen in phase 2.  16-byte pieces are XOR-swizzled by the row so
+// both phases are bank-conflict free.  Returns false (nothing done) when the chunk does not qualify: caller falls back.
+__device__ __forceinline__ bool epilogue_store_staged(const KParams& p, const float (&acc)[32], int b, int l_base, int lane, int n0,
+                                                      const float* s_bias, const float* s_gate, float* stg) {
+    const GemmEpilogue& e = p.epi;
+    if (n0 + 32 > p.N) return false;                                     // warp-uniform
+    const long col0 = (long)n0 + e.out_shift;
+    if (((e.ld_out | col0 | e.out_bstride) & 3) != 0) return false;      // 16-byte alignment of every row segment
+    // per-column terms of this chunk, staged in smem once per tile (s_bias / s_gate point at this chunk's 32 entries)
+    float4* s4 = reinterpret_cast<float4*>(stg);
+#pragma unroll
+    for (int i = 0; i < 8; ++i) {
+        const float4 bz = reinterpret_cast<const float4*>(s_bias)[i], gz = reinterpret_cast<const float4*>(s_gate)[i];
+        s4[lane * 8 + (i ^ (lane & 7))] = make_float4((acc[4 * i] + bz.x) * gz.x, (acc[4 * i + 1] + bz.y) * gz.y,
+                                                      (acc[4 * i + 2] + bz.z) * gz.z, (acc[4 * i + 3] + bz.w) * gz.w);
+    }
+    __syncwarp();
+    const int seg = lane & 7;                 // this lane's 4 columns: n0 + 4 seg ..
+    long off[8];
+    bool ok[8];
+#pragma unroll
+    for (int k = 0; k < 8; ++k) {
+        const int l = l_base + 4 * k + (lane >> 3);
+        const long flat0 = (long)l * e.ld_out + col0;   // chunk start inside the sample
+        ok[k] = l < p.l_out && flat0 >= 0 && flat0 + 32 <= e.out_valid;
+        off[k] = (long)b * e.out_bstride + flat0 + 4 * seg;
+    }
+    if (e.atomic) {
+#pragma unroll
+        for (int k = 0; k < 8; ++k) {
+            const int rr = 4 * k + (lane >> 3);
+            const float4 t = s4[rr * 8 + (seg ^ (rr & 7))];
+            if (ok[k])
+                asm volatile("red.global.add.v4.f32 [%0], {%1, %2, %3, %4};" ::"l"(e.out_f32 + off[k]), "f"(t.x), "f"(t.y), "f"(t.z), "f"(t.w) : "memory");
+        }
+        __syncwarp();
+        return true;
+    }
+    float4 res[8];
+    if (e.resid) {  // all eight row segments in flight before the first use
+#pragma unroll
+        for (int k = 0; k < 8; ++k) res[k] = ok[k] ? __ldcg(reinterpret_cast<const float4*>(e.resid + off[k])) : make_float4(0.f, 0.f, 0.f, 0.f);
+    }
+    float4 sa = make_float4(0.f, 0.f, 0.f, 0.f), sb = sa;
+    if (e.out_f16 && e.snake_alpha) {
+        const int c0 = (e.snake_period ? (n0 % e.snake_period) : n0) + 4 * seg;
+        sa = __ldg(reinterpret_cast<const float4*>(e.snake_alpha + c0));
+        sb = __ldg(reinterpret_cast<const float4*>(e.snake_invbeta + c0));
+    }
+#pragma unroll
+    for (int k = 0; k < 8; ++k) {
+        const int rr = 4 * k + (lane >> 3);
+        float4 t = s4[rr * 8 + (seg ^ (rr & 7))];
+        if (!ok[k]) continue;
+        if (e.resid) { t.x += res[k].x; t.y += res[k].y; t.z += res[k].z; t.w += res[k].w; }
+        if (e.out_f32) *reinterpret_cast<float4*>(e.out_f32 + off[k]) = t;
+        if (e.out_f16) {
+            if (e.snake_alpha) {
+                t.x = snake_f(t.x, sa.x, sb.x); t.y = snake_f(t.y, sa.y, sb.y);
+                t.z = snake_f(t.z, sa.z, sb.z); t.w = snake_f(t.w, sa.w, sb.w);
+            } else if (e.silu_f16) {
+                t.x = __fdividef(t.x, 1.0f + __expf(-t.x)); t.y = __fdividef(t.y, 1.0f + __expf(-t.y));
+                t.z = __fdividef(t.z, 1.0f + __expf(-t.z)); t.w = __fdividef(t.w, 1.0f + __expf(-t.w));
+            }
+            const __half2 h0 = __floats2half2_rn(t.x, t.y), h1 = __floats2half2_rn(t.z, t.w);
+            *reinterpret_cast<uint2*>(e.out_f16 + off[k]) = make_uint2(h2u(h0), h2u(h1));
+        }
+    }
+    __syncwarp();  // buffer is reused by the next chunk
+    return true;
+}
+
+// Column vectors of one tile for the staged epilogue: bias (0 when absent / not this split's job) and AdaLN gate (1 when
+// absent) of the tile's BN columns, fetched by the epilogue warps while the tile's MMAs are still running.
+template <int BN, int NTHREADS>
+__device__ __forceinline__ void stage_column_terms(const KParams& p, int b, int n_base, bool add_bias, int tid, float* s_bias, float* s_gate) {
+    const GemmEpilogue& e = p.epi;
+    for (int j = tid; j < BN; j += NTHREADS) {
+        const int n = n_base + j;
+        const bool in = n < p.N;
+        s_bias[j] = (in && e.bias && add_bias) ? __ldg(e.bias + n) : 0.f;
+        s_gate[j] = (in && e.gate) ? __ldg(e.gate + (long)b * e.gate_bstride + n) : 1.f;
+    }
+}
+__device__ __forceinline__ void epi_bar_sync(int nthreads) {  // named barrier 1: the epilogue warps only
+    asm volatile("bar.sync 1, %0;" ::"r"(nthreads) : "memory");
 }
 
 // EPI_HEADNORM: one head (128 accumulator columns) of one row.  Pass 1 reads the four 32-column chunks from TMEM for
@@ -295,7 +392,7 @@ __device__ __forceinline__ void epilogue_head128(const KParams& p, uint32_t tadd
                 ss = fmaf(v, v, ss);
             }
         }
-        inv = 1.0f / sqrtf(ss * (1.0f / 128.0f) + e.hn_eps);
+        inv = rsqrtf(ss * (1.0f / 128.0f) + e.hn_eps);
     }
     const float2* rt = (w && e.rope) ? e.rope + (long)(row_ok ? l : 0) * 64 : nullptr;
 #pragma unroll 1
@@ -346,12 +443,14 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const KParams p) {
     constexpr int TMEM_COLS = 2 * BN;  // two accumulators
 
     if (threadIdx.x == 0) trace_stamp(p, TR_START);
-    extern __shared__ uint8_t smem_raw[];
-    uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
+    extern __shared__ __align__(1024) uint8_t smem[];
+    if (threadIdx.x == 0 && (ptx::smem_u32(smem) & 1023u) != 0) __trap();  // the 128-byte swizzle needs 1 KB aligned tiles
     uint8_t* sA = smem;                                  // [STAGES][16 KB]
     uint8_t* sB = sA + STAGES * A_STAGE_BYTES;           // [STAGES][SUBS*16 KB]
     uint8_t* sR = sB + STAGES * SL::B_STAGE;             // [STAGES][SUBS*RAW_MAX] (QUANT only)
-    uint64_t* bars = reinterpret_cast<uint64_t*>(sR + STAGES * SL::RAW_STAGE);
+    float* sStg = reinterpret_cast<float*>(sR + STAGES * SL::RAW_STAGE);  // [EPI_WARPS][32 x 32 fp32]
+    float* sCol = sStg + SL::STG_BYTES / 4;  // [2][BN]: bias, gate of the current tile
+    uint64_t* bars = reinterpret_cast<uint64_t*>(reinterpret_cast<uint8_t*>(sCol) + SL::COL_BYTES);
     uint64_t* full = bars;                  // [STAGES] operands of stage s are in smem
     uint64_t* empty = bars + STAGES;        // [STAGES] MMAs reading stage s have completed
     uint64_t* raw_full = bars + 2 * STAGES; // [STAGES] packed codes landed
@@ -518,6 +617,12 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const KParams p) {
             k_range(sp, kb0, kb1);
             const int a = it & 1;
             const uint32_t aph = (it >> 1) & 1;
+            constexpr int EPI_THREADS = SL::EPI_WARPS * 32;
+            if (p.epi.mode == EPI_STORE) {  // column terms of this tile, fetched under the tile's MMAs
+                epi_bar_sync(EPI_THREADS);  // every warp is done reading the previous tile's terms
+                stage_column_terms<BN, EPI_THREADS>(p, b, nt * BN, sp == 0, QUANT ? (int)threadIdx.x - 128 : (int)threadIdx.x, sCol, sCol + BN);
+                epi_bar_sync(EPI_THREADS);
+            }
             ptx::mbar_wait(&acc_full[a], aph);
             ptx::tc_fence_after();
             if (warp == 4 && lane == 0) trace_stamp(p, TR_ACC_READY);
@@ -538,10 +643,16 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const KParams p) {
                 uint32_t r[32];
                 ptx::tmem_ld32(taddr + c * 32, r);
                 ptx::tmem_ld_wait();
+                if (warp == 4 && lane == 0 && c == part) trace_stamp(p, TR_EPI_LD0);
                 float acc[32];
 #pragma unroll
                 for (int i = 0; i < 32; ++i) acc[i] = __uint_as_float(r[i]);
-                if (kb1 > kb0) epilogue_row32(p, acc, b, l, n0, sp == 0);
+                if (kb1 > kb0) {
+                    float* stg = sStg + (QUANT ? q : warp) * (STG_WARP_BYTES / 4);
+                    if (p.epi.mode != EPI_STORE || !epilogue_store_staged(p, acc, b, l0 + q * 32, lane, n0, sCol + c * 32, sCol + BN + c * 32, stg))
+                        epilogue_row32(p, acc, b, l, n0, sp == 0);
+                }
+                if (warp == 4 && lane == 0 && c == part) trace_stamp(p, TR_EPI_CHUNK0);
             }
             ptx::tc_fence_before();
             __syncwarp();
@@ -569,17 +680,19 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const KParams p) {
 // both CTAs, and both CTAs' epilogue warps arrive on the leader's acc_empty.
 constexpr int STAGES2 = 6;
 constexpr int STAGE2_BYTES = A_STAGE_BYTES + W_SUB_BYTES;  // 32 KB
-constexpr int SMEM2_BYTES = STAGES2 * STAGE2_BYTES + 512 + 1024;
+constexpr int SMEM2_BYTES = STAGES2 * STAGE2_BYTES + 8 * STG_WARP_BYTES + 2 * 256 * 4 + 512;
 
 __global__ void __launch_bounds__(NUM_THREADS, 1)
 gemm_tc2_kernel(const __grid_constant__ CUtensorMap tmA, const KParams p) {
     constexpr int BN = 256;
     constexpr int TMEM_COLS = 2 * BN;
-    extern __shared__ uint8_t smem_raw[];
-    uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
+    extern __shared__ __align__(1024) uint8_t smem[];
+    if (threadIdx.x == 0 && (ptx::smem_u32(smem) & 1023u) != 0) __trap();
     uint8_t* sA = smem;                            // [STAGES2][16 KB]
     uint8_t* sB = sA + STAGES2 * A_STAGE_BYTES;    // [STAGES2][16 KB]  this CTA's half of the weight tile
-    uint64_t* bars = reinterpret_cast<uint64_t*>(sB + STAGES2 * W_SUB_BYTES);
+    float* sStg = reinterpret_cast<float*>(sB + STAGES2 * W_SUB_BYTES);  // [8][32 x 32 fp32] epilogue transpose buffers
+    float* sCol = sStg + 8 * (STG_WARP_BYTES / 4);  // [2][256]: bias, gate of the current tile
+    uint64_t* bars = reinterpret_cast<uint64_t*>(sCol + 2 * 256);
     uint64_t* full = bars;                    // [S] local operands landed
     uint64_t* empty = bars + STAGES2;         // [S] MMAs reading this CTA's stage completed (multicast commit)
     uint64_t* peer_full = bars + 2 * STAGES2; // [S] leader only: CTA 1's stage landed
@@ -717,6 +830,11 @@ gemm_tc2_kernel(const __grid_constant__ CUtensorMap tmA, const KParams p) {
             k_range(sp, kb0, kb1);
             const int a = it & 1;
             const uint32_t aph = (it >> 1) & 1;
+            if (p.epi.mode == EPI_STORE) {
+                epi_bar_sync(256);
+                stage_column_terms<BN, 256>(p, b, nt * BN, sp == 0, (int)threadIdx.x, sCol, sCol + BN);
+                epi_bar_sync(256);
+            }
             ptx::mbar_wait(&acc_full[a], aph);
             ptx::tc_fence_after();
             const int l = l0 + q * 32 + lane;
@@ -739,7 +857,11 @@ gemm_tc2_kernel(const __grid_constant__ CUtensorMap tmA, const KParams p) {
                 float acc[32];
 #pragma unroll
                 for (int i = 0; i < 32; ++i) acc[i] = __uint_as_float(r[i]);
-                if (kb1 > kb0) epilogue_row32(p, acc, b, l, n0, sp == 0);
+                if (kb1 > kb0) {
+                    float* stg = sStg + warp * (STG_WARP_BYTES / 4);
+                    if (p.epi.mode != EPI_STORE || !epilogue_store_staged(p, acc, b, l0 + q * 32, lane, n0, sCol + c * 32, sCol + BN + c * 32, stg))
+                        epilogue_row32(p, acc, b, l, n0, sp == 0);
+                }
             }
             ptx::tc_fence_before();
             __syncwarp();
@@ -1029,7 +1151,6 @@ cudaError_t gemm_launch(const GemmProblem& g, cudaStream_t stream, bool simt) {
     // In-place accumulation (out += gate*acc + bias, the DiT residual updates) goes through red.global.add: no
     // read-modify-write latency in the epilogue, and it is what makes a K split legal.
     const bool accumulate = g.epi.mode == EPI_STORE && g.epi.out_f32 && g.epi.resid == g.epi.out_f32 && !g.epi.out_f16;
-    if (accumulate) kp.epi.atomic = 1;
     const int sms = device_sm_count();
     const int m_tiles = kp.B * kp.m_tiles_per_b;
     // tile shape: 128x256 halves the operand traffic per FLOP (L2 -> SM bandwidth is the limiter of the 128x128 tile);
@@ -1061,6 +1182,12 @@ cudaError_t gemm_launch(const GemmProblem& g, cudaStream_t stream, bool simt) {
     }
     if (sk > 1 && !accumulate) return cudaErrorInvalidValue;
     kp.split_k = std::min(sk, kp.kb_total);
+    // in-place accumulation always goes through red.add, split or not: fire-and-forget, where a read-add-write would put
+    // an L2 round trip per row group on the epilogue's critical path (trace: 8.0 k vs 2.2 k cycles per 32-column chunk)
+    if (accumulate) kp.epi.atomic = 1;
+    if (const char* fa = std::getenv("ACE_B200_GEMM_ATOMIC")) {  // tuning knob: 0 = plain read-add-write when K is not split
+        if (std::atoi(fa) == 0 && accumulate && kp.split_k == 1) kp.epi.atomic = 0;
+    }
     if (g.C != w.K) return cudaErrorInvalidValue;
 
     if (simt || gemm_force_simt()) {
@@ -1101,8 +1228,9 @@ cudaError_t gemm_launch(const GemmProblem& g, cudaStream_t stream, bool simt) {
             for (int c = 0; c < ctas; ++c)
                 for (int i = 0; i < TR_N; ++i) acc[i] += (double)(h[(size_t)c * TR_N + i] - h[(size_t)c * TR_N + TR_START]);
             std::fprintf(stderr, "[gemm trace] M=%d N=%d K=%d bn=%d sk=%d ctas=%d | cycles from CTA start (mean): setup %.0f first_full %.0f last_mma_issued %.0f "
-                                 "acc_ready(last tile) %.0f epi_done(last tile) %.0f end %.0f\n", M, N, K, bn, sk, ctas, acc[TR_SETUP] / ctas,
-                         acc[TR_FIRST_FULL] / ctas, acc[TR_LAST_MMA] / ctas, acc[TR_ACC_READY] / ctas, acc[TR_EPI_DONE] / ctas, acc[TR_END] / ctas);
+                                 "acc_ready(last tile) %.0f ld0 %.0f chunk0 %.0f epi_done(last tile) %.0f end %.0f\n", M, N, K, bn, sk, ctas, acc[TR_SETUP] / ctas,
+                         acc[TR_FIRST_FULL] / ctas, acc[TR_LAST_MMA] / ctas, acc[TR_ACC_READY] / ctas, acc[TR_EPI_LD0] / ctas, acc[TR_EPI_CHUNK0] / ctas,
+                         acc[TR_EPI_DONE] / ctas, acc[TR_END] / ctas);
         }
     } trace_dump{tracing, trace_buf, (int)(tiles < sms ? tiles : sms), stream, g.B * g.l_out, w.N, w.K * w.taps, bn256 ? 256 : 128, kp.split_k};
     if (pair) return launch_tc2(tm, kp, (int)(tiles < units ? tiles : units), stream);

@@ -242,6 +242,18 @@ class B200Bridge:
         self._ensure_ok(st, "ace_b200_generate_latents")
         return out
 
+    def vae_decode_time_split(self, latents_tfirst: np.ndarray, rank: int, world: int, halo: int = 16) -> np.ndarray:
+        """this rank's slice of a time-split decode of one clip (shard.time_split_plan): decodes the halo'd window and
+        returns only the core samples [(c1-c0)*hop, audio_channels]; stitch with shard.gather_time_slices."""
+        from . import shard
+        lat = _f32(latents_tfirst, 2)
+        w0, w1, c0, c1 = shard.time_split_plan(lat.shape[0], rank, world, halo)
+        if c1 <= c0:
+            return np.zeros((0, self.audio_channels), np.float32)
+        audio = self.vae_decode_tfirst(lat[w0:w1])
+        s0 = (c0 - w0) * self.hop_length
+        return np.ascontiguousarray(audio[s0:s0 + (c1 - c0) * self.hop_length])
+
     def vae_decode_batched(self, latents) -> np.ndarray:
         lat = _f32(latents, 3)
         B, T = int(lat.shape[0]), int(lat.shape[1])

@@ -31,6 +31,40 @@ def shard(arr: Optional[np.ndarray], rank: int, world: int) -> Optional[np.ndarr
     return np.ascontiguousarray(arr[rank::world])
 
 
+def time_split_plan(n_frames: int, rank: int, world: int, halo: int = 16):
+    """Time-split of ONE long clip's VAE decode: rank r decodes latent frames [w0, w1) = its core
+    [c0, c1) widened by `halo` frames per side (clamped to the clip, so the clip ends keep the reference's zero padding)
+    and keeps the core.  halo >= 10 covers the decoder's receptive field (conv1 +-3 frames, block-0 residual units
+    +-3.9, later blocks < 1, conv-transpose taps ~1.2: about 9.5 frames per side), so the stitched result equals the
+    un-split decode — the same argument that makes the reference's chunk 128 / overlap 32 tiling exact
+    (acestep_ggml.cpp:2114-2229).  Returns (w0, w1, c0, c1)."""
+    if world <= 0 or not (0 <= rank < world):
+        raise ValueError(f"bad rank/world {rank}/{world}")
+    c0 = rank * n_frames // world
+    c1 = (rank + 1) * n_frames // world
+    return max(0, c0 - halo), min(n_frames, c1 + halo), c0, c1
+
+
+def gather_time_slices(local_audio: np.ndarray, n_frames: int, hop: int, dist=None) -> Optional[np.ndarray]:
+    """concatenate the per-rank core slices [ (c1-c0)*hop, channels ] in rank order on rank 0 (the one exchange step)"""
+    if dist is None or dist.get_world_size() == 1:
+        return local_audio
+    import torch
+
+    world, rank = dist.get_world_size(), dist.get_rank()
+    lens = [((r + 1) * n_frames // world - r * n_frames // world) * hop for r in range(world)]
+    mx = max(lens)
+    pad = np.zeros((mx,) + tuple(local_audio.shape[1:]), dtype=local_audio.dtype)
+    pad[: local_audio.shape[0]] = local_audio
+    dev = torch.device("cuda", torch.cuda.current_device()) if dist.get_backend() == "nccl" else torch.device("cpu")
+    t = torch.from_numpy(pad).to(dev)
+    bufs = [torch.empty_like(t) for _ in range(world)] if rank == 0 else None
+    dist.gather(t, bufs, dst=0)
+    if rank != 0:
+        return None
+    return np.concatenate([bufs[r].cpu().numpy()[: lens[r]] for r in range(world)], axis=0)
+
+
 def gather_results(local: np.ndarray, n_songs: int, dist=None) -> Optional[np.ndarray]:
     """inverse of `shard`: rank 0 receives [n_songs, ...] in the original song order; other ranks get None.
     `dist` = an initialised torch.distributed module (None = single process)."""

@@ -102,6 +102,8 @@ attention_tc_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_consta
     __syncthreads();
     ptx::tc_fence_after();
     const uint32_t tmem_base = *tmem_slot;
+    ptx::pdl_wait();
+    ptx::pdl_launch();
 
     if (warp == 4) {
         // ===================== producer =====================
@@ -358,6 +360,8 @@ attention_tc8_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_const
     __syncthreads();
     ptx::tc_fence_after();
     const uint32_t tmem_base = *tmem_slot;
+    ptx::pdl_wait();
+    ptx::pdl_launch();
 
     if (warp == 8) {
         // ===================== producer =====================
@@ -604,9 +608,8 @@ cudaError_t launch_attention_tc(const __half* Q, long q_stride, const __half* K,
     AttnParams p{O, o_stride, key_mask, q_len, k_len, n_heads / n_kv_heads, window};
     dim3 grid((q_len + BQ - 1) / BQ, n_heads, B);
     const char* env = std::getenv("ACE_B200_ATTN");
-    if (env && std::string(env) == "tc4") attention_tc_kernel<<<grid, ATT_TC_THREADS, ATT_TC_SMEM, st>>>(tq, tk, tv, p);
-    else attention_tc8_kernel<<<grid, ATT8_THREADS, ATT_TC_SMEM, st>>>(tq, tk, tv, p);
-    return cudaGetLastError();
+    if (env && std::string(env) == "tc4") return launch_pdl(attention_tc_kernel, grid, dim3(ATT_TC_THREADS), (size_t)ATT_TC_SMEM, st, tq, tk, tv, p);
+    return launch_pdl(attention_tc8_kernel, grid, dim3(ATT8_THREADS), (size_t)ATT_TC_SMEM, st, tq, tk, tv, p);
 }
 
 }  // namespace ace

@@ -114,6 +114,8 @@ rmsnorm_mod_kernel(const float* __restrict__ x, const float* __restrict__ w, con
                    const float* __restrict__ shift, long mod_bstride, __half* __restrict__ y, long rows, int rows_per_b,
                    int H, float eps) {
     __shared__ float red[4];
+    asm volatile("griddepcontrol.wait;" ::: "memory");             // PDL: the residual stream comes from the previous GEMM
+    asm volatile("griddepcontrol.launch_dependents;" ::: "memory");
     const long row = blockIdx.x;
     const int tid = threadIdx.x;
     const float* xr = x + row * H;
@@ -341,7 +343,7 @@ void launch_rmsnorm_mod(const float* x, const float* w, const float* scale1, con
     note_launch();
     ProfScope prof_scope(PROF_ELEM, 0.0, 0.0, st);
     const long rows = (long)B * rows_per_b;
-    rmsnorm_mod_kernel<<<(unsigned)rows, 128, 0, st>>>(x, w, scale1, shift, mod_bstride, y, rows, rows_per_b, H, eps);
+    launch_pdl(rmsnorm_mod_kernel, dim3((unsigned)rows), dim3(128), 0, st, x, w, scale1, shift, mod_bstride, y, rows, rows_per_b, H, eps);
 }
 void launch_headnorm_rope(__half* buf, long row_stride, int col0, int n_heads, const float* w, const float2* rope_tab,
                           int B, int rows_per_b, float eps, cudaStream_t st) {

@@ -487,6 +487,8 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const KParams p) {
     __syncthreads();
     ptx::tc_fence_after();
     const uint32_t tmem_base = *tmem_slot;
+    ptx::pdl_wait();    // everything above overlapped the previous kernel's tail
+    ptx::pdl_launch();
     if (threadIdx.x == 0) trace_stamp(p, TR_SETUP);
 
     auto decode_tile_index = [&](int t, int& nt, int& sp, int& b, int& l0) {
@@ -730,6 +732,8 @@ gemm_tc2_kernel(const __grid_constant__ CUtensorMap tmA, const KParams p) {
     ptx::cluster_sync();
     ptx::tc_fence_after();
     const uint32_t tmem_base = *tmem_slot;
+    ptx::pdl_wait();
+    ptx::pdl_launch();
 
     auto decode_tile_index = [&](int t, int& nt, int& sp, int& b, int& l0) {
         const int mt = t % m_tiles;
@@ -1057,13 +1061,15 @@ cudaError_t launch_tc2(const CUtensorMap& tm, const KParams& kp, int clusters, c
     cfg.blockDim = dim3(NUM_THREADS);
     cfg.dynamicSmemBytes = SMEM2_BYTES;
     cfg.stream = stream;
-    cudaLaunchAttribute at[1];
+    cudaLaunchAttribute at[2];
     at[0].id = cudaLaunchAttributeClusterDimension;
     at[0].val.clusterDim.x = 2;
     at[0].val.clusterDim.y = 1;
     at[0].val.clusterDim.z = 1;
+    at[1].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+    at[1].val.programmaticStreamSerializationAllowed = 1;
     cfg.attrs = at;
-    cfg.numAttrs = 1;
+    cfg.numAttrs = pdl_enabled() ? 2 : 1;
     return cudaLaunchKernelEx(&cfg, gemm_tc2_kernel, tm, kp);
 }
 
@@ -1096,8 +1102,7 @@ cudaError_t launch_tc(const CUtensorMap& tm, const KParams& kp, int grid, cudaSt
         if (e != cudaSuccess) return e;
         attr_set = true;
     }
-    gemm_tc_kernel<BN, QUANT><<<grid, NUM_THREADS, SL::BYTES, stream>>>(tm, kp);
-    return cudaGetLastError();
+    return launch_pdl(gemm_tc_kernel<BN, QUANT>, dim3((unsigned)grid), dim3(NUM_THREADS), (size_t)SL::BYTES, stream, tm, kp);
 }
 
 }  // namespace

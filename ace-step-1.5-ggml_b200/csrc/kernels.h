@@ -37,6 +37,25 @@ struct ProfScope {
     }
 };
 
+// Launch with the programmatic-stream-serialization attribute (PDL): the kernel may start while its predecessor in the
+// stream drains; every kernel launched this way executes ptx::pdl_wait() before its first global access.
+// ACE_B200_PDL=0 turns the attribute off (plain stream order).
+bool pdl_enabled();
+template <typename... KArgs, typename... Args>
+inline cudaError_t launch_pdl(void (*kernel)(KArgs...), dim3 grid, dim3 block, size_t smem, cudaStream_t st, Args&&... args) {
+    cudaLaunchConfig_t cfg = {};
+    cfg.gridDim = grid;
+    cfg.blockDim = block;
+    cfg.dynamicSmemBytes = smem;
+    cfg.stream = st;
+    cudaLaunchAttribute at[1];
+    at[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+    at[0].val.programmaticStreamSerializationAllowed = 1;
+    cfg.attrs = at;
+    cfg.numAttrs = pdl_enabled() ? 1 : 0;
+    return cudaLaunchKernelEx(&cfg, kernel, static_cast<KArgs>(args)...);
+}
+
 // ---- DiT input side ------------------------------------------------------------------------------
 // x0[b, p, k*in_ch + c] = (c < ctx_dim ? context[b, 2p+k, c] : hidden[b, 2p+k, c-ctx_dim]), zero past T
 // reference: acestep_dit_model.cpp:1343-1377 (pack + zero pad to a patch multiple)

@@ -1,5 +1,6 @@
 // Per-kernel-family device timing behind kernels.h:prof_* (measurement aid for bench.py's roofline line).
 #include "kernels.h"
+#include <cstdlib>
 
 #include <mutex>
 #include <vector>
@@ -66,6 +67,16 @@ void prof_collect(ProfTotals& out) {
             out.launches[r.cat] += 1;
         }
     }
+}
+
+
+bool pdl_enabled() {
+    static int v = -1;
+    if (v < 0) {
+        const char* e = std::getenv("ACE_B200_PDL");
+        v = (e && e[0] == '0') ? 0 : 1;
+    }
+    return v == 1;
 }
 
 }  // namespace ace

@@ -237,6 +237,13 @@ __device__ __forceinline__ void umma_commit_2cta(uint64_t* bar, uint16_t cta_mas
                  : "memory");
 }
 
+// ---------------------------------------------------------------- programmatic dependent launch
+// pdl_wait: block until every kernel this one depends on has completed and flushed (no-op without the launch attribute).
+// pdl_launch: allow the next kernel in the stream to start its own prologue (barrier init, TMEM alloc, descriptor
+// prefetch) while this one is still running; it blocks in its pdl_wait before touching any global data.
+__device__ __forceinline__ void pdl_wait() { asm volatile("griddepcontrol.wait;" ::: "memory"); }
+__device__ __forceinline__ void pdl_launch() { asm volatile("griddepcontrol.launch_dependents;" ::: "memory"); }
+
 __device__ __forceinline__ bool elect_one() {
     uint32_t pred;
     asm volatile(

@@ -164,6 +164,21 @@ def test_vae_tiled_reference_policy_equals_untiled(br, root):
     assert metrics(b2[0], out)["rel_l2"] <= 1e-6
 
 
+@pytest.mark.parametrize("world", [2, 5])
+def test_vae_time_split_equals_unsplit(br, root, world):
+    """one clip decoded as `world` halo'd time slices (halo 16 >= receptive field) == the un-split decode"""
+    d = make_vae_dir(root)
+    br.load_vae(d)
+    lat = fx.vae_latents(fx.VAE_TOY, 150, seed=21)
+    full = br.vae_decode_tfirst(lat)
+    parts = [br.vae_decode_time_split(lat, r, world, halo=16) for r in range(world)]
+    st = np.concatenate(parts, axis=0)
+    assert st.shape == full.shape
+    assert metrics(st, full)["rel_l2"] <= 1e-6, metrics(st, full)
+    short = np.concatenate([br.vae_decode_time_split(lat, r, world, halo=2) for r in range(world)], axis=0)
+    assert metrics(short, full)["rel_l2"] > 1e-4  # a halo below the receptive field is visibly wrong: the test can fail
+
+
 def test_error_behaviour(br, root, tmp_path):
     """status codes and messages of the boundary (acestep_ggml.cpp:1318-1329, 666-680, 277-279)"""
     import ctypes

@@ -22,6 +22,18 @@ def test_partition_covers_every_song_once(n, world):
     assert sum(shard.evaluations_per_step(n, r, world, True) for r in range(world)) == 2 * n
 
 
+@pytest.mark.parametrize("T,world,halo", [(15000, 8, 16), (100, 3, 16), (7, 8, 16), (64, 4, 0)])
+def test_time_split_plan(T, world, halo):
+    cores = []
+    for r in range(world):
+        w0, w1, c0, c1 = shard.time_split_plan(T, r, world, halo)
+        assert 0 <= w0 <= c0 <= c1 <= w1 <= T
+        assert c0 - w0 == min(halo, c0) and w1 - c1 == min(halo, T - c1)  # halo only where the clip continues
+        cores.append((c0, c1))
+    assert cores[0][0] == 0 and cores[-1][1] == T
+    assert all(cores[i][1] == cores[i + 1][0] for i in range(world - 1))
+
+
 def _worker(rank, world, port, q):
     import torch.distributed as dist
     os.environ.update(MASTER_ADDR="127.0.0.1", MASTER_PORT=str(port), RANK=str(rank), WORLD_SIZE=str(world))
@@ -30,8 +42,14 @@ def _worker(rank, world, port, q):
     songs = np.arange(n * 6, dtype=np.float32).reshape(n, 3, 2)
     mine = shard.shard(songs, rank, world)
     out = shard.gather_results(mine * 2.0 + 1.0, n, dist)  # stand-in for the per-rank sampler + decode
+    # time split of one clip: every rank "decodes" (here: repeats x hop) its halo'd window and keeps the core
+    T, hop = 37, 3
+    lat = np.arange(T, dtype=np.float32)
+    w0, w1, c0, c1 = shard.time_split_plan(T, rank, world, 4)
+    win = np.repeat(lat[w0:w1], hop)[:, None]
+    stitched = shard.gather_time_slices(win[(c0 - w0) * hop:(c0 - w0) * hop + (c1 - c0) * hop], T, hop, dist)
     if rank == 0:
-        q.put(out)
+        q.put((out, stitched))
     dist.barrier()
     dist.destroy_process_group()
 
@@ -47,7 +65,8 @@ def test_two_rank_gloo_shard_and_gather():
     procs = [ctx.Process(target=_worker, args=(r, 2, port, q)) for r in range(2)]
     for p in procs:
         p.start()
-    out = q.get(timeout=120)
+    out, stitched = q.get(timeout=120)
+    assert np.array_equal(stitched[:, 0], np.repeat(np.arange(37, dtype=np.float32), 3))
     for p in procs:
         p.join(timeout=60)
         assert p.exitcode == 0

@@ -577,6 +577,274 @@ attention_tc8_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_const
     }
 }
 
+// ---------------------------------------------------------------- P in tensor memory, two interleaved tile chains
+// The 4-/8-warp kernels above run ONE dependency chain per CTA (S_j -> softmax_j -> P_j via smem -> PV_j -> pv_done ->
+// P_{j+1} may be written): ~3.4 k cycles per key tile against 512 cycles of MMA (ncu: tensor 30 %, issue 31 %, MUFU 33 %).
+// Here P_j is written back into the TMEM columns S_j came from (tcgen05.st, fp16 pairs) and the second MMA takes its A
+// operand from tensor memory.  With S double-buffered that makes P double-buffered too, and the single-thread issue order
+//     S_0 S_1 | PV_0 S_2 | PV_1 S_3 | ...         (tensor-core ops of one thread execute in order: S_{j+2} overwrites
+//                                                  buffer j&1 only after PV_j has read P_j from it)
+// leaves two independent chains (even / odd tiles) in flight: while the tensor core runs PV_j and S_{j+2}, the softmax warps
+// are already on tile j+1.  No P buffer in shared memory (96 KB per CTA), no generic->async proxy fence, no wait on the
+// previous PV before P is written; the only time the softmax warps wait for a PV is the rare lazy rescale of O.
+constexpr int P3_OFF_K = Q_BYTES;
+constexpr int P3_OFF_V = P3_OFF_K + 2 * (KV_TILE / 2) * 2;   // K stages: 2 x 16 KB
+constexpr int P3_OFF_BAR = P3_OFF_V + 2 * KV_TILE;           // V stages: 2 x 16 KB  -> 98 304
+constexpr int ATT_P3_SMEM = P3_OFF_BAR + 256;
+
+__global__ void __launch_bounds__(ATT_TC_THREADS, 2)
+attention_tcp_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__ CUtensorMap tmK,
+                     const __grid_constant__ CUtensorMap tmV, const AttnParams p) {
+    extern __shared__ __align__(1024) uint8_t smem[];
+    uint8_t* sQ = smem;
+    uint8_t* sK = smem + P3_OFF_K;
+    uint8_t* sV = smem + P3_OFF_V;
+    uint64_t* bars = reinterpret_cast<uint64_t*>(smem + P3_OFF_BAR);
+    uint64_t* q_full = bars;           // [1]
+    uint64_t* k_full = bars + 1;       // [2]
+    uint64_t* k_empty = bars + 3;      // [2]  S_j completed
+    uint64_t* v_full = bars + 5;       // [2]
+    uint64_t* v_empty = bars + 7;      // [2]  PV_j completed
+    uint64_t* s_ready = bars + 9;      // [2]
+    uint64_t* p_ready = bars + 11;     // [2]  4 softmax warps
+    uint64_t* pv_done = bars + 13;     // [2]  by tile parity
+    uint64_t* kmask = bars + 15;       // [4]  by tile index & 3
+    uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + 19);
+
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    const int q0 = blockIdx.x * BQ;
+    const int h = blockIdx.y, b = blockIdx.z;
+    const int hk = h / p.n_rep;
+
+    int kb_lo = 0, kb_hi = (p.k_len + BKV - 1) / BKV - 1;
+    if (p.window >= 0) {
+        kb_lo = max(0, (q0 - p.window) / BKV);
+        kb_hi = min(kb_hi, (min(q0 + BQ - 1, p.q_len - 1) + p.window) / BKV);
+    }
+    const int n_tiles = kb_hi - kb_lo + 1;
+
+    if (threadIdx.x == 0) {
+        if ((ptx::smem_u32(smem) & 1023u) != 0) __trap();
+        ptx::mbar_init(q_full, 1);
+        for (int s = 0; s < 2; ++s) {
+            ptx::mbar_init(&k_full[s], 1);
+            ptx::mbar_init(&k_empty[s], 1);
+            ptx::mbar_init(&v_full[s], 1);
+            ptx::mbar_init(&v_empty[s], 1);
+            ptx::mbar_init(&s_ready[s], 1);
+            ptx::mbar_init(&p_ready[s], 4);
+            ptx::mbar_init(&pv_done[s], 1);
+        }
+        ptx::fence_mbar_init();
+    }
+    if (warp == 5) ptx::tmem_alloc<TMEM_COLS>(tmem_slot);
+    if (warp == 4 && lane == 0) {
+        ptx::prefetch_tmap(&tmQ);
+        ptx::prefetch_tmap(&tmK);
+        ptx::prefetch_tmap(&tmV);
+    }
+    ptx::tc_fence_before();
+    __syncthreads();
+    ptx::tc_fence_after();
+    const uint32_t tmem_base = *tmem_slot;
+    ptx::pdl_wait();
+    ptx::pdl_launch();
+
+    if (warp == 4) {
+        // ===================== producer =====================
+        if (lane == 0) {
+            ptx::mbar_expect_tx(q_full, Q_BYTES);
+            ptx::tma_load_4d(sQ, &tmQ, q_full, 0, h, q0, b);
+            ptx::tma_load_4d(sQ + Q_BYTES / 2, &tmQ, q_full, 64, h, q0, b);
+        }
+        const int32_t* mb = p.key_mask ? p.key_mask + (long)b * p.k_len : nullptr;
+        for (int j = 0; j < n_tiles; ++j) {
+            const int s = j & 1;
+            const uint32_t ph = (j >> 1) & 1;
+            const int k0 = (kb_lo + j) * BKV;
+            const int ka = k0 + lane, kb2 = k0 + 32 + lane;
+            const bool ok_a = ka < p.k_len && (!mb || mb[ka] != 0);
+            const bool ok_b = kb2 < p.k_len && (!mb || mb[kb2] != 0);
+            const uint32_t lo = __ballot_sync(0xffffffffu, ok_a), hi = __ballot_sync(0xffffffffu, ok_b);
+            ptx::mbar_wait(&k_empty[s], ph ^ 1);
+            if (lane == 0) {
+                kmask[j & 3] = (uint64_t)lo | ((uint64_t)hi << 32);
+                ptx::mbar_expect_tx(&k_full[s], KV_TILE);
+                ptx::tma_load_4d(sK + s * KV_TILE, &tmK, &k_full[s], 0, hk, k0, b);
+                ptx::tma_load_4d(sK + s * KV_TILE + KV_TILE / 2, &tmK, &k_full[s], 64, hk, k0, b);
+            }
+            ptx::mbar_wait(&v_empty[s], ph ^ 1);
+            if (lane == 0) {
+                ptx::mbar_expect_tx(&v_full[s], KV_TILE);
+                ptx::tma_load_4d(sV + s * KV_TILE, &tmV, &v_full[s], 0, hk, k0, b);
+                ptx::tma_load_4d(sV + s * KV_TILE + KV_TILE / 2, &tmV, &v_full[s], 64, hk, k0, b);
+            }
+            __syncwarp();
+        }
+    } else if (warp == 5) {
+        // ===================== MMA issuer =====================
+        constexpr uint32_t idesc_s = ptx::umma_idesc_f16(BQ, BKV);
+        constexpr uint32_t idesc_o = ptx::umma_idesc_f16_bmn(BQ, HD);
+        const uint32_t q_addr = ptx::smem_u32(sQ);
+        auto issue_s = [&](int j) {  // S[j&1] = Q . K_j^T, then release the K stage
+            const int s = j & 1;
+            const uint32_t k_addr = ptx::smem_u32(sK + s * KV_TILE);
+#pragma unroll
+            for (int kk = 0; kk < HD / 16; ++kk) {
+                const uint64_t da = ptx::umma_desc_sw128(q_addr + (kk >> 2) * (Q_BYTES / 2) + (kk & 3) * 32);
+                const uint64_t db = ptx::umma_desc_sw128(k_addr + (kk >> 2) * (KV_TILE / 2) + (kk & 3) * 32);
+                ptx::umma_f16(tmem_base + (uint32_t)(s * BKV), da, db, idesc_s, kk > 0 ? 1u : 0u);
+            }
+            ptx::umma_commit(&s_ready[s]);
+            ptx::umma_commit(&k_empty[s]);
+        };
+        ptx::mbar_wait(q_full, 0);
+        ptx::mbar_wait(&k_full[0], 0);
+        ptx::tc_fence_after();
+        if (lane == 0) issue_s(0);
+        __syncwarp();
+        if (n_tiles > 1) {
+            ptx::mbar_wait(&k_full[1], 0);
+            ptx::tc_fence_after();
+            if (lane == 0) issue_s(1);
+            __syncwarp();
+        }
+        for (int j = 0; j < n_tiles; ++j) {
+            const int s = j & 1;
+            const uint32_t ph = (j >> 1) & 1;
+            ptx::mbar_wait(&p_ready[s], ph);
+            ptx::mbar_wait(&v_full[s], ph);
+            ptx::tc_fence_after();
+            if (lane == 0) {
+                const uint32_t v_addr = ptx::smem_u32(sV + s * KV_TILE);
+#pragma unroll
+                for (int kk = 0; kk < BKV / 16; ++kk) {  // A = P_j from TMEM: 16 keys = 8 packed columns per step
+                    const uint64_t db = ptx::umma_desc_mn_sw128(v_addr + kk * 2048, KV_TILE / 2, 1024);
+                    ptx::umma_f16_ts(tmem_base + 128u, tmem_base + (uint32_t)(s * BKV + kk * 8), db, idesc_o, (j > 0 || kk > 0) ? 1u : 0u);
+                }
+                ptx::umma_commit(&v_empty[s]);
+                ptx::umma_commit(&pv_done[s]);
+            }
+            __syncwarp();
+            if (j + 2 < n_tiles) {
+                ptx::mbar_wait(&k_full[s], ((j + 2) >> 1) & 1);
+                ptx::tc_fence_after();
+                if (lane == 0) issue_s(j + 2);
+                __syncwarp();
+            }
+        }
+    } else {
+        // ===================== softmax (warps 0..3): thread = query row = TMEM lane =====================
+        const int r = warp * 32 + lane;
+        const int q = q0 + r;
+        const uint32_t lane_addr = tmem_base + ((uint32_t)(warp * 32) << 16);
+        const float sc = 0.08838834764831845f * 1.4426950408889634f;
+        float m_used = -INFINITY, l = 0.f;
+        for (int j = 0; j < n_tiles; ++j) {
+            const int s = j & 1;
+            const int k0 = (kb_lo + j) * BKV;
+            ptx::mbar_wait(&s_ready[s], (j >> 1) & 1);
+            ptx::tc_fence_after();
+            uint32_t r0[32], r1[32];
+            ptx::tmem_ld32(lane_addr + (uint32_t)(s * BKV), r0);
+            ptx::tmem_ld32(lane_addr + (uint32_t)(s * BKV + 32), r1);
+            ptx::tmem_ld_wait();
+            const uint64_t km = kmask[j & 3];
+            float v[64];
+#pragma unroll
+            for (int i = 0; i < 32; ++i) {
+                v[i] = __uint_as_float(r0[i]) * sc;
+                v[32 + i] = __uint_as_float(r1[i]) * sc;
+            }
+            const bool band_edge = p.window >= 0 && ((q0 + BQ - 1) - k0 > p.window || (k0 + BKV - 1) - q0 > p.window);
+            if (km != ~0ull) {
+                const uint32_t klo = (uint32_t)km, khi = (uint32_t)(km >> 32);
+#pragma unroll
+                for (int i = 0; i < 32; ++i) {
+                    if (!((klo >> i) & 1u)) v[i] = -INFINITY;
+                    if (!((khi >> i) & 1u)) v[32 + i] = -INFINITY;
+                }
+            }
+            if (band_edge) {
+#pragma unroll
+                for (int i = 0; i < 64; ++i) {
+                    const int d = q - (k0 + i);
+                    if (d > p.window || d < -p.window) v[i] = -INFINITY;
+                }
+            }
+            float mx0 = v[0], mx1 = v[1], mx2 = v[2], mx3 = v[3];  // four short chains instead of one 64-long
+#pragma unroll
+            for (int i = 4; i < 64; i += 4) {
+                mx0 = fmaxf(mx0, v[i]); mx1 = fmaxf(mx1, v[i + 1]); mx2 = fmaxf(mx2, v[i + 2]); mx3 = fmaxf(mx3, v[i + 3]);
+            }
+            const float mx = fmaxf(fmaxf(mx0, mx1), fmaxf(mx2, mx3));
+            const float m_new = fmaxf(m_used, mx);
+            const bool need = m_new > m_used + RESCALE_THRESHOLD;
+            const float alpha = need ? ptx::ex2(m_used - m_new) : 1.0f;
+            if (need) m_used = m_new;
+            if (j > 0 && __any_sync(0xffffffffu, need)) {  // rare: O must be quiescent -> the previous PV has completed
+                ptx::mbar_wait(&pv_done[(j - 1) & 1], ((j - 1) >> 1) & 1);
+                ptx::tc_fence_after();
+#pragma unroll 1
+                for (int c = 0; c < 4; ++c) {
+                    uint32_t o[32];
+                    ptx::tmem_ld32(lane_addr + 128u + (uint32_t)(c * 32), o);
+                    ptx::tmem_ld_wait();
+#pragma unroll
+                    for (int i = 0; i < 32; ++i) o[i] = __float_as_uint(__uint_as_float(o[i]) * alpha);
+                    ptx::tmem_st32(lane_addr + 128u + (uint32_t)(c * 32), o);
+                }
+            }
+            const float msafe = (m_used == -INFINITY) ? 0.f : m_used;
+            uint32_t ph[32];
+            float ps0 = 0.f, ps1 = 0.f;
+#pragma unroll
+            for (int i = 0; i < 32; ++i) {
+                const float p0 = ptx::ex2(v[2 * i] - msafe), p1 = ptx::ex2(v[2 * i + 1] - msafe);
+                ps0 += p0;
+                ps1 += p1;
+                const __half2 hh = __floats2half2_rn(p0, p1);
+                ph[i] = *reinterpret_cast<const uint32_t*>(&hh);
+            }
+            l = l * alpha + (ps0 + ps1);
+            ptx::tmem_st32(lane_addr + (uint32_t)(s * BKV), ph);  // P_j over the first 32 columns of S_j
+            ptx::tmem_st_wait();
+            ptx::tc_fence_before();
+            __syncwarp();
+            if (lane == 0) ptx::mbar_arrive(&p_ready[s]);
+        }
+        // ---- finalise
+        ptx::mbar_wait(&pv_done[(n_tiles - 1) & 1], ((n_tiles - 1) >> 1) & 1);
+        ptx::tc_fence_after();
+        const float inv = l > 0.f ? 1.0f / l : 0.f;
+        __half* op = p.O + ((long)b * p.q_len + q) * p.o_stride + (long)h * HD;
+#pragma unroll 1
+        for (int c = 0; c < 4; ++c) {
+            uint32_t o[32];
+            ptx::tmem_ld32(lane_addr + 128u + (uint32_t)(c * 32), o);
+            ptx::tmem_ld_wait();
+            if (q < p.q_len) {
+                uint32_t w[16];
+#pragma unroll
+                for (int i = 0; i < 16; ++i) {
+                    const __half2 hh = __floats2half2_rn(__uint_as_float(o[2 * i]) * inv, __uint_as_float(o[2 * i + 1]) * inv);
+                    w[i] = *reinterpret_cast<const uint32_t*>(&hh);
+                }
+#pragma unroll
+                for (int i = 0; i < 4; ++i)
+                    *reinterpret_cast<uint4*>(op + c * 32 + i * 8) = make_uint4(w[4 * i], w[4 * i + 1], w[4 * i + 2], w[4 * i + 3]);
+            }
+        }
+    }
+
+    ptx::tc_fence_before();
+    __syncthreads();
+    if (warp == 5) {
+        ptx::tc_fence_after();
+        ptx::tmem_dealloc<TMEM_COLS>(tmem_base);
+    }
+}
+
 bool make_qkv_tmap(CUtensorMap* tm, const __half* base, long row_stride, int rows, int heads, int B, int box_rows) {
     const uint64_t dims[4] = {(uint64_t)HD, (uint64_t)heads, (uint64_t)rows, (uint64_t)B};
     const uint64_t strides[3] = {(uint64_t)HD * 2, (uint64_t)row_stride * 2, (uint64_t)rows * (uint64_t)row_stride * 2};
@@ -602,6 +870,7 @@ cudaError_t launch_attention_tc(const __half* Q, long q_stride, const __half* K,
     if (!attr) {
         cudaError_t e = cudaFuncSetAttribute(attention_tc_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, ATT_TC_SMEM);
         if (e == cudaSuccess) e = cudaFuncSetAttribute(attention_tc8_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, ATT_TC_SMEM);
+        if (e == cudaSuccess) e = cudaFuncSetAttribute(attention_tcp_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, ATT_P3_SMEM);
         if (e != cudaSuccess) return e;
         attr = true;
     }
@@ -609,7 +878,8 @@ cudaError_t launch_attention_tc(const __half* Q, long q_stride, const __half* K,
     dim3 grid((q_len + BQ - 1) / BQ, n_heads, B);
     const char* env = std::getenv("ACE_B200_ATTN");
     if (env && std::string(env) == "tc4") return launch_pdl(attention_tc_kernel, grid, dim3(ATT_TC_THREADS), (size_t)ATT_TC_SMEM, st, tq, tk, tv, p);
-    return launch_pdl(attention_tc8_kernel, grid, dim3(ATT8_THREADS), (size_t)ATT_TC_SMEM, st, tq, tk, tv, p);
+    if (env && std::string(env) == "tc8") return launch_pdl(attention_tc8_kernel, grid, dim3(ATT8_THREADS), (size_t)ATT_TC_SMEM, st, tq, tk, tv, p);
+    return launch_pdl(attention_tcp_kernel, grid, dim3(ATT_TC_THREADS), (size_t)ATT_P3_SMEM, st, tq, tk, tv, p);
 }
 
 }  // namespace ace

@@ -189,12 +189,12 @@ def attention_ref(Q, K, V, key_mask, n_heads, n_kv, window):
     return out.reshape(B, ql, n_heads * 128)
 
 
-@pytest.mark.parametrize("impl", ["tcgen05", "mma"])
+@pytest.mark.parametrize("impl", ["tcp", "tc4", "tc8", "mma"])  # P-in-TMEM (default) / smem-P 4 and 8 softmax warps / mma.sync
 @pytest.mark.parametrize("ql,kl,window,masked", [(64, 64, -1, False), (200, 200, -1, False), (375, 375, 128, False),
                                                    (130, 77, -1, True), (300, 300, 16, True), (1, 5, -1, False),
                                                    (700, 700, -1, False), (1000, 1000, 128, False), (300, 512, -1, True)])
 def test_attention(br, ql, kl, window, masked, impl, monkeypatch):
-    monkeypatch.setenv("ACE_B200_ATTN", "mma" if impl == "mma" else "tc")
+    monkeypatch.setenv("ACE_B200_ATTN", impl)
     g = np.random.default_rng(ql + kl)
     B, nh, nkv = 2, 4, 2
     Q = g.standard_normal((B, ql, nh * 128), dtype=np.float32)
@@ -264,10 +264,11 @@ def test_gemm_cta_pair_splitk_residual(br, monkeypatch):
         assert rel_err(o[0], ref) < 1e-4, sk
 
 
-def test_attention_lazy_rescale(br, monkeypatch):
+@pytest.mark.parametrize("impl", ["tcp", "tc4", "tc8"])
+def test_attention_lazy_rescale(br, impl, monkeypatch):
     """scores that grow by far more than 2^8 along the key axis force the tcgen05 kernel through its O / l rescale path
     (stale reference max) several times; the result must not depend on it"""
-    monkeypatch.setenv("ACE_B200_ATTN", "tc")
+    monkeypatch.setenv("ACE_B200_ATTN", impl)
     g = np.random.default_rng(3)
     B, nh, nkv, ql, kl = 1, 2, 1, 256, 640
     Q = g.standard_normal((B, ql, nh * 128), dtype=np.float32)

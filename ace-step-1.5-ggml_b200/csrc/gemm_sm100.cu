@@ -40,6 +40,7 @@ struct KParams {
     int  B, l_out, m_tiles_per_b;
     int  split_k;
     GemmEpilogue epi;
+    int  tma_reduce;             // accumulate epilogue goes out as TMA reduce-add tiles through tmOut
     long long* trace;            // debug (ACE_B200_GEMM_TRACE=1): per-CTA clock64 stamps of the pipeline phases, else null
 };
 
@@ -285,12 +286,16 @@ __device__ __forceinline__ void epilogue_row32(const KParams& p, const float (&a
 // tile (profiles/r1_gemm_trace_tr1.log) because each 16-byte piece was its own L2 transaction.  The residual read, the fp32
 // store / red.add and the fp16 (Snake / SiLU) store all happen in phase 2.  16-byte pieces are XOR-swizzled by the row so
 // both phases are bank-conflict free.  Returns false (nothing done) when the chunk does not qualify: caller falls back.
-__device__ __forceinline__ bool epilogue_store_staged(const KParams& p, const float (&acc)[32], int b, int l_base, int lane, int n0,
-                                                      const float* s_bias, const float* s_gate, float* stg) {
+__device__ __forceinline__ bool epilogue_store_staged(const KParams& p, const CUtensorMap* tmOut, const float (&acc)[32], int b, int l_base,
+                                                      int lane, int n0, const float* s_bias, const float* s_gate, float* stg) {
     const GemmEpilogue& e = p.epi;
     if (n0 + 32 > p.N) return false;                                     // warp-uniform
     const long col0 = (long)n0 + e.out_shift;
     if (((e.ld_out | col0 | e.out_bstride) & 3) != 0) return false;      // 16-byte alignment of every row segment
+    if (p.tma_reduce) {  // the previous chunk's reduce-add has finished READING this buffer (its global side may still run)
+        if (lane == 0) ptx::bulk_wait_read0();
+        __syncwarp();
+    }
     // per-column terms of this chunk, staged in smem once per tile (s_bias / s_gate point at this chunk's 32 entries)
     float4* s4 = reinterpret_cast<float4*>(stg);
 #pragma unroll
@@ -298,6 +303,18 @@ __device__ __forceinline__ bool epilogue_store_staged(const KParams& p, const fl
         const float4 bz = reinterpret_cast<const float4*>(s_bias)[i], gz = reinterpret_cast<const float4*>(s_gate)[i];
         s4[lane * 8 + (i ^ (lane & 7))] = make_float4((acc[4 * i] + bz.x) * gz.x, (acc[4 * i + 1] + bz.y) * gz.y,
                                                       (acc[4 * i + 2] + bz.z) * gz.z, (acc[4 * i + 3] + bz.w) * gz.w);
+    }
+    if (p.tma_reduce) {
+        // x += tile: one TMA reduce-add of the 32 x 32 fp32 box per chunk (the staging layout IS the 128-byte-swizzle box
+        // image); rows >= l_out and columns >= N are clipped by the tensor map.  Replaces 1024 per-element red ops whose
+        // per-SM issue rate (~2.2 k cycles per chunk) was the exposed part of the small-M GEMMs.
+        ptx::fence_proxy_async_smem();
+        __syncwarp();
+        if (lane == 0) {
+            ptx::tma_reduce_add_3d(tmOut, stg, n0, l_base, b);
+            ptx::bulk_commit();
+        }
+        return true;
     }
     __syncwarp();
     const int seg = lane & 7;                 // this lane's 4 columns: n0 + 4 seg ..
@@ -436,7 +453,7 @@ namespace {
 // ---------------------------------------------------------------- the tensor-core kernel
 template <int BN, bool QUANT>
 __global__ void __launch_bounds__(NUM_THREADS, 1)
-gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const KParams p) {
+gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmOut, const KParams p) {
     using SL = SmemLayout<BN, QUANT>;
     constexpr int STAGES = SL::STAGES;
     constexpr int SUBS = SL::SUBS;
@@ -651,7 +668,7 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const KParams p) {
                 for (int i = 0; i < 32; ++i) acc[i] = __uint_as_float(r[i]);
                 if (kb1 > kb0) {
                     float* stg = sStg + (QUANT ? q : warp) * (STG_WARP_BYTES / 4);
-                    if (p.epi.mode != EPI_STORE || !epilogue_store_staged(p, acc, b, l0 + q * 32, lane, n0, sCol + c * 32, sCol + BN + c * 32, stg))
+                    if (p.epi.mode != EPI_STORE || !epilogue_store_staged(p, &tmOut, acc, b, l0 + q * 32, lane, n0, sCol + c * 32, sCol + BN + c * 32, stg))
                         epilogue_row32(p, acc, b, l, n0, sp == 0);
                 }
                 if (warp == 4 && lane == 0 && c == part) trace_stamp(p, TR_EPI_CHUNK0);
@@ -663,6 +680,7 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const KParams p) {
         }
     }
 
+    if (p.tma_reduce) ptx::bulk_wait0();  // every reduce-add this thread issued has been performed
     ptx::tc_fence_before();
     __syncthreads();
     if (warp == 9) {
@@ -685,7 +703,7 @@ constexpr int STAGE2_BYTES = A_STAGE_BYTES + W_SUB_BYTES;  // 32 KB
 constexpr int SMEM2_BYTES = STAGES2 * STAGE2_BYTES + 8 * STG_WARP_BYTES + 2 * 256 * 4 + 512;
 
 __global__ void __launch_bounds__(NUM_THREADS, 1)
-gemm_tc2_kernel(const __grid_constant__ CUtensorMap tmA, const KParams p) {
+gemm_tc2_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmOut, const KParams p) {
     constexpr int BN = 256;
     constexpr int TMEM_COLS = 2 * BN;
     extern __shared__ __align__(1024) uint8_t smem[];
@@ -863,7 +881,7 @@ gemm_tc2_kernel(const __grid_constant__ CUtensorMap tmA, const KParams p) {
                 for (int i = 0; i < 32; ++i) acc[i] = __uint_as_float(r[i]);
                 if (kb1 > kb0) {
                     float* stg = sStg + warp * (STG_WARP_BYTES / 4);
-                    if (p.epi.mode != EPI_STORE || !epilogue_store_staged(p, acc, b, l0 + q * 32, lane, n0, sCol + c * 32, sCol + BN + c * 32, stg))
+                    if (p.epi.mode != EPI_STORE || !epilogue_store_staged(p, &tmOut, acc, b, l0 + q * 32, lane, n0, sCol + c * 32, sCol + BN + c * 32, stg))
                         epilogue_row32(p, acc, b, l, n0, sp == 0);
                 }
             }
@@ -873,6 +891,7 @@ gemm_tc2_kernel(const __grid_constant__ CUtensorMap tmA, const KParams p) {
         }
     }
 
+    if (p.tma_reduce) ptx::bulk_wait0();
     ptx::tc_fence_before();
     __syncthreads();
     ptx::cluster_sync();  // the peer's smem / barriers stay alive until every MMA and remote arrive has landed
@@ -1055,7 +1074,7 @@ int max_active_pairs() {
     return n;
 }
 
-cudaError_t launch_tc2(const CUtensorMap& tm, const KParams& kp, int clusters, cudaStream_t stream) {
+cudaError_t launch_tc2(const CUtensorMap& tm, const CUtensorMap& tmo, const KParams& kp, int clusters, cudaStream_t stream) {
     cudaLaunchConfig_t cfg = {};
     cfg.gridDim = dim3((unsigned)(2 * clusters));
     cfg.blockDim = dim3(NUM_THREADS);
@@ -1070,13 +1089,23 @@ cudaError_t launch_tc2(const CUtensorMap& tm, const KParams& kp, int clusters, c
     at[1].val.programmaticStreamSerializationAllowed = 1;
     cfg.attrs = at;
     cfg.numAttrs = pdl_enabled() ? 2 : 1;
-    return cudaLaunchKernelEx(&cfg, gemm_tc2_kernel, tm, kp);
+    return cudaLaunchKernelEx(&cfg, gemm_tc2_kernel, tm, tmo, kp);
 }
 
 }  // namespace
 
+static bool make_tmap_sw128(CUtensorMapDataType dt, CUtensorMap* tm, const void* base, int rank, const uint64_t* dims,
+                            const uint64_t* strides_bytes, const uint32_t* box);
 bool make_tmap_f16_sw128(CUtensorMap* tm, const void* base, int rank, const uint64_t* dims, const uint64_t* strides_bytes,
                          const uint32_t* box) {
+    return make_tmap_sw128(CU_TENSOR_MAP_DATA_TYPE_FLOAT16, tm, base, rank, dims, strides_bytes, box);
+}
+bool make_tmap_f32_sw128(CUtensorMap* tm, const void* base, int rank, const uint64_t* dims, const uint64_t* strides_bytes,
+                         const uint32_t* box) {
+    return make_tmap_sw128(CU_TENSOR_MAP_DATA_TYPE_FLOAT32, tm, base, rank, dims, strides_bytes, box);
+}
+static bool make_tmap_sw128(CUtensorMapDataType dt, CUtensorMap* tm, const void* base, int rank, const uint64_t* dims,
+                            const uint64_t* strides_bytes, const uint32_t* box) {
     PFN_encodeTiled enc = get_encode_fn();
     if (!enc || rank < 1 || rank > 5) return false;
     cuuint64_t d[5], s[4];
@@ -1087,14 +1116,14 @@ bool make_tmap_f16_sw128(CUtensorMap* tm, const void* base, int rank, const uint
         es[i] = 1;
         if (i > 0) s[i - 1] = strides_bytes[i - 1];
     }
-    return enc(tm, CU_TENSOR_MAP_DATA_TYPE_FLOAT16, (cuuint32_t)rank, const_cast<void*>(base), d, s, bx, es, CU_TENSOR_MAP_INTERLEAVE_NONE,
+    return enc(tm, dt, (cuuint32_t)rank, const_cast<void*>(base), d, s, bx, es, CU_TENSOR_MAP_INTERLEAVE_NONE,
                CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_128B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE) == CUDA_SUCCESS;
 }
 
 namespace {
 
 template <int BN, bool QUANT>
-cudaError_t launch_tc(const CUtensorMap& tm, const KParams& kp, int grid, cudaStream_t stream) {
+cudaError_t launch_tc(const CUtensorMap& tm, const CUtensorMap& tmo, const KParams& kp, int grid, cudaStream_t stream) {
     using SL = SmemLayout<BN, QUANT>;
     static bool attr_set = false;
     if (!attr_set) {
@@ -1102,7 +1131,7 @@ cudaError_t launch_tc(const CUtensorMap& tm, const KParams& kp, int grid, cudaSt
         if (e != cudaSuccess) return e;
         attr_set = true;
     }
-    return launch_pdl(gemm_tc_kernel<BN, QUANT>, dim3((unsigned)grid), dim3(NUM_THREADS), (size_t)SL::BYTES, stream, tm, kp);
+    return launch_pdl(gemm_tc_kernel<BN, QUANT>, dim3((unsigned)grid), dim3(NUM_THREADS), (size_t)SL::BYTES, stream, tm, tmo, kp);
 }
 
 }  // namespace
@@ -1133,6 +1162,8 @@ cudaError_t gemm_launch(const GemmProblem& g, cudaStream_t stream, bool simt) {
     ProfScope prof_scope(PROF_GEMM, 2.0 * g.B * (double)g.l_out * w.N * (double)w.K * w.taps,
                          (double)w.bytes + (double)g.B * g.L * g.C * 2.0, stream);
     KParams kp;
+    kp.tma_reduce = 0;
+    kp.trace = nullptr;
     kp.W = static_cast<const uint8_t*>(w.dev);
     kp.wtype = w.wtype;
     kp.tile_bytes = w.tile_bytes;
@@ -1238,11 +1269,26 @@ cudaError_t gemm_launch(const GemmProblem& g, cudaStream_t stream, bool simt) {
                          acc[TR_EPI_DONE] / ctas, acc[TR_END] / ctas);
         }
     } trace_dump{tracing, trace_buf, (int)(tiles < sms ? tiles : sms), stream, g.B * g.l_out, w.N, w.K * w.taps, bn256 ? 256 : 128, kp.split_k};
-    if (pair) return launch_tc2(tm, kp, (int)(tiles < units ? tiles : units), stream);
+    // accumulate epilogue as TMA reduce-add tiles (plain [B, l_out, N] fp32 output, no crop shift); ACE_B200_GEMM_TMARED=0 = red.add
+    CUtensorMap tmo = tm;
+    kp.tma_reduce = 0;
+    {
+        const char* ft = std::getenv("ACE_B200_GEMM_TMARED");
+        const bool want = !(ft && ft[0] == '0');
+        const GemmEpilogue& e = kp.epi;
+        if (want && e.atomic && e.mode == EPI_STORE && e.out_shift == 0 && e.out_valid == (long)g.l_out * e.ld_out && (e.ld_out & 3) == 0 &&
+            (e.out_bstride & 3) == 0 && (reinterpret_cast<uintptr_t>(e.out_f32) & 15) == 0) {
+            const uint64_t dims[3] = {(uint64_t)w.N, (uint64_t)g.l_out, (uint64_t)g.B};
+            const uint64_t strides[2] = {(uint64_t)e.ld_out * 4, (uint64_t)(g.B > 1 ? e.out_bstride : (long)g.l_out * e.ld_out) * 4};
+            const uint32_t box[3] = {32, 32, 1};
+            if (make_tmap_f32_sw128(&tmo, e.out_f32, 3, dims, strides, box)) kp.tma_reduce = 1;
+        }
+    }
+    if (pair) return launch_tc2(tm, tmo, kp, (int)(tiles < units ? tiles : units), stream);
     const int grid = (int)(tiles < sms ? tiles : sms);
     const bool quant = kp.wtype != W_F16;
-    if (bn256) return quant ? launch_tc<256, true>(tm, kp, grid, stream) : launch_tc<256, false>(tm, kp, grid, stream);
-    return quant ? launch_tc<128, true>(tm, kp, grid, stream) : launch_tc<128, false>(tm, kp, grid, stream);
+    if (bn256) return quant ? launch_tc<256, true>(tm, tmo, kp, grid, stream) : launch_tc<256, false>(tm, tmo, kp, grid, stream);
+    return quant ? launch_tc<128, true>(tm, tmo, kp, grid, stream) : launch_tc<128, false>(tm, tmo, kp, grid, stream);
 }
 
 }  // namespace ace

@@ -11,4 +11,8 @@ namespace ace {
 bool make_tmap_f16_sw128(CUtensorMap* tm, const void* base, int rank, const uint64_t* dims, const uint64_t* strides_bytes,
                          const uint32_t* box);
 
+// same for an fp32 tensor (used for the TMA reduce-add epilogue)
+bool make_tmap_f32_sw128(CUtensorMap* tm, const void* base, int rank, const uint64_t* dims, const uint64_t* strides_bytes,
+                         const uint32_t* box);
+
 }  // namespace ace

@@ -38,4 +38,17 @@ for (M, N, K, bn, sk) in [(750, 2048, 2048, 128, 1), (750, 2048, 2048, 128, 3), 
         os.environ["ACE_B200_GEMM_TRACE"] = "1"
         br.debug_gemm(A, W, w_type=0, N=N, resid=R)
         os.environ.pop("ACE_B200_GEMM_ATOMIC", None)
+# SwiGLU epilogue (gate_up projection): no residual, fp16 output of N/2 columns
+os.environ.pop("ACE_B200_GEMM_SPLITK", None)
+os.environ["ACE_B200_GEMM_BN"] = "256"
+A = g.standard_normal((1, 750, 2048), dtype=np.float32)
+W = g.standard_normal((12288, 2048), dtype=np.float32) * 0.02
+os.environ.pop("ACE_B200_GEMM_TRACE", None)
+best = 1e9
+for _ in range(4):
+    br.debug_gemm(A, W, w_type=0, N=12288, swiglu=True)
+    best = min(best, br.last_device_ms())
+print(f"SwiGLU M=750 N=12288 K=2048: {best * 1e3:.1f} us", flush=True)
+os.environ["ACE_B200_GEMM_TRACE"] = "1"
+br.debug_gemm(A, W, w_type=0, N=12288, swiglu=True)
 br.close()

@@ -41,6 +41,7 @@ struct KParams {
     int  split_k;
     GemmEpilogue epi;
     int  tma_reduce;             // accumulate epilogue goes out as TMA reduce-add tiles through tmOut
+    int  epi_variant;            // EPI_STORE fast path chosen on the host (store_variant()); 0 = generic code
     long long* trace;            // debug (ACE_B200_GEMM_TRACE=1): per-CTA clock64 stamps of the pipeline phases, else null
 };
 
@@ -155,14 +156,11 @@ __device__ __forceinline__ void decode_tile(int wtype, const uint8_t* raw, uint8
 }
 
 // ---------------------------------------------------------------- fused epilogue for 32 consecutive columns of one row
-// Snake: v + sin^2(a v) / b.  sin^2 has period pi: reduce with a two-term Cody-Waite split so the
-// MUFU sine only ever sees |r| <= pi/2 (abs error ~1e-6, independent of |a v|).
+// Snake: v + sin^2(a v) / b through the MUFU sine and its own range reduction: abs phase error ~|a v| * 1e-7 rad, far below
+// the fp16 rounding of the activation it produces.  5 instructions per element (a two-term Cody-Waite reduction in front of
+// the MUFU cost 10 and made the VAE epilogues issue-bound).
 __device__ __forceinline__ float snake_f(float v, float a, float inv_b) {
-    const float t = a * v;
-    const float k = rintf(t * 0.318309886183790672f);
-    float r = fmaf(-k, 3.140625f, t);
-    r = fmaf(-k, 9.67653589793e-4f, r);
-    const float s = __sinf(r);
+    const float s = __sinf(a * v);
     return fmaf(s * s, inv_b, v);
 }
 
@@ -279,6 +277,45 @@ __device__ __forceinline__ void epilogue_row32(const KParams& p, const float (&a
     }
 }
 
+// Specialised phase 2 of the staged EPI_STORE chunk for a chunk that lies entirely inside the output (no per-row predicates,
+// no run-time feature tests in the loop).  ncu on the last-level VAE convolutions showed the generic code at ~1200 warp
+// instructions per 32x32 chunk — issue-bound, 8.5 k cycles of epilogue per 128x128 tile against 3.6 k of MMAs
+// (profiles/r1_vae_conv_ncu.md); this form needs ~350.
+enum { SV_GENERIC = 0, SV_F16 = 1, SV_F16_SNAKE = 2, SV_F16_SILU = 3, SV_F32 = 4, SV_RES_F32_F16SNAKE = 5, SV_RES_F16SNAKE = 6, SV_F32_F16SNAKE = 7 };
+template <int ACT, bool RESID, bool OUT32, bool OUT16>
+__device__ __forceinline__ void staged_phase2_fast(const GemmEpilogue& e, const float4* s4, long off0, long step, int lane, int n0) {
+    const int seg = lane & 7, r0 = lane >> 3;
+    float4 res[8];
+    if (RESID) {
+#pragma unroll
+        for (int k = 0; k < 8; ++k) res[k] = __ldcg(reinterpret_cast<const float4*>(e.resid + off0 + k * step));
+    }
+    float4 sa = make_float4(0.f, 0.f, 0.f, 0.f), sb = sa;
+    if (ACT == 1) {
+        const int c0 = (e.snake_period ? (n0 % e.snake_period) : n0) + 4 * seg;
+        sa = __ldg(reinterpret_cast<const float4*>(e.snake_alpha + c0));
+        sb = __ldg(reinterpret_cast<const float4*>(e.snake_invbeta + c0));
+    }
+#pragma unroll
+    for (int k = 0; k < 8; ++k) {
+        const int rr = 4 * k + r0;
+        float4 t = s4[rr * 8 + (seg ^ (rr & 7))];
+        if (RESID) { t.x += res[k].x; t.y += res[k].y; t.z += res[k].z; t.w += res[k].w; }
+        if (OUT32) *reinterpret_cast<float4*>(e.out_f32 + off0 + k * step) = t;
+        if (OUT16) {
+            if (ACT == 1) {
+                t.x = snake_f(t.x, sa.x, sb.x); t.y = snake_f(t.y, sa.y, sb.y);
+                t.z = snake_f(t.z, sa.z, sb.z); t.w = snake_f(t.w, sa.w, sb.w);
+            } else if (ACT == 2) {
+                t.x = __fdividef(t.x, 1.0f + __expf(-t.x)); t.y = __fdividef(t.y, 1.0f + __expf(-t.y));
+                t.z = __fdividef(t.z, 1.0f + __expf(-t.z)); t.w = __fdividef(t.w, 1.0f + __expf(-t.w));
+            }
+            const __half2 h0 = __floats2half2_rn(t.x, t.y), h1 = __floats2half2_rn(t.z, t.w);
+            *reinterpret_cast<uint2*>(e.out_f16 + off0 + k * step) = make_uint2(h2u(h0), h2u(h1));
+        }
+    }
+}
+
 // EPI_STORE for a full 32-column chunk, through the warp's shared-memory transpose buffer.
 // Phase 1 (thread = accumulator row, as tcgen05.ld delivers it) applies the per-column terms (bias, AdaLN gate) and parks
 // the row in smem; phase 2 re-reads it so that 8 lanes cover one row's 128 contiguous bytes and one warp instruction
@@ -298,11 +335,19 @@ __device__ __forceinline__ bool epilogue_store_staged(const KParams& p, const CU
     }
     // per-column terms of this chunk, staged in smem once per tile (s_bias / s_gate point at this chunk's 32 entries)
     float4* s4 = reinterpret_cast<float4*>(stg);
+    if (e.gate) {
 #pragma unroll
-    for (int i = 0; i < 8; ++i) {
-        const float4 bz = reinterpret_cast<const float4*>(s_bias)[i], gz = reinterpret_cast<const float4*>(s_gate)[i];
-        s4[lane * 8 + (i ^ (lane & 7))] = make_float4((acc[4 * i] + bz.x) * gz.x, (acc[4 * i + 1] + bz.y) * gz.y,
-                                                      (acc[4 * i + 2] + bz.z) * gz.z, (acc[4 * i + 3] + bz.w) * gz.w);
+        for (int i = 0; i < 8; ++i) {
+            const float4 bz = reinterpret_cast<const float4*>(s_bias)[i], gz = reinterpret_cast<const float4*>(s_gate)[i];
+            s4[lane * 8 + (i ^ (lane & 7))] = make_float4((acc[4 * i] + bz.x) * gz.x, (acc[4 * i + 1] + bz.y) * gz.y,
+                                                          (acc[4 * i + 2] + bz.z) * gz.z, (acc[4 * i + 3] + bz.w) * gz.w);
+        }
+    } else {
+#pragma unroll
+        for (int i = 0; i < 8; ++i) {
+            const float4 bz = reinterpret_cast<const float4*>(s_bias)[i];
+            s4[lane * 8 + (i ^ (lane & 7))] = make_float4(acc[4 * i] + bz.x, acc[4 * i + 1] + bz.y, acc[4 * i + 2] + bz.z, acc[4 * i + 3] + bz.w);
+        }
     }
     if (p.tma_reduce) {
         // x += tile: one TMA reduce-add of the 32 x 32 fp32 box per chunk (the staging layout IS the 128-byte-swizzle box
@@ -317,6 +362,25 @@ __device__ __forceinline__ bool epilogue_store_staged(const KParams& p, const CU
         return true;
     }
     __syncwarp();
+    if (p.epi_variant != SV_GENERIC) {
+        // whole chunk inside the output?  (rows ascend with l, so the first and the last row bound the flat range)
+        const long first = (long)l_base * e.ld_out + col0, last = first + 31 * e.ld_out;
+        if (l_base + 32 <= p.l_out && first >= 0 && last + 32 <= e.out_valid) {
+            const long off0 = (long)b * e.out_bstride + first + (long)(lane >> 3) * e.ld_out + 4 * (lane & 7);
+            const long step = 4 * e.ld_out;
+            switch (p.epi_variant) {
+                case SV_F16:              staged_phase2_fast<0, false, false, true>(e, s4, off0, step, lane, n0); break;
+                case SV_F16_SNAKE:        staged_phase2_fast<1, false, false, true>(e, s4, off0, step, lane, n0); break;
+                case SV_F16_SILU:         staged_phase2_fast<2, false, false, true>(e, s4, off0, step, lane, n0); break;
+                case SV_F32:              staged_phase2_fast<0, false, true, false>(e, s4, off0, step, lane, n0); break;
+                case SV_RES_F32_F16SNAKE: staged_phase2_fast<1, true, true, true>(e, s4, off0, step, lane, n0); break;
+                case SV_RES_F16SNAKE:     staged_phase2_fast<1, true, false, true>(e, s4, off0, step, lane, n0); break;
+                default:                  staged_phase2_fast<1, false, true, true>(e, s4, off0, step, lane, n0); break;
+            }
+            __syncwarp();  // buffer is reused by the next chunk
+            return true;
+        }
+    }
     const int seg = lane & 7;                 // this lane's 4 columns: n0 + 4 seg ..
     long off[8];
     bool ok[8];
@@ -523,76 +587,88 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
 
     if (warp == 8) {
         // ===================== TMA producer =====================
+        // One thread; all ring / tap / weight-pointer state advances incrementally (a division and two 64-bit multiplies per
+        // k-block were most of this loop's latency).
         if (lane == 0) {
-            uint32_t g = 0;
+            uint32_t s = 0, ph = 0;
+            const size_t sub_stride = (size_t)p.kb_total * (QUANT ? (size_t)p.tile_bytes : (size_t)W_SUB_BYTES);
             for (int t = blockIdx.x; t < total_tiles; t += gridDim.x) {
                 int nt, sp, b, l0, kb0, kb1;
                 decode_tile_index(t, nt, sp, b, l0);
                 k_range(sp, kb0, kb1);
                 const int subs_valid = min(SUBS, p.n_tiles128 - nt * SUBS);
-                for (int kb = kb0; kb < kb1; ++kb, ++g) {
-                    const int s = g % STAGES;
-                    const uint32_t ph = (g / STAGES) & 1;
-                    const int tap = kb / p.kb_per_tap;
-                    const int c0 = (kb - tap * p.kb_per_tap) * BK;
-                    const int row = l0 + tap * p.tap_stride + p.tap_offset;
+                int tap = kb0 / p.kb_per_tap;
+                int kc = kb0 - tap * p.kb_per_tap;
+                int row = l0 + tap * p.tap_stride + p.tap_offset;
+                const uint8_t* wptr = p.W + (size_t)(nt * SUBS) * sub_stride + (size_t)kb0 * (QUANT ? (size_t)p.tile_bytes : (size_t)W_SUB_BYTES);
+                for (int kb = kb0; kb < kb1; ++kb) {
                     ptx::mbar_wait(&empty[s], ph ^ 1);
                     if (QUANT) {
                         ptx::mbar_expect_tx(&full[s], A_STAGE_BYTES);
-                        ptx::tma_load_3d(sA + s * A_STAGE_BYTES, &tmA, &full[s], c0, row, b);
+                        ptx::tma_load_3d(sA + s * A_STAGE_BYTES, &tmA, &full[s], kc * BK, row, b);
                         ptx::mbar_wait(&raw_empty[s], ph ^ 1);
                         ptx::mbar_expect_tx(&raw_full[s], (uint32_t)(subs_valid * p.tile_bytes));
-                        for (int sub = 0; sub < subs_valid; ++sub) {
-                            const size_t off = ((size_t)(nt * SUBS + sub) * p.kb_total + kb) * p.tile_bytes;
-                            ptx::bulk_load(sR + s * SL::RAW_STAGE + sub * RAW_MAX_BYTES, p.W + off, p.tile_bytes, &raw_full[s]);
-                        }
+                        for (int sub = 0; sub < subs_valid; ++sub)
+                            ptx::bulk_load(sR + s * SL::RAW_STAGE + sub * RAW_MAX_BYTES, wptr + sub * sub_stride, p.tile_bytes, &raw_full[s]);
+                        wptr += p.tile_bytes;
                     } else {
                         ptx::mbar_expect_tx(&full[s], A_STAGE_BYTES + subs_valid * W_SUB_BYTES);
-                        ptx::tma_load_3d(sA + s * A_STAGE_BYTES, &tmA, &full[s], c0, row, b);
-                        for (int sub = 0; sub < subs_valid; ++sub) {
-                            const size_t off = ((size_t)(nt * SUBS + sub) * p.kb_total + kb) * W_SUB_BYTES;
-                            ptx::bulk_load(sB + s * SL::B_STAGE + sub * W_SUB_BYTES, p.W + off, W_SUB_BYTES, &full[s]);
-                        }
+                        ptx::tma_load_3d(sA + s * A_STAGE_BYTES, &tmA, &full[s], kc * BK, row, b);
+                        for (int sub = 0; sub < subs_valid; ++sub)
+                            ptx::bulk_load(sB + s * SL::B_STAGE + sub * W_SUB_BYTES, wptr + sub * sub_stride, W_SUB_BYTES, &full[s]);
+                        wptr += W_SUB_BYTES;
+                    }
+                    if (++kc == p.kb_per_tap) {
+                        kc = 0;
+                        row += p.tap_stride;
+                    }
+                    if (++s == (uint32_t)STAGES) {
+                        s = 0;
+                        ph ^= 1;
                     }
                 }
             }
         }
     } else if (warp == 9) {
         // ===================== MMA issuer =====================
-        constexpr uint32_t idesc = ptx::umma_idesc_f16(BM, BN);
-        uint32_t g = 0;
-        int it = 0;
-        for (int t = blockIdx.x; t < total_tiles; t += gridDim.x, ++it) {
-            int nt, sp, b, l0, kb0, kb1;
-            decode_tile_index(t, nt, sp, b, l0);
-            k_range(sp, kb0, kb1);
-            const int a = it & 1;
-            const uint32_t aph = (it >> 1) & 1;
-            ptx::mbar_wait(&acc_empty[a], aph ^ 1);
-            ptx::tc_fence_after();
-            const uint32_t d_tmem = tmem_base + (uint32_t)(a * BN);
-            for (int kb = kb0; kb < kb1; ++kb, ++g) {
-                const int s = g % STAGES;
-                const uint32_t ph = (g / STAGES) & 1;
-                ptx::mbar_wait(&full[s], ph);
+        // ONE thread runs the whole loop (no per-k-block warp reconvergence / elect), descriptors advance by adding to the
+        // 14-bit start-address field: ncu showed this warp instruction-latency bound at ~745 cycles per k-block of four
+        // N=128 MMAs whose tensor-pipe time is 256 (profiles/r1_vae_conv_ncu.md); a bare issue loop reaches 84 cycles/MMA.
+        if (lane == 0) {
+            constexpr uint32_t idesc = ptx::umma_idesc_f16(BM, BN);
+            const uint64_t desc_a0 = ptx::umma_desc_sw128(ptx::smem_u32(sA)), desc_b0 = ptx::umma_desc_sw128(ptx::smem_u32(sB));
+            uint32_t s = 0, ph = 0;
+            bool first = true;
+            int it = 0;
+            for (int t = blockIdx.x; t < total_tiles; t += gridDim.x, ++it) {
+                int nt, sp, b, l0, kb0, kb1;
+                decode_tile_index(t, nt, sp, b, l0);
+                k_range(sp, kb0, kb1);
+                const int a = it & 1;
+                const uint32_t aph = (it >> 1) & 1;
+                ptx::mbar_wait(&acc_empty[a], aph ^ 1);
                 ptx::tc_fence_after();
-                if (lane == 0) {
-                    if (g == 0) trace_stamp(p, TR_FIRST_FULL);
-                    const uint32_t a_addr = ptx::smem_u32(sA + s * A_STAGE_BYTES);
-                    const uint32_t b_addr = ptx::smem_u32(sB + s * SL::B_STAGE);
-#pragma unroll
-                    for (int k = 0; k < BK / 16; ++k) {
-                        const uint64_t da = ptx::umma_desc_sw128(a_addr + k * 32);
-                        const uint64_t db = ptx::umma_desc_sw128(b_addr + k * 32);
-                        ptx::umma_f16(d_tmem, da, db, idesc, (kb > kb0 || k > 0) ? 1u : 0u);
+                const uint32_t d_tmem = tmem_base + (uint32_t)(a * BN);
+                uint32_t acc_flag = 0;
+                for (int kb = kb0; kb < kb1; ++kb) {
+                    ptx::mbar_wait(&full[s], ph);
+                    ptx::tc_fence_after();
+                    if (first) {
+                        trace_stamp(p, TR_FIRST_FULL);
+                        first = false;
                     }
+                    const uint64_t da = desc_a0 + (uint64_t)(s * (A_STAGE_BYTES >> 4)), db = desc_b0 + (uint64_t)(s * (SL::B_STAGE >> 4));
+#pragma unroll
+                    for (int k = 0; k < BK / 16; ++k) ptx::umma_f16(d_tmem, da + 2 * k, db + 2 * k, idesc, k > 0 ? 1u : acc_flag);
+                    acc_flag = 1;
                     ptx::umma_commit(&empty[s]);
-                    if (kb == kb1 - 1) {
-                        ptx::umma_commit(&acc_full[a]);
-                        trace_stamp(p, TR_LAST_MMA);
+                    if (++s == (uint32_t)STAGES) {
+                        s = 0;
+                        ph ^= 1;
                     }
                 }
-                __syncwarp();
+                ptx::umma_commit(&acc_full[a]);
+                trace_stamp(p, TR_LAST_MMA);
             }
         }
     } else if (QUANT && warp < 4) {
@@ -769,74 +845,83 @@ gemm_tc2_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__
     if (warp == 8) {
         // ===================== TMA producer (both CTAs) =====================
         if (lane == 0) {
-            uint32_t g = 0;
+            uint32_t s = 0, ph = 0;
+            const size_t sub_stride = (size_t)p.kb_total * W_SUB_BYTES;
             for (int t = cluster_id; t < total_tiles; t += n_clusters) {
                 int nt, sp, b, l0, kb0, kb1;
                 decode_tile_index(t, nt, sp, b, l0);
                 k_range(sp, kb0, kb1);
-                for (int kb = kb0; kb < kb1; ++kb, ++g) {
-                    const int s = g % STAGES2;
-                    const uint32_t ph = (g / STAGES2) & 1;
-                    const int tap = kb / p.kb_per_tap;
-                    const int c0 = (kb - tap * p.kb_per_tap) * BK;
-                    const int row = l0 + tap * p.tap_stride + p.tap_offset;
+                int tap = kb0 / p.kb_per_tap;
+                int kc = kb0 - tap * p.kb_per_tap;
+                int row = l0 + tap * p.tap_stride + p.tap_offset;
+                const uint8_t* wptr = p.W + (size_t)(nt * 2 + (int)rank) * sub_stride + (size_t)kb0 * W_SUB_BYTES;
+                for (int kb = kb0; kb < kb1; ++kb) {
                     ptx::mbar_wait(&empty[s], ph ^ 1);
                     ptx::mbar_expect_tx(&full[s], STAGE2_BYTES);
-                    ptx::tma_load_3d(sA + s * A_STAGE_BYTES, &tmA, &full[s], c0, row, b);
-                    const size_t off = ((size_t)(nt * 2 + (int)rank) * p.kb_total + kb) * W_SUB_BYTES;
-                    ptx::bulk_load(sB + s * W_SUB_BYTES, p.W + off, W_SUB_BYTES, &full[s]);
+                    ptx::tma_load_3d(sA + s * A_STAGE_BYTES, &tmA, &full[s], kc * BK, row, b);
+                    ptx::bulk_load(sB + s * W_SUB_BYTES, wptr, W_SUB_BYTES, &full[s]);
+                    wptr += W_SUB_BYTES;
+                    if (++kc == p.kb_per_tap) {
+                        kc = 0;
+                        row += p.tap_stride;
+                    }
+                    if (++s == (uint32_t)STAGES2) {
+                        s = 0;
+                        ph ^= 1;
+                    }
                 }
             }
         }
     } else if (warp == 9) {
         if (rank == 0) {
-            // ===================== MMA issuer (leader CTA) =====================
-            constexpr uint32_t idesc = ptx::umma_idesc_f16(2 * BM, BN);
-            uint32_t g = 0;
-            int it = 0;
-            for (int t = cluster_id; t < total_tiles; t += n_clusters, ++it) {
-                int nt, sp, b, l0, kb0, kb1;
-                decode_tile_index(t, nt, sp, b, l0);
-                k_range(sp, kb0, kb1);
-                const int a = it & 1;
-                const uint32_t aph = (it >> 1) & 1;
-                ptx::mbar_wait(&acc_empty[a], aph ^ 1);
-                ptx::tc_fence_after();
-                const uint32_t d_tmem = tmem_base + (uint32_t)(a * BN);
-                for (int kb = kb0; kb < kb1; ++kb, ++g) {
-                    const int s = g % STAGES2;
-                    const uint32_t ph = (g / STAGES2) & 1;
-                    ptx::mbar_wait(&full[s], ph);
-                    ptx::mbar_wait(&peer_full[s], ph);
+            // ===================== MMA issuer (leader CTA), one thread =====================
+            if (lane == 0) {
+                constexpr uint32_t idesc = ptx::umma_idesc_f16(2 * BM, BN);
+                const uint64_t desc_a0 = ptx::umma_desc_sw128(ptx::smem_u32(sA)), desc_b0 = ptx::umma_desc_sw128(ptx::smem_u32(sB));
+                uint32_t s = 0, ph = 0;
+                int it = 0;
+                for (int t = cluster_id; t < total_tiles; t += n_clusters, ++it) {
+                    int nt, sp, b, l0, kb0, kb1;
+                    decode_tile_index(t, nt, sp, b, l0);
+                    k_range(sp, kb0, kb1);
+                    const int a = it & 1;
+                    const uint32_t aph = (it >> 1) & 1;
+                    ptx::mbar_wait(&acc_empty[a], aph ^ 1);
                     ptx::tc_fence_after();
-                    if (lane == 0) {
-                        const uint32_t a_addr = ptx::smem_u32(sA + s * A_STAGE_BYTES);
-                        const uint32_t b_addr = ptx::smem_u32(sB + s * W_SUB_BYTES);
+                    const uint32_t d_tmem = tmem_base + (uint32_t)(a * BN);
+                    uint32_t acc_flag = 0;
+                    for (int kb = kb0; kb < kb1; ++kb) {
+                        ptx::mbar_wait(&full[s], ph);
+                        ptx::mbar_wait(&peer_full[s], ph);
+                        ptx::tc_fence_after();
+                        const uint64_t da = desc_a0 + (uint64_t)(s * (A_STAGE_BYTES >> 4)), db = desc_b0 + (uint64_t)(s * (W_SUB_BYTES >> 4));
 #pragma unroll
-                        for (int k = 0; k < BK / 16; ++k) {
-                            const uint64_t da = ptx::umma_desc_sw128(a_addr + k * 32);
-                            const uint64_t db = ptx::umma_desc_sw128(b_addr + k * 32);
-                            ptx::umma_f16_2cta(d_tmem, da, db, idesc, (kb > kb0 || k > 0) ? 1u : 0u);
-                        }
+                        for (int k = 0; k < BK / 16; ++k) ptx::umma_f16_2cta(d_tmem, da + 2 * k, db + 2 * k, idesc, k > 0 ? 1u : acc_flag);
+                        acc_flag = 1;
                         ptx::umma_commit_2cta(&empty[s], 3);
-                        if (kb == kb1 - 1) ptx::umma_commit_2cta(&acc_full[a], 3);
+                        if (++s == (uint32_t)STAGES2) {
+                            s = 0;
+                            ph ^= 1;
+                        }
                     }
-                    __syncwarp();
+                    ptx::umma_commit_2cta(&acc_full[a], 3);
                 }
             }
         } else {
             // ===================== relay (CTA 1): local "stage landed" -> leader's peer_full =====================
             if (lane == 0) {
-                uint32_t g = 0;
+                uint32_t s = 0, ph = 0;
                 for (int t = cluster_id; t < total_tiles; t += n_clusters) {
                     int nt, sp, b, l0, kb0, kb1;
                     decode_tile_index(t, nt, sp, b, l0);
                     k_range(sp, kb0, kb1);
-                    for (int kb = kb0; kb < kb1; ++kb, ++g) {
-                        const int s = g % STAGES2;
-                        const uint32_t ph = (g / STAGES2) & 1;
+                    for (int kb = kb0; kb < kb1; ++kb) {
                         ptx::mbar_wait(&full[s], ph);
                         ptx::mbar_arrive_cluster(ptx::mapa(&peer_full[s], 0));
+                        if (++s == (uint32_t)STAGES2) {
+                            s = 0;
+                            ph ^= 1;
+                        }
                     }
                 }
             }
@@ -1184,6 +1269,20 @@ cudaError_t gemm_launch(const GemmProblem& g, cudaStream_t stream, bool simt) {
     kp.m_tiles_per_b = (g.l_out + BM - 1) / BM;
     kp.epi = g.epi;
     if (kp.epi.out_valid == 0) kp.epi.out_valid = (long)g.l_out * kp.epi.ld_out;
+    {  // specialised store path of the staged epilogue (exact feature set only; anything else runs the generic code)
+        const GemmEpilogue& e = kp.epi;
+        int v = SV_GENERIC;
+        const bool snake = e.snake_alpha != nullptr, plain = e.mode == EPI_STORE && !e.atomic && !e.gate && e.ld_out > 0;
+        if (plain && !e.resid) {
+            if (e.out_f16 && !e.out_f32) v = snake ? SV_F16_SNAKE : (e.silu_f16 ? SV_F16_SILU : SV_F16);
+            else if (e.out_f32 && !e.out_f16) v = SV_F32;
+            else if (e.out_f32 && e.out_f16 && snake) v = SV_F32_F16SNAKE;
+        } else if (plain && e.resid && e.out_f16 && snake) {
+            v = e.out_f32 ? SV_RES_F32_F16SNAKE : SV_RES_F16SNAKE;
+        }
+        if (const char* ev = std::getenv("ACE_B200_GEMM_EPIFAST")) if (std::atoi(ev) == 0) v = SV_GENERIC;
+        kp.epi_variant = v;
+    }
     // In-place accumulation (out += gate*acc + bias, the DiT residual updates) goes through red.global.add: no
     // read-modify-write latency in the epilogue, and it is what makes a K split legal.
     const bool accumulate = g.epi.mode == EPI_STORE && g.epi.out_f32 && g.epi.resid == g.epi.out_f32 && !g.epi.out_f16;

@@ -133,6 +133,24 @@ def measured_peaks():
         return {"hbm_gbs": 6650.0, "bf16_tflops": 1590.0, "bf16_tflops_sustained": 1400.0}, "fallback"
 
 
+_REAL_STDOUT = None
+
+
+def guard_stdout():
+    """stdout carries exactly ONE JSON line: everything libraries print (NCCL's version banner, torchrun notes) goes to stderr."""
+    global _REAL_STDOUT
+    if _REAL_STDOUT is None:
+        sys.stdout.flush()
+        _REAL_STDOUT = os.dup(1)
+        os.dup2(2, 1)
+
+
+def emit(line):
+    sys.stdout.flush()
+    data = (json.dumps(line) + "\n").encode()
+    os.write(_REAL_STDOUT if _REAL_STDOUT is not None else 1, data)
+
+
 def dist_setup(n_gpus):
     world = int(os.environ.get("WORLD_SIZE", "1"))
     rank = int(os.environ.get("RANK", "0"))
@@ -153,7 +171,7 @@ def run_reference_arm(a, world, rank):
         return
     from oracle import refbridge
     if not refbridge.ref_available():
-        print(json.dumps({"impl": "reference", "unavailable": "oracle/_ref not built (needs /root/reference at build time)"}))
+        emit({"impl": "reference", "unavailable": "oracle/_ref not built (needs /root/reference at build time)"})
         return
     d = ensure_dit_fixture()
     noise, ctx, enc = synth_inputs(T_FRAMES, ENC_LEN)
@@ -176,7 +194,7 @@ def run_reference_arm(a, world, rank):
             "data": "synthetic", "config": {"workload": WORKLOAD, "timing": "wall clock around each reference call"},
             "cpu_baseline": {"value": value, "unit": UNIT, "cores": cores, "kind": "reference", "sample": sample},
             "e2e": {"value": value, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}, "gpu_launches": 0}
-    print(json.dumps(line))
+    emit(line)
 
 
 def main():
@@ -188,6 +206,7 @@ def main():
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-song", action="store_true", help="skip the 240 s song (DiT + VAE) measurement")
     a = ap.parse_args()
+    guard_stdout()
     a.warmup = max(a.warmup, 3) if a.impl == "b200" else a.warmup
     world, rank, local, dist = dist_setup(a.gpus)
 
@@ -296,7 +315,7 @@ def main():
                 line["song_240s"] = {"error": str(ex)[:200]}
         if world == 1 and not a.no_cpu_baseline:
             line["cpu_baseline"] = cpu_baseline(d, noise, ctx, enc)
-        print(json.dumps(line))
+        emit(line)
     br.close()
     if dist:
         dist.barrier()

@@ -1,0 +1,78 @@
+// Raw tcgen05.mma (kind::f16, cta_group::1, M=128, K=16) rate per SM: one thread issues a long chain of MMAs on operands that
+// already sit in shared memory (K-major, 128-byte swizzle; contents irrelevant), no loads, no epilogue.
+//   variant 0: every MMA accumulates into the same TMEM tile          variant 1: two accumulators alternate
+//   variant 2: operands walk 4 k-slices of 4 stages like the GEMM main loop (same chain), commit per 4 MMAs
+// build: nvcc -O3 -std=c++17 -gencode arch=compute_100a,code=sm_100a -I ace-step-1.5-ggml_b200/csrc scripts/probes/mma_rate_probe.cu -o /tmp/m
+#include <cuda_runtime.h>
+#include <cstdio>
+#include <vector>
+#include "ptx.cuh"
+using namespace ptx;
+
+template <int N>
+__global__ void __launch_bounds__(128) probe(int variant, int iters, long long* cycles) {
+    extern __shared__ __align__(1024) uint8_t smem[];
+    __shared__ uint64_t bar;
+    __shared__ uint32_t slot;
+    const int warp = threadIdx.x >> 5;
+    for (int i = threadIdx.x; i < (4 * 49152) / 4; i += blockDim.x) reinterpret_cast<uint32_t*>(smem)[i] = 0x3c003c00u;  // 1.0h
+    if (threadIdx.x == 0) { mbar_init(&bar, 1); fence_mbar_init(); }
+    if (warp == 0) tmem_alloc<512>(&slot);
+    fence_proxy_async_smem();
+    tc_fence_before();
+    __syncthreads();
+    tc_fence_after();
+    const uint32_t tb = slot;
+    if (threadIdx.x == 32) {
+        constexpr uint32_t idesc = umma_idesc_f16(128, N);
+        const uint32_t a0 = smem_u32(smem), b0 = a0 + 16384;
+        long long t0 = clock64();
+        for (int i = 0; i < iters; ++i) {
+            const int s = (variant == 2) ? (i >> 2) & 3 : 0;
+            const int k = (variant == 2) ? (i & 3) : 0;
+            const uint64_t da = umma_desc_sw128(a0 + s * 49152 + k * 32), db = umma_desc_sw128(b0 + s * 49152 + k * 32);
+            const uint32_t d = tb + ((variant == 1 && (i & 1)) ? 256u : 0u);
+            umma_f16(d, da, db, idesc, i > 1 ? 1u : 0u);
+            if (variant == 2 && (i & 3) == 3) umma_commit(&bar);   // one commit per "k-block" (arrivals just cycle the phase)
+        }
+        umma_commit(&bar);
+        const long long t1 = clock64();
+        // variant 2 cycled the barrier many times: just wait for quiescence by polling both parities briefly
+        if (variant != 2) mbar_wait(&bar, 0);
+        else { for (int j = 0; j < 200000; ++j) asm volatile("nanosleep.u32 20;"); }
+        const long long t2 = clock64();
+        cycles[blockIdx.x * 2] = t1 - t0;
+        cycles[blockIdx.x * 2 + 1] = t2 - t0;
+    }
+    tc_fence_before();
+    __syncthreads();
+    if (warp == 0) { tc_fence_after(); tmem_dealloc<512>(tb); }
+}
+
+template <int N>
+void run(int grid, long long* cyc) {
+    cudaFuncSetAttribute(probe<N>, cudaFuncAttributeMaxDynamicSharedMemorySize, 4 * 49152);
+    for (int variant = 0; variant < 3; ++variant) {
+        const int iters = 20000;
+        for (int rep = 0; rep < 2; ++rep) probe<N><<<grid, 128, 4 * 49152>>>(variant, iters, cyc);
+        cudaError_t e = cudaDeviceSynchronize();
+        if (e != cudaSuccess) { printf("failed: %s\n", cudaGetErrorString(e)); exit(1); }
+        std::vector<long long> h(2 * grid);
+        cudaMemcpy(h.data(), cyc, 2 * grid * 8, cudaMemcpyDeviceToHost);
+        double a = 0, b = 0;
+        for (int i = 0; i < grid; ++i) { a += h[2 * i]; b += h[2 * i + 1]; }
+        printf("N=%3d grid %3d variant %d: issue %6.1f cycles/MMA, complete %6.1f cycles/MMA (floor %d)  -> %.0f flop/clk/SM\n", N, grid, variant,
+               a / grid / iters, b / grid / iters, N / 2, 128.0 * N * 16 * 2 / (b / grid / iters));
+    }
+}
+
+int main() {
+    long long* cyc;
+    cudaMalloc(&cyc, 148 * 16);
+    for (int grid : {1, 148}) {
+        run<64>(grid, cyc);
+        run<128>(grid, cyc);
+        run<256>(grid, cyc);
+    }
+    return 0;
+}

@@ -41,6 +41,7 @@ struct KParams {
     int  split_k;
     GemmEpilogue epi;
     int  tma_reduce;             // accumulate epilogue goes out as TMA reduce-add tiles through tmOut
+    int  warm_epi;               // epilogue warps run the epilogue once as a dry run (stores predicated off) while the first tile's MMAs are in flight
     int  epi_variant;            // EPI_STORE fast path chosen on the host (store_variant()); 0 = generic code
     long long* trace;            // debug (ACE_B200_GEMM_TRACE=1): per-CTA clock64 stamps of the pipeline phases, else null
 };
@@ -156,6 +157,36 @@ __device__ __forceinline__ void decode_tile(int wtype, const uint8_t* raw, uint8
 }
 
 // ---------------------------------------------------------------- fused epilogue for 32 consecutive columns of one row
+// Stores that a run-time flag can switch off WITHOUT changing the instruction stream: the epilogue warm-up pass (`warm_epi`)
+// executes the real code with `live` = false, so the code is fetched and the loads are issued, but nothing is written.
+// No memory clobber: the values stored depend on every load they must follow, and nothing re-reads these addresses.
+template <bool W>
+__device__ __forceinline__ void st_v4_f32_if(bool live, float* ptr, float4 v) {
+    if (!W) {
+        *reinterpret_cast<float4*>(ptr) = v;
+        return;
+    }
+    asm volatile("{\n\t.reg .pred p;\n\tsetp.ne.b32 p, %0, 0;\n\t@p st.global.v4.f32 [%1], {%2, %3, %4, %5};\n\t}" ::"r"((int)live), "l"(ptr), "f"(v.x),
+                 "f"(v.y), "f"(v.z), "f"(v.w));
+}
+template <bool W>
+__device__ __forceinline__ void st_v2_b32_if(bool live, void* ptr, uint32_t x, uint32_t y) {
+    if (!W) {
+        *reinterpret_cast<uint2*>(ptr) = make_uint2(x, y);
+        return;
+    }
+    asm volatile("{\n\t.reg .pred p;\n\tsetp.ne.b32 p, %0, 0;\n\t@p st.global.v2.b32 [%1], {%2, %3};\n\t}" ::"r"((int)live), "l"(ptr), "r"(x), "r"(y));
+}
+template <bool W>
+__device__ __forceinline__ void st_v4_b32_if(bool live, void* ptr, uint4 v) {
+    if (!W) {
+        *reinterpret_cast<uint4*>(ptr) = v;
+        return;
+    }
+    asm volatile("{\n\t.reg .pred p;\n\tsetp.ne.b32 p, %0, 0;\n\t@p st.global.v4.b32 [%1], {%2, %3, %4, %5};\n\t}" ::"r"((int)live), "l"(ptr), "r"(v.x),
+                 "r"(v.y), "r"(v.z), "r"(v.w));
+}
+
 // Snake: v + sin^2(a v) / b through the MUFU sine and its own range reduction: abs phase error ~|a v| * 1e-7 rad, far below
 // the fp16 rounding of the activation it produces.  5 instructions per element (a two-term Cody-Waite reduction in front of
 // the MUFU cost 10 and made the VAE epilogues issue-bound).
@@ -164,10 +195,11 @@ __device__ __forceinline__ float snake_f(float v, float a, float inv_b) {
     return fmaf(s * s, inv_b, v);
 }
 
+template <bool W>
 __device__ __forceinline__ void epilogue_row32(const KParams& p, const float (&acc)[32], int b, int l, int n0,
-                                               bool add_bias) {
+                                               bool add_bias, bool dry) {
     const GemmEpilogue& e = p.epi;
-    if (l >= p.l_out) return;
+    if (l >= p.l_out && !(W && dry && e.mode == EPI_SWIGLU)) return;
     if (e.mode == EPI_SWIGLU) {
         // columns (2j, 2j+1) = (gate_j, up_j)
         const int nout = p.N >> 1;
@@ -179,14 +211,16 @@ __device__ __forceinline__ void epilogue_row32(const KParams& p, const float (&a
             const float g = acc[2 * i], u = acc[2 * i + 1];
             h[i] = __float2half_rn(__fdividef(g, 1.0f + __expf(-g)) * u);  // fast divide: the result is rounded to fp16
         }
+        const bool live = !(W && dry) && l < p.l_out;
         if (j0 + 16 <= nout) {
-            *reinterpret_cast<uint4*>(o) = *reinterpret_cast<const uint4*>(h);
-            *reinterpret_cast<uint4*>(o + 8) = *reinterpret_cast<const uint4*>(h + 8);
-        } else {
+            st_v4_b32_if<W>(live, o, *reinterpret_cast<const uint4*>(h));
+            st_v4_b32_if<W>(live, o + 8, *reinterpret_cast<const uint4*>(h + 8));
+        } else if (live) {
             for (int i = 0; i < 16 && j0 + i < nout; ++i) o[i] = h[i];
         }
         return;
     }
+    if (W && dry) return;
     const long flat0 = (long)l * e.ld_out + n0 + e.out_shift;  // position inside the sample
     const long base = (long)b * e.out_bstride + flat0;
     const int ncols = min(32, p.N - n0);
@@ -282,8 +316,8 @@ __device__ __forceinline__ void epilogue_row32(const KParams& p, const float (&a
 // instructions per 32x32 chunk — issue-bound, 8.5 k cycles of epilogue per 128x128 tile against 3.6 k of MMAs
 // (profiles/r1_vae_conv_ncu.md); this form needs ~350.
 enum { SV_GENERIC = 0, SV_F16 = 1, SV_F16_SNAKE = 2, SV_F16_SILU = 3, SV_F32 = 4, SV_RES_F32_F16SNAKE = 5, SV_RES_F16SNAKE = 6, SV_F32_F16SNAKE = 7 };
-template <int ACT, bool RESID, bool OUT32, bool OUT16>
-__device__ __forceinline__ void staged_phase2_fast(const GemmEpilogue& e, const float4* s4, long off0, long step, int lane, int n0) {
+template <bool W, int ACT, bool RESID, bool OUT32, bool OUT16>
+__device__ __forceinline__ void staged_phase2_fast(const GemmEpilogue& e, const float4* s4, long off0, long step, int lane, int n0, bool live) {
     const int seg = lane & 7, r0 = lane >> 3;
     float4 res[8];
     if (RESID) {
@@ -301,7 +335,7 @@ __device__ __forceinline__ void staged_phase2_fast(const GemmEpilogue& e, const 
         const int rr = 4 * k + r0;
         float4 t = s4[rr * 8 + (seg ^ (rr & 7))];
         if (RESID) { t.x += res[k].x; t.y += res[k].y; t.z += res[k].z; t.w += res[k].w; }
-        if (OUT32) *reinterpret_cast<float4*>(e.out_f32 + off0 + k * step) = t;
+        if (OUT32) st_v4_f32_if<W>(live, e.out_f32 + off0 + k * step, t);
         if (OUT16) {
             if (ACT == 1) {
                 t.x = snake_f(t.x, sa.x, sb.x); t.y = snake_f(t.y, sa.y, sb.y);
@@ -311,7 +345,7 @@ __device__ __forceinline__ void staged_phase2_fast(const GemmEpilogue& e, const 
                 t.z = __fdividef(t.z, 1.0f + __expf(-t.z)); t.w = __fdividef(t.w, 1.0f + __expf(-t.w));
             }
             const __half2 h0 = __floats2half2_rn(t.x, t.y), h1 = __floats2half2_rn(t.z, t.w);
-            *reinterpret_cast<uint2*>(e.out_f16 + off0 + k * step) = make_uint2(h2u(h0), h2u(h1));
+            st_v2_b32_if<W>(live, e.out_f16 + off0 + k * step, h2u(h0), h2u(h1));
         }
     }
 }
@@ -323,8 +357,9 @@ __device__ __forceinline__ void staged_phase2_fast(const GemmEpilogue& e, const 
 // tile (profiles/r1_gemm_trace_tr1.log) because each 16-byte piece was its own L2 transaction.  The residual read, the fp32
 // store / red.add and the fp16 (Snake / SiLU) store all happen in phase 2.  16-byte pieces are XOR-swizzled by the row so
 // both phases are bank-conflict free.  Returns false (nothing done) when the chunk does not qualify: caller falls back.
+template <bool W>
 __device__ __forceinline__ bool epilogue_store_staged(const KParams& p, const CUtensorMap* tmOut, const float (&acc)[32], int b, int l_base,
-                                                      int lane, int n0, const float* s_bias, const float* s_gate, float* stg) {
+                                                      int lane, int n0, const float* s_bias, const float* s_gate, float* stg, bool dry) {
     const GemmEpilogue& e = p.epi;
     if (n0 + 32 > p.N) return false;                                     // warp-uniform
     const long col0 = (long)n0 + e.out_shift;
@@ -355,7 +390,7 @@ __device__ __forceinline__ bool epilogue_store_staged(const KParams& p, const CU
         // per-SM issue rate (~2.2 k cycles per chunk) was the exposed part of the small-M GEMMs.
         ptx::fence_proxy_async_smem();
         __syncwarp();
-        if (lane == 0) {
+        if (lane == 0 && !(W && dry)) {
             ptx::tma_reduce_add_3d(tmOut, stg, n0, l_base, b);
             ptx::bulk_commit();
         }
@@ -368,19 +403,21 @@ __device__ __forceinline__ bool epilogue_store_staged(const KParams& p, const CU
         if (l_base + 32 <= p.l_out && first >= 0 && last + 32 <= e.out_valid) {
             const long off0 = (long)b * e.out_bstride + first + (long)(lane >> 3) * e.ld_out + 4 * (lane & 7);
             const long step = 4 * e.ld_out;
+            const bool live = !(W && dry);
             switch (p.epi_variant) {
-                case SV_F16:              staged_phase2_fast<0, false, false, true>(e, s4, off0, step, lane, n0); break;
-                case SV_F16_SNAKE:        staged_phase2_fast<1, false, false, true>(e, s4, off0, step, lane, n0); break;
-                case SV_F16_SILU:         staged_phase2_fast<2, false, false, true>(e, s4, off0, step, lane, n0); break;
-                case SV_F32:              staged_phase2_fast<0, false, true, false>(e, s4, off0, step, lane, n0); break;
-                case SV_RES_F32_F16SNAKE: staged_phase2_fast<1, true, true, true>(e, s4, off0, step, lane, n0); break;
-                case SV_RES_F16SNAKE:     staged_phase2_fast<1, true, false, true>(e, s4, off0, step, lane, n0); break;
-                default:                  staged_phase2_fast<1, false, true, true>(e, s4, off0, step, lane, n0); break;
+                case SV_F16:              staged_phase2_fast<W, 0, false, false, true>(e, s4, off0, step, lane, n0, live); break;
+                case SV_F16_SNAKE:        staged_phase2_fast<W, 1, false, false, true>(e, s4, off0, step, lane, n0, live); break;
+                case SV_F16_SILU:         staged_phase2_fast<W, 2, false, false, true>(e, s4, off0, step, lane, n0, live); break;
+                case SV_F32:              staged_phase2_fast<W, 0, false, true, false>(e, s4, off0, step, lane, n0, live); break;
+                case SV_RES_F32_F16SNAKE: staged_phase2_fast<W, 1, true, true, true>(e, s4, off0, step, lane, n0, live); break;
+                case SV_RES_F16SNAKE:     staged_phase2_fast<W, 1, true, false, true>(e, s4, off0, step, lane, n0, live); break;
+                default:                  staged_phase2_fast<W, 1, false, true, true>(e, s4, off0, step, lane, n0, live); break;
             }
             __syncwarp();  // buffer is reused by the next chunk
             return true;
         }
     }
+    if (W && dry) return true;  // the generic tail is not worth warming
     const int seg = lane & 7;                 // this lane's 4 columns: n0 + 4 seg ..
     long off[8];
     bool ok[8];
@@ -448,17 +485,32 @@ __device__ __forceinline__ void stage_column_terms(const KParams& p, int b, int 
         s_gate[j] = (in && e.gate) ? __ldg(e.gate + (long)b * e.gate_bstride + n) : 1.f;
     }
 }
+// EPI_HEADNORM: q/k norm weights of the tile's heads (128 floats per head, zeros for V heads) into smem, under the MMAs.
+template <int BN, int NTHREADS>
+__device__ __forceinline__ void stage_head_weights(const KParams& p, int n_base, int tid, float* s_w) {
+    const GemmEpilogue& e = p.epi;
+    for (int jx = tid; jx < BN; jx += NTHREADS) {
+        const int n0 = n_base + (jx & ~127);
+        const float* w = n0 < e.hn_na ? e.hn_wa : (n0 < e.hn_na + e.hn_nb ? e.hn_wb : nullptr);
+        s_w[jx] = w ? __ldg(w + (jx & 127)) : 0.f;
+    }
+}
 __device__ __forceinline__ void epi_bar_sync(int nthreads) {  // named barrier 1: the epilogue warps only
     asm volatile("bar.sync 1, %0;" ::"r"(nthreads) : "memory");
 }
 
-// EPI_HEADNORM: one head (128 accumulator columns) of one row.  Pass 1 reads the four 32-column chunks from TMEM for
-// the sum of squares, pass 2 re-reads them as rotate-half pairs (chunk c with chunk c+2), normalises, rotates, stores.
-__device__ __forceinline__ void epilogue_head128(const KParams& p, uint32_t taddr, int b, int l, int n0) {
+// EPI_HEADNORM: one head (128 accumulator columns) of the warp's 32 rows.  Pass 1 (thread = accumulator row) reads the four
+// 32-column chunks from TMEM for the sum of squares.  Pass 2 re-reads them as rotate-half pairs (chunk c with chunk c+2),
+// applies inv-rms x norm weight, and parks 16 + 16 columns per row in the warp's transpose buffer; phase 2 then gives every
+// row to 4 lanes (8 rows per step), so the RoPE table is read and the fp16 head written as 128 / 32 contiguous bytes per row:
+// 8 lines per warp instruction instead of 32.  The thread-per-row form was L1-request bound: 64 loads x 32 lines per head and
+// warp = ~17 k cycles of epilogue behind a 19 k cycle main loop (profiles/r1_trace_dit_hn.log).
+// `c_begin / c_step` let two warp groups split one head by chunk pair (128-column tiles have a single head).
+template <bool W>
+__device__ __forceinline__ void epilogue_head128(const KParams& p, uint32_t taddr, int b, bool live, int l_base, int lane, int n0,
+                                                 float* stg, const float* s_w, int c_begin, int c_step) {
     const GemmEpilogue& e = p.epi;
-    const float* w = n0 < e.hn_na ? e.hn_wa : (n0 < e.hn_na + e.hn_nb ? e.hn_wb : nullptr);
-    __half* o = e.out_f16 + (long)b * e.out_bstride + (long)l * e.ld_out + n0;
-    const bool row_ok = l < p.l_out;
+    const float* w = (n0 < e.hn_na + e.hn_nb) ? s_w : nullptr;  // norm weights of this head, staged in smem by stage_head_weights
     uint32_t r0[32], r1[32];
     float inv = 1.f;
     if (w) {
@@ -475,37 +527,64 @@ __device__ __forceinline__ void epilogue_head128(const KParams& p, uint32_t tadd
         }
         inv = rsqrtf(ss * (1.0f / 128.0f) + e.hn_eps);
     }
-    const float2* rt = (w && e.rope) ? e.rope + (long)(row_ok ? l : 0) * 64 : nullptr;
+    const bool rope = w && e.rope;
+    float4* s4 = reinterpret_cast<float4*>(stg);
+    const int j = lane & 3, rq = lane >> 2;
 #pragma unroll 1
-    for (int c = 0; c < 2; ++c) {
+    for (int c = c_begin; c < 2; c += c_step) {
         ptx::tmem_ld32(taddr + c * 32, r0);
         ptx::tmem_ld32(taddr + (c + 2) * 32, r1);
         ptx::tmem_ld_wait();
-        __align__(16) __half h0[32], h1[32];
 #pragma unroll
-        for (int i = 0; i < 32; ++i) {
-            float a = __uint_as_float(r0[i]), bb = __uint_as_float(r1[i]);
-            if (w) {
-                a *= inv * __ldg(w + c * 32 + i);
-                bb *= inv * __ldg(w + 64 + c * 32 + i);
-                if (rt) {
-                    const float2 cs = __ldg(rt + c * 32 + i);
-                    const float ra = a * cs.x - bb * cs.y;
-                    bb = a * cs.y + bb * cs.x;
-                    a = ra;
+        for (int h = 0; h < 2; ++h) {
+            // this lane's RoPE entries of the four row groups, requested before the staging work so the L2 round trip
+            // (L1 is nearly all shared memory here) overlaps it
+            float4 cs[4][2];
+            if (rope) {
+#pragma unroll
+                for (int k = 0; k < 4; ++k) {
+                    const int l = min(l_base + 8 * k + rq, p.l_out - 1);
+                    const float4* rp = reinterpret_cast<const float4*>(e.rope + (long)l * 64 + c * 32 + h * 16 + 4 * j);
+                    cs[k][0] = __ldg(rp);
+                    cs[k][1] = __ldg(rp + 1);
                 }
             }
-            h0[i] = __float2half_rn(a);
-            h1[i] = __float2half_rn(bb);
-        }
-        if (row_ok) {
-            uint4* o0 = reinterpret_cast<uint4*>(o + c * 32);
-            uint4* o1 = reinterpret_cast<uint4*>(o + 64 + c * 32);
 #pragma unroll
-            for (int i = 0; i < 4; ++i) {
-                o0[i] = reinterpret_cast<const uint4*>(h0)[i];
-                o1[i] = reinterpret_cast<const uint4*>(h1)[i];
+            for (int i4 = 0; i4 < 4; ++i4) {
+                const int col = h * 16 + 4 * i4;
+                float4 av = make_float4(__uint_as_float(r0[col]), __uint_as_float(r0[col + 1]), __uint_as_float(r0[col + 2]), __uint_as_float(r0[col + 3]));
+                float4 bv = make_float4(__uint_as_float(r1[col]), __uint_as_float(r1[col + 1]), __uint_as_float(r1[col + 2]), __uint_as_float(r1[col + 3]));
+                if (w) {
+                    const float4 wa = *reinterpret_cast<const float4*>(w + c * 32 + col);
+                    const float4 wb = *reinterpret_cast<const float4*>(w + 64 + c * 32 + col);
+                    av.x *= inv * wa.x; av.y *= inv * wa.y; av.z *= inv * wa.z; av.w *= inv * wa.w;
+                    bv.x *= inv * wb.x; bv.y *= inv * wb.y; bv.z *= inv * wb.z; bv.w *= inv * wb.w;
+                }
+                s4[lane * 8 + (i4 ^ (lane & 7))] = av;
+                s4[lane * 8 + ((4 + i4) ^ (lane & 7))] = bv;
             }
+            __syncwarp();
+#pragma unroll
+            for (int k = 0; k < 4; ++k) {
+                const int rr = 8 * k + rq;
+                const int l = l_base + rr;
+                float4 av = s4[rr * 8 + (j ^ (rr & 7))], bv = s4[rr * 8 + ((4 + j) ^ (rr & 7))];
+                if (l < p.l_out) {
+                    const int col = c * 32 + h * 16 + 4 * j;
+                    if (rope) {
+                        const float4 cs01 = cs[k][0], cs23 = cs[k][1];
+                        float t;
+                        t = av.x * cs01.x - bv.x * cs01.y; bv.x = av.x * cs01.y + bv.x * cs01.x; av.x = t;
+                        t = av.y * cs01.z - bv.y * cs01.w; bv.y = av.y * cs01.w + bv.y * cs01.z; av.y = t;
+                        t = av.z * cs23.x - bv.z * cs23.y; bv.z = av.z * cs23.y + bv.z * cs23.x; av.z = t;
+                        t = av.w * cs23.z - bv.w * cs23.w; bv.w = av.w * cs23.w + bv.w * cs23.z; av.w = t;
+                    }
+                    __half* o = e.out_f16 + (long)b * e.out_bstride + (long)l * e.ld_out + n0 + col;
+                    st_v2_b32_if<W>(live, o, h2u(__floats2half2_rn(av.x, av.y)), h2u(__floats2half2_rn(av.z, av.w)));
+                    st_v2_b32_if<W>(live, o + 64, h2u(__floats2half2_rn(bv.x, bv.y)), h2u(__floats2half2_rn(bv.z, bv.w)));
+                }
+            }
+            __syncwarp();
         }
     }
 }
@@ -515,7 +594,7 @@ __device__ __forceinline__ void epilogue_head128(const KParams& p, uint32_t tadd
 namespace {
 
 // ---------------------------------------------------------------- the tensor-core kernel
-template <int BN, bool QUANT>
+template <int BN, bool QUANT, bool WARM>
 __global__ void __launch_bounds__(NUM_THREADS, 1)
 gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmOut, const KParams p) {
     using SL = SmemLayout<BN, QUANT>;
@@ -706,29 +785,46 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
         const int part = QUANT ? 0 : (warp >> 2);
         constexpr int NPARTS = QUANT ? 1 : 2;
         int it = 0;
-        for (int t = blockIdx.x; t < total_tiles; t += gridDim.x, ++it) {
+        // Warm-up pass: with one or two tiles per CTA the epilogue is straight-line code that runs once, at instruction-fetch
+        // speed (ncu: `no_inst` stalls all over it).  The epilogue warps are idle while the first tile's MMAs run, so they
+        // execute the SAME code once as a dry run (loop iteration with `dry` set: garbage accumulator, real loads, stores
+        // predicated off) and the real pass finds it in the instruction cache.
+        bool dry = WARM;
+        for (int t = blockIdx.x; t < total_tiles;) {
             int nt, sp, b, l0, kb0, kb1;
             decode_tile_index(t, nt, sp, b, l0);
             k_range(sp, kb0, kb1);
             const int a = it & 1;
             const uint32_t aph = (it >> 1) & 1;
             constexpr int EPI_THREADS = SL::EPI_WARPS * 32;
-            if (p.epi.mode == EPI_STORE) {  // column terms of this tile, fetched under the tile's MMAs
-                epi_bar_sync(EPI_THREADS);  // every warp is done reading the previous tile's terms
-                stage_column_terms<BN, EPI_THREADS>(p, b, nt * BN, sp == 0, QUANT ? (int)threadIdx.x - 128 : (int)threadIdx.x, sCol, sCol + BN);
-                epi_bar_sync(EPI_THREADS);
+            if (!dry) {
+                if (p.epi.mode == EPI_STORE) {  // column terms of this tile, fetched under the tile's MMAs
+                    epi_bar_sync(EPI_THREADS);  // every warp is done reading the previous tile's terms
+                    stage_column_terms<BN, EPI_THREADS>(p, b, nt * BN, sp == 0, QUANT ? (int)threadIdx.x - 128 : (int)threadIdx.x, sCol, sCol + BN);
+                    epi_bar_sync(EPI_THREADS);
+                } else if (p.epi.mode == EPI_HEADNORM) {
+                    epi_bar_sync(EPI_THREADS);
+                    stage_head_weights<BN, EPI_THREADS>(p, nt * BN, QUANT ? (int)threadIdx.x - 128 : (int)threadIdx.x, sCol);
+                    epi_bar_sync(EPI_THREADS);
+                }
+                ptx::mbar_wait(&acc_full[a], aph);
+                ptx::tc_fence_after();
+                if (warp == 4 && lane == 0) trace_stamp(p, TR_ACC_READY);
             }
-            ptx::mbar_wait(&acc_full[a], aph);
-            ptx::tc_fence_after();
-            if (warp == 4 && lane == 0) trace_stamp(p, TR_ACC_READY);
             const int l = l0 + q * 32 + lane;
             const uint32_t taddr = tmem_base + ((uint32_t)(q * 32) << 16) + (uint32_t)(a * BN);
             if (p.epi.mode == EPI_HEADNORM) {
+                float* stg = sStg + (QUANT ? q : warp) * (STG_WARP_BYTES / 4);
+                if (NPARTS == 2 && BN == 128) {  // a single head per tile: the two warp groups split it by chunk pair
+                    const int n0 = nt * BN;
+                    if (n0 < p.N && kb1 > kb0) epilogue_head128<WARM>(p, taddr, b, !dry, l0 + q * 32, lane, n0, stg, sCol, part, 2);
+                } else {
 #pragma unroll 1
-                for (int hh = part; hh < BN / 128; hh += NPARTS) {
-                    const int n0 = nt * BN + hh * 128;
-                    if (n0 >= p.N) break;  // warp-uniform
-                    if (kb1 > kb0) epilogue_head128(p, taddr + hh * 128, b, l, n0);
+                    for (int hh = part; hh < BN / 128; hh += NPARTS) {
+                        const int n0 = nt * BN + hh * 128;
+                        if (n0 >= p.N) break;  // warp-uniform
+                        if (kb1 > kb0) epilogue_head128<WARM>(p, taddr + hh * 128, b, !dry, l0 + q * 32, lane, n0, stg, sCol + hh * 128, 0, 1);
+                    }
                 }
             } else
 #pragma unroll 1
@@ -744,15 +840,21 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
                 for (int i = 0; i < 32; ++i) acc[i] = __uint_as_float(r[i]);
                 if (kb1 > kb0) {
                     float* stg = sStg + (QUANT ? q : warp) * (STG_WARP_BYTES / 4);
-                    if (p.epi.mode != EPI_STORE || !epilogue_store_staged(p, &tmOut, acc, b, l0 + q * 32, lane, n0, sCol + c * 32, sCol + BN + c * 32, stg))
-                        epilogue_row32(p, acc, b, l, n0, sp == 0);
+                    if (p.epi.mode != EPI_STORE || !epilogue_store_staged<WARM>(p, &tmOut, acc, b, l0 + q * 32, lane, n0, sCol + c * 32, sCol + BN + c * 32, stg, dry))
+                        epilogue_row32<WARM>(p, acc, b, l, n0, sp == 0, dry);
                 }
                 if (warp == 4 && lane == 0 && c == part) trace_stamp(p, TR_EPI_CHUNK0);
+            }
+            if (dry) {
+                dry = false;
+                continue;  // same tile again, for real
             }
             ptx::tc_fence_before();
             __syncwarp();
             if (lane == 0) ptx::mbar_arrive(&acc_empty[a]);
             if (warp == 4 && lane == 0) trace_stamp(p, TR_EPI_DONE);
+            t += gridDim.x;
+            ++it;
         }
     }
 
@@ -778,6 +880,7 @@ constexpr int STAGES2 = 6;
 constexpr int STAGE2_BYTES = A_STAGE_BYTES + W_SUB_BYTES;  // 32 KB
 constexpr int SMEM2_BYTES = STAGES2 * STAGE2_BYTES + 8 * STG_WARP_BYTES + 2 * 256 * 4 + 512;
 
+template <bool WARM>
 __global__ void __launch_bounds__(NUM_THREADS, 1)
 gemm_tc2_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmOut, const KParams p) {
     constexpr int BN = 256;
@@ -931,19 +1034,26 @@ gemm_tc2_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__
         const int q = warp & 3;
         const int part = warp >> 2;
         int it = 0;
-        for (int t = cluster_id; t < total_tiles; t += n_clusters, ++it) {
+        bool dry = WARM;  // instruction-cache warm-up pass, see gemm_tc_kernel
+        for (int t = cluster_id; t < total_tiles;) {
             int nt, sp, b, l0, kb0, kb1;
             decode_tile_index(t, nt, sp, b, l0);
             k_range(sp, kb0, kb1);
             const int a = it & 1;
             const uint32_t aph = (it >> 1) & 1;
-            if (p.epi.mode == EPI_STORE) {
-                epi_bar_sync(256);
-                stage_column_terms<BN, 256>(p, b, nt * BN, sp == 0, (int)threadIdx.x, sCol, sCol + BN);
-                epi_bar_sync(256);
+            if (!dry) {
+                if (p.epi.mode == EPI_STORE) {
+                    epi_bar_sync(256);
+                    stage_column_terms<BN, 256>(p, b, nt * BN, sp == 0, (int)threadIdx.x, sCol, sCol + BN);
+                    epi_bar_sync(256);
+                } else if (p.epi.mode == EPI_HEADNORM) {
+                    epi_bar_sync(256);
+                    stage_head_weights<BN, 256>(p, nt * BN, (int)threadIdx.x, sCol);
+                    epi_bar_sync(256);
+                }
+                ptx::mbar_wait(&acc_full[a], aph);
+                ptx::tc_fence_after();
             }
-            ptx::mbar_wait(&acc_full[a], aph);
-            ptx::tc_fence_after();
             const int l = l0 + q * 32 + lane;
             const uint32_t taddr = tmem_base + ((uint32_t)(q * 32) << 16) + (uint32_t)(a * BN);
             if (p.epi.mode == EPI_HEADNORM) {
@@ -951,7 +1061,7 @@ gemm_tc2_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__
                 for (int hh = part; hh < BN / 128; hh += 2) {
                     const int n0 = nt * BN + hh * 128;
                     if (n0 >= p.N) break;
-                    if (kb1 > kb0) epilogue_head128(p, taddr + hh * 128, b, l, n0);
+                    if (kb1 > kb0) epilogue_head128<WARM>(p, taddr + hh * 128, b, !dry, l0 + q * 32, lane, n0, sStg + warp * (STG_WARP_BYTES / 4), sCol + hh * 128, 0, 1);
                 }
             } else
 #pragma unroll 1
@@ -966,13 +1076,19 @@ gemm_tc2_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__
                 for (int i = 0; i < 32; ++i) acc[i] = __uint_as_float(r[i]);
                 if (kb1 > kb0) {
                     float* stg = sStg + warp * (STG_WARP_BYTES / 4);
-                    if (p.epi.mode != EPI_STORE || !epilogue_store_staged(p, &tmOut, acc, b, l0 + q * 32, lane, n0, sCol + c * 32, sCol + BN + c * 32, stg))
-                        epilogue_row32(p, acc, b, l, n0, sp == 0);
+                    if (p.epi.mode != EPI_STORE || !epilogue_store_staged<WARM>(p, &tmOut, acc, b, l0 + q * 32, lane, n0, sCol + c * 32, sCol + BN + c * 32, stg, dry))
+                        epilogue_row32<WARM>(p, acc, b, l, n0, sp == 0, dry);
                 }
+            }
+            if (dry) {
+                dry = false;
+                continue;  // same tile again, for real
             }
             ptx::tc_fence_before();
             __syncwarp();
             if (lane == 0) ptx::mbar_arrive_cluster(ptx::mapa(&acc_empty[a], 0));
+            t += n_clusters;
+            ++it;
         }
     }
 
@@ -1049,7 +1165,7 @@ __global__ void gemm_simt_kernel(const __half* A, long a_lstride, long a_bstride
     KParams q = p;
     q.epi.atomic = 0;  // debug kernel never splits K: plain read-modify-write
     if (p.epi.atomic) q.epi.resid = p.epi.out_f32;
-    epilogue_row32(q, acc, b, l, n0, true);
+    epilogue_row32<false>(q, acc, b, l, n0, true, false);
 }
 
 // ---------------------------------------------------------------- one-off decode of a packed tile to its F16 image
@@ -1138,7 +1254,8 @@ int max_active_pairs() {
     static int n = -1;
     if (n < 0) {
         n = 0;
-        if (cudaFuncSetAttribute(gemm_tc2_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, SMEM2_BYTES) == cudaSuccess) {
+        if (cudaFuncSetAttribute(gemm_tc2_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, SMEM2_BYTES) == cudaSuccess &&
+            cudaFuncSetAttribute(gemm_tc2_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, SMEM2_BYTES) == cudaSuccess) {
             cudaLaunchConfig_t cfg = {};
             cfg.gridDim = dim3(2 * 148);
             cfg.blockDim = dim3(NUM_THREADS);
@@ -1151,7 +1268,7 @@ int max_active_pairs() {
             cfg.attrs = at;
             cfg.numAttrs = 1;
             int c = 0;
-            if (cudaOccupancyMaxActiveClusters(&c, gemm_tc2_kernel, &cfg) == cudaSuccess) n = c;
+            if (cudaOccupancyMaxActiveClusters(&c, gemm_tc2_kernel<false>, &cfg) == cudaSuccess) n = c;
             else cudaGetLastError();
             if (std::getenv("ACE_B200_DEBUG")) std::fprintf(stderr, "[ace_b200] max active CTA pairs: %d\n", n);
         } else cudaGetLastError();
@@ -1174,7 +1291,7 @@ cudaError_t launch_tc2(const CUtensorMap& tm, const CUtensorMap& tmo, const KPar
     at[1].val.programmaticStreamSerializationAllowed = 1;
     cfg.attrs = at;
     cfg.numAttrs = pdl_enabled() ? 2 : 1;
-    return cudaLaunchKernelEx(&cfg, gemm_tc2_kernel, tm, tmo, kp);
+    return kp.warm_epi ? cudaLaunchKernelEx(&cfg, gemm_tc2_kernel<true>, tm, tmo, kp) : cudaLaunchKernelEx(&cfg, gemm_tc2_kernel<false>, tm, tmo, kp);
 }
 
 }  // namespace
@@ -1207,16 +1324,16 @@ static bool make_tmap_sw128(CUtensorMapDataType dt, CUtensorMap* tm, const void*
 
 namespace {
 
-template <int BN, bool QUANT>
+template <int BN, bool QUANT, bool WARM>
 cudaError_t launch_tc(const CUtensorMap& tm, const CUtensorMap& tmo, const KParams& kp, int grid, cudaStream_t stream) {
     using SL = SmemLayout<BN, QUANT>;
     static bool attr_set = false;
     if (!attr_set) {
-        cudaError_t e = cudaFuncSetAttribute(gemm_tc_kernel<BN, QUANT>, cudaFuncAttributeMaxDynamicSharedMemorySize, SL::BYTES);
+        cudaError_t e = cudaFuncSetAttribute(gemm_tc_kernel<BN, QUANT, WARM>, cudaFuncAttributeMaxDynamicSharedMemorySize, SL::BYTES);
         if (e != cudaSuccess) return e;
         attr_set = true;
     }
-    return launch_pdl(gemm_tc_kernel<BN, QUANT>, dim3((unsigned)grid), dim3(NUM_THREADS), (size_t)SL::BYTES, stream, tm, tmo, kp);
+    return launch_pdl(gemm_tc_kernel<BN, QUANT, WARM>, dim3((unsigned)grid), dim3(NUM_THREADS), (size_t)SL::BYTES, stream, tm, tmo, kp);
 }
 
 }  // namespace
@@ -1282,6 +1399,7 @@ cudaError_t gemm_launch(const GemmProblem& g, cudaStream_t stream, bool simt) {
         }
         if (const char* ev = std::getenv("ACE_B200_GEMM_EPIFAST")) if (std::atoi(ev) == 0) v = SV_GENERIC;
         kp.epi_variant = v;
+        kp.warm_epi = 1;  // narrowed below once the tile count is known
     }
     // In-place accumulation (out += gate*acc + bias, the DiT residual updates) goes through red.global.add: no
     // read-modify-write latency in the epilogue, and it is what makes a K split legal.
@@ -1299,9 +1417,12 @@ cudaError_t gemm_launch(const GemmProblem& g, cudaStream_t stream, bool simt) {
     // Measured (profiles/r1_gemm_sweep_pair2.log): the pair wins once a cluster runs several tiles (M = 6000: +6..17 %),
     // and loses at M = 750 where its longer per-tile ramp (relay hop, cluster syncs) is not amortised -> rows >= 2048.
     const bool pair_ok = kp.wtype == W_F16 && (kp.n_tiles128 & 1) == 0 && kp.n_tiles128 >= 2;
-    bool pair = pair_ok && (long)g.B * g.l_out >= 2048;
-    if (const char* fp = std::getenv("ACE_B200_GEMM_2CTA")) pair = pair_ok && std::atoi(fp) != 0;
     const long tiles_pair = (long)(kp.n_tiles128 / 2) * m_pairs;
+    // ... and below that when every cluster still gets >= ~28 k-blocks of work (M = 750: MLP up-projection N = 12288 792 vs
+    // 647 TFLOP/s, down-projection K = 6144 612 vs 526; QKV / o-proj stay single-CTA: profiles/r1_gemm_sweep_issue1.log)
+    const int pairs_avail = std::max(1, max_active_pairs());
+    bool pair = pair_ok && ((long)g.B * g.l_out >= 2048 || tiles_pair * (long)kp.kb_total >= 28L * pairs_avail);
+    if (const char* fp = std::getenv("ACE_B200_GEMM_2CTA")) pair = pair_ok && std::atoi(fp) != 0;
     if (pair && max_active_pairs() < 8) pair = false;
     const int units = pair ? max_active_pairs() : sms;  // schedulable units: clusters or CTAs
     const long tiles_nosplit = pair ? tiles_pair : (bn256 ? tiles256 : tiles128);
@@ -1317,6 +1438,11 @@ cudaError_t gemm_launch(const GemmProblem& g, cudaStream_t stream, bool simt) {
     }
     if (sk > 1 && !accumulate) return cudaErrorInvalidValue;
     kp.split_k = std::min(sk, kp.kb_total);
+    {  // the dry-run epilogue pass pays off only where a CTA runs a handful of tiles (it costs one extra epilogue per CTA)
+        const long work_tiles = tiles_nosplit * kp.split_k;
+        kp.warm_epi = work_tiles <= 4L * units ? 1 : 0;
+        if (const char* ew = std::getenv("ACE_B200_GEMM_WARM")) kp.warm_epi = std::atoi(ew) != 0;
+    }
     // in-place accumulation always goes through red.add, split or not: fire-and-forget, where a read-add-write would put
     // an L2 round trip per row group on the epilogue's critical path (trace: 8.0 k vs 2.2 k cycles per 32-column chunk)
     if (accumulate) kp.epi.atomic = 1;
@@ -1386,8 +1512,12 @@ cudaError_t gemm_launch(const GemmProblem& g, cudaStream_t stream, bool simt) {
     if (pair) return launch_tc2(tm, tmo, kp, (int)(tiles < units ? tiles : units), stream);
     const int grid = (int)(tiles < sms ? tiles : sms);
     const bool quant = kp.wtype != W_F16;
-    if (bn256) return quant ? launch_tc<256, true>(tm, tmo, kp, grid, stream) : launch_tc<256, false>(tm, tmo, kp, grid, stream);
-    return quant ? launch_tc<128, true>(tm, tmo, kp, grid, stream) : launch_tc<128, false>(tm, tmo, kp, grid, stream);
+    if (kp.warm_epi) {
+        if (bn256) return quant ? launch_tc<256, true, true>(tm, tmo, kp, grid, stream) : launch_tc<256, false, true>(tm, tmo, kp, grid, stream);
+        return quant ? launch_tc<128, true, true>(tm, tmo, kp, grid, stream) : launch_tc<128, false, true>(tm, tmo, kp, grid, stream);
+    }
+    if (bn256) return quant ? launch_tc<256, true, false>(tm, tmo, kp, grid, stream) : launch_tc<256, false, false>(tm, tmo, kp, grid, stream);
+    return quant ? launch_tc<128, true, false>(tm, tmo, kp, grid, stream) : launch_tc<128, false, false>(tm, tmo, kp, grid, stream);
 }
 
 }  // namespace ace

@@ -17,6 +17,7 @@ def main():
     br = B200Bridge()
     g = np.random.default_rng(0)
     shapes = [(750, 4096, 2048), (750, 2048, 2048), (750, 12288, 2048), (750, 2048, 6144),
+              (3000, 4096, 2048), (3000, 2048, 2048), (3000, 12288, 2048), (3000, 2048, 6144),
               (6000, 4096, 2048), (6000, 2048, 2048), (6000, 12288, 2048), (6000, 2048, 6144)]
     wtypes = [0, 12] if len(sys.argv) < 2 else [int(x) for x in sys.argv[1].split(",")]
     for wt in wtypes:

@@ -129,6 +129,36 @@ cudaError_t dit_forward_device(const DitModel& m, DitWorkspace& ws, int B, int T
     // ---- inputs: pack + patch-embed
     launch_pack_dit_input(ws.d_hidden, ws.d_context, ws.x0, B, T, S, P, ctx, A, st);
     launch_patch_mask(opts.has_mask ? ws.d_mask : nullptr, ws.d_pmask, B, T, S, P, st);
+    // ---- timestep embeddings -> AdaLN tables   (M = B rows; HBM-bound GEMVs through the same kernel)
+    launch_timestep_features(ws.d_t, ws.tfreq, 2 * B, st);
+    for (int which = 0; which < 2; ++which) {
+        const DitTimeEmbed& te = which == 0 ? m.te : m.te_r;
+        float* temb = which == 0 ? ws.temb : ws.temb_r;
+        GemmEpilogue e1;
+        e1.bias = te.b1;
+        e1.out_f16 = ws.th1;
+        e1.silu_f16 = 1;
+        e1.ld_out = H;
+        f.gemm(ws.tfreq + (size_t)which * B * 256, 256, 1, B, te.w1, e1, false);
+        GemmEpilogue e2;
+        e2.bias = te.b2;
+        e2.out_f32 = temb;
+        e2.out_f16 = ws.th2;
+        e2.silu_f16 = 1;
+        e2.ld_out = H;
+        f.gemm(ws.th1, H, 1, B, te.w2, e2, false);
+        GemmEpilogue e3;
+        e3.bias = te.b_proj;
+        e3.out_f32 = ws.tproj;
+        e3.resid = which == 0 ? nullptr : ws.tproj;  // proj = proj_t + proj_r
+        e3.ld_out = 6 * H;
+        f.gemm(ws.th2, H, 1, B, te.w_proj, e3, false);
+    }
+    launch_build_modulation(m.layer_tables, ws.tproj, ws.mod, m.out_table, ws.temb, ws.temb_r, ws.out_mod, B, layers_all, H, st);
+    const long mod_bs = (long)layers_all * 6 * H;
+
+    // ---- patch-embed and condition embedder.  They run AFTER the modulation tables on purpose: rmsnorm_mod reads its scale /
+    // shift before its PDL wait, which is only safe when the kernel that wrote them is not its immediate predecessor.
     {
         GemmEpilogue e;
         e.bias = m.proj_in_b;
@@ -158,33 +188,6 @@ cudaError_t dit_forward_device(const DitModel& m, DitWorkspace& ws, int B, int T
             f.gemm(ws.encp, H, 1, B * E, ly.cross_kv, ek, false);
         }
     }
-    // ---- timestep embeddings -> AdaLN tables   (M = B rows; HBM-bound GEMVs through the same kernel)
-    launch_timestep_features(ws.d_t, ws.tfreq, 2 * B, st);
-    for (int which = 0; which < 2; ++which) {
-        const DitTimeEmbed& te = which == 0 ? m.te : m.te_r;
-        float* temb = which == 0 ? ws.temb : ws.temb_r;
-        GemmEpilogue e1;
-        e1.bias = te.b1;
-        e1.out_f16 = ws.th1;
-        e1.silu_f16 = 1;
-        e1.ld_out = H;
-        f.gemm(ws.tfreq + (size_t)which * B * 256, 256, 1, B, te.w1, e1, false);
-        GemmEpilogue e2;
-        e2.bias = te.b2;
-        e2.out_f32 = temb;
-        e2.out_f16 = ws.th2;
-        e2.silu_f16 = 1;
-        e2.ld_out = H;
-        f.gemm(ws.th1, H, 1, B, te.w2, e2, false);
-        GemmEpilogue e3;
-        e3.bias = te.b_proj;
-        e3.out_f32 = ws.tproj;
-        e3.resid = which == 0 ? nullptr : ws.tproj;  // proj = proj_t + proj_r
-        e3.ld_out = 6 * H;
-        f.gemm(ws.th2, H, 1, B, te.w_proj, e3, false);
-    }
-    launch_build_modulation(m.layer_tables, ws.tproj, ws.mod, m.out_table, ws.temb, ws.temb_r, ws.out_mod, B, layers_all, H, st);
-    const long mod_bs = (long)layers_all * 6 * H;
 
     // ---- transformer layers
     for (int i = 0; i < n_layers; ++i) {

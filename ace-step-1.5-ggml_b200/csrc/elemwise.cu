@@ -114,13 +114,28 @@ rmsnorm_mod_kernel(const float* __restrict__ x, const float* __restrict__ w, con
                    const float* __restrict__ shift, long mod_bstride, __half* __restrict__ y, long rows, int rows_per_b,
                    int H, float eps) {
     __shared__ float red[4];
-    asm volatile("griddepcontrol.wait;" ::: "memory");             // PDL: the residual stream comes from the previous GEMM
-    asm volatile("griddepcontrol.launch_dependents;" ::: "memory");
     const long row = blockIdx.x;
     const int tid = threadIdx.x;
-    const float* xr = x + row * H;
     const int b = (int)(row / rows_per_b);
+    const float* s1 = scale1 ? scale1 + (long)b * mod_bstride : nullptr;
+    const float* sh = shift ? shift + (long)b * mod_bstride : nullptr;
     constexpr int MAXV = 4;  // up to H = 2048 held in registers; wider rows re-read from L1/L2
+    // norm weight and AdaLN scale / shift do not depend on the previous kernel: fetch them before the PDL wait so their L2
+    // round trip overlaps its tail instead of following the reduction
+    float4 ww[MAXV], sc[MAXV], sf[MAXV];
+#pragma unroll
+    for (int i = 0; i < MAXV; ++i) {
+        const int c = (i * 128 + tid) * 4;
+        ww[i] = sc[i] = sf[i] = make_float4(0.f, 0.f, 0.f, 0.f);
+        if (c < H) {
+            ww[i] = __ldg(reinterpret_cast<const float4*>(w + c));
+            if (s1) sc[i] = __ldg(reinterpret_cast<const float4*>(s1 + c));
+            if (sh) sf[i] = __ldg(reinterpret_cast<const float4*>(sh + c));
+        }
+    }
+    asm volatile("griddepcontrol.wait;" ::: "memory");             // PDL: the residual stream comes from the previous GEMM
+    asm volatile("griddepcontrol.launch_dependents;" ::: "memory");
+    const float* xr = x + row * H;
     float4 v[MAXV];
     float ss = 0.f;
 #pragma unroll
@@ -140,19 +155,14 @@ rmsnorm_mod_kernel(const float* __restrict__ x, const float* __restrict__ w, con
     __syncthreads();
     ss = red[0] + red[1] + red[2] + red[3];
     const float inv = 1.0f / sqrtf(ss / (float)H + eps);
-    const float* s1 = scale1 ? scale1 + (long)b * mod_bstride : nullptr;
-    const float* sh = shift ? shift + (long)b * mod_bstride : nullptr;
     __half* yr = y + row * H;
-    auto emit = [&](int c, float4 t) {
-        const float4 ww = *reinterpret_cast<const float4*>(w + c);
-        float o0 = t.x * inv * ww.x, o1 = t.y * inv * ww.y, o2 = t.z * inv * ww.z, o3 = t.w * inv * ww.w;
+    auto emit = [&](int c, float4 t, float4 wv, float4 a1, float4 a2) {
+        float o0 = t.x * inv * wv.x, o1 = t.y * inv * wv.y, o2 = t.z * inv * wv.z, o3 = t.w * inv * wv.w;
         if (s1) {
-            const float4 a = *reinterpret_cast<const float4*>(s1 + c);
-            o0 *= a.x; o1 *= a.y; o2 *= a.z; o3 *= a.w;
+            o0 *= a1.x; o1 *= a1.y; o2 *= a1.z; o3 *= a1.w;
         }
         if (sh) {
-            const float4 a = *reinterpret_cast<const float4*>(sh + c);
-            o0 += a.x; o1 += a.y; o2 += a.z; o3 += a.w;
+            o0 += a2.x; o1 += a2.y; o2 += a2.z; o3 += a2.w;
         }
         __half2 h0 = __floats2half2_rn(o0, o1), h1 = __floats2half2_rn(o2, o3);
         uint2 o;
@@ -163,9 +173,13 @@ rmsnorm_mod_kernel(const float* __restrict__ x, const float* __restrict__ w, con
 #pragma unroll
     for (int i = 0; i < MAXV; ++i) {
         const int c = (i * 128 + tid) * 4;
-        if (c < H) emit(c, v[i]);
+        if (c < H) emit(c, v[i], ww[i], sc[i], sf[i]);
     }
-    for (int c = (MAXV * 128 + tid) * 4; c < H; c += 512) emit(c, *reinterpret_cast<const float4*>(xr + c));
+    for (int c = (MAXV * 128 + tid) * 4; c < H; c += 512) {
+        const float4 z = make_float4(0.f, 0.f, 0.f, 0.f);
+        emit(c, *reinterpret_cast<const float4*>(xr + c), *reinterpret_cast<const float4*>(w + c),
+             s1 ? *reinterpret_cast<const float4*>(s1 + c) : z, sh ? *reinterpret_cast<const float4*>(sh + c) : z);
+    }
 }
 
 // ---------------------------------------------------------------- per-head RMSNorm + NEOX RoPE, in place (head_dim 128)

@@ -69,6 +69,28 @@ def test_dit_per_block_parity(br, root, k, monkeypatch):
     assert m["rel_l2"] <= 5e-3 and m["cos"] >= 0.99999, (k, m)
 
 
+@pytest.mark.parametrize("knob", [("ACE_B200_GEMM_WARM", "0"), ("ACE_B200_GEMM_WARM", "1"), ("ACE_B200_GEMM_EPIFAST", "0"), ("ACE_B200_GEMM_2CTA", "1"),
+                                  ("ACE_B200_GEMM_2CTA", "0"), ("ACE_B200_GEMM_TMARED", "0"), ("ACE_B200_PDL", "0")])
+def test_dit_kernel_routes_agree_and_match_reference(br, root, knob, monkeypatch):
+    """MID dims at S = 640 rows (several tiles per CTA / CTA pair): every kernel route of the tap-GEMM — epilogue warm-up
+    pass on / off, generic store epilogue, CTA-pair kernel forced on / off, red.add instead of TMA reduce-add, no programmatic
+    dependent launch — computes the same forward: each one is held to the reference tolerance and to the default route."""
+    need_ref()
+    d = make_dit_dir(root, fx.MID, 0, "F16")
+    T, E = 1280, 40
+    inp = fx.dit_inputs(fx.MID, T, E, seed=99)
+    br.load_dit(d)
+    base = br.dit_forward_tfirst(inp["hidden_states"], inp["context_latents"], inp["encoder_hidden_states"], None, None, 0.7, 0.7)
+    monkeypatch.setenv(*knob)
+    alt = br.dit_forward_tfirst(inp["hidden_states"], inp["context_latents"], inp["encoder_hidden_states"], None, None, 0.7, 0.7)
+    m = metrics(alt, base)
+    assert m["rel_l2"] <= 1e-3, (knob, m)      # same math, different accumulation / rounding order only
+    if knob == ("ACE_B200_GEMM_WARM", "0"):    # one reference run is enough (it takes seconds on the host cores)
+        ref, _ = ref_dit_forward(d, inp, 0.7, 0.7)
+        mr = metrics(base, ref)
+        assert mr["rel_l2"] <= 5e-3 and mr["cos"] >= 0.99999, mr
+
+
 def test_dit_masks_and_tr(br, root):
     """key-padding masks on both attentions, t != t_r, enc_len = 0 (cross-attention skipped)"""
     need_ref()

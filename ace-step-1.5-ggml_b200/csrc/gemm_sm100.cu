@@ -29,6 +29,9 @@ constexpr int A_STAGE_BYTES = BM * BK * 2;     // 16 KB
 constexpr int W_SUB_BYTES   = TILE_N * BK * 2; // 16 KB per 128-row sub-tile
 constexpr int RAW_MAX_BYTES = 8704;            // largest packed tile (Q8_0)
 constexpr int NUM_THREADS   = 320;
+constexpr int SLAB_MAX_ROWS = 184;              // 128 + 6 taps x dilation 9 = 182, rounded to whole 8-row swizzle atoms
+constexpr int SLAB_PANEL_BYTES = SLAB_MAX_ROWS * 128;  // one 64-channel panel of an activation slab (23 KB, 1 KB aligned)
+constexpr int SLAB_BYTES = 2 * SLAB_PANEL_BYTES;       // C <= 128
 constexpr int STG_WARP_BYTES = 32 * 32 * 4;    // one epilogue warp's transpose buffer: 32 rows x 32 fp32 columns
 
 struct KParams {
@@ -41,13 +44,15 @@ struct KParams {
     int  split_k;
     GemmEpilogue epi;
     int  tma_reduce;             // accumulate epilogue goes out as TMA reduce-add tiles through tmOut
+    int  slab_rows;              // SLAB kernel: rows of the activation slab of one tile = 128 + (taps-1) * tap_stride
     int  warm_epi;               // epilogue warps run the epilogue once as a dry run (stores predicated off) while the first tile's MMAs are in flight
     int  epi_variant;            // EPI_STORE fast path chosen on the host (store_variant()); 0 = generic code
     long long* trace;            // debug (ACE_B200_GEMM_TRACE=1): per-CTA clock64 stamps of the pipeline phases, else null
 };
 
 // trace slots per CTA
-enum { TR_START = 0, TR_SETUP = 1, TR_FIRST_FULL = 2, TR_LAST_MMA = 3, TR_ACC_READY = 4, TR_EPI_DONE = 5, TR_END = 6, TR_EPI_LD0 = 7, TR_EPI_CHUNK0 = 8, TR_N = 12 };
+enum { TR_START = 0, TR_SETUP = 1, TR_FIRST_FULL = 2, TR_LAST_MMA = 3, TR_ACC_READY = 4, TR_EPI_DONE = 5, TR_END = 6, TR_EPI_LD0 = 7, TR_EPI_CHUNK0 = 8,
+       TR_T8_MMA_WAIT = 9, TR_T8_MMA_GO = 10, TR_T8_MMA_DONE = 11, TR_T8_EPI_WAIT = 12, TR_T8_EPI_GO = 13, TR_T8_EPI_DONE = 14, TR_N = 16 };  // T8_*: the CTA's 9th tile (steady state)
 __device__ __forceinline__ void trace_stamp(const KParams& p, int slot) {
     if (p.trace) p.trace[(size_t)blockIdx.x * TR_N + slot] = clock64();
 }
@@ -594,7 +599,7 @@ __device__ __forceinline__ void epilogue_head128(const KParams& p, uint32_t tadd
 namespace {
 
 // ---------------------------------------------------------------- the tensor-core kernel
-template <int BN, bool QUANT, bool WARM>
+template <int BN, bool QUANT, bool WARM, bool SLAB = false>
 __global__ void __launch_bounds__(NUM_THREADS, 1)
 gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmOut, const KParams p) {
     using SL = SmemLayout<BN, QUANT>;
@@ -605,8 +610,12 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
     if (threadIdx.x == 0) trace_stamp(p, TR_START);
     extern __shared__ __align__(1024) uint8_t smem[];
     if (threadIdx.x == 0 && (ptx::smem_u32(smem) & 1023u) != 0) __trap();  // the 128-byte swizzle needs 1 KB aligned tiles
-    uint8_t* sA = smem;                                  // [STAGES][16 KB]
-    uint8_t* sB = sA + STAGES * A_STAGE_BYTES;           // [STAGES][SUBS*16 KB]
+    // SLAB (k7 convolutions, C <= 128): instead of one 128-row activation box per k-block, the 128 + (taps-1)*dilation rows a
+    // tile needs are loaded ONCE as 64-channel panels (double-buffered across tiles) and tap t reads them at row offset
+    // t*dilation: a K-major SWIZZLE_128B operand may start at any 128-byte row of a TMA-written panel because the swizzle is
+    // a function of the shared-memory address (scripts/probes/umma_rowshift_probe.cu: exact for every shift, base_offset 0).
+    uint8_t* sA = smem;                                  // [STAGES][16 KB]   |  SLAB: [2][SLAB_BYTES]
+    uint8_t* sB = sA + (SLAB ? 2 * SLAB_BYTES : STAGES * A_STAGE_BYTES);  // [STAGES][SUBS*16 KB]
     uint8_t* sR = sB + STAGES * SL::B_STAGE;             // [STAGES][SUBS*RAW_MAX] (QUANT only)
     float* sStg = reinterpret_cast<float*>(sR + STAGES * SL::RAW_STAGE);  // [EPI_WARPS][32 x 32 fp32]
     float* sCol = sStg + SL::STG_BYTES / 4;  // [2][BN]: bias, gate of the current tile
@@ -632,6 +641,10 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
             ptx::mbar_init(&empty[s], 1);
             ptx::mbar_init(&raw_full[s], 1);
             ptx::mbar_init(&raw_empty[s], 4);
+        }
+        if (SLAB) {  // raw_full[0..1] / raw_empty[0..1] serve as slab_full / slab_empty
+            ptx::mbar_init(&raw_empty[0], 1);
+            ptx::mbar_init(&raw_empty[1], 1);
         }
         for (int a = 0; a < 2; ++a) {
             ptx::mbar_init(&acc_full[a], 1);
@@ -666,9 +679,43 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
 
     if (warp == 8) {
         // ===================== TMA producer =====================
-        // One thread; all ring / tap / weight-pointer state advances incrementally (a division and two 64-bit multiplies per
-        // k-block were most of this loop's latency).
-        if (lane == 0) {
+        // Ring / tap / weight-pointer state advances incrementally (no division or 64-bit multiply per k-block).
+        // The whole warp runs the loop on warp-uniform values and one elected lane issues: TMA instructions take their
+        // operands from uniform registers, a single divergent thread pays an ELECT + R2UR waterfall per instruction.
+        if (SLAB) {
+            uint32_t s = 0, ph = 0;
+            const size_t sub_stride = (size_t)p.kb_total * W_SUB_BYTES;
+            const uint32_t panel_bytes = (uint32_t)p.slab_rows * 128u;
+            int it = 0;
+            for (int t = blockIdx.x; t < total_tiles; t += gridDim.x, ++it) {
+                int nt, sp, b, l0, kb0, kb1;
+                decode_tile_index(t, nt, sp, b, l0);
+                k_range(sp, kb0, kb1);
+                const int buf = it & 1;
+                ptx::mbar_wait(&raw_empty[buf], ((it >> 1) & 1) ^ 1);
+                if (ptx::elect_one()) {
+                    ptx::mbar_expect_tx(&raw_full[buf], panel_bytes * (uint32_t)p.kb_per_tap);
+                    for (int pnl = 0; pnl < p.kb_per_tap; ++pnl)
+                        ptx::tma_load_3d(sA + buf * SLAB_BYTES + pnl * SLAB_PANEL_BYTES, &tmA, &raw_full[buf], pnl * BK, l0 + p.tap_offset, b);
+                }
+                __syncwarp();
+                const int subs_valid = min(SUBS, p.n_tiles128 - nt * SUBS);
+                const uint8_t* wptr = p.W + (size_t)(nt * SUBS) * sub_stride + (size_t)kb0 * W_SUB_BYTES;
+                for (int kb = kb0; kb < kb1; ++kb, wptr += W_SUB_BYTES) {
+                    ptx::mbar_wait(&empty[s], ph ^ 1);
+                    if (ptx::elect_one()) {
+                        ptx::mbar_expect_tx(&full[s], subs_valid * W_SUB_BYTES);
+                        for (int sub = 0; sub < subs_valid; ++sub)
+                            ptx::bulk_load(sB + s * SL::B_STAGE + sub * W_SUB_BYTES, wptr + sub * sub_stride, W_SUB_BYTES, &full[s]);
+                    }
+                    __syncwarp();
+                    if (++s == (uint32_t)STAGES) {
+                        s = 0;
+                        ph ^= 1;
+                    }
+                }
+            }
+        } else {
             uint32_t s = 0, ph = 0;
             const size_t sub_stride = (size_t)p.kb_total * (QUANT ? (size_t)p.tile_bytes : (size_t)W_SUB_BYTES);
             for (int t = blockIdx.x; t < total_tiles; t += gridDim.x) {
@@ -683,20 +730,25 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
                 for (int kb = kb0; kb < kb1; ++kb) {
                     ptx::mbar_wait(&empty[s], ph ^ 1);
                     if (QUANT) {
-                        ptx::mbar_expect_tx(&full[s], A_STAGE_BYTES);
-                        ptx::tma_load_3d(sA + s * A_STAGE_BYTES, &tmA, &full[s], kc * BK, row, b);
                         ptx::mbar_wait(&raw_empty[s], ph ^ 1);
-                        ptx::mbar_expect_tx(&raw_full[s], (uint32_t)(subs_valid * p.tile_bytes));
-                        for (int sub = 0; sub < subs_valid; ++sub)
-                            ptx::bulk_load(sR + s * SL::RAW_STAGE + sub * RAW_MAX_BYTES, wptr + sub * sub_stride, p.tile_bytes, &raw_full[s]);
+                        if (ptx::elect_one()) {
+                            ptx::mbar_expect_tx(&full[s], A_STAGE_BYTES);
+                            ptx::tma_load_3d(sA + s * A_STAGE_BYTES, &tmA, &full[s], kc * BK, row, b);
+                            ptx::mbar_expect_tx(&raw_full[s], (uint32_t)(subs_valid * p.tile_bytes));
+                            for (int sub = 0; sub < subs_valid; ++sub)
+                                ptx::bulk_load(sR + s * SL::RAW_STAGE + sub * RAW_MAX_BYTES, wptr + sub * sub_stride, p.tile_bytes, &raw_full[s]);
+                        }
                         wptr += p.tile_bytes;
                     } else {
-                        ptx::mbar_expect_tx(&full[s], A_STAGE_BYTES + subs_valid * W_SUB_BYTES);
-                        ptx::tma_load_3d(sA + s * A_STAGE_BYTES, &tmA, &full[s], kc * BK, row, b);
-                        for (int sub = 0; sub < subs_valid; ++sub)
-                            ptx::bulk_load(sB + s * SL::B_STAGE + sub * W_SUB_BYTES, wptr + sub * sub_stride, W_SUB_BYTES, &full[s]);
+                        if (ptx::elect_one()) {
+                            ptx::mbar_expect_tx(&full[s], A_STAGE_BYTES + subs_valid * W_SUB_BYTES);
+                            ptx::tma_load_3d(sA + s * A_STAGE_BYTES, &tmA, &full[s], kc * BK, row, b);
+                            for (int sub = 0; sub < subs_valid; ++sub)
+                                ptx::bulk_load(sB + s * SL::B_STAGE + sub * W_SUB_BYTES, wptr + sub * sub_stride, W_SUB_BYTES, &full[s]);
+                        }
                         wptr += W_SUB_BYTES;
                     }
+                    __syncwarp();
                     if (++kc == p.kb_per_tap) {
                         kc = 0;
                         row += p.tap_stride;
@@ -710,11 +762,13 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
         }
     } else if (warp == 9) {
         // ===================== MMA issuer =====================
-        // ONE thread runs the whole loop (no per-k-block warp reconvergence / elect), descriptors advance by adding to the
-        // 14-bit start-address field: ncu showed this warp instruction-latency bound at ~745 cycles per k-block of four
-        // N=128 MMAs whose tensor-pipe time is 256 (profiles/r1_vae_conv_ncu.md); a bare issue loop reaches 84 cycles/MMA.
-        if (lane == 0) {
+        // The WHOLE warp runs the loop on warp-uniform values (ring state, descriptors, TMEM address — the latter made
+        // provably uniform with a shuffle) and one elected lane issues.  tcgen05.mma / commit take their operands from
+        // UNIFORM registers: when a single divergent thread ran this loop every MMA was wrapped in an ELECT + 5x R2UR
+        // waterfall (~150 cycles per MMA, 650 per k-block against 256 of tensor-pipe time: profiles/r1_vae_conv_ncu.md).
+        {
             constexpr uint32_t idesc = ptx::umma_idesc_f16(BM, BN);
+            const uint32_t tmem_u = __shfl_sync(0xffffffffu, tmem_base, 0);
             const uint64_t desc_a0 = ptx::umma_desc_sw128(ptx::smem_u32(sA)), desc_b0 = ptx::umma_desc_sw128(ptx::smem_u32(sB));
             uint32_t s = 0, ph = 0;
             bool first = true;
@@ -725,29 +779,51 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
                 k_range(sp, kb0, kb1);
                 const int a = it & 1;
                 const uint32_t aph = (it >> 1) & 1;
+                if (lane == 0 && it == 8) trace_stamp(p, TR_T8_MMA_WAIT);
                 ptx::mbar_wait(&acc_empty[a], aph ^ 1);
+                if (SLAB) ptx::mbar_wait(&raw_full[it & 1], (it >> 1) & 1);  // this tile's activation slab has landed
                 ptx::tc_fence_after();
-                const uint32_t d_tmem = tmem_base + (uint32_t)(a * BN);
+                if (lane == 0 && it == 8) trace_stamp(p, TR_T8_MMA_GO);
+                const uint32_t d_tmem = tmem_u + (uint32_t)(a * BN);
                 uint32_t acc_flag = 0;
+                // SLAB: descriptor of (panel kc, row offset tap * dilation) inside the tile's slab, advanced incrementally
+                uint32_t slab_off = (uint32_t)((it & 1) * (SLAB_BYTES >> 4)) + (uint32_t)((kb0 / p.kb_per_tap) * p.tap_stride * 8);
+                int kc = kb0 % p.kb_per_tap;
                 for (int kb = kb0; kb < kb1; ++kb) {
                     ptx::mbar_wait(&full[s], ph);
                     ptx::tc_fence_after();
                     if (first) {
-                        trace_stamp(p, TR_FIRST_FULL);
+                        if (lane == 0) trace_stamp(p, TR_FIRST_FULL);
                         first = false;
                     }
-                    const uint64_t da = desc_a0 + (uint64_t)(s * (A_STAGE_BYTES >> 4)), db = desc_b0 + (uint64_t)(s * (SL::B_STAGE >> 4));
+                    const uint64_t da = SLAB ? desc_a0 + (uint64_t)(slab_off + (uint32_t)kc * (SLAB_PANEL_BYTES >> 4))
+                                             : desc_a0 + (uint64_t)(s * (A_STAGE_BYTES >> 4));
+                    const uint64_t db = desc_b0 + (uint64_t)(s * (SL::B_STAGE >> 4));
+                    if (SLAB && ++kc == p.kb_per_tap) {
+                        kc = 0;
+                        slab_off += (uint32_t)(p.tap_stride * 8);  // next tap: `dilation` rows of 128 bytes further down
+                    }
+                    if (ptx::elect_one()) {
 #pragma unroll
-                    for (int k = 0; k < BK / 16; ++k) ptx::umma_f16(d_tmem, da + 2 * k, db + 2 * k, idesc, k > 0 ? 1u : acc_flag);
+                        for (int k = 0; k < BK / 16; ++k) ptx::umma_f16(d_tmem, da + 2 * k, db + 2 * k, idesc, k > 0 ? 1u : acc_flag);
+                        ptx::umma_commit(&empty[s]);
+                    }
+                    __syncwarp();
                     acc_flag = 1;
-                    ptx::umma_commit(&empty[s]);
                     if (++s == (uint32_t)STAGES) {
                         s = 0;
                         ph ^= 1;
                     }
                 }
-                ptx::umma_commit(&acc_full[a]);
-                trace_stamp(p, TR_LAST_MMA);
+                if (ptx::elect_one()) {
+                    ptx::umma_commit(&acc_full[a]);
+                    if (SLAB) ptx::umma_commit(&raw_empty[it & 1]);  // every MMA reading this slab has completed
+                }
+                __syncwarp();
+                if (lane == 0) {
+                    trace_stamp(p, TR_LAST_MMA);
+                    if (it == 8) trace_stamp(p, TR_T8_MMA_DONE);
+                }
             }
         }
     } else if (QUANT && warp < 4) {
@@ -807,9 +883,11 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
                     stage_head_weights<BN, EPI_THREADS>(p, nt * BN, QUANT ? (int)threadIdx.x - 128 : (int)threadIdx.x, sCol);
                     epi_bar_sync(EPI_THREADS);
                 }
+                if (warp == 4 && lane == 0 && it == 8) trace_stamp(p, TR_T8_EPI_WAIT);
                 ptx::mbar_wait(&acc_full[a], aph);
                 ptx::tc_fence_after();
                 if (warp == 4 && lane == 0) trace_stamp(p, TR_ACC_READY);
+                if (warp == 4 && lane == 0 && it == 8) trace_stamp(p, TR_T8_EPI_GO);
             }
             const int l = l0 + q * 32 + lane;
             const uint32_t taddr = tmem_base + ((uint32_t)(q * 32) << 16) + (uint32_t)(a * BN);
@@ -853,6 +931,7 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
             __syncwarp();
             if (lane == 0) ptx::mbar_arrive(&acc_empty[a]);
             if (warp == 4 && lane == 0) trace_stamp(p, TR_EPI_DONE);
+            if (warp == 4 && lane == 0 && it == 8) trace_stamp(p, TR_T8_EPI_DONE);
             t += gridDim.x;
             ++it;
         }
@@ -946,8 +1025,8 @@ gemm_tc2_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__
     };
 
     if (warp == 8) {
-        // ===================== TMA producer (both CTAs) =====================
-        if (lane == 0) {
+        // ===================== TMA producer (both CTAs): whole warp, elected lane issues =====================
+        {
             uint32_t s = 0, ph = 0;
             const size_t sub_stride = (size_t)p.kb_total * W_SUB_BYTES;
             for (int t = cluster_id; t < total_tiles; t += n_clusters) {
@@ -960,9 +1039,12 @@ gemm_tc2_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__
                 const uint8_t* wptr = p.W + (size_t)(nt * 2 + (int)rank) * sub_stride + (size_t)kb0 * W_SUB_BYTES;
                 for (int kb = kb0; kb < kb1; ++kb) {
                     ptx::mbar_wait(&empty[s], ph ^ 1);
-                    ptx::mbar_expect_tx(&full[s], STAGE2_BYTES);
-                    ptx::tma_load_3d(sA + s * A_STAGE_BYTES, &tmA, &full[s], kc * BK, row, b);
-                    ptx::bulk_load(sB + s * W_SUB_BYTES, wptr, W_SUB_BYTES, &full[s]);
+                    if (ptx::elect_one()) {
+                        ptx::mbar_expect_tx(&full[s], STAGE2_BYTES);
+                        ptx::tma_load_3d(sA + s * A_STAGE_BYTES, &tmA, &full[s], kc * BK, row, b);
+                        ptx::bulk_load(sB + s * W_SUB_BYTES, wptr, W_SUB_BYTES, &full[s]);
+                    }
+                    __syncwarp();
                     wptr += W_SUB_BYTES;
                     if (++kc == p.kb_per_tap) {
                         kc = 0;
@@ -977,38 +1059,41 @@ gemm_tc2_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__
         }
     } else if (warp == 9) {
         if (rank == 0) {
-            // ===================== MMA issuer (leader CTA), one thread =====================
-            if (lane == 0) {
-                constexpr uint32_t idesc = ptx::umma_idesc_f16(2 * BM, BN);
-                const uint64_t desc_a0 = ptx::umma_desc_sw128(ptx::smem_u32(sA)), desc_b0 = ptx::umma_desc_sw128(ptx::smem_u32(sB));
-                uint32_t s = 0, ph = 0;
-                int it = 0;
-                for (int t = cluster_id; t < total_tiles; t += n_clusters, ++it) {
-                    int nt, sp, b, l0, kb0, kb1;
-                    decode_tile_index(t, nt, sp, b, l0);
-                    k_range(sp, kb0, kb1);
-                    const int a = it & 1;
-                    const uint32_t aph = (it >> 1) & 1;
-                    ptx::mbar_wait(&acc_empty[a], aph ^ 1);
+            // ===================== MMA issuer (leader CTA): whole warp on uniform values, elected lane issues =====================
+            constexpr uint32_t idesc = ptx::umma_idesc_f16(2 * BM, BN);
+            const uint32_t tmem_u = __shfl_sync(0xffffffffu, tmem_base, 0);
+            const uint64_t desc_a0 = ptx::umma_desc_sw128(ptx::smem_u32(sA)), desc_b0 = ptx::umma_desc_sw128(ptx::smem_u32(sB));
+            uint32_t s = 0, ph = 0;
+            int it = 0;
+            for (int t = cluster_id; t < total_tiles; t += n_clusters, ++it) {
+                int nt, sp, b, l0, kb0, kb1;
+                decode_tile_index(t, nt, sp, b, l0);
+                k_range(sp, kb0, kb1);
+                const int a = it & 1;
+                const uint32_t aph = (it >> 1) & 1;
+                ptx::mbar_wait(&acc_empty[a], aph ^ 1);
+                ptx::tc_fence_after();
+                const uint32_t d_tmem = tmem_u + (uint32_t)(a * BN);
+                uint32_t acc_flag = 0;
+                for (int kb = kb0; kb < kb1; ++kb) {
+                    ptx::mbar_wait(&full[s], ph);
+                    ptx::mbar_wait(&peer_full[s], ph);
                     ptx::tc_fence_after();
-                    const uint32_t d_tmem = tmem_base + (uint32_t)(a * BN);
-                    uint32_t acc_flag = 0;
-                    for (int kb = kb0; kb < kb1; ++kb) {
-                        ptx::mbar_wait(&full[s], ph);
-                        ptx::mbar_wait(&peer_full[s], ph);
-                        ptx::tc_fence_after();
-                        const uint64_t da = desc_a0 + (uint64_t)(s * (A_STAGE_BYTES >> 4)), db = desc_b0 + (uint64_t)(s * (W_SUB_BYTES >> 4));
+                    const uint64_t da = desc_a0 + (uint64_t)(s * (A_STAGE_BYTES >> 4)), db = desc_b0 + (uint64_t)(s * (W_SUB_BYTES >> 4));
+                    if (ptx::elect_one()) {
 #pragma unroll
                         for (int k = 0; k < BK / 16; ++k) ptx::umma_f16_2cta(d_tmem, da + 2 * k, db + 2 * k, idesc, k > 0 ? 1u : acc_flag);
-                        acc_flag = 1;
                         ptx::umma_commit_2cta(&empty[s], 3);
-                        if (++s == (uint32_t)STAGES2) {
-                            s = 0;
-                            ph ^= 1;
-                        }
                     }
-                    ptx::umma_commit_2cta(&acc_full[a], 3);
+                    __syncwarp();
+                    acc_flag = 1;
+                    if (++s == (uint32_t)STAGES2) {
+                        s = 0;
+                        ph ^= 1;
+                    }
                 }
+                if (ptx::elect_one()) ptx::umma_commit_2cta(&acc_full[a], 3);
+                __syncwarp();
             }
         } else {
             // ===================== relay (CTA 1): local "stage landed" -> leader's peer_full =====================
@@ -1235,13 +1320,13 @@ PFN_encodeTiled get_encode_fn() {
     return fn;
 }
 
-bool make_tmap_a(const GemmProblem& g, CUtensorMap* tm) {
+bool make_tmap_a(const GemmProblem& g, CUtensorMap* tm, int box_rows = BM) {
     PFN_encodeTiled enc = get_encode_fn();
     if (!enc) return false;
     const long bstride = g.B > 1 ? g.a_bstride : (long)g.L * g.a_lstride;
     cuuint64_t dims[3] = {(cuuint64_t)g.C, (cuuint64_t)g.L, (cuuint64_t)g.B};
     cuuint64_t strides[2] = {(cuuint64_t)g.a_lstride * 2, (cuuint64_t)bstride * 2};
-    cuuint32_t box[3] = {(cuuint32_t)BK, (cuuint32_t)BM, 1};
+    cuuint32_t box[3] = {(cuuint32_t)BK, (cuuint32_t)box_rows, 1};
     cuuint32_t estr[3] = {1, 1, 1};
     const CUresult r = enc(tm, CU_TENSOR_MAP_DATA_TYPE_FLOAT16, 3, const_cast<__half*>(g.A), dims, strides, box, estr,
                            CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_128B,
@@ -1334,6 +1419,19 @@ cudaError_t launch_tc(const CUtensorMap& tm, const CUtensorMap& tmo, const KPara
         attr_set = true;
     }
     return launch_pdl(gemm_tc_kernel<BN, QUANT, WARM>, dim3((unsigned)grid), dim3(NUM_THREADS), (size_t)SL::BYTES, stream, tm, tmo, kp);
+}
+
+cudaError_t launch_tc_slab(const CUtensorMap& tm, const CUtensorMap& tmo, const KParams& kp, int grid, cudaStream_t stream) {
+    using SL = SmemLayout<128, false>;
+    constexpr int BYTES = 2 * SLAB_BYTES + SL::STAGES * SL::B_STAGE + SL::STG_BYTES + SL::COL_BYTES + 256;
+    static_assert(BYTES <= 227 * 1024, "slab layout exceeds shared memory");
+    static bool attr_set = false;
+    if (!attr_set) {
+        cudaError_t e = cudaFuncSetAttribute(gemm_tc_kernel<128, false, false, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, BYTES);
+        if (e != cudaSuccess) return e;
+        attr_set = true;
+    }
+    return launch_pdl(gemm_tc_kernel<128, false, false, true>, dim3((unsigned)grid), dim3(NUM_THREADS), (size_t)BYTES, stream, tm, tmo, kp);
 }
 
 }  // namespace
@@ -1467,9 +1565,18 @@ cudaError_t gemm_launch(const GemmProblem& g, cudaStream_t stream, bool simt) {
         return cudaGetLastError();
     }
 
-    CUtensorMap tm;
-    if (!make_tmap_a(g, &tm)) return cudaErrorInvalidValue;
     const long tiles = tiles_nosplit * kp.split_k;
+    // activation slab (see gemm_tc_kernel): stride-d taps over <= 128 channels, 128-column tiles, persistent launches only
+    kp.slab_rows = 0;
+    {
+        const int rows = BM + (w.taps - 1) * g.tap_stride;
+        bool slab = kp.wtype == W_F16 && !pair && !bn256 && kp.split_k == 1 && w.taps > 1 && g.tap_stride >= 1 && kp.kb_per_tap <= 2 &&
+                    rows <= SLAB_MAX_ROWS && !kp.warm_epi && tiles >= 2L * sms;
+        if (const char* fs = std::getenv("ACE_B200_GEMM_SLAB")) slab = slab && std::atoi(fs) != 0;
+        if (slab) kp.slab_rows = rows;
+    }
+    CUtensorMap tm;
+    if (!make_tmap_a(g, &tm, kp.slab_rows ? kp.slab_rows : BM)) return cudaErrorInvalidValue;
     kp.trace = nullptr;
     static long long* trace_buf = nullptr;
     const bool tracing = std::getenv("ACE_B200_GEMM_TRACE") != nullptr && !pair;
@@ -1486,12 +1593,20 @@ cudaError_t gemm_launch(const GemmProblem& g, cudaStream_t stream, bool simt) {
             std::vector<long long> h((size_t)ctas * TR_N);
             cudaMemcpy(h.data(), buf, h.size() * sizeof(long long), cudaMemcpyDeviceToHost);
             double acc[TR_N] = {0};
-            for (int c = 0; c < ctas; ++c)
+            double waited = 0;
+            for (int c = 0; c < ctas; ++c) {
                 for (int i = 0; i < TR_N; ++i) acc[i] += (double)(h[(size_t)c * TR_N + i] - h[(size_t)c * TR_N + TR_START]);
+                waited += (double)h[(size_t)c * TR_N + 15];
+            }
             std::fprintf(stderr, "[gemm trace] M=%d N=%d K=%d bn=%d sk=%d ctas=%d | cycles from CTA start (mean): setup %.0f first_full %.0f last_mma_issued %.0f "
                                  "acc_ready(last tile) %.0f ld0 %.0f chunk0 %.0f epi_done(last tile) %.0f end %.0f\n", M, N, K, bn, sk, ctas, acc[TR_SETUP] / ctas,
                          acc[TR_FIRST_FULL] / ctas, acc[TR_LAST_MMA] / ctas, acc[TR_ACC_READY] / ctas, acc[TR_EPI_LD0] / ctas, acc[TR_EPI_CHUNK0] / ctas,
                          acc[TR_EPI_DONE] / ctas, acc[TR_END] / ctas);
+            if (acc[TR_T8_MMA_DONE] > 0)
+                std::fprintf(stderr, "             9th tile of a CTA, cycles from the MMA thread reaching it: accumulator free +%.0f, MMAs issued +%.0f | epilogue warp: "
+                                     "starts waiting %+.0f, accumulator ready %+.0f, done %+.0f | MMA thread waited %.0f cycles for operands\n", (acc[TR_T8_MMA_GO] - acc[TR_T8_MMA_WAIT]) / ctas,
+                             (acc[TR_T8_MMA_DONE] - acc[TR_T8_MMA_WAIT]) / ctas, (acc[TR_T8_EPI_WAIT] - acc[TR_T8_MMA_WAIT]) / ctas,
+                             (acc[TR_T8_EPI_GO] - acc[TR_T8_MMA_WAIT]) / ctas, (acc[TR_T8_EPI_DONE] - acc[TR_T8_MMA_WAIT]) / ctas, waited / ctas);
         }
     } trace_dump{tracing, trace_buf, (int)(tiles < sms ? tiles : sms), stream, g.B * g.l_out, w.N, w.K * w.taps, bn256 ? 256 : 128, kp.split_k};
     // accumulate epilogue as TMA reduce-add tiles (plain [B, l_out, N] fp32 output, no crop shift); ACE_B200_GEMM_TMARED=0 = red.add
@@ -1512,6 +1627,7 @@ cudaError_t gemm_launch(const GemmProblem& g, cudaStream_t stream, bool simt) {
     if (pair) return launch_tc2(tm, tmo, kp, (int)(tiles < units ? tiles : units), stream);
     const int grid = (int)(tiles < sms ? tiles : sms);
     const bool quant = kp.wtype != W_F16;
+    if (kp.slab_rows) return launch_tc_slab(tm, tmo, kp, grid, stream);
     if (kp.warm_epi) {
         if (bn256) return quant ? launch_tc<256, true, true>(tm, tmo, kp, grid, stream) : launch_tc<256, false, true>(tm, tmo, kp, grid, stream);
         return quant ? launch_tc<128, true, true>(tm, tmo, kp, grid, stream) : launch_tc<128, false, true>(tm, tmo, kp, grid, stream);

@@ -13,7 +13,7 @@ constexpr int OPER = 3 * 49152;         // MMA operand stages
 constexpr int RING = 2 * 16384;         // TMA noise ring
 constexpr int STG = 8 * 4096;           // LSU noise buffers
 template <int N>
-__global__ void __launch_bounds__(320) probe(int noise, int iters, const uint8_t* gsrc, long long* cycles, float* sink) {
+__global__ void __launch_bounds__(320) probe(int noise, int iters, const uint8_t* gsrc, long long* cycles, float* sink, long long* ldcount) {
     extern __shared__ __align__(1024) uint8_t smem[];
     __shared__ uint64_t bar, nbar[2];
     __shared__ uint32_t slot;
@@ -33,6 +33,7 @@ __global__ void __launch_bounds__(320) probe(int noise, int iters, const uint8_t
             const uint64_t da0 = umma_desc_sw128(smem_u32(smem)), db0 = umma_desc_sw128(smem_u32(smem) + 16384);
             long long t0 = clock64();
             uint32_t s = 0;
+            if (iters < 0) while (clock64() - t0 < 2000000) {}
             for (int i = 0; i < iters; i += 4) {
                 const uint64_t da = da0 + (uint64_t)(s * (49152 >> 4)), db = db0 + (uint64_t)(s * (49152 >> 4));
 #pragma unroll
@@ -84,11 +85,14 @@ __global__ void __launch_bounds__(320) probe(int noise, int iters, const uint8_t
         }
         if ((noise == 3 || noise == 5) && w < 4) {
             uint32_t r[32];
+            long long n = 0;
             while (!done) {
                 tmem_ld32(tb + ((uint32_t)(w * 32) << 16) + 256, r);   // the accumulator buffer the MMAs do NOT write
                 tmem_ld_wait();
                 acc += __uint_as_float(r[lane]);
+                ++n;
             }
+            if (lane == 0) ldcount[blockIdx.x * 4 + w] = n;
         }
         if (acc == 123.456f) sink[threadIdx.x] = acc;
     }
@@ -98,12 +102,12 @@ __global__ void __launch_bounds__(320) probe(int noise, int iters, const uint8_t
 }
 
 template <int N>
-void run(int grid, const uint8_t* g, long long* cyc, float* sink) {
+void run(int grid, const uint8_t* g, long long* cyc, float* sink, long long* ldc) {
     const int smem_bytes = OPER + RING + STG;
     cudaFuncSetAttribute(probe<N>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem_bytes);
     for (int noise = 0; noise < 6; ++noise) {
         const int iters = 20000;
-        for (int rep = 0; rep < 2; ++rep) probe<N><<<grid, 320, smem_bytes>>>(noise, iters, g, cyc, sink);
+        for (int rep = 0; rep < 2; ++rep) probe<N><<<grid, 320, smem_bytes>>>(noise, iters, g, cyc, sink, ldc);
         cudaError_t e = cudaGetLastError(); if (e == cudaSuccess) e = cudaDeviceSynchronize();
         if (e != cudaSuccess) { printf("failed: %s\n", cudaGetErrorString(e)); exit(1); }
         std::vector<long long> h(2 * grid);
@@ -112,6 +116,20 @@ void run(int grid, const uint8_t* g, long long* cyc, float* sink) {
         for (int i = 0; i < grid; ++i) { a += h[2 * i]; b += h[2 * i + 1]; }
         printf("N=%3d grid %3d noise %d: issue %6.1f cycles/MMA, complete %6.1f cycles/MMA (tensor-pipe floor %d)\n", N, grid, noise, a / grid / iters,
                b / grid / iters, N / 2);
+        if (noise == 3) {  // how fast do the tcgen05.ld warps run next to the MMA stream, and with the tensor pipe idle?
+            std::vector<long long> hc(4 * grid);
+            cudaMemcpy(hc.data(), ldc, hc.size() * 8, cudaMemcpyDeviceToHost);
+            double n = 0;
+            for (auto v : hc) n += (double)v;
+            const double busy = (b / grid) / (n / (4 * grid));
+            probe<N><<<grid, 320, smem_bytes>>>(noise, -1, g, cyc, sink, ldc);
+            cudaDeviceSynchronize();
+            cudaMemcpy(hc.data(), ldc, hc.size() * 8, cudaMemcpyDeviceToHost);
+            n = 0;
+            for (auto v : hc) n += (double)v;
+            printf("      tcgen05.ld 32x32b.x32 + wait, 4 warps: %.0f cycles per load next to the MMA stream, %.0f with the tensor pipe idle\n", busy,
+                   2000000.0 / (n / (4 * grid)));
+        }
     }
 }
 
@@ -123,7 +141,9 @@ int main() {
     uint8_t* g;
     cudaMalloc(&g, 148 * 65536);
     cudaMemset(g, 0, 148 * 65536);
-    run<128>(148, g, cyc, sink);
-    run<256>(148, g, cyc, sink);
+    long long* ldc;
+    cudaMalloc(&ldc, 148 * 4 * 8);
+    run<128>(148, g, cyc, sink, ldc);
+    run<256>(148, g, cyc, sink, ldc);
     return 0;
 }

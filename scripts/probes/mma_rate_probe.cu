@@ -2,6 +2,8 @@
 // already sit in shared memory (K-major, 128-byte swizzle; contents irrelevant), no loads, no epilogue.
 //   variant 0: every MMA accumulates into the same TMEM tile          variant 1: two accumulators alternate
 //   variant 2: operands walk 4 k-slices of 4 stages like the GEMM main loop (same chain), commit per 4 MMAs
+//   variant 3: variant 2 + tcgen05.fence::after_thread_sync before every group of 4 (as after an mbarrier wait)
+//   variant 4: variant 3 + a try_wait on an already completed mbarrier before the fence
 // build: nvcc -O3 -std=c++17 -gencode arch=compute_100a,code=sm_100a -I ace-step-1.5-ggml_b200/csrc scripts/probes/mma_rate_probe.cu -o /tmp/m
 #include <cuda_runtime.h>
 #include <cstdio>
@@ -12,11 +14,11 @@ using namespace ptx;
 template <int N>
 __global__ void __launch_bounds__(128) probe(int variant, int iters, long long* cycles) {
     extern __shared__ __align__(1024) uint8_t smem[];
-    __shared__ uint64_t bar;
+    __shared__ uint64_t bar, ready;
     __shared__ uint32_t slot;
     const int warp = threadIdx.x >> 5;
     for (int i = threadIdx.x; i < (4 * 49152) / 4; i += blockDim.x) reinterpret_cast<uint32_t*>(smem)[i] = 0x3c003c00u;  // 1.0h
-    if (threadIdx.x == 0) { mbar_init(&bar, 1); fence_mbar_init(); }
+    if (threadIdx.x == 0) { mbar_init(&bar, 1); mbar_init(&ready, 1); fence_mbar_init(); mbar_arrive(&ready); }
     if (warp == 0) tmem_alloc<512>(&slot);
     fence_proxy_async_smem();
     tc_fence_before();
@@ -28,17 +30,21 @@ __global__ void __launch_bounds__(128) probe(int variant, int iters, long long* 
         const uint32_t a0 = smem_u32(smem), b0 = a0 + 16384;
         long long t0 = clock64();
         for (int i = 0; i < iters; ++i) {
-            const int s = (variant == 2) ? (i >> 2) & 3 : 0;
-            const int k = (variant == 2) ? (i & 3) : 0;
+            const int s = (variant >= 2) ? (i >> 2) & 3 : 0;
+            const int k = (variant >= 2) ? (i & 3) : 0;
+            if (variant >= 3 && k == 0) {
+                if (variant == 4) mbar_wait(&ready, 0);
+                tc_fence_after();
+            }
             const uint64_t da = umma_desc_sw128(a0 + s * 49152 + k * 32), db = umma_desc_sw128(b0 + s * 49152 + k * 32);
             const uint32_t d = tb + ((variant == 1 && (i & 1)) ? 256u : 0u);
             umma_f16(d, da, db, idesc, i > 1 ? 1u : 0u);
-            if (variant == 2 && (i & 3) == 3) umma_commit(&bar);   // one commit per "k-block" (arrivals just cycle the phase)
+            if (variant >= 2 && (i & 3) == 3) umma_commit(&bar);   // one commit per "k-block" (arrivals just cycle the phase)
         }
         umma_commit(&bar);
         const long long t1 = clock64();
         // variant 2 cycled the barrier many times: just wait for quiescence by polling both parities briefly
-        if (variant != 2) mbar_wait(&bar, 0);
+        if (variant < 2) mbar_wait(&bar, 0);
         else { for (int j = 0; j < 200000; ++j) asm volatile("nanosleep.u32 20;"); }
         const long long t2 = clock64();
         cycles[blockIdx.x * 2] = t1 - t0;
@@ -52,7 +58,7 @@ __global__ void __launch_bounds__(128) probe(int variant, int iters, long long* 
 template <int N>
 void run(int grid, long long* cyc) {
     cudaFuncSetAttribute(probe<N>, cudaFuncAttributeMaxDynamicSharedMemorySize, 4 * 49152);
-    for (int variant = 0; variant < 3; ++variant) {
+    for (int variant = 0; variant < 5; ++variant) {
         const int iters = 20000;
         for (int rep = 0; rep < 2; ++rep) probe<N><<<grid, 128, 4 * 49152>>>(variant, iters, cyc);
         cudaError_t e = cudaDeviceSynchronize();

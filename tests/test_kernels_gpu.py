@@ -98,6 +98,29 @@ def test_gemm_conv7(br, dil):
     assert rel_err(out, ref) < 1e-4
 
 
+@pytest.mark.parametrize("dil,C", [(1, 128), (3, 128), (9, 128), (1, 64)])
+def test_gemm_conv7_activation_slab(br, dil, C, monkeypatch):
+    """persistent k7 convolution (>= 2 tiles per SM) through the activation-slab route — the tile's 128 + 6*dilation rows
+    staged once, taps read at row offsets — against the per-k-block route: same MMAs in the same order, so bit-identical;
+    and against the float64 restatement on the first / last rows (zero padding on both ends, ragged last tile) and a middle slice."""
+    g = np.random.default_rng(100 + dil)
+    B, L, N = 2, 148 * 128 + 77, 128
+    A = g.standard_normal((B, L, C), dtype=np.float32)
+    W = (g.standard_normal((N, 7, C), dtype=np.float32) * (7 * C) ** -0.5).astype(np.float32)
+    bias = g.standard_normal((N,), dtype=np.float32)
+    kw = dict(w_type=0, N=N, bias=bias, taps=7, tap_stride=dil, tap_offset=-3 * dil)
+    monkeypatch.setenv("ACE_B200_GEMM_SLAB", "0")
+    plain = br.debug_gemm(A, W, **kw)
+    monkeypatch.setenv("ACE_B200_GEMM_SLAB", "1")
+    slab = br.debug_gemm(A, W, **kw)
+    assert np.array_equal(plain, slab)
+    for lo, hi in ((0, 300), (L // 2, L // 2 + 300), (L - 300, L)):
+        pad = 3 * dil
+        a0, a1 = max(0, lo - pad), min(L, hi + pad)
+        ref = tap_gemm_ref(h16(A[:, a0:a1]), h16(W), 7, dil, -3 * dil, a1 - a0)[:, lo - a0:hi - a0] + bias
+        assert rel_err(slab[:, lo:hi], ref) < 1e-4, (lo, hi)
+
+
 def test_gemm_conv_transpose_phases(br):
     """conv-transpose k=2s as 2 taps (rows i, i-1) x s phase columns (acestep_vae_model.cpp:696-707)."""
     g = np.random.default_rng(11)

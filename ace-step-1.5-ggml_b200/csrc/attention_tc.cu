@@ -652,7 +652,7 @@ attention_tcp_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_const
 
     if (warp == 4) {
         // ===================== producer =====================
-        if (lane == 0) {
+        if (ptx::elect_one()) {
             ptx::mbar_expect_tx(q_full, Q_BYTES);
             ptx::tma_load_4d(sQ, &tmQ, q_full, 0, h, q0, b);
             ptx::tma_load_4d(sQ + Q_BYTES / 2, &tmQ, q_full, 64, h, q0, b);
@@ -667,14 +667,14 @@ attention_tcp_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_const
             const bool ok_b = kb2 < p.k_len && (!mb || mb[kb2] != 0);
             const uint32_t lo = __ballot_sync(0xffffffffu, ok_a), hi = __ballot_sync(0xffffffffu, ok_b);
             ptx::mbar_wait(&k_empty[s], ph ^ 1);
-            if (lane == 0) {
+            if (ptx::elect_one()) {
                 kmask[j & 3] = (uint64_t)lo | ((uint64_t)hi << 32);
                 ptx::mbar_expect_tx(&k_full[s], KV_TILE);
                 ptx::tma_load_4d(sK + s * KV_TILE, &tmK, &k_full[s], 0, hk, k0, b);
                 ptx::tma_load_4d(sK + s * KV_TILE + KV_TILE / 2, &tmK, &k_full[s], 64, hk, k0, b);
             }
             ptx::mbar_wait(&v_empty[s], ph ^ 1);
-            if (lane == 0) {
+            if (ptx::elect_one()) {
                 ptx::mbar_expect_tx(&v_full[s], KV_TILE);
                 ptx::tma_load_4d(sV + s * KV_TILE, &tmV, &v_full[s], 0, hk, k0, b);
                 ptx::tma_load_4d(sV + s * KV_TILE + KV_TILE / 2, &tmV, &v_full[s], 64, hk, k0, b);
@@ -683,31 +683,37 @@ attention_tcp_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_const
         }
     } else if (warp == 5) {
         // ===================== MMA issuer =====================
+        // whole warp on warp-uniform values, one elected lane issues: tcgen05.mma takes uniform-register operands, a
+        // `lane == 0` block on per-thread values costs an ELECT + R2UR waterfall per instruction (see gemm_sm100.cu)
         constexpr uint32_t idesc_s = ptx::umma_idesc_f16(BQ, BKV);
         constexpr uint32_t idesc_o = ptx::umma_idesc_f16_bmn(BQ, HD);
-        const uint32_t q_addr = ptx::smem_u32(sQ);
+        const uint32_t tmem_u = __shfl_sync(0xffffffffu, tmem_base, 0);
+        const uint64_t dq0 = ptx::umma_desc_sw128(ptx::smem_u32(sQ));
+        const uint64_t dk0 = ptx::umma_desc_sw128(ptx::smem_u32(sK));
+        const uint64_t dv0 = ptx::umma_desc_mn_sw128(ptx::smem_u32(sV), KV_TILE / 2, 1024);
         auto issue_s = [&](int j) {  // S[j&1] = Q . K_j^T, then release the K stage
             const int s = j & 1;
-            const uint32_t k_addr = ptx::smem_u32(sK + s * KV_TILE);
+            const uint64_t dk = dk0 + (uint64_t)(s * (KV_TILE >> 4));
+            if (ptx::elect_one()) {
 #pragma unroll
-            for (int kk = 0; kk < HD / 16; ++kk) {
-                const uint64_t da = ptx::umma_desc_sw128(q_addr + (kk >> 2) * (Q_BYTES / 2) + (kk & 3) * 32);
-                const uint64_t db = ptx::umma_desc_sw128(k_addr + (kk >> 2) * (KV_TILE / 2) + (kk & 3) * 32);
-                ptx::umma_f16(tmem_base + (uint32_t)(s * BKV), da, db, idesc_s, kk > 0 ? 1u : 0u);
+                for (int kk = 0; kk < HD / 16; ++kk) {
+                    const uint64_t da = dq0 + (uint64_t)(((kk >> 2) * (Q_BYTES / 2) + (kk & 3) * 32) >> 4);
+                    const uint64_t db = dk + (uint64_t)(((kk >> 2) * (KV_TILE / 2) + (kk & 3) * 32) >> 4);
+                    ptx::umma_f16(tmem_u + (uint32_t)(s * BKV), da, db, idesc_s, kk > 0 ? 1u : 0u);
+                }
+                ptx::umma_commit(&s_ready[s]);
+                ptx::umma_commit(&k_empty[s]);
             }
-            ptx::umma_commit(&s_ready[s]);
-            ptx::umma_commit(&k_empty[s]);
+            __syncwarp();
         };
         ptx::mbar_wait(q_full, 0);
         ptx::mbar_wait(&k_full[0], 0);
         ptx::tc_fence_after();
-        if (lane == 0) issue_s(0);
-        __syncwarp();
+        issue_s(0);
         if (n_tiles > 1) {
             ptx::mbar_wait(&k_full[1], 0);
             ptx::tc_fence_after();
-            if (lane == 0) issue_s(1);
-            __syncwarp();
+            issue_s(1);
         }
         for (int j = 0; j < n_tiles; ++j) {
             const int s = j & 1;
@@ -715,13 +721,12 @@ attention_tcp_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_const
             ptx::mbar_wait(&p_ready[s], ph);
             ptx::mbar_wait(&v_full[s], ph);
             ptx::tc_fence_after();
-            if (lane == 0) {
-                const uint32_t v_addr = ptx::smem_u32(sV + s * KV_TILE);
+            const uint64_t dv = dv0 + (uint64_t)(s * (KV_TILE >> 4));
+            const uint32_t acc = j > 0 ? 1u : 0u;
+            if (ptx::elect_one()) {
 #pragma unroll
-                for (int kk = 0; kk < BKV / 16; ++kk) {  // A = P_j from TMEM: 16 keys = 8 packed columns per step
-                    const uint64_t db = ptx::umma_desc_mn_sw128(v_addr + kk * 2048, KV_TILE / 2, 1024);
-                    ptx::umma_f16_ts(tmem_base + 128u, tmem_base + (uint32_t)(s * BKV + kk * 8), db, idesc_o, (j > 0 || kk > 0) ? 1u : 0u);
-                }
+                for (int kk = 0; kk < BKV / 16; ++kk)  // A = P_j from TMEM: 16 keys = 8 packed columns per step
+                    ptx::umma_f16_ts(tmem_u + 128u, tmem_u + (uint32_t)(s * BKV + kk * 8), dv + (uint64_t)((kk * 2048) >> 4), idesc_o, kk > 0 ? 1u : acc);
                 ptx::umma_commit(&v_empty[s]);
                 ptx::umma_commit(&pv_done[s]);
             }
@@ -729,8 +734,7 @@ attention_tcp_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_const
             if (j + 2 < n_tiles) {
                 ptx::mbar_wait(&k_full[s], ((j + 2) >> 1) & 1);
                 ptx::tc_fence_after();
-                if (lane == 0) issue_s(j + 2);
-                __syncwarp();
+                issue_s(j + 2);
             }
         }
     } else {

@@ -789,9 +789,16 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
                 // SLAB: descriptor of (panel kc, row offset tap * dilation) inside the tile's slab, advanced incrementally
                 uint32_t slab_off = (uint32_t)((it & 1) * (SLAB_BYTES >> 4)) + (uint32_t)((kb0 / p.kb_per_tap) * p.tap_stride * 8);
                 int kc = kb0 % p.kb_per_tap;
+                long long waited = 0;
                 for (int kb = kb0; kb < kb1; ++kb) {
+                    const bool timed = p.trace != nullptr && it == 8;
+                    const long long tw = timed ? clock64() : 0;
                     ptx::mbar_wait(&full[s], ph);
                     ptx::tc_fence_after();
+                    if (timed) {
+                        waited += clock64() - tw;
+                        if (lane == 0) p.trace[(size_t)blockIdx.x * TR_N + 15] = waited;  // cycles waiting for operands in the 9th tile
+                    }
                     if (first) {
                         if (lane == 0) trace_stamp(p, TR_FIRST_FULL);
                         first = false;

@@ -13,13 +13,17 @@ constexpr int OPER = 3 * 49152;         // MMA operand stages
 constexpr int RING = 2 * 16384;         // TMA noise ring
 constexpr int STG = 8 * 4096;           // LSU noise buffers
 template <int N>
-__global__ void __launch_bounds__(320) probe(int noise, int iters, const uint8_t* gsrc, long long* cycles, float* sink, long long* ldcount) {
+__global__ void __launch_bounds__(320) probe(int noise, int iters, const uint8_t* gsrc, long long* cycles, float* sink, long long* ldcount, int random_data) {
     extern __shared__ __align__(1024) uint8_t smem[];
     __shared__ uint64_t bar, nbar[2];
     __shared__ uint32_t slot;
     __shared__ volatile int done;
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-    for (int i = threadIdx.x; i < OPER / 4; i += blockDim.x) reinterpret_cast<uint32_t*>(smem)[i] = 0x3c003c00u;
+    for (int i = threadIdx.x; i < OPER / 4; i += blockDim.x) {  // operands: all 1.0, or random fp16 in (-2, 2) (data toggling = power)
+        uint32_t h = (uint32_t)i * 2654435761u + blockIdx.x * 40503u;
+        h ^= h >> 15; h *= 2246822519u; h ^= h >> 13;
+        reinterpret_cast<uint32_t*>(smem)[i] = random_data ? ((h & 0x83ff83ffu) | 0x3c003c00u) : 0x3c003c00u;
+    }
     if (threadIdx.x == 0) { mbar_init(&bar, 1); mbar_init(&nbar[0], 1); mbar_init(&nbar[1], 1); fence_mbar_init(); done = 0; }
     if (warp == 0) tmem_alloc<512>(&slot);
     fence_proxy_async_smem();
@@ -102,19 +106,20 @@ __global__ void __launch_bounds__(320) probe(int noise, int iters, const uint8_t
 }
 
 template <int N>
-void run(int grid, const uint8_t* g, long long* cyc, float* sink, long long* ldc) {
+void run(int grid, const uint8_t* g, long long* cyc, float* sink, long long* ldc, int rnd, int iters_arg) {
     const int smem_bytes = OPER + RING + STG;
     cudaFuncSetAttribute(probe<N>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem_bytes);
     for (int noise = 0; noise < 6; ++noise) {
-        const int iters = 20000;
-        for (int rep = 0; rep < 2; ++rep) probe<N><<<grid, 320, smem_bytes>>>(noise, iters, g, cyc, sink, ldc);
+        const int iters = iters_arg;
+        if (rnd && noise != 0 && noise != 5) continue;
+        for (int rep = 0; rep < 2; ++rep) probe<N><<<grid, 320, smem_bytes>>>(noise, iters, g, cyc, sink, ldc, rnd);
         cudaError_t e = cudaGetLastError(); if (e == cudaSuccess) e = cudaDeviceSynchronize();
         if (e != cudaSuccess) { printf("failed: %s\n", cudaGetErrorString(e)); exit(1); }
         std::vector<long long> h(2 * grid);
         cudaMemcpy(h.data(), cyc, 2 * grid * 8, cudaMemcpyDeviceToHost);
         double a = 0, b = 0;
         for (int i = 0; i < grid; ++i) { a += h[2 * i]; b += h[2 * i + 1]; }
-        printf("N=%3d grid %3d noise %d: issue %6.1f cycles/MMA, complete %6.1f cycles/MMA (tensor-pipe floor %d)\n", N, grid, noise, a / grid / iters,
+        printf("%s N=%3d grid %3d noise %d: issue %6.1f cycles/MMA, complete %6.1f cycles/MMA (tensor-pipe floor %d)\n", rnd ? "random operands, 2M MMAs" : "all-1.0 operands", N, grid, noise, a / grid / iters,
                b / grid / iters, N / 2);
         if (noise == 3) {  // how fast do the tcgen05.ld warps run next to the MMA stream, and with the tensor pipe idle?
             std::vector<long long> hc(4 * grid);
@@ -122,7 +127,7 @@ void run(int grid, const uint8_t* g, long long* cyc, float* sink, long long* ldc
             double n = 0;
             for (auto v : hc) n += (double)v;
             const double busy = (b / grid) / (n / (4 * grid));
-            probe<N><<<grid, 320, smem_bytes>>>(noise, -1, g, cyc, sink, ldc);
+            probe<N><<<grid, 320, smem_bytes>>>(noise, -1, g, cyc, sink, ldc, rnd);
             cudaDeviceSynchronize();
             cudaMemcpy(hc.data(), ldc, hc.size() * 8, cudaMemcpyDeviceToHost);
             n = 0;
@@ -143,7 +148,9 @@ int main() {
     cudaMemset(g, 0, 148 * 65536);
     long long* ldc;
     cudaMalloc(&ldc, 148 * 4 * 8);
-    run<128>(148, g, cyc, sink, ldc);
-    run<256>(148, g, cyc, sink, ldc);
+    run<128>(148, g, cyc, sink, ldc, 0, 20000);
+    run<256>(148, g, cyc, sink, ldc, 0, 20000);
+    run<128>(148, g, cyc, sink, ldc, 1, 2000000);
+    run<256>(148, g, cyc, sink, ldc, 1, 2000000);
     return 0;
 }

@@ -12,12 +12,17 @@
 using namespace ptx;
 
 template <int N>
-__global__ void __launch_bounds__(128) probe(int variant, int iters, long long* cycles) {
+__global__ void __launch_bounds__(128) probe(int variant, int iters, long long* cycles, int random_data) {
     extern __shared__ __align__(1024) uint8_t smem[];
     __shared__ uint64_t bar, ready;
     __shared__ uint32_t slot;
     const int warp = threadIdx.x >> 5;
-    for (int i = threadIdx.x; i < (4 * 49152) / 4; i += blockDim.x) reinterpret_cast<uint32_t*>(smem)[i] = 0x3c003c00u;  // 1.0h
+    for (int i = threadIdx.x; i < (4 * 49152) / 4; i += blockDim.x) {
+        uint32_t h = (uint32_t)i * 2654435761u + blockIdx.x * 40503u;
+        h ^= h >> 15; h *= 2246822519u; h ^= h >> 13;
+        // random_data: two fp16 values in (-2, 2) with random mantissas (exponent bits 0x3c00 | sign) instead of all 1.0
+        reinterpret_cast<uint32_t*>(smem)[i] = random_data ? ((h & 0x83ff83ffu) | 0x3c003c00u) : 0x3c003c00u;
+    }
     if (threadIdx.x == 0) { mbar_init(&bar, 1); mbar_init(&ready, 1); fence_mbar_init(); mbar_arrive(&ready); }
     if (warp == 0) tmem_alloc<512>(&slot);
     fence_proxy_async_smem();
@@ -56,18 +61,18 @@ __global__ void __launch_bounds__(128) probe(int variant, int iters, long long* 
 }
 
 template <int N>
-void run(int grid, long long* cyc) {
+void run(int grid, long long* cyc, int rnd) {
     cudaFuncSetAttribute(probe<N>, cudaFuncAttributeMaxDynamicSharedMemorySize, 4 * 49152);
-    for (int variant = 0; variant < 5; ++variant) {
-        const int iters = 20000;
-        for (int rep = 0; rep < 2; ++rep) probe<N><<<grid, 128, 4 * 49152>>>(variant, iters, cyc);
+    for (int variant = 0; variant < 1; ++variant) {
+        const int iters = 400000;
+        for (int rep = 0; rep < 2; ++rep) probe<N><<<grid, 128, 4 * 49152>>>(variant, iters, cyc, rnd);
         cudaError_t e = cudaDeviceSynchronize();
         if (e != cudaSuccess) { printf("failed: %s\n", cudaGetErrorString(e)); exit(1); }
         std::vector<long long> h(2 * grid);
         cudaMemcpy(h.data(), cyc, 2 * grid * 8, cudaMemcpyDeviceToHost);
         double a = 0, b = 0;
         for (int i = 0; i < grid; ++i) { a += h[2 * i]; b += h[2 * i + 1]; }
-        printf("N=%3d grid %3d variant %d: issue %6.1f cycles/MMA, complete %6.1f cycles/MMA (floor %d)  -> %.0f flop/clk/SM\n", N, grid, variant,
+        printf("%s data N=%3d grid %3d variant %d: issue %6.1f cycles/MMA, complete %6.1f cycles/MMA (floor %d)  -> %.0f flop/clk/SM\n", rnd ? "random" : "all-1.0", N, grid, variant,
                a / grid / iters, b / grid / iters, N / 2, 128.0 * N * 16 * 2 / (b / grid / iters));
     }
 }
@@ -75,10 +80,10 @@ void run(int grid, long long* cyc) {
 int main() {
     long long* cyc;
     cudaMalloc(&cyc, 148 * 16);
-    for (int grid : {1, 148}) {
-        run<64>(grid, cyc);
-        run<128>(grid, cyc);
-        run<256>(grid, cyc);
-    }
+    for (int rnd : {0, 1})
+        for (int grid : {1, 148}) {
+            run<128>(grid, cyc, rnd);
+            run<256>(grid, cyc, rnd);
+        }
     return 0;
 }

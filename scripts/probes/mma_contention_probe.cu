@@ -15,16 +15,18 @@ constexpr int STG = 8 * 4096;           // LSU noise buffers
 template <int N>
 __global__ void __launch_bounds__(320) probe(int noise, int iters, const uint8_t* gsrc, long long* cycles, float* sink, long long* ldcount, int random_data) {
     extern __shared__ __align__(1024) uint8_t smem[];
-    __shared__ uint64_t bar, nbar[2];
+    __shared__ uint64_t bar, nbar[2], ready, cyc_bar;
     __shared__ uint32_t slot;
     __shared__ volatile int done;
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    const bool handshake = noise >= 10;
+    if (handshake) noise -= 10;
     for (int i = threadIdx.x; i < OPER / 4; i += blockDim.x) {  // operands: all 1.0, or random fp16 in (-2, 2) (data toggling = power)
         uint32_t h = (uint32_t)i * 2654435761u + blockIdx.x * 40503u;
         h ^= h >> 15; h *= 2246822519u; h ^= h >> 13;
         reinterpret_cast<uint32_t*>(smem)[i] = random_data ? ((h & 0x83ff83ffu) | 0x3c003c00u) : 0x3c003c00u;
     }
-    if (threadIdx.x == 0) { mbar_init(&bar, 1); mbar_init(&nbar[0], 1); mbar_init(&nbar[1], 1); fence_mbar_init(); done = 0; }
+    if (threadIdx.x == 0) { mbar_init(&bar, 1); mbar_init(&nbar[0], 1); mbar_init(&nbar[1], 1); mbar_init(&ready, 1); mbar_init(&cyc_bar, 1); fence_mbar_init(); mbar_arrive(&ready); done = 0; }
     if (warp == 0) tmem_alloc<512>(&slot);
     fence_proxy_async_smem();
     tc_fence_before();
@@ -40,8 +42,13 @@ __global__ void __launch_bounds__(320) probe(int noise, int iters, const uint8_t
             if (iters < 0) while (clock64() - t0 < 2000000) {}
             for (int i = 0; i < iters; i += 4) {
                 const uint64_t da = da0 + (uint64_t)(s * (49152 >> 4)), db = db0 + (uint64_t)(s * (49152 >> 4));
+                if (handshake) {   // what the GEMM main loop does around every k-block
+                    mbar_wait(&ready, 0);
+                    tc_fence_after();
+                }
 #pragma unroll
                 for (int k = 0; k < 4; ++k) umma_f16(tb, da + 2 * k, db + 2 * k, idesc, (i | k) ? 1u : 0u);
+                if (handshake) umma_commit(&cyc_bar);
                 s = (s == 2) ? 0 : s + 1;
             }
             umma_commit(&bar);
@@ -109,9 +116,10 @@ template <int N>
 void run(int grid, const uint8_t* g, long long* cyc, float* sink, long long* ldc, int rnd, int iters_arg) {
     const int smem_bytes = OPER + RING + STG;
     cudaFuncSetAttribute(probe<N>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem_bytes);
-    for (int noise = 0; noise < 6; ++noise) {
+    for (int noise : {0, 1, 2, 3, 4, 5, 10, 15}) {
         const int iters = iters_arg;
         if (rnd && noise != 0 && noise != 5) continue;
+        if (noise >= 10 && rnd) continue;
         for (int rep = 0; rep < 2; ++rep) probe<N><<<grid, 320, smem_bytes>>>(noise, iters, g, cyc, sink, ldc, rnd);
         cudaError_t e = cudaGetLastError(); if (e == cudaSuccess) e = cudaDeviceSynchronize();
         if (e != cudaSuccess) { printf("failed: %s\n", cudaGetErrorString(e)); exit(1); }

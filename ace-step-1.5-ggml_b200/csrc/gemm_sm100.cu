@@ -701,15 +701,21 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
                 __syncwarp();
                 const int subs_valid = min(SUBS, p.n_tiles128 - nt * SUBS);
                 const uint8_t* wptr = p.W + (size_t)(nt * SUBS) * sub_stride + (size_t)kb0 * W_SUB_BYTES;
-                for (int kb = kb0; kb < kb1; ++kb, wptr += W_SUB_BYTES) {
+                // weight tiles of TWO k-blocks per ring slot: one full/empty handshake per eight MMAs (the ~440 cycles of issue-side
+                // latency of a handshake do not hide under four 64-cycle N=128 MMAs, profiles/r1_probe_mma_handshake.log)
+                for (int kb = kb0; kb < kb1; kb += 2) {
+                    const int n = min(2, kb1 - kb);
                     ptx::mbar_wait(&empty[s], ph ^ 1);
                     if (ptx::elect_one()) {
-                        ptx::mbar_expect_tx(&full[s], subs_valid * W_SUB_BYTES);
-                        for (int sub = 0; sub < subs_valid; ++sub)
-                            ptx::bulk_load(sB + s * SL::B_STAGE + sub * W_SUB_BYTES, wptr + sub * sub_stride, W_SUB_BYTES, &full[s]);
+                        ptx::mbar_expect_tx(&full[s], (uint32_t)(n * subs_valid * W_SUB_BYTES));
+                        for (int i = 0; i < n; ++i)
+                            for (int sub = 0; sub < subs_valid; ++sub)
+                                ptx::bulk_load(sB + (2 * s + i) * SL::B_STAGE + sub * W_SUB_BYTES, wptr + (size_t)i * W_SUB_BYTES + sub * sub_stride,
+                                               W_SUB_BYTES, &full[s]);
                     }
                     __syncwarp();
-                    if (++s == (uint32_t)STAGES) {
+                    wptr += (size_t)n * W_SUB_BYTES;
+                    if (++s == (uint32_t)(STAGES / 2)) {
                         s = 0;
                         ph ^= 1;
                     }
@@ -789,6 +795,42 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
                 // SLAB: descriptor of (panel kc, row offset tap * dilation) inside the tile's slab, advanced incrementally
                 uint32_t slab_off = (uint32_t)((it & 1) * (SLAB_BYTES >> 4)) + (uint32_t)((kb0 / p.kb_per_tap) * p.tap_stride * 8);
                 int kc = kb0 % p.kb_per_tap;
+                if (SLAB) {  // ring slot = two k-blocks of weight tiles, A from the slab
+                    for (int kb = kb0; kb < kb1; kb += 2) {
+                        const int n = min(2, kb1 - kb);
+                        ptx::mbar_wait(&full[s], ph);
+                        ptx::tc_fence_after();
+                        if (first) {
+                            if (lane == 0) trace_stamp(p, TR_FIRST_FULL);
+                            first = false;
+                        }
+                        uint64_t da2[2];
+#pragma unroll
+                        for (int i = 0; i < 2; ++i) {
+                            da2[i] = desc_a0 + (uint64_t)(slab_off + (uint32_t)kc * (SLAB_PANEL_BYTES >> 4));
+                            if (++kc == p.kb_per_tap) {
+                                kc = 0;
+                                slab_off += (uint32_t)(p.tap_stride * 8);
+                            }
+                        }
+                        const uint64_t db = desc_b0 + (uint64_t)(2 * s * (SL::B_STAGE >> 4));
+                        if (ptx::elect_one()) {
+#pragma unroll
+                            for (int k = 0; k < BK / 16; ++k) ptx::umma_f16(d_tmem, da2[0] + 2 * k, db + 2 * k, idesc, k > 0 ? 1u : acc_flag);
+                            if (n > 1) {
+#pragma unroll
+                                for (int k = 0; k < BK / 16; ++k) ptx::umma_f16(d_tmem, da2[1] + 2 * k, db + (SL::B_STAGE >> 4) + 2 * k, idesc, 1u);
+                            }
+                            ptx::umma_commit(&empty[s]);
+                        }
+                        __syncwarp();
+                        acc_flag = 1;
+                        if (++s == (uint32_t)(STAGES / 2)) {
+                            s = 0;
+                            ph ^= 1;
+                        }
+                    }
+                } else {
                 long long waited = 0;
                 for (int kb = kb0; kb < kb1; ++kb) {
                     const bool timed = p.trace != nullptr && it == 8;
@@ -821,6 +863,7 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
                         s = 0;
                         ph ^= 1;
                     }
+                }
                 }
                 if (ptx::elect_one()) {
                     ptx::umma_commit(&acc_full[a]);

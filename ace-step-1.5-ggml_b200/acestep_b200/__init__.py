@@ -1,1 +1,1 @@
-"""Host-side Python for the B200-native acestep_ggml hot path (ctypes bridge, fixtures, build helper)."""
+"""Host-side Python for the B200-native acestep_ggml hot path (ctypes bridge, sample sharding)."""

@@ -208,7 +208,9 @@ class B200Bridge:
 
     # ------------------------------------------------------------------ batched / device-resident extensions
     def dit_forward_batched(self, hidden, context, enc, attention_mask, encoder_attention_mask,
-                            timesteps: Sequence[float], timesteps_r: Sequence[float]) -> np.ndarray:
+                            timesteps: Sequence[float], timesteps_r: Sequence[float],
+                            out: Optional[np.ndarray] = None) -> np.ndarray:
+        """B samples per call; `out` (optional, e.g. pinned memory) receives the velocities [B, T, D]."""
         hs, cx = _f32(hidden, 3), _f32(context, 3)
         en = _f32(enc, 3) if enc is not None else None
         am, eam = _i32(attention_mask), _i32(encoder_attention_mask)
@@ -216,7 +218,10 @@ class B200Bridge:
         E = int(en.shape[1]) if en is not None else 0
         t = _f32(np.broadcast_to(np.asarray(timesteps, dtype=np.float32), (B,)))
         tr = _f32(np.broadcast_to(np.asarray(timesteps_r, dtype=np.float32), (B,)))
-        out = np.empty_like(hs)
+        if out is None:
+            out = np.empty_like(hs)
+        elif out.dtype != np.float32 or out.shape != hs.shape or not out.flags.c_contiguous:
+            raise ValueError("out must be a C-contiguous float32 array shaped like hidden")
         st = self.lib.ace_b200_dit_forward_batched(self.ctx, _f(hs), _f(cx), _f(en) if E else None, _i(am), _i(eam),
                                                    B, T, E, _f(t), _f(tr), _f(out), out.nbytes)
         self._ensure_ok(st, "ace_b200_dit_forward_batched")

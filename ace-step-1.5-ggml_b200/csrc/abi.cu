@@ -80,11 +80,12 @@ ace_ggml_status dit_forward_impl(ace_ggml_context* ctx, const float* hidden, con
     e = dit_forward_device(ctx->dit, ctx->dws, B, T, E, ctx->dws.d_out, o, ctx->stream);
     cudaEventRecord(ctx->ev1, ctx->stream);
     if (e != cudaSuccess) return cuda_fail(ctx, "dit forward launch failed", e);
-    e = cudaStreamSynchronize(ctx->stream);  // also makes the pageable `tt` upload safe to drop
+    // the D2H rides the same stream (no second blocking copy): truly asynchronous into pinned caller memory, staged by the
+    // driver for pageable memory; one synchronise ends the call (and makes the pageable `tt` upload safe to drop)
+    e = cudaMemcpyAsync(out, ctx->dws.d_out, needed, cudaMemcpyDeviceToHost, ctx->stream);
+    if (e == cudaSuccess) e = cudaStreamSynchronize(ctx->stream);
     if (e != cudaSuccess) return cuda_fail(ctx, "dit forward failed", e);
     const auto t_done = Clock::now();
-    e = cudaMemcpy(out, ctx->dws.d_out, needed, cudaMemcpyDeviceToHost);
-    if (e != cudaSuccess) return cuda_fail(ctx, "output download failed", e);
     float ms = 0.f;
     cudaEventElapsedTime(&ms, ctx->ev0, ctx->ev1);
     ctx->last_device_ms = ms;
@@ -99,27 +100,52 @@ ace_ggml_status dit_forward_impl(ace_ggml_context* ctx, const float* hidden, con
     return ACE_GGML_OK;
 }
 
+// Clips of one call are decoded in groups whose activation workspace stays under ~40 GB (a 240 s clip needs ~13 GB of
+// fp32 / fp16 level buffers; every decode already fills the machine, so grouping costs nothing).  ACE_B200_VAE_GROUP_FRAMES
+// overrides the cap (frames per group, summed over the clips of the group).
+int vae_group_size(int B, int n_frames) {
+    long cap = 18000;
+    if (const char* v = std::getenv("ACE_B200_VAE_GROUP_FRAMES")) cap = std::max(1L, std::atol(v));
+    return (int)std::max(1L, std::min<long>(B, cap / std::max(1, n_frames)));
+}
+
+// latents: device [B, n_frames, C] -> audio: device [B, n_frames*hop, ch]; both caller-owned device buffers
+cudaError_t vae_decode_grouped(ace_ggml_context* ctx, const float* d_latents, int B, int n_frames, float* d_audio, std::string& err) {
+    const VaeConfig& c = ctx->vae.cfg;
+    const int G = vae_group_size(B, n_frames);
+    if (!vae_workspace_reserve(ctx->vae, ctx->vws, G, n_frames, err)) return cudaErrorMemoryAllocation;
+    const size_t lat_per = (size_t)n_frames * c.decoder_input_channels, aud_per = (size_t)n_frames * c.hop_length * c.audio_channels;
+    for (int b0 = 0; b0 < B; b0 += G) {
+        const int g = std::min(G, B - b0);
+        cudaError_t e = cudaMemcpyAsync(ctx->vws.d_lat, d_latents + (size_t)b0 * lat_per, (size_t)g * lat_per * 4, cudaMemcpyDeviceToDevice, ctx->stream);
+        if (e == cudaSuccess) e = vae_decode_device(ctx->vae, ctx->vws, g, n_frames, d_audio + (size_t)b0 * aud_per, ctx->stream);
+        if (e != cudaSuccess) return e;
+    }
+    return cudaSuccess;
+}
+
 ace_ggml_status vae_decode_impl(ace_ggml_context* ctx, const float* latents, int B, int n_frames, float* out, size_t out_size) {
     const auto t0 = Clock::now();
     DeviceGuard guard(ctx->device);
     const VaeConfig& c = ctx->vae.cfg;
     const size_t expected = (size_t)B * n_frames * c.hop_length * c.audio_channels * sizeof(float);
     if (out_size < expected) return set_error(ctx, ACE_GGML_ERR_INVALID_ARG, "output buffer too small");
-    std::string err;
-    if (!vae_workspace_reserve(ctx->vae, ctx->vws, B, n_frames, err)) return set_error(ctx, ACE_GGML_ERR, err);
+    const size_t lat_bytes = (size_t)B * n_frames * c.decoder_input_channels * 4;
+    if (!ctx->io.reserve(lat_bytes, expected)) return set_error(ctx, ACE_GGML_ERR, "VAE I/O buffer allocation failed");
     const auto t_init = Clock::now();
-    cudaError_t e = cudaMemcpyAsync(ctx->vws.d_lat, latents, (size_t)B * n_frames * c.decoder_input_channels * 4,
-                                    cudaMemcpyHostToDevice, ctx->stream);
+    cudaError_t e = cudaMemcpyAsync(ctx->io.d_in, latents, lat_bytes, cudaMemcpyHostToDevice, ctx->stream);
     if (e != cudaSuccess) return cuda_fail(ctx, "latent upload failed", e);
     cudaEventRecord(ctx->ev0, ctx->stream);
-    e = vae_decode_device(ctx->vae, ctx->vws, B, n_frames, ctx->vws.d_audio, ctx->stream);
+    std::string err;
+    e = vae_decode_grouped(ctx, static_cast<const float*>(ctx->io.d_in), B, n_frames, static_cast<float*>(ctx->io.d_out), err);
     cudaEventRecord(ctx->ev1, ctx->stream);
-    if (e != cudaSuccess) return cuda_fail(ctx, "vae decode launch failed", e);
-    e = cudaStreamSynchronize(ctx->stream);
+    if (e != cudaSuccess) return err.empty() ? cuda_fail(ctx, "vae decode launch failed", e) : set_error(ctx, ACE_GGML_ERR, err);
+    const auto t_done_launch = Clock::now();
+    (void)t_done_launch;
+    e = cudaMemcpyAsync(out, ctx->io.d_out, expected, cudaMemcpyDeviceToHost, ctx->stream);
+    if (e == cudaSuccess) e = cudaStreamSynchronize(ctx->stream);
     if (e != cudaSuccess) return cuda_fail(ctx, "vae decode failed", e);
     const auto t_done = Clock::now();
-    e = cudaMemcpy(out, ctx->vws.d_audio, expected, cudaMemcpyDeviceToHost);
-    if (e != cudaSuccess) return cuda_fail(ctx, "audio download failed", e);
     float ms = 0.f;
     cudaEventElapsedTime(&ms, ctx->ev0, ctx->ev1);
     ctx->last_device_ms = ms;
@@ -261,6 +287,7 @@ void ace_ggml_destroy(ace_ggml_context* ctx) {
         ctx->dws.release();
         ctx->vae.release();
         ctx->vws.release();
+        ctx->io.release();
         if (ctx->d_x) cudaFree(ctx->d_x);
         if (ctx->d_v) cudaFree(ctx->d_v);
         for (void* p : ctx->dbg_allocs) cudaFree(p);

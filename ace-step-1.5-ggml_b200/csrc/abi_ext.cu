@@ -65,21 +65,19 @@ ace_ggml_status ace_b200_generate_audio(ace_ggml_context* ctx, const float* nois
     const VaeConfig& vc = ctx->vae.cfg;
     const size_t a_bytes = (size_t)batch * seq_len * vc.hop_length * vc.audio_channels * 4;
     if (out_audio_size < a_bytes) return set_error(ctx, ACE_GGML_ERR_INVALID_ARG, "output buffer too small");
-    std::string err;
-    if (!vae_workspace_reserve(ctx->vae, ctx->vws, batch, seq_len, err)) return set_error(ctx, ACE_GGML_ERR, err);
+    if (!ctx->io.reserve(0, a_bytes)) return set_error(ctx, ACE_GGML_ERR, "audio buffer allocation failed");
     ace_ggml_status s = sample_latents_device(ctx, noise, context_latents, encoder_hidden_states, uncond_encoder_hidden_states,
                                               attention_mask, encoder_attention_mask, batch, seq_len, enc_len, schedule, n_steps, guidance);
     if (s != ACE_GGML_OK) return s;
     const size_t l_bytes = (size_t)batch * seq_len * vc.decoder_input_channels * 4;
-    cudaError_t e = cudaMemcpyAsync(ctx->vws.d_lat, ctx->d_x, l_bytes, cudaMemcpyDeviceToDevice, ctx->stream);
-    if (e == cudaSuccess) e = vae_decode_device(ctx->vae, ctx->vws, batch, seq_len, ctx->vws.d_audio, ctx->stream);
+    std::string err;
+    cudaError_t e = vae_decode_grouped(ctx, ctx->d_x, batch, seq_len, static_cast<float*>(ctx->io.d_out), err);
     cudaEventRecord(ctx->ev1, ctx->stream);
-    if (e != cudaSuccess) return cuda_fail(ctx, "vae decode launch failed", e);
-    e = cudaStreamSynchronize(ctx->stream);
+    if (e != cudaSuccess) return err.empty() ? cuda_fail(ctx, "vae decode launch failed", e) : set_error(ctx, ACE_GGML_ERR, err);
+    e = cudaMemcpyAsync(out_audio, ctx->io.d_out, a_bytes, cudaMemcpyDeviceToHost, ctx->stream);
+    if (e == cudaSuccess && out_latents) e = cudaMemcpyAsync(out_latents, ctx->d_x, l_bytes, cudaMemcpyDeviceToHost, ctx->stream);
+    if (e == cudaSuccess) e = cudaStreamSynchronize(ctx->stream);
     if (e != cudaSuccess) return cuda_fail(ctx, "generate_audio failed", e);
-    e = cudaMemcpy(out_audio, ctx->vws.d_audio, a_bytes, cudaMemcpyDeviceToHost);
-    if (e == cudaSuccess && out_latents) e = cudaMemcpy(out_latents, ctx->d_x, l_bytes, cudaMemcpyDeviceToHost);
-    if (e != cudaSuccess) return cuda_fail(ctx, "output download failed", e);
     float ms = 0.f;
     cudaEventElapsedTime(&ms, ctx->ev0, ctx->ev1);
     ctx->last_device_ms = ms;

@@ -14,6 +14,35 @@
 #include <string>
 #include <vector>
 
+// device staging of a call's host inputs / outputs (grown on demand, freed with the context)
+struct IoBuffers {
+    void *d_in = nullptr, *d_out = nullptr;
+    size_t cap_in = 0, cap_out = 0;
+    bool reserve(size_t in_bytes, size_t out_bytes) {
+        if (in_bytes > cap_in) {
+            if (d_in) cudaFree(d_in);
+            d_in = nullptr;
+            cap_in = 0;
+            if (cudaMalloc(&d_in, in_bytes) != cudaSuccess) { cudaGetLastError(); return false; }
+            cap_in = in_bytes;
+        }
+        if (out_bytes > cap_out) {
+            if (d_out) cudaFree(d_out);
+            d_out = nullptr;
+            cap_out = 0;
+            if (cudaMalloc(&d_out, out_bytes) != cudaSuccess) { cudaGetLastError(); return false; }
+            cap_out = out_bytes;
+        }
+        return true;
+    }
+    void release() {
+        if (d_in) cudaFree(d_in);
+        if (d_out) cudaFree(d_out);
+        d_in = d_out = nullptr;
+        cap_in = cap_out = 0;
+    }
+};
+
 struct ace_ggml_context {
     int device = 0;
     int n_threads = 1;
@@ -24,6 +53,7 @@ struct ace_ggml_context {
     ace::DitWorkspace dws;
     ace::VaeModel vae;
     ace::VaeWorkspace vws;
+    IoBuffers io;
     std::string last_error;
     std::string info;
     double last_device_ms = 0.0;
@@ -81,5 +111,6 @@ ace_ggml_status sample_latents_device(ace_ggml_context* ctx, const float* noise,
                                       const float* uncond_enc, const int32_t* mask, const int32_t* enc_mask, int B, int T,
                                       int E, const float* schedule, int n_steps, float guidance);
 int env_max_layers();
+cudaError_t vae_decode_grouped(ace_ggml_context* ctx, const float* d_latents, int B, int n_frames, float* d_audio, std::string& err);
 
 }  // namespace ace_abi

@@ -255,11 +255,8 @@ void launch_attention(const __half* Q, long q_stride, const __half* K, long k_st
         if (e == cudaSuccess) return;
         std::fprintf(stderr, "[ace_b200] tcgen05 attention launch failed (%s); using the mma.sync kernel\n", cudaGetErrorString(e));
     }
-    static bool attr = false;
-    if (!attr) {
-        cudaFuncSetAttribute(attention_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, ATT_SMEM);
-        attr = true;
-    }
+    static DeviceOnce attr;
+    attr.run([](int&) { return cudaFuncSetAttribute(attention_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, ATT_SMEM); });
     dim3 grid((q_len + BQ - 1) / BQ, n_heads, B);
     attention_kernel<<<grid, ATT_THREADS, ATT_SMEM, st>>>(Q, q_stride, K, k_stride, V, v_stride, O, o_stride, key_mask,
                                                           q_len, k_len, n_heads / n_kv_heads, window);

@@ -870,14 +870,14 @@ cudaError_t launch_attention_tc(const __half* Q, long q_stride, const __half* K,
     if (!make_qkv_tmap(&tq, Q, q_stride, q_len, n_heads, B, BQ) || !make_qkv_tmap(&tk, K, k_stride, k_len, n_kv_heads, B, BKV) ||
         !make_qkv_tmap(&tv, V, v_stride, k_len, n_kv_heads, B, BKV))
         return cudaErrorInvalidValue;
-    static bool attr = false;
-    if (!attr) {
+    static DeviceOnce attr;
+    const cudaError_t ea = attr.run([](int&) {
         cudaError_t e = cudaFuncSetAttribute(attention_tc_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, ATT_TC_SMEM);
         if (e == cudaSuccess) e = cudaFuncSetAttribute(attention_tc8_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, ATT_TC_SMEM);
         if (e == cudaSuccess) e = cudaFuncSetAttribute(attention_tcp_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, ATT_P3_SMEM);
-        if (e != cudaSuccess) return e;
-        attr = true;
-    }
+        return e;
+    });
+    if (ea != cudaSuccess) return ea;
     AttnParams p{O, o_stride, key_mask, q_len, k_len, n_heads / n_kv_heads, window};
     dim3 grid((q_len + BQ - 1) / BQ, n_heads, B);
     const char* env = std::getenv("ACE_B200_ATTN");

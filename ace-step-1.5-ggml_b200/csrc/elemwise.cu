@@ -3,6 +3,7 @@
 #include "kernels.h"
 
 #include <cmath>
+#include <cstdio>
 
 namespace ace {
 
@@ -323,58 +324,58 @@ conv_small_out_kernel(const __half* __restrict__ xs, const __half* __restrict__ 
 void launch_pack_dit_input(const float* hidden, const float* context, __half* x0, int B, int T, int S, int patch,
                            int ctx_dim, int audio_dim, cudaStream_t st) {
     note_launch();
-    ProfScope prof_scope(PROF_ELEM, 0.0, 0.0, st);
     const long total = (long)B * S * patch * (ctx_dim + audio_dim);
+    ProfScope prof_scope(PROF_ELEM, 0.0, (double)B * T * (ctx_dim + audio_dim) * 4.0 + total * 2.0, st);
     pack_dit_input_kernel<<<blocks_for(total, 256), 256, 0, st>>>(hidden, context, x0, B, T, S, patch, ctx_dim, audio_dim);
 }
 void launch_f32_to_f16(const float* src, __half* dst, long n, cudaStream_t st) {
     note_launch();
-    ProfScope prof_scope(PROF_ELEM, 0.0, 0.0, st);
+    ProfScope prof_scope(PROF_ELEM, 0.0, n * 6.0, st);
     if (n <= 0) return;
     f32_to_f16_kernel<<<blocks_for((n + 3) / 4, 256), 256, 0, st>>>(src, dst, n);
 }
 void launch_patch_mask(const int32_t* mask, int32_t* pm, int B, int T, int S, int patch, cudaStream_t st) {
     note_launch();
-    ProfScope prof_scope(PROF_ELEM, 0.0, 0.0, st);
+    ProfScope prof_scope(PROF_ELEM, 0.0, (mask ? (double)B * T * 4.0 : 0.0) + (double)B * S * 4.0, st);
     patch_mask_kernel<<<blocks_for((long)B * S, 256), 256, 0, st>>>(mask, pm, B, T, S, patch);
 }
 void launch_timestep_features(const float* t, __half* out, int n, cudaStream_t st) {
     note_launch();
-    ProfScope prof_scope(PROF_ELEM, 0.0, 0.0, st);
+    ProfScope prof_scope(PROF_ELEM, 0.0, n * (4.0 + 512.0), st);
     timestep_features_kernel<<<blocks_for((long)n * 128, 128), 128, 0, st>>>(t, out, n);
 }
 void launch_build_modulation(const float* tables, const float* proj, float* mod, const float* out_table,
                              const float* temb_a, const float* temb_b, float* out_mod, int B, int layers, int H,
                              cudaStream_t st) {
     note_launch();
-    ProfScope prof_scope(PROF_ELEM, 0.0, 0.0, st);
     const long total = (long)B * layers * 6 * H + (long)B * 2 * H;
+    ProfScope prof_scope(PROF_ELEM, 0.0, total * 4.0 + ((double)layers * 6 * H + 2.0 * H + 8.0 * B * H) * 4.0, st);
     build_modulation_kernel<<<blocks_for(total, 256), 256, 0, st>>>(tables, proj, mod, out_table, temb_a, temb_b, out_mod,
                                                                     B, layers, H);
 }
 void launch_rmsnorm_mod(const float* x, const float* w, const float* scale1, const float* shift, long mod_bstride,
                         __half* y, int B, int rows_per_b, int H, float eps, cudaStream_t st) {
     note_launch();
-    ProfScope prof_scope(PROF_ELEM, 0.0, 0.0, st);
     const long rows = (long)B * rows_per_b;
+    ProfScope prof_scope(PROF_ELEM, 0.0, (double)rows * H * 6.0, st);  // fp32 in, fp16 out; weight / scale / shift are L2-resident vectors
     launch_pdl(rmsnorm_mod_kernel, dim3((unsigned)rows), dim3(128), 0, st, x, w, scale1, shift, mod_bstride, y, rows, rows_per_b, H, eps);
 }
 void launch_headnorm_rope(__half* buf, long row_stride, int col0, int n_heads, const float* w, const float2* rope_tab,
                           int B, int rows_per_b, float eps, cudaStream_t st) {
     note_launch();
-    ProfScope prof_scope(PROF_ELEM, 0.0, 0.0, st);
     const long rows = (long)B * rows_per_b;
+    ProfScope prof_scope(PROF_ELEM, 0.0, (double)rows * n_heads * 128.0 * 4.0, st);
     headnorm_rope_kernel<<<blocks_for(rows * n_heads, 8), 256, 0, st>>>(buf, row_stride, col0, n_heads, w, rope_tab, rows,
                                                                         rows_per_b, eps);
 }
 void launch_build_rope_table(float2* tab, int S, int half_dim, float theta, cudaStream_t st) {
     note_launch();
-    ProfScope prof_scope(PROF_ELEM, 0.0, 0.0, st);
+    ProfScope prof_scope(PROF_ELEM, 0.0, (double)S * half_dim * 8.0, st);
     rope_table_kernel<<<blocks_for((long)S * half_dim, 256), 256, 0, st>>>(tab, S, half_dim, theta);
 }
 void launch_euler_step(float* x, const float* vc, const float* vu, float g, float dt, long n, cudaStream_t st) {
     note_launch();
-    ProfScope prof_scope(PROF_ELEM, 0.0, 0.0, st);
+    ProfScope prof_scope(PROF_ELEM, 0.0, (double)n * 4.0 * (vu ? 4.0 : 3.0), st);
     euler_step_kernel<<<blocks_for(n, 256), 256, 0, st>>>(x, vc, vu, g, dt, n);
 }
 void launch_conv_small_out(const __half* xs, const __half* w, const float* bias, float* out, int B, long L, int C,
@@ -383,10 +384,11 @@ void launch_conv_small_out(const __half* xs, const __half* w, const float* bias,
     ProfScope prof_scope(PROF_VAE_TAIL, 2.0 * B * L * C * Cout * taps, (double)B * L * (C * 2.0 + Cout * 4.0), st);
     // loaders guarantee C % 16 == 0 (vae.cu: channel levels are multiples of 32) and Cout <= 8
     const size_t smem = ((size_t)(CSO_TL + taps - 1) * (C + 8) + (size_t)8 * taps * C) * sizeof(__half);
-    static size_t attr = 0;
-    if (smem > attr) {
-        cudaFuncSetAttribute(conv_small_out_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
-        attr = smem;
+    static DeviceOnce attr;  // the largest layout the loaders admit (C <= 2048 would not fit; C = 128 is the model's)
+    attr.run([](int&) { return cudaFuncSetAttribute(conv_small_out_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024); });
+    if (smem > 200 * 1024) {  // vae_load refuses such a model (conv2 input channels > 512); never reached through the ABI
+        std::fprintf(stderr, "[ace_b200] conv_small_out: %zu bytes of shared memory needed, 200 KB available\n", smem);
+        return;
     }
     dim3 grid((unsigned)((L + CSO_TL - 1) / CSO_TL), (unsigned)B);
     conv_small_out_kernel<<<grid, CSO_THREADS, smem, st>>>(xs, w, bias, out, L, C, Cout, taps, pad);

@@ -1386,8 +1386,9 @@ bool make_tmap_a(const GemmProblem& g, CUtensorMap* tm, int box_rows = BM) {
 
 // co-resident CTA pairs on this device (a GPC with an odd SM count cannot pair its last SM); 0 = pairs unavailable
 int max_active_pairs() {
-    static int n = -1;
-    if (n < 0) {
+    static DeviceOnce once;
+    int result = 0;
+    once.run([](int& n) {
         n = 0;
         if (cudaFuncSetAttribute(gemm_tc2_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, SMEM2_BYTES) == cudaSuccess &&
             cudaFuncSetAttribute(gemm_tc2_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, SMEM2_BYTES) == cudaSuccess) {
@@ -1407,8 +1408,9 @@ int max_active_pairs() {
             else cudaGetLastError();
             if (std::getenv("ACE_B200_DEBUG")) std::fprintf(stderr, "[ace_b200] max active CTA pairs: %d\n", n);
         } else cudaGetLastError();
-    }
-    return n;
+        return cudaSuccess;
+    }, &result);
+    return result;
 }
 
 cudaError_t launch_tc2(const CUtensorMap& tm, const CUtensorMap& tmo, const KParams& kp, int clusters, cudaStream_t stream) {
@@ -1462,12 +1464,9 @@ namespace {
 template <int BN, bool QUANT, bool WARM>
 cudaError_t launch_tc(const CUtensorMap& tm, const CUtensorMap& tmo, const KParams& kp, int grid, cudaStream_t stream) {
     using SL = SmemLayout<BN, QUANT>;
-    static bool attr_set = false;
-    if (!attr_set) {
-        cudaError_t e = cudaFuncSetAttribute(gemm_tc_kernel<BN, QUANT, WARM>, cudaFuncAttributeMaxDynamicSharedMemorySize, SL::BYTES);
-        if (e != cudaSuccess) return e;
-        attr_set = true;
-    }
+    static DeviceOnce attr;  // one per template instantiation, once per device
+    const cudaError_t ea = attr.run([](int&) { return cudaFuncSetAttribute(gemm_tc_kernel<BN, QUANT, WARM>, cudaFuncAttributeMaxDynamicSharedMemorySize, SL::BYTES); });
+    if (ea != cudaSuccess) return ea;
     return launch_pdl(gemm_tc_kernel<BN, QUANT, WARM>, dim3((unsigned)grid), dim3(NUM_THREADS), (size_t)SL::BYTES, stream, tm, tmo, kp);
 }
 
@@ -1475,25 +1474,23 @@ cudaError_t launch_tc_slab(const CUtensorMap& tm, const CUtensorMap& tmo, const 
     using SL = SmemLayout<128, false>;
     constexpr int BYTES = 2 * SLAB_BYTES + SL::STAGES * SL::B_STAGE + SL::STG_BYTES + SL::COL_BYTES + 256;
     static_assert(BYTES <= 227 * 1024, "slab layout exceeds shared memory");
-    static bool attr_set = false;
-    if (!attr_set) {
-        cudaError_t e = cudaFuncSetAttribute(gemm_tc_kernel<128, false, false, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, BYTES);
-        if (e != cudaSuccess) return e;
-        attr_set = true;
-    }
+    static DeviceOnce attr;
+    const cudaError_t ea = attr.run([](int&) { return cudaFuncSetAttribute(gemm_tc_kernel<128, false, false, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, BYTES); });
+    if (ea != cudaSuccess) return ea;
     return launch_pdl(gemm_tc_kernel<128, false, false, true>, dim3((unsigned)grid), dim3(NUM_THREADS), (size_t)BYTES, stream, tm, tmo, kp);
 }
 
 }  // namespace
 
 int device_sm_count() {
-    static int sms = 0;
-    if (sms == 0) {
+    static DeviceOnce once;
+    int sms = 148;
+    once.run([](int& v) {
         int dev = 0;
         cudaGetDevice(&dev);
-        cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
-        if (sms <= 0) sms = 148;
-    }
+        if (cudaDeviceGetAttribute(&v, cudaDevAttrMultiProcessorCount, dev) != cudaSuccess || v <= 0) v = 148;
+        return cudaSuccess;
+    }, &sms);
     return sms;
 }
 
@@ -1628,7 +1625,10 @@ cudaError_t gemm_launch(const GemmProblem& g, cudaStream_t stream, bool simt) {
     CUtensorMap tm;
     if (!make_tmap_a(g, &tm, kp.slab_rows ? kp.slab_rows : BM)) return cudaErrorInvalidValue;
     kp.trace = nullptr;
-    static long long* trace_buf = nullptr;
+    static long long* trace_bufs[ACE_MAX_DEVICES] = {};  // debug aid (ACE_B200_GEMM_TRACE), one buffer per device
+    int trace_dev = 0;
+    cudaGetDevice(&trace_dev);
+    long long*& trace_buf = trace_bufs[trace_dev & (ACE_MAX_DEVICES - 1)];
     const bool tracing = std::getenv("ACE_B200_GEMM_TRACE") != nullptr && !pair;
     if (tracing) {
         if (!trace_buf) cudaMalloc(&trace_buf, (size_t)sms * TR_N * sizeof(long long));

@@ -37,6 +37,38 @@ struct ProfScope {
     }
 };
 
+// Function attributes (MaxDynamicSharedMemorySize), SM counts and occupancy answers are per DEVICE, not per process: a second
+// context on another device of the same process must set / query them again.  `DeviceOnce` runs `fn` once per device
+// (thread-safe; the fast path is one relaxed atomic load) and caches one int per device.
+constexpr int ACE_MAX_DEVICES = 64;
+struct DeviceOnce {
+    std::atomic<int> done[ACE_MAX_DEVICES];
+    int value[ACE_MAX_DEVICES];
+    std::atomic_flag lock = ATOMIC_FLAG_INIT;
+    DeviceOnce() {
+        for (auto& d : done) d.store(0, std::memory_order_relaxed);
+        for (auto& v : value) v = 0;
+    }
+    // fn(int& value) -> cudaError_t ; the result is remembered only on success
+    template <typename F>
+    cudaError_t run(F&& fn, int* out_value = nullptr) {
+        int dev = 0;
+        cudaGetDevice(&dev);
+        if (dev < 0 || dev >= ACE_MAX_DEVICES) return cudaErrorInvalidDevice;
+        cudaError_t e = cudaSuccess;
+        if (!done[dev].load(std::memory_order_acquire)) {
+            while (lock.test_and_set(std::memory_order_acquire)) {}
+            if (!done[dev].load(std::memory_order_relaxed)) {
+                e = fn(value[dev]);
+                if (e == cudaSuccess) done[dev].store(1, std::memory_order_release);
+            }
+            lock.clear(std::memory_order_release);
+        }
+        if (out_value) *out_value = value[dev];
+        return e;
+    }
+};
+
 // Launch with the programmatic-stream-serialization attribute (PDL): the kernel may start while its predecessor in the
 // stream drains; every kernel launched this way executes ptx::pdl_wait() before its first global access.
 // ACE_B200_PDL=0 turns the attribute off (plain stream order).

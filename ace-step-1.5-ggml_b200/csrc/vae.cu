@@ -230,7 +230,7 @@ int vae_load(const std::string& model_dir_in, VaeModel& m, std::string& err) {
         std::vector<int64_t> sh;
         if (L.folded("decoder.conv2", w, sh)) {
             const int co = (int)sh[0], ci = (int)sh[1], k = (int)sh[2];
-            if (co != c.audio_channels || ci != ch[(size_t)nb] || k != 7 || co > 2 || ci % 8 != 0) ok = L.fail(4, "unsupported decoder.conv2 shape");
+            if (co != c.audio_channels || ci != ch[(size_t)nb] || k != 7 || co > 2 || ci % 8 != 0 || ci > 512) ok = L.fail(4, "unsupported decoder.conv2 shape");
             else {
                 std::vector<uint16_t> h((size_t)co * k * ci);
                 for (int o = 0; o < co; ++o)
@@ -282,7 +282,6 @@ bool vae_workspace_reserve(const VaeModel& m, VaeWorkspace& ws, int B, int n_fra
     alloc(ws.x, BF * max_level);
     alloc(ws.xs, BF * max_level);
     alloc(ws.h, BF * max_level);
-    alloc(ws.d_audio, BF * m.cfg.hop_length * m.cfg.audio_channels);
     // block inputs ping-pong with xs: reuse a region that is never live at the same time is not possible for every
     // level, so they get their own buffer (<= half of a full level)
     __half* blk = nullptr;

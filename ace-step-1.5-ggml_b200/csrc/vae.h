@@ -63,7 +63,6 @@ struct VaeWorkspace {
     float* x = nullptr;       // fp32 residual stream (largest level)
     __half* xs = nullptr;     // snake'd fp16 copy feeding the next conv
     __half* h = nullptr;      // fp16 intermediate inside a residual unit / conv-transpose input
-    float* d_audio = nullptr; // [B, T*hop, audio_channels]
     std::vector<void*> allocs;
     void release();
 };

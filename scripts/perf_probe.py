@@ -12,7 +12,7 @@ import numpy as np
 ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 sys.path[:0] = [ROOT, os.path.join(ROOT, "ace-step-1.5-ggml_b200")]
 
-from acestep_b200 import fixtures as fx  # noqa: E402
+from tools import fixtures as fx  # noqa: E402
 from acestep_b200.bridge import B200Bridge  # noqa: E402
 
 

@@ -28,7 +28,7 @@ HERE = os.path.dirname(os.path.abspath(__file__))
 ROOT = os.path.dirname(os.path.dirname(HERE))
 sys.path[:0] = [ROOT, os.path.join(ROOT, "ace-step-1.5-ggml_b200"), os.path.join(ROOT, "tests")]
 
-from acestep_b200 import fixtures as fx  # noqa: E402
+from tools import fixtures as fx  # noqa: E402
 from oracle import refbridge  # noqa: E402
 from parity_common import make_dit_dir, make_vae_dir, ref_dit_forward  # noqa: E402
 

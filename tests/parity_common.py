@@ -5,7 +5,7 @@ import os
 
 import numpy as np
 
-from acestep_b200 import fixtures as fx
+from tools import fixtures as fx
 from oracle import refbridge
 
 
@@ -73,3 +73,53 @@ def dequantised_gguf_tensors(path: str) -> dict:
         else:
             out[t.name] = gq.dequantize(np.asarray(t.data), t.tensor_type).astype(np.float32).reshape(shape)
     return out
+
+
+# ---------------------------------------------------------------- real-dimension fixtures (BASELINE configs)
+
+def fixtures_root() -> str:
+    r = os.environ.get("ACE_B200_FIXTURES", "/tmp/ace_b200_fixtures")
+    os.makedirs(r, exist_ok=True)
+    return r
+
+
+def turbo_dit_dir(quant: str) -> str:
+    """turbo-dimension DiT as a GGUF-only directory (seed 0, torch CPU generator; shared with bench.py)."""
+    d = os.path.join(fixtures_root(), f"turbo_{quant}")
+    if not os.path.exists(os.path.join(d, "model.gguf")):
+        tmp = d + f".tmp{os.getpid()}"
+        lib = refbridge.ref_lib() if (quant != "F16" and refbridge.ref_available()) else None
+        if quant != "F16" and lib is None:
+            raise RuntimeError("quantised turbo fixtures need ggml_quantize_chunk from oracle/_ref")
+        fx.make_dit_fixture(tmp, fx.TURBO, 0, safetensors=False, gguf_quant=quant, ggml_lib=lib, fast=True)
+        try:
+            os.rename(tmp, d)
+        except OSError:
+            pass
+    return d
+
+
+def full_vae_dir() -> str:
+    d = os.path.join(fixtures_root(), "vae_full")
+    if not os.path.exists(os.path.join(d, "config.json")):
+        fx.make_vae_fixture(d, fx.VAE_FULL, 0, fast=True)
+    return d
+
+
+def fixture_checksums(dit_dir: str) -> dict:
+    """crc32 of the raw bytes of three tensors of model.gguf: tells 'the regenerated fixture differs from the one the
+    golden was made on' apart from 'the kernel differs'."""
+    import zlib
+
+    import gguf
+    want = ("decoder.layers.0.self_attn.q_proj.weight", "decoder.time_embed.time_proj.weight", "decoder.proj_in.1.weight")
+    out = {}
+    for t in gguf.GGUFReader(os.path.join(dit_dir, "model.gguf")).tensors:
+        if t.name in want:
+            out["wsum_" + t.name.replace(".", "_")] = np.int64(zlib.crc32(np.ascontiguousarray(t.data).tobytes()))
+    return out
+
+
+def shift_schedule(shift: float, n: int) -> np.ndarray:
+    u = 1.0 - np.arange(n, dtype=np.float64) / n
+    return (shift * u / (1.0 + (shift - 1.0) * u)).astype(np.float32)

@@ -7,7 +7,7 @@ import os
 import numpy as np
 import pytest
 
-from acestep_b200 import fixtures as fx
+from tools import fixtures as fx
 from oracle import refbridge
 from parity_common import make_dit_dir, make_vae_dir, metrics
 

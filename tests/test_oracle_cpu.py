@@ -14,7 +14,7 @@ import os
 import numpy as np
 import pytest
 
-from acestep_b200 import fixtures as fx
+from tools import fixtures as fx
 from oracle import dit_numpy as dn
 from oracle import vae_numpy as vn
 from parity_common import metrics

@@ -13,7 +13,7 @@ import os
 import numpy as np
 import pytest
 
-from acestep_b200 import fixtures as fx
+from tools import fixtures as fx
 from oracle import refbridge
 from parity_common import make_dit_dir, make_vae_dir, metrics, ref_dit_forward
 
@@ -146,6 +146,39 @@ def test_sampler_per_step_parity(br, root):
                               schedule=sched)
     assert metrics(lat[0], outs["x_final"])["rel_l2"] <= 2e-2
     assert metrics(lat[0], x)["rel_l2"] <= 1e-3
+
+
+@pytest.mark.parametrize("batch", [1, 3])
+def test_cfg_sampler_matches_composed_reference(br, root, batch):
+    """CFG (north_star (3)): ONE batched forward of 2B samples + `v_u + g (v_c - v_u)` in the Euler kernel vs the oracle by composition
+    (SURVEY 8c): two reference forwards per step (conditional / unconditional encoder states) combined on the host.  F32 weights, 4 steps,
+    g = 7; bound = per-forward tolerance x (1 + 2 g) because both branches' rounding noise enters the update 7 times."""
+    need_ref()
+    d = make_dit_dir(root, fx.TOY, 0, None)
+    T, E, g = 32, 8, 7.0
+    sched = [float(x) for x in br.shift_schedule(3.0, 4)]
+    ins = [fx.dit_inputs(fx.TOY, T, E, seed=40 + b) for b in range(batch)]
+    unc = [fx.dit_inputs(fx.TOY, T, E, seed=90 + b)["encoder_hidden_states"] * np.float32(0.1) for b in range(batch)]
+    refs = []
+    for b in range(batch):
+        x = ins[b]["hidden_states"].copy()
+        for i, t in enumerate(sched):
+            calls = [{"op": "dit_forward", "t": t, "t_r": t, "hidden": "x", "out": "vc"},
+                     {"op": "dit_forward", "t": t, "t_r": t, "hidden": "x", "enc": "unc", "out": "vu"}]
+            o, _ = refbridge.run_ref(calls, dict(ins[b], x=x, unc=unc[b]), dit_dir=d)
+            v = o["vu"] + np.float32(g) * (o["vc"] - o["vu"])
+            dt = t if i == len(sched) - 1 else t - sched[i + 1]
+            x = (x - v * np.float32(dt)).astype(np.float32)
+        refs.append(x)
+    br.load_dit(d)
+    lat = br.generate_latents(np.stack([i["hidden_states"] for i in ins]), np.stack([i["context_latents"] for i in ins]),
+                              np.stack([i["encoder_hidden_states"] for i in ins]), uncond_enc=np.stack(unc), schedule=sched, guidance=g)
+    plain = br.generate_latents(np.stack([i["hidden_states"] for i in ins]), np.stack([i["context_latents"] for i in ins]),
+                                np.stack([i["encoder_hidden_states"] for i in ins]), schedule=sched)
+    for b in range(batch):
+        m = metrics(lat[b], refs[b])
+        assert m["rel_l2"] <= 15 * 5e-3, (b, m)
+        assert metrics(plain[b], refs[b])["rel_l2"] > 4 * max(m["rel_l2"], 1e-3)  # guidance changes the result: the test can fail
 
 
 def test_shift_schedule_tables(br):

@@ -1,0 +1,153 @@
+"""GPU parity at the REAL model dimensions of BASELINE.json's configs (turbo DiT: hidden 2048, 24 layers, 16/8 heads x 128, MLP 6144;
+full Oobleck VAE 2048 -> 128 channels) against golden outputs of the unmodified reference (tests/golden/turbo_*.npz, vae_full.npz,
+made by tests/golden/make_golden_turbo.py on the ggml CPU backend).  Weights and inputs are regenerated from seeds; a crc32 of three
+tensors of the regenerated GGUF is compared with the one stored next to the golden so that a fixture drift is reported as such.
+
+Tolerances are the ones of test_parity_gpu.py / DESIGN.md (never loosened here):
+  F16 weights rel-L2 <= 5e-3, cos >= 0.99999;  Q8_0 / Q6_K / Q4_K rel-L2 <= 2e-2, cos >= 0.9998 (the reference re-quantises
+  activations to int8 per block, this library keeps fp16);  per Euler step x_i rel-L2 <= 2e-2;  VAE waveform cos >= 0.9999, SNR >= 40 dB.
+CFG (v = v_u + g (v_c - v_u), g = 7): the difference v_c - v_u is amplified 7x, so is each side's rounding noise; the bound is the
+per-forward tolerance x (1 + 2 g) on the final latents (stated at the test)."""
+import os
+
+import numpy as np
+import pytest
+
+from tools import fixtures as fx
+from parity_common import fixture_checksums, full_vae_dir, metrics, shift_schedule, turbo_dit_dir
+
+pytestmark = pytest.mark.gpu
+GOLD = os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden")
+TOL = {"F16": (5e-3, 0.99999), "Q8_0": (2e-2, 0.9998), "Q6_K": (2e-2, 0.9998), "Q4_K": (2e-2, 0.9998)}
+
+
+@pytest.fixture(scope="module")
+def br():
+    from acestep_b200.bridge import B200Bridge
+    b = B200Bridge()
+    yield b
+    b.close()
+
+
+def gold(name):
+    return dict(np.load(os.path.join(GOLD, name + ".npz")))
+
+
+def check_fixture(d, g, suffix=""):
+    for k, v in fixture_checksums(d).items():
+        assert int(g[k + suffix]) == int(v), f"regenerated fixture {d} differs from the one the golden was made on ({k})"
+
+
+def fwd(br, inp, t, hidden=None):
+    h = inp["hidden_states"] if hidden is None else hidden
+    return br.dit_forward_tfirst(h, inp["context_latents"], inp["encoder_hidden_states"], None, None, t, t)
+
+
+# ---------------------------------------------------------------- configs[0]: turbo Q8_0, 30 s clip
+
+@pytest.fixture(scope="module")
+def q8(br):
+    d = turbo_dit_dir("Q8_0")
+    g = gold("turbo_q8_30s")
+    check_fixture(d, g)
+    return d, g, fx.dit_inputs(fx.TURBO, 750, 512, seed=1234)
+
+
+@pytest.mark.parametrize("k", [1, 2, 6, 12, 24])
+def test_config0_q8_per_block(br, q8, k, monkeypatch):
+    """per DiT block: network truncated to k layers (ACE_GGML_DIT_MAX_LAYERS, acestep_dit_model.cpp:1457-1464)"""
+    d, g, inp = q8
+    monkeypatch.setenv("ACE_GGML_DIT_MAX_LAYERS", str(k))
+    br.load_dit(d)
+    m = metrics(fwd(br, inp, 0.7), g[f"v_layers{k}"])
+    assert m["rel_l2"] <= TOL["Q8_0"][0] and m["cos"] >= TOL["Q8_0"][1], (k, m)
+
+
+def test_config0_q8_per_step_and_device_sampler(br, q8):
+    """per denoise step: 8-step turbo Euler loop (acestep_ggml.cpp:2056-2086), x_i against the reference's x_i at every i; then
+    the device-resident sampler (cached cross K/V, no host round trips) against the same trace's end point"""
+    d, g, inp = q8
+    br.load_dit(d)
+    sched = [float(x) for x in shift_schedule(3.0, 8)]
+    x = inp["hidden_states"].copy()
+    for i, t in enumerate(sched):
+        v = fwd(br, inp, t, hidden=x)
+        dt = t if i == len(sched) - 1 else t - sched[i + 1]
+        x = (x - v * np.float32(dt)).astype(np.float32)
+        m = metrics(x, g["x_steps"][i])
+        assert m["rel_l2"] <= 2e-2, (i, m)
+    lat = br.generate_latents(inp["hidden_states"][None], inp["context_latents"][None], inp["encoder_hidden_states"][None], schedule=sched)
+    assert metrics(lat[0], g["x_steps"][-1])["rel_l2"] <= 2e-2
+    assert metrics(lat[0], x)["rel_l2"] <= 2e-3  # same arithmetic, K/V cached instead of recomputed
+
+
+# ---------------------------------------------------------------- configs[1]: turbo F16, 60 s clip (+ CFG on the 30 s clip)
+
+def test_config1_f16_60s_full_forward(br):
+    d = turbo_dit_dir("F16")
+    g = gold("turbo_f16_60s")
+    check_fixture(d, g)
+    inp = fx.dit_inputs(fx.TURBO, 1500, 512, seed=1234)
+    br.load_dit(d)
+    for key, t in (("v", 1.0), ("v1", 0.9)):
+        m = metrics(fwd(br, inp, t), g[key])
+        assert m["rel_l2"] <= TOL["F16"][0] and m["cos"] >= TOL["F16"][1], (key, m)
+
+
+@pytest.mark.parametrize("quant,gname", [("F16", "turbo_f16_cfg"), ("Q8_0", "turbo_q8_30s")])
+def test_cfg_sampler_vs_composed_reference(br, quant, gname):
+    """CFG: the 2B-sample batched forward + combine of the device sampler vs two reference forwards per step composed as
+    v_u + 7 (v_c - v_u) (uncond = all-zero encoder states, same mask), two Euler steps t = 1.0, 0.5.
+    bound on the final latents: per-forward tolerance x (1 + 2 g) = 15x (both branches' rounding noise enters 7x)"""
+    path = os.path.join(GOLD, gname + ".npz")
+    if not os.path.exists(path):
+        pytest.skip(f"{gname}.npz not generated")
+    g = gold(gname)
+    if "x_cfg2" not in g:
+        pytest.skip("no CFG golden in this file")
+    d = turbo_dit_dir(quant)
+    check_fixture(d, g)
+    inp = fx.dit_inputs(fx.TURBO, 750, 512, seed=1234)
+    br.load_dit(d)
+    zero = np.zeros_like(inp["encoder_hidden_states"])
+    lat = br.generate_latents(inp["hidden_states"][None], inp["context_latents"][None], inp["encoder_hidden_states"][None],
+                              uncond_enc=zero[None], schedule=[1.0, 0.5], guidance=7.0)
+    m = metrics(lat[0], g["x_cfg2"])
+    assert np.isfinite(lat).all()
+    assert m["rel_l2"] <= 15 * TOL[quant][0], (quant, m)
+    # the guided result must differ from the unguided one by far more than the tolerance (the test can fail)
+    plain = br.generate_latents(inp["hidden_states"][None], inp["context_latents"][None], inp["encoder_hidden_states"][None], schedule=[1.0, 0.5])
+    assert metrics(plain[0], g["x_cfg2"])["rel_l2"] > 4 * m["rel_l2"]
+
+
+# ---------------------------------------------------------------- configs[2] shape: K-quants at 240 s (S = 3000), depth the CPU's RAM allows
+
+@pytest.mark.parametrize("quant", ["Q4_K", "Q6_K"])
+@pytest.mark.parametrize("k", [1, 2])
+def test_config2_kquant_240s_truncated(br, quant, k, monkeypatch):
+    g = gold("turbo_kq_240s")
+    d = turbo_dit_dir(quant)
+    check_fixture(d, g, "_" + quant)
+    inp = fx.dit_inputs(fx.TURBO, 6000, 512, seed=1234)
+    monkeypatch.setenv("ACE_GGML_DIT_MAX_LAYERS", str(k))
+    br.load_dit(d)
+    out = fwd(br, inp, 0.7)
+    m = metrics(out[::4], g[f"v_{quant}_layers{k}"])  # the golden keeps every 4th frame
+    assert np.isfinite(out).all()
+    assert m["rel_l2"] <= TOL[quant][0] and m["cos"] >= TOL[quant][1], (quant, k, m)
+
+
+# ---------------------------------------------------------------- full-size VAE waveform
+
+@pytest.mark.parametrize("n_frames", [8, 40])
+def test_vae_full_waveform(br, n_frames):
+    d = full_vae_dir()
+    g = gold("vae_full")
+    br.load_vae(d)
+    assert (br.latent_channels, br.audio_channels, br.hop_length) == (64, 2, 1920)
+    lat = fx.vae_latents(fx.VAE_FULL, n_frames, seed=7)
+    out = br.vae_decode_tfirst(lat)
+    ref = g[f"audio_{n_frames}"]
+    assert out.shape == ref.shape
+    m = metrics(out, ref)
+    assert m["cos"] >= 0.9999 and m["snr_db"] >= 40.0, m

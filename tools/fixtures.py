@@ -221,10 +221,23 @@ class _ChunkQuantizer:
             raise RuntimeError("ggml_quantize_chunk size mismatch")
         return out
 
+    def quantize_parallel(self, f32_2d: np.ndarray, qtype_value: int, q_byte_row: int) -> np.ndarray:
+        from concurrent.futures import ThreadPoolExecutor
+        rows = f32_2d.shape[0]
+        n = min(os.cpu_count() or 1, max(1, rows // 64))
+        if n <= 1:
+            return self.quantize(f32_2d, qtype_value, q_byte_row)
+        cuts = [rows * i // n for i in range(n + 1)]
+        with ThreadPoolExecutor(n) as ex:
+            parts = list(ex.map(lambda i: self.quantize(f32_2d[cuts[i]:cuts[i + 1]], qtype_value, q_byte_row), range(n)))
+        return np.concatenate(parts, axis=0)
+
 
 def save_gguf(path: str, tensors: Dict[str, np.ndarray], quant: str,
-              ggml_lib: Optional[str] = None, arch: str = "acestep") -> Dict[str, str]:
-    """Write a GGUF twin of ``tensors`` under the exporter's rule. Returns name->type."""
+              ggml_lib: Optional[str] = None, arch: str = "acestep", fast: bool = False) -> Dict[str, str]:
+    """Write a GGUF twin of ``tensors`` under the exporter's rule. Returns name->type.
+    ``fast`` (the 1.6 G-parameter fixtures): every quantised type goes through ggml_quantize_chunk, rows split over
+    a thread pool (ctypes drops the GIL); otherwise Q8_0 uses gguf-py's NumPy quantiser."""
     import gguf
     from gguf import quants as gq
 
@@ -243,13 +256,16 @@ def save_gguf(path: str, tensors: Dict[str, np.ndarray], quant: str,
         if is_q and a.ndim >= 2 and a.shape[-1] % blk == 0:
             rows = int(np.prod(a.shape[:-1]))
             a2 = a.reshape(rows, a.shape[-1])
-            try:
-                q = gq.quantize(a2, qtype)
-            except NotImplementedError:
-                if chunk is None:
-                    raise RuntimeError(f"{quant} export needs ggml_lib (ggml_quantize_chunk)")
-                brow = gq.quant_shape_to_byte_shape((rows, a.shape[-1]), qtype)[-1]
-                q = chunk.quantize(a2, int(qtype), int(brow))
+            brow = gq.quant_shape_to_byte_shape((rows, a.shape[-1]), qtype)[-1]
+            if fast and chunk is not None:
+                q = chunk.quantize_parallel(a2, int(qtype), int(brow))
+            else:
+                try:
+                    q = gq.quantize(a2, qtype)
+                except NotImplementedError:
+                    if chunk is None:
+                        raise RuntimeError(f"{quant} export needs ggml_lib (ggml_quantize_chunk)")
+                    q = chunk.quantize(a2, int(qtype), int(brow))
             q = q.reshape(tuple(a.shape[:-1]) + (q.shape[-1],))
             w.add_tensor(name, q, raw_dtype=qtype)
             kinds[name] = quant
@@ -275,7 +291,7 @@ def make_dit_fixture(out_dir: str, dims: DitDims = TOY, seed: int = 0, *,
     if safetensors:
         save_safetensors(os.path.join(out_dir, "model.safetensors"), T)
     if gguf_quant:
-        save_gguf(os.path.join(out_dir, "model.gguf"), T, gguf_quant, ggml_lib)
+        save_gguf(os.path.join(out_dir, "model.gguf"), T, gguf_quant, ggml_lib, fast=fast)
     return out_dir
 
 

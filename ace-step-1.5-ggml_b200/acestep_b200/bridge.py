@@ -70,6 +70,10 @@ SIGNATURES = {
     "ace_b200_generate_audio": (ctypes.c_int, [_P, _F, _F, _F, _F, _I, _I, ctypes.c_int32, ctypes.c_int32,
                                                ctypes.c_int32, _F, ctypes.c_int32, ctypes.c_float, _F, _F,
                                                ctypes.c_size_t]),
+    "ace_b200_generate_audio_from_encoder": (ctypes.c_int, [_P, _F, _I, ctypes.c_int32, ctypes.c_int32, ctypes.c_float,
+                                                            ctypes.c_int32, _F, ctypes.c_size_t, _I, _I]),
+    "ace_b200_lyric_encoder_forward": (ctypes.c_int, [_P, _F, ctypes.c_int32, _F, ctypes.c_size_t]),
+    "ace_b200_timbre_encoder_forward": (ctypes.c_int, [_P, _F, ctypes.c_int32, _F, ctypes.c_size_t]),
     "ace_b200_shift_schedule": (ctypes.c_int, [ctypes.c_float, ctypes.c_int32, _F]),
     "ace_b200_last_device_ms": (ctypes.c_double, [_P]),
     "ace_b200_kernel_launches": (ctypes.c_uint64, []),
@@ -138,6 +142,7 @@ class B200Bridge:
         self.latent_channels = 0
         self.audio_channels = 0
         self.hop_length = 0
+        self.text_hidden = 0
         self.dit_dims = None
 
     # ------------------------------------------------------------------ plumbing
@@ -169,6 +174,9 @@ class B200Bridge:
     # ------------------------------------------------------------------ loads
     def load_text_encoder(self, model_dir) -> None:
         self._ensure_ok(self.lib.ace_ggml_load_text_encoder(self.ctx, str(model_dir).encode()), "ace_ggml_load_text_encoder")
+        import json
+        root = Path(model_dir).parent if str(model_dir).endswith(".gguf") else Path(model_dir)
+        self.text_hidden = int(json.load(open(root / "config.json"))["hidden_size"])
 
     def load_dit(self, model_dir) -> None:
         self._ensure_ok(self.lib.ace_ggml_load_dit(self.ctx, str(model_dir).encode()), "ace_ggml_load_dit")
@@ -179,6 +187,98 @@ class B200Bridge:
         self._ensure_ok(self.lib.ace_ggml_vae_get_info(self.ctx, ctypes.byref(a), ctypes.byref(b), ctypes.byref(c)),
                         "ace_ggml_vae_get_info")
         self.latent_channels, self.audio_channels, self.hop_length = a.value, b.value, c.value
+
+    # ------------------------------------------------------------------ text encoder / VAE encode / self-contained sampler
+    def text_encoder_forward(self, token_ids, attention_mask=None, n_layers: Optional[int] = None, apply_final_norm: bool = True,
+                             hidden_size: Optional[int] = None) -> np.ndarray:
+        """token ids [n] -> hidden states [n, hidden] (causal; optional key mask / layer truncation).  hidden_size defaults to the
+        value remembered by load_text_encoder."""
+        ids = _i32(token_ids)
+        n = int(ids.shape[0])
+        H = int(hidden_size or self.text_hidden)
+        out = np.empty((n, H), dtype=np.float32)
+        am = _i32(attention_mask)
+        if n_layers is not None:
+            st = self.lib.ace_ggml_text_encoder_forward_layers(self.ctx, _i(ids), _i(am), n, int(n_layers), 1 if apply_final_norm else 0,
+                                                               _f(out), out.nbytes)
+            where = "ace_ggml_text_encoder_forward_layers"
+        elif am is not None:
+            st = self.lib.ace_ggml_text_encoder_forward_masked(self.ctx, _i(ids), _i(am), n, _f(out), out.nbytes)
+            where = "ace_ggml_text_encoder_forward_masked"
+        else:
+            st = self.lib.ace_ggml_text_encoder_forward(self.ctx, _i(ids), n, _f(out), out.nbytes)
+            where = "ace_ggml_text_encoder_forward"
+        self._ensure_ok(st, where)
+        return out
+
+    def text_encoder_embeddings(self, token_ids, hidden_size: Optional[int] = None) -> np.ndarray:
+        ids = _i32(token_ids)
+        n = int(ids.shape[0])
+        out = np.empty((n, int(hidden_size or self.text_hidden)), dtype=np.float32)
+        self._ensure_ok(self.lib.ace_ggml_text_encoder_forward_embeddings(self.ctx, _i(ids), n, _f(out), out.nbytes),
+                        "ace_ggml_text_encoder_forward_embeddings")
+        return out
+
+    def vae_encode_tfirst(self, audio_tfirst: np.ndarray) -> np.ndarray:
+        """audio [n_samples, channels] -> posterior-mean latents [frames, latent_channels]"""
+        a = _f32(audio_tfirst, 2)
+        n = int(a.shape[0])
+        out = np.empty((max(n // self.hop_length, 1) + 2, self.latent_channels), dtype=np.float32)
+        self._ensure_ok(self.lib.ace_ggml_vae_encode(self.ctx, _f(a), n, _f(out), out.nbytes), "ace_ggml_vae_encode")
+        return out[: n // self.hop_length]
+
+    def lyric_encoder_forward(self, lyric_embeds: np.ndarray, hidden_size: int) -> np.ndarray:
+        x = _f32(lyric_embeds, 2)
+        out = np.empty((x.shape[0], hidden_size), np.float32)
+        self._ensure_ok(self.lib.ace_b200_lyric_encoder_forward(self.ctx, _f(x), int(x.shape[0]), _f(out), out.nbytes), "ace_b200_lyric_encoder_forward")
+        return out
+
+    def timbre_encoder_forward(self, refer_states: np.ndarray, hidden_size: int) -> np.ndarray:
+        x = _f32(refer_states, 2)
+        out = np.empty((hidden_size,), np.float32)
+        self._ensure_ok(self.lib.ace_b200_timbre_encoder_forward(self.ctx, _f(x), int(x.shape[0]), _f(out), out.nbytes), "ace_b200_timbre_encoder_forward")
+        return out
+
+    def _audio_out(self, seq_len: int):
+        return np.zeros((seq_len * self.hop_length, self.audio_channels), dtype=np.float32), ctypes.c_int32(), ctypes.c_int32()
+
+    def generate_audio_from_encoder(self, enc, enc_mask, seq_len: int, shift: float = 3.0, seed: int = 0) -> np.ndarray:
+        e = _f32(enc, 2)
+        em = _i32(enc_mask)
+        out, ns, nc = self._audio_out(seq_len)
+        st = self.lib.ace_b200_generate_audio_from_encoder(self.ctx, _f(e), _i(em), int(e.shape[0]), int(seq_len), float(shift), int(seed),
+                                                           _f(out), out.nbytes, ctypes.byref(ns), ctypes.byref(nc))
+        self._ensure_ok(st, "ace_b200_generate_audio_from_encoder")
+        return out[: ns.value]
+
+    def generate_audio_simple(self, token_ids, seq_len: int, shift: float = 3.0, seed: int = 0) -> np.ndarray:
+        ids = _i32(token_ids)
+        out, ns, nc = self._audio_out(seq_len)
+        st = self.lib.ace_ggml_generate_audio_simple(self.ctx, _i(ids), int(ids.shape[0]), int(seq_len), float(shift), int(seed), _f(out),
+                                                     out.nbytes, ctypes.byref(ns), ctypes.byref(nc))
+        self._ensure_ok(st, "ace_ggml_generate_audio_simple")
+        return out[: ns.value]
+
+    def generate_audio_style_lyric_timbre(self, style_ids, lyric_ids, refer=None, seq_len: int = 0, shift: float = 3.0,
+                                          seed: int = 0) -> np.ndarray:
+        """refer: [n_refer, refer_len, timbre_dim] or None (then the style+lyric entry point is used)"""
+        sid = _i32(style_ids) if style_ids is not None else None
+        lid = _i32(lyric_ids) if lyric_ids is not None else None
+        ns_, nl_ = (0 if sid is None else int(sid.shape[0])), (0 if lid is None else int(lid.shape[0]))
+        out, ns, nc = self._audio_out(seq_len)
+        if refer is None:
+            st = self.lib.ace_ggml_generate_audio_style_lyric_simple(self.ctx, _i(sid), ns_, _i(lid), nl_, int(seq_len), float(shift), int(seed),
+                                                                     _f(out), out.nbytes, ctypes.byref(ns), ctypes.byref(nc))
+            where = "ace_ggml_generate_audio_style_lyric_simple"
+        else:
+            r = _f32(refer, 3)
+            order = np.zeros((r.shape[0],), np.int32)
+            st = self.lib.ace_ggml_generate_audio_style_lyric_timbre_simple(self.ctx, _i(sid), ns_, _i(lid), nl_, _f(r), _i(order), int(r.shape[0]),
+                                                                            int(r.shape[1]), int(seq_len), float(shift), int(seed), _f(out),
+                                                                            out.nbytes, ctypes.byref(ns), ctypes.byref(nc))
+            where = "ace_ggml_generate_audio_style_lyric_timbre_simple"
+        self._ensure_ok(st, where)
+        return out[: ns.value]
 
     # ------------------------------------------------------------------ reference-shaped calls (one sample)
     def vae_decode_tfirst(self, latents_tfirst: np.ndarray) -> np.ndarray:

@@ -234,15 +234,6 @@ ace_ggml_status sample_latents_device(ace_ggml_context* ctx, const float* noise,
 
 using namespace ace_abi;
 
-namespace {
-ace_ggml_status unsupported(ace_ggml_context* ctx, const char* what) {
-    if (!ctx) return ACE_GGML_ERR_INVALID_ARG;
-    return set_error(ctx, ACE_GGML_ERR_UNSUPPORTED,
-                     std::string(what) + " is not part of the B200 hot path (DiT forward + VAE decode); see INTEGRATION.md");
-}
-
-}  // namespace
-
 extern "C" {
 
 ace_ggml_status ace_ggml_create(const ace_ggml_init_params* params, ace_ggml_context** out_ctx) {
@@ -287,6 +278,9 @@ void ace_ggml_destroy(ace_ggml_context* ctx) {
         ctx->dws.release();
         ctx->vae.release();
         ctx->vws.release();
+        ctx->vews.release();
+        ctx->text.release();
+        ctx->ews.release();
         ctx->io.release();
         if (ctx->d_x) cudaFree(ctx->d_x);
         if (ctx->d_v) cudaFree(ctx->d_v);
@@ -301,15 +295,6 @@ void ace_ggml_destroy(ace_ggml_context* ctx) {
 const char* ace_ggml_last_error(const ace_ggml_context* ctx) {
     if (!ctx) return "ace_ggml_last_error: null context";
     return ctx->last_error.c_str();
-}
-
-ace_ggml_status ace_ggml_load_lm(ace_ggml_context* ctx, const char* model_dir) {
-    if (!ctx || !model_dir) return ACE_GGML_ERR_INVALID_ARG;
-    return unsupported(ctx, "ace_ggml_load_lm");
-}
-ace_ggml_status ace_ggml_load_text_encoder(ace_ggml_context* ctx, const char* model_dir) {
-    if (!ctx || !model_dir) return ACE_GGML_ERR_INVALID_ARG;
-    return unsupported(ctx, "ace_ggml_load_text_encoder");
 }
 
 ace_ggml_status ace_ggml_load_dit(ace_ggml_context* ctx, const char* model_dir) {
@@ -331,6 +316,7 @@ ace_ggml_status ace_ggml_load_vae(ace_ggml_context* ctx, const char* model_dir) 
     cudaStreamSynchronize(ctx->stream);
     ctx->vae_loaded = false;
     ctx->vws.release();
+    ctx->vews.release();
     std::string err;
     const int st = vae_load(model_dir, ctx->vae, err);
     if (st != 0) return set_error(ctx, map_load_status(st), err);
@@ -353,22 +339,6 @@ ace_ggml_status ace_ggml_vae_decode(ace_ggml_context* ctx, const float* latents,
     return vae_decode_impl(ctx, latents, 1, n_frames, out, out_size);
 }
 
-ace_ggml_status ace_ggml_vae_encode(ace_ggml_context* ctx, const float*, int32_t, float*, size_t) {
-    return unsupported(ctx, "ace_ggml_vae_encode");
-}
-ace_ggml_status ace_ggml_text_encoder_forward(ace_ggml_context* ctx, const int32_t*, int32_t, float*, size_t) {
-    return unsupported(ctx, "ace_ggml_text_encoder_forward");
-}
-ace_ggml_status ace_ggml_text_encoder_forward_masked(ace_ggml_context* ctx, const int32_t*, const int32_t*, int32_t, float*, size_t) {
-    return unsupported(ctx, "ace_ggml_text_encoder_forward_masked");
-}
-ace_ggml_status ace_ggml_text_encoder_forward_embeddings(ace_ggml_context* ctx, const int32_t*, int32_t, float*, size_t) {
-    return unsupported(ctx, "ace_ggml_text_encoder_forward_embeddings");
-}
-ace_ggml_status ace_ggml_text_encoder_forward_layers(ace_ggml_context* ctx, const int32_t*, const int32_t*, int32_t, int32_t, int32_t, float*, size_t) {
-    return unsupported(ctx, "ace_ggml_text_encoder_forward_layers");
-}
-
 ace_ggml_status ace_ggml_dit_forward(ace_ggml_context* ctx, const float* hidden_states, const float* context_latents,
                                      const float* encoder_hidden_states, const int32_t* attention_mask,
                                      const int32_t* encoder_attention_mask, int32_t seq_len, int32_t enc_len, float timestep,
@@ -378,19 +348,6 @@ ace_ggml_status ace_ggml_dit_forward(ace_ggml_context* ctx, const float* hidden_
     if (enc_len < 0) enc_len = 0;
     return dit_forward_impl(ctx, hidden_states, context_latents, encoder_hidden_states, attention_mask, encoder_attention_mask, 1,
                             seq_len, enc_len, &timestep, &timestep_r, out, out_size, "ace_ggml_dit_forward");
-}
-
-ace_ggml_status ace_ggml_generate_audio_simple(ace_ggml_context* ctx, const int32_t*, int32_t, int32_t, float, int32_t, float*, size_t, int32_t*, int32_t*) {
-    return unsupported(ctx, "ace_ggml_generate_audio_simple (needs the text encoder)");
-}
-ace_ggml_status ace_ggml_generate_audio_style_lyric_simple(ace_ggml_context* ctx, const int32_t*, int32_t, const int32_t*, int32_t, int32_t, float, int32_t,
-                                                           float*, size_t, int32_t*, int32_t*) {
-    return unsupported(ctx, "ace_ggml_generate_audio_style_lyric_simple (needs the text / lyric encoders)");
-}
-ace_ggml_status ace_ggml_generate_audio_style_lyric_timbre_simple(ace_ggml_context* ctx, const int32_t*, int32_t, const int32_t*, int32_t, const float*,
-                                                                  const int32_t*, int32_t, int32_t, int32_t, float, int32_t, float*, size_t, int32_t*,
-                                                                  int32_t*) {
-    return unsupported(ctx, "ace_ggml_generate_audio_style_lyric_timbre_simple (needs the text / lyric / timbre encoders)");
 }
 
 }  // extern "C"

@@ -5,6 +5,7 @@
 #include "dit.h"
 #include "gemm.h"
 #include "kernels.h"
+#include "qwen.h"
 #include "vae.h"
 
 #include <algorithm>
@@ -53,6 +54,9 @@ struct ace_ggml_context {
     ace::DitWorkspace dws;
     ace::VaeModel vae;
     ace::VaeWorkspace vws;
+    ace::VaeEncWorkspace vews;
+    ace::QwenModel text;       // Qwen3 text encoder (ace_ggml_load_lm fills the same slot, as in the reference: acestep_ggml.cpp:246-258)
+    ace::EncWorkspace ews;     // shared by the text encoder and the lyric / timbre condition encoders
     IoBuffers io;
     std::string last_error;
     std::string info;

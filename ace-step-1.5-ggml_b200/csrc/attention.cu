@@ -65,7 +65,7 @@ __device__ __forceinline__ void load_tile(uint32_t sdst, const __half* base, lon
 __global__ void __launch_bounds__(ATT_THREADS)
 attention_kernel(const __half* __restrict__ Q, long q_stride, const __half* __restrict__ K, long k_stride,
                  const __half* __restrict__ V, long v_stride, __half* __restrict__ O, long o_stride,
-                 const int32_t* __restrict__ key_mask, int q_len, int k_len, int n_rep, int window) {
+                 const int32_t* __restrict__ key_mask, int q_len, int k_len, int n_rep, int window, int causal) {
     extern __shared__ __align__(128) uint8_t smem[];
     const uint32_t sQ = smem_u32(smem);
     const uint32_t sK = sQ + TILE_BYTES;       // 2 stages
@@ -89,6 +89,7 @@ attention_kernel(const __half* __restrict__ Q, long q_stride, const __half* __re
         kb_lo = max(0, (q0 - window) / BKEY);
         kb_hi = min(kb_hi, (min(q0 + BQ - 1, q_len - 1) + window) / BKEY);
     }
+    if (causal) kb_hi = min(kb_hi, min(q0 + BQ - 1, q_len - 1) / BKEY);  // keys after the last query of the tile are never visible
 
     auto issue_kv = [&](int kb, int stage) {
         load_tile(sK + stage * TILE_BYTES, Kb, k_stride, kb * BKEY, k_len);
@@ -160,9 +161,10 @@ attention_kernel(const __half* __restrict__ Q, long q_stride, const __half* __re
                 const int kl = nt * 8 + 2 * t4 + (e & 1);
                 const int r = e >> 1;
                 float v = s[nt][e] * sc + kbz[kl];
-                if (window >= 0) {
+                if (window >= 0 || causal) {
                     const int d = qrow[r] - (kb * BKEY + kl);
-                    if (d > window || d < -window) v = -INFINITY;
+                    if (window >= 0 && (d > window || d < -window)) v = -INFINITY;
+                    if (causal && d < 0) v = -INFINITY;  // qwen_model.cpp:611-613 / acestep_dit_model.cpp:1148-1150
                 }
                 s[nt][e] = v;
                 mx[r] = fmaxf(mx[r], v);
@@ -245,11 +247,11 @@ attention_kernel(const __half* __restrict__ Q, long q_stride, const __half* __re
 
 void launch_attention(const __half* Q, long q_stride, const __half* K, long k_stride, const __half* V, long v_stride,
                       __half* O, long o_stride, const int32_t* key_mask, int B, int q_len, int k_len, int n_heads,
-                      int n_kv_heads, int window, cudaStream_t st) {
+                      int n_kv_heads, int window, cudaStream_t st, bool causal) {
     note_launch();
     const double k_eff = window >= 0 ? (double)(2 * window + 1 < k_len ? 2 * window + 1 : k_len) : (double)k_len;
     ProfScope prof_scope(PROF_ATTN, 4.0 * B * n_heads * (double)q_len * k_eff * 128.0, 0.0, st);
-    if (attention_use_tc()) {
+    if (attention_use_tc() && !causal) {  // the causal mask (text encoder, once per song) lives in the mma.sync kernel only
         const cudaError_t e = launch_attention_tc(Q, q_stride, K, k_stride, V, v_stride, O, o_stride, key_mask, B, q_len, k_len, n_heads,
                                                   n_kv_heads, window, st);
         if (e == cudaSuccess) return;
@@ -259,7 +261,7 @@ void launch_attention(const __half* Q, long q_stride, const __half* K, long k_st
     attr.run([](int&) { return cudaFuncSetAttribute(attention_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, ATT_SMEM); });
     dim3 grid((q_len + BQ - 1) / BQ, n_heads, B);
     attention_kernel<<<grid, ATT_THREADS, ATT_SMEM, st>>>(Q, q_stride, K, k_stride, V, v_stride, O, o_stride, key_mask,
-                                                          q_len, k_len, n_heads / n_kv_heads, window);
+                                                          q_len, k_len, n_heads / n_kv_heads, window, causal ? 1 : 0);
 }
 
 }  // namespace ace

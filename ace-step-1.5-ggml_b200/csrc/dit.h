@@ -9,6 +9,7 @@
 #include <cuda_fp16.h>
 #include <cuda_runtime.h>
 
+#include "encoders.h"
 #include "wpack.h"
 
 namespace ace {
@@ -22,6 +23,9 @@ struct DitConfig {
     bool use_sliding_window = false;
     int sliding_window = 0;
     std::vector<std::string> layer_types;
+    // condition encoders (optional keys, acestep_dit_config.cpp:74-78)
+    int text_hidden_dim = 0, num_lyric_encoder_hidden_layers = 0, timbre_hidden_dim = 0, num_timbre_encoder_hidden_layers = 0;
+    int timbre_fix_frame = 0;
 };
 
 struct DitLayer {
@@ -54,6 +58,11 @@ struct DitModel {
     float* out_table = nullptr;   // [2, H]
     float* layer_tables = nullptr;  // [layers, 6, H]
     DitTimeEmbed te, te_r;
+    // condition side (`encoder.*` tensors; all optional — acestep_dit_model.cpp:885-994): text projector, lyric / timbre encoders
+    PackedWeight text_projector, lyric_embed, timbre_embed;
+    bool has_text_projector = false, has_lyric_embed = false, has_timbre_embed = false;
+    float *lyric_embed_b = nullptr, *timbre_embed_b = nullptr;
+    EncStack lyric, timbre;
     std::vector<void*> allocs;    // every device allocation owned by the model
     size_t weight_bytes = 0;
     std::string weight_desc;      // e.g. "gguf:Q8_0" / "safetensors:F32->F16"

@@ -4,6 +4,7 @@
 #include "dit.h"
 #include "gemm.h"
 #include "tensor_file.h"
+#include "loader.h"
 
 #include <algorithm>
 #include <cstdlib>
@@ -13,126 +14,7 @@ namespace ace {
 
 namespace {
 
-struct Loader {
-    const TensorFile* tf;
-    DitModel* m;
-    std::string err;
-    int status = 0;
-    int online_q = -1;  // W_Q8_0 when ACE_GGML_*_WEIGHT_QTYPE asks for it (safetensors only)
-
-    bool fail(int st, const std::string& e) {
-        if (status == 0) {
-            status = st;
-            err = e;
-        }
-        return false;
-    }
-    void* dev_alloc(size_t bytes) {
-        void* p = nullptr;
-        if (cudaMalloc(&p, bytes ? bytes : 16) != cudaSuccess) {
-            fail(1, "cudaMalloc failed (" + std::to_string(bytes) + " bytes): " + cudaGetErrorString(cudaGetLastError()));
-            return nullptr;
-        }
-        m->allocs.push_back(p);
-        m->weight_bytes += bytes;
-        return p;
-    }
-    bool upload(PackedWeight& w, const std::vector<uint8_t>& img) {
-        w.dev = dev_alloc(img.size());
-        if (!w.dev) return false;
-        if (cudaMemcpy(w.dev, img.data(), img.size(), cudaMemcpyHostToDevice) != cudaSuccess)
-            return fail(1, std::string("cudaMemcpy failed: ") + cudaGetErrorString(cudaGetLastError()));
-        if (w.wtype != W_F16 && predecode_enabled()) {  // decoded F16 twin for the compute-bound regime (gemm.h)
-            w.dev_f16 = dev_alloc(gemm_predecode_bytes(w));
-            if (!w.dev_f16) return false;
-            const cudaError_t e = gemm_predecode(w, w.dev_f16, nullptr);
-            if (e != cudaSuccess) return fail(1, std::string("weight predecode failed: ") + cudaGetErrorString(e));
-        }
-        return true;
-    }
-    float* upload_f32(const std::vector<float>& v) {
-        float* d = static_cast<float*>(dev_alloc(v.size() * 4));
-        if (!d) return nullptr;
-        if (cudaMemcpy(d, v.data(), v.size() * 4, cudaMemcpyHostToDevice) != cudaSuccess) {
-            fail(1, std::string("cudaMemcpy failed: ") + cudaGetErrorString(cudaGetLastError()));
-            return nullptr;
-        }
-        return d;
-    }
-    bool vec(const std::string& name, int64_t expect, float*& out) {
-        std::vector<float> v;
-        std::string e;
-        if (!tf->read_f32(name, v, nullptr, e)) return fail(3, e);
-        if ((int64_t)v.size() != expect) return fail(3, "unexpected size for " + name);
-        out = upload_f32(v);
-        return out != nullptr;
-    }
-
-    // Row-concatenation (or pairwise interleave) of 2-D weights [N_i, K] -> one packed matrix.
-    bool linear(const std::vector<std::string>& names, bool interleave, int K, PackedWeight& out) {
-        std::vector<const TensorInfo*> ti;
-        int N = 0;
-        for (const auto& n : names) {
-            const TensorInfo* t = tf->find(n);
-            if (!t) return fail(3, "missing tensor: " + n);
-            if (t->shape.size() != 2 || t->shape[1] != K) return fail(3, "invalid tensor shape for " + n);
-            ti.push_back(t);
-            N += (int)t->shape[0];
-        }
-        if (interleave && (ti.size() != 2 || ti[0]->shape[0] != ti[1]->shape[0])) return fail(1, "bad interleave request");
-        const int gt = ti[0]->ggml_type;
-        bool same = true;
-        for (auto* t : ti) same = same && t->ggml_type == gt;
-        const bool quant_file = same && (gt == GGML_Q8_0 || gt == GGML_Q4_K || gt == GGML_Q6_K) && K % TILE_K == 0;
-        std::vector<uint8_t> img;
-        std::string e;
-        if (quant_file) {
-            const size_t rb = ggml_row_bytes(gt, K);
-            std::vector<uint8_t> rows((size_t)N * rb);
-            if (interleave) {
-                const int half = (int)ti[0]->shape[0];
-                for (int j = 0; j < half; ++j) {
-                    std::memcpy(rows.data() + (size_t)(2 * j) * rb, ti[0]->data + (size_t)j * rb, rb);
-                    std::memcpy(rows.data() + (size_t)(2 * j + 1) * rb, ti[1]->data + (size_t)j * rb, rb);
-                }
-            } else {
-                size_t off = 0;
-                for (auto* t : ti) {
-                    std::memcpy(rows.data() + off, t->data, (size_t)t->shape[0] * rb);
-                    off += (size_t)t->shape[0] * rb;
-                }
-            }
-            if (!pack_tiles_ggml(rows.data(), gt, N, K, img, out, e)) return fail(1, e);
-        } else {
-            std::vector<float> w((size_t)N * K);
-            if (interleave) {
-                std::vector<float> a, b;
-                if (!tf->read_f32(names[0], a, nullptr, e) || !tf->read_f32(names[1], b, nullptr, e)) return fail(3, e);
-                const int half = (int)ti[0]->shape[0];
-                for (int j = 0; j < half; ++j) {
-                    std::memcpy(w.data() + (size_t)(2 * j) * K, a.data() + (size_t)j * K, (size_t)K * 4);
-                    std::memcpy(w.data() + (size_t)(2 * j + 1) * K, b.data() + (size_t)j * K, (size_t)K * 4);
-                }
-            } else {
-                size_t off = 0;
-                for (const auto& n : names) {
-                    std::vector<float> a;
-                    if (!tf->read_f32(n, a, nullptr, e)) return fail(3, e);
-                    std::memcpy(w.data() + off, a.data(), a.size() * 4);
-                    off += a.size();
-                }
-            }
-            if (!pack_f32(w, N, K, img, out)) return false;
-        }
-        return upload(out, img);
-    }
-    bool pack_f32(const std::vector<float>& w, int N, int K, std::vector<uint8_t>& img, PackedWeight& out) {
-        std::string e;
-        const int wt = (online_q == W_Q8_0 && !tf->is_gguf() && K % 32 == 0 && K % TILE_K == 0) ? W_Q8_0 : W_F16;
-        if (!pack_tiles_f32(w.data(), N, 1, K, wt, img, out, e)) return fail(1, e);
-        return true;
-    }
-};
+using Loader = WeightLoader;
 
 bool parse_config(const std::string& path, DitConfig& c, std::string& err) {
     JsonValue root;
@@ -165,6 +47,11 @@ bool parse_config(const std::string& path, DitConfig& c, std::string& err) {
     if (!need_int("patch_size", c.patch_size) || !need_int("in_channels", c.in_channels) ||
         !need_int("audio_acoustic_hidden_dim", c.audio_acoustic_hidden_dim))
         return false;
+    if (root.get_int("text_hidden_dim", iv)) c.text_hidden_dim = (int)iv;
+    if (root.get_int("num_lyric_encoder_hidden_layers", iv)) c.num_lyric_encoder_hidden_layers = (int)iv;
+    if (root.get_int("timbre_hidden_dim", iv)) c.timbre_hidden_dim = (int)iv;
+    if (root.get_int("num_timbre_encoder_hidden_layers", iv)) c.num_timbre_encoder_hidden_layers = (int)iv;
+    if (root.get_int("timbre_fix_frame", iv)) c.timbre_fix_frame = (int)iv;
     (void)root.get_bool("use_sliding_window", c.use_sliding_window);
     if (root.get_int("sliding_window", iv)) c.sliding_window = (int)iv;
     if (root.get_num("rope_theta", d)) c.rope_theta = (float)d;
@@ -210,6 +97,10 @@ void DitModel::release() {
     for (void* p : allocs) cudaFree(p);
     allocs.clear();
     layers.clear();
+    lyric = EncStack();
+    timbre = EncStack();
+    has_text_projector = has_lyric_embed = has_timbre_embed = false;
+    lyric_embed_b = timbre_embed_b = nullptr;
     weight_bytes = 0;
 }
 
@@ -242,7 +133,7 @@ int dit_load(const std::string& model_dir, DitModel& m, std::string& err) {
     else tf = TensorFile::open_safetensors(model_dir + "/model.safetensors", err);
     if (!tf) return 3;
 
-    Loader L{tf.get(), &m, {}, 0, -1};
+    Loader L{tf.get(), &m.allocs, &m.weight_bytes, {}, 0, -1};
     std::string unsup;
     L.online_q = parse_online_qtype(unsup);
     if (L.online_q == -2 && !tf->is_gguf()) {
@@ -339,6 +230,46 @@ int dit_load(const std::string& model_dir, DitModel& m, std::string& err) {
     if (ok) {
         m.layer_tables = L.upload_f32(tables);
         ok = m.layer_tables != nullptr;
+    }
+    // ---- condition side: `encoder.*` (acestep_dit_model.cpp:885-994).  Projections are optional (loaded when present); the
+    // layer stacks are required as soon as config.json announces them, exactly like the reference loader.
+    auto init_stack = [&](EncStack& st) {
+        st.H = H;
+        st.I = I;
+        st.n_heads = c.num_attention_heads;
+        st.n_kv = c.num_key_value_heads;
+        st.hd = hd;
+        st.eps = c.rms_norm_eps;
+        st.theta = c.rope_theta;
+        st.sliding_window = c.sliding_window;
+    };
+    auto opt_linear = [&](const std::string& name, PackedWeight& w, bool& has) {
+        const TensorInfo* t = tf->find(name);
+        has = false;
+        if (!t) return true;
+        if (t->shape.size() != 2 || t->shape[1] % 8 != 0) return L.fail(3, "invalid tensor shape for " + name);
+        has = L.linear({name}, false, (int)t->shape[1], w);
+        return has;
+    };
+    auto opt_vec = [&](const std::string& name, int64_t n, float*& dst) { return !tf->find(name) || L.vec(name, n, dst); };
+    ok = ok && opt_linear("encoder.text_projector.weight", m.text_projector, m.has_text_projector);
+    ok = ok && opt_linear("encoder.lyric_encoder.embed_tokens.weight", m.lyric_embed, m.has_lyric_embed);
+    ok = ok && opt_vec("encoder.lyric_encoder.embed_tokens.bias", H, m.lyric_embed_b);
+    init_stack(m.lyric);
+    init_stack(m.timbre);
+    ok = ok && opt_vec("encoder.lyric_encoder.norm.weight", H, m.lyric.final_norm);
+    if (ok && c.num_lyric_encoder_hidden_layers > 0) {
+        ok = enc_stack_load(L, "encoder.lyric_encoder.layers.", c.num_lyric_encoder_hidden_layers, m.lyric);
+        for (int i = 0; ok && i < c.num_lyric_encoder_hidden_layers; ++i)  // layer_types of the decoder index the encoder layers too (:933-935)
+            m.lyric.layers[(size_t)i].sliding = i < (int)c.layer_types.size() && c.layer_types[(size_t)i] == "sliding_attention";
+    }
+    ok = ok && opt_linear("encoder.timbre_encoder.embed_tokens.weight", m.timbre_embed, m.has_timbre_embed);
+    ok = ok && opt_vec("encoder.timbre_encoder.embed_tokens.bias", H, m.timbre_embed_b);
+    ok = ok && opt_vec("encoder.timbre_encoder.norm.weight", H, m.timbre.final_norm);
+    if (ok && c.num_timbre_encoder_hidden_layers > 0) {
+        ok = enc_stack_load(L, "encoder.timbre_encoder.layers.", c.num_timbre_encoder_hidden_layers, m.timbre);
+        for (int i = 0; ok && i < c.num_timbre_encoder_hidden_layers; ++i)
+            m.timbre.layers[(size_t)i].sliding = i < (int)c.layer_types.size() && c.layer_types[(size_t)i] == "sliding_attention";
     }
     if (!ok) {
         err = L.err;

@@ -113,7 +113,7 @@ __global__ void build_modulation_kernel(const float* __restrict__ tables, const 
 __global__ void __launch_bounds__(128)
 rmsnorm_mod_kernel(const float* __restrict__ x, const float* __restrict__ w, const float* __restrict__ scale1,
                    const float* __restrict__ shift, long mod_bstride, __half* __restrict__ y, long rows, int rows_per_b,
-                   int H, float eps) {
+                   int H, float eps, float* __restrict__ y32) {
     __shared__ float red[4];
     const long row = blockIdx.x;
     const int tid = threadIdx.x;
@@ -165,6 +165,8 @@ rmsnorm_mod_kernel(const float* __restrict__ x, const float* __restrict__ w, con
         if (sh) {
             o0 += a2.x; o1 += a2.y; o2 += a2.z; o3 += a2.w;
         }
+        if (y32) *reinterpret_cast<float4*>(y32 + row * H + c) = make_float4(o0, o1, o2, o3);
+        if (!y) return;
         __half2 h0 = __floats2half2_rn(o0, o1), h1 = __floats2half2_rn(o2, o3);
         uint2 o;
         o.x = *reinterpret_cast<uint32_t*>(&h0);
@@ -319,7 +321,50 @@ conv_small_out_kernel(const __half* __restrict__ xs, const __half* __restrict__ 
     }
 }
 
+__global__ void gather_rows_kernel(const float* __restrict__ table, const int32_t* __restrict__ ids, float* __restrict__ out,
+                                   int n, int width, int vocab) {
+    const long idx = (long)blockIdx.x * blockDim.x + threadIdx.x;  // one float4 per thread
+    const int w4 = width >> 2;
+    if (idx >= (long)n * w4) return;
+    const int r = (int)(idx / w4), c = (int)(idx % w4);
+    const int id = ids[r];
+    float4 v = make_float4(0.f, 0.f, 0.f, 0.f);
+    if (id >= 0 && id < vocab) v = __ldg(reinterpret_cast<const float4*>(table + (long)id * width) + c);
+    reinterpret_cast<float4*>(out + (long)r * width)[c] = v;
+}
+
+__global__ void pad_channels_f16_kernel(const float* __restrict__ src, __half* __restrict__ dst, long rows, int c_src, int c_dst) {
+    const long idx = (long)blockIdx.x * blockDim.x + threadIdx.x;
+    if (idx >= rows * c_dst) return;
+    const long r = idx / c_dst;
+    const int c = (int)(idx % c_dst);
+    dst[idx] = __float2half_rn(c < c_src ? src[r * c_src + c] : 0.f);
+}
+
+__global__ void take_channels_f32_kernel(const float* __restrict__ src, float* __restrict__ dst, long rows, int c_src, int c_dst) {
+    const long idx = (long)blockIdx.x * blockDim.x + threadIdx.x;
+    if (idx >= rows * c_dst) return;
+    const long r = idx / c_dst;
+    dst[idx] = src[r * c_src + (idx % c_dst)];
+}
+
 }  // namespace
+
+void launch_gather_rows(const float* table, const int32_t* ids, float* out, int n, int width, int vocab, cudaStream_t st) {
+    note_launch();
+    ProfScope prof_scope(PROF_ELEM, 0.0, (double)n * width * 8.0, st);
+    gather_rows_kernel<<<blocks_for((long)n * (width >> 2), 256), 256, 0, st>>>(table, ids, out, n, width, vocab);
+}
+void launch_pad_channels_f16(const float* src, __half* dst, long rows, int c_src, int c_dst, cudaStream_t st) {
+    note_launch();
+    ProfScope prof_scope(PROF_ELEM, 0.0, (double)rows * (c_src * 4.0 + c_dst * 2.0), st);
+    pad_channels_f16_kernel<<<blocks_for(rows * c_dst, 256), 256, 0, st>>>(src, dst, rows, c_src, c_dst);
+}
+void launch_take_channels_f32(const float* src, float* dst, long rows, int c_src, int c_dst, cudaStream_t st) {
+    note_launch();
+    ProfScope prof_scope(PROF_ELEM, 0.0, (double)rows * c_dst * 8.0, st);
+    take_channels_f32_kernel<<<blocks_for(rows * c_dst, 256), 256, 0, st>>>(src, dst, rows, c_src, c_dst);
+}
 
 void launch_pack_dit_input(const float* hidden, const float* context, __half* x0, int B, int T, int S, int patch,
                            int ctx_dim, int audio_dim, cudaStream_t st) {
@@ -354,11 +399,11 @@ void launch_build_modulation(const float* tables, const float* proj, float* mod,
                                                                     B, layers, H);
 }
 void launch_rmsnorm_mod(const float* x, const float* w, const float* scale1, const float* shift, long mod_bstride,
-                        __half* y, int B, int rows_per_b, int H, float eps, cudaStream_t st) {
+                        __half* y, int B, int rows_per_b, int H, float eps, cudaStream_t st, float* y32) {
     note_launch();
     const long rows = (long)B * rows_per_b;
-    ProfScope prof_scope(PROF_ELEM, 0.0, (double)rows * H * 6.0, st);  // fp32 in, fp16 out; weight / scale / shift are L2-resident vectors
-    launch_pdl(rmsnorm_mod_kernel, dim3((unsigned)rows), dim3(128), 0, st, x, w, scale1, shift, mod_bstride, y, rows, rows_per_b, H, eps);
+    ProfScope prof_scope(PROF_ELEM, 0.0, (double)rows * H * (4.0 + (y ? 2.0 : 0.0) + (y32 ? 4.0 : 0.0)), st);  // weight / scale / shift are L2-resident vectors
+    launch_pdl(rmsnorm_mod_kernel, dim3((unsigned)rows), dim3(128), 0, st, x, w, scale1, shift, mod_bstride, y, rows, rows_per_b, H, eps, y32);
 }
 void launch_headnorm_rope(__half* buf, long row_stride, int col0, int n_heads, const float* w, const float2* rope_tab,
                           int B, int rows_per_b, float eps, cudaStream_t st) {

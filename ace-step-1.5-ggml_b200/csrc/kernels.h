@@ -109,8 +109,15 @@ void launch_build_modulation(const float* tables /*[layers,6,H]*/, const float* 
 // ---- normalisation -------------------------------------------------------------------------------
 // y = fp16( x / sqrt(mean(x^2)+eps) * w * scale1[b] + shift[b] );  scale1/shift may be null (plain RMSNorm)
 // reference: ggml_rms_norm (ggml-cpu/ops.cpp:3646-3697) + acestep_dit_model.cpp:1097-1106, 1477-1481
+// y32 (optional) receives the same result unrounded (final norms of the condition / text encoders, whose output is fp32)
 void launch_rmsnorm_mod(const float* x, const float* w, const float* scale1, const float* shift, long mod_bstride,
-                        __half* y, int B, int rows_per_b, int H, float eps, cudaStream_t st);
+                        __half* y, int B, int rows_per_b, int H, float eps, cudaStream_t st, float* y32 = nullptr);
+// out[i, :] = table[ids[i], :]  (fp32 rows; ggml_get_rows + cast, qwen_model.cpp:553-554); ids outside [0, vocab) give zeros
+void launch_gather_rows(const float* table, const int32_t* ids, float* out, int n, int width, int vocab, cudaStream_t st);
+// dst[l, 0..c_dst) = fp16(src[l, 0..c_src)) zero-padded (VAE encoder input: 2 audio channels -> 8, acestep_vae_model.cpp:1018-1027)
+void launch_pad_channels_f16(const float* src, __half* dst, long rows, int c_src, int c_dst, cudaStream_t st);
+// dst[l, 0..c_dst) = src[l, 0..c_dst) of rows c_src wide (posterior mean = first half of the encoder's channels, :1039-1043)
+void launch_take_channels_f32(const float* src, float* dst, long rows, int c_src, int c_dst, cudaStream_t st);
 // in place on a token-major fp16 buffer: per (token, head) RMSNorm over head_dim=128 with weight w, then NEOX RoPE
 // (pairs (i, i+64), angle pos * theta^(-2i/128)) when rope_tab != null.  rope_tab: [S, 64] (cos, sin) float2.
 // reference: acestep_dit_model.cpp:1202-1210, ggml_rope_ext NEOX (ggml-cpu/ops.cpp:5637-5777)
@@ -121,11 +128,11 @@ void launch_build_rope_table(float2* tab, int S, int half_dim, float theta, cuda
 // ---- attention -----------------------------------------------------------------------------------
 // O[b, q, h, :] = softmax_k( Q[b,q,h,:].K[b,k,h/rep,:] / sqrt(128) + mask ) V      (head_dim = 128)
 // Q/K/V/O are token-major fp16 with independent row strides; key k is visible to query q iff
-// (window < 0 or |q-k| <= window) and (key_mask == null or key_mask[b,k] != 0).
-// reference: acestep_dit_model.cpp:1132-1173 (mask), 1212-1256 (GQA repeat, scale, softmax, PV)
+// (window < 0 or |q-k| <= window) and (key_mask == null or key_mask[b,k] != 0) and (not causal or k <= q).
+// reference: acestep_dit_model.cpp:1132-1173 (mask), 1212-1256 (GQA repeat, scale, softmax, PV); qwen_model.cpp:603-624 (causal)
 void launch_attention(const __half* Q, long q_stride, const __half* K, long k_stride, const __half* V, long v_stride,
                       __half* O, long o_stride, const int32_t* key_mask, int B, int q_len, int k_len, int n_heads,
-                      int n_kv_heads, int window, cudaStream_t st);
+                      int n_kv_heads, int window, cudaStream_t st, bool causal = false);
 
 // tcgen05 / TMEM / TMA implementation (attention_tc.cu), the default; ACE_B200_ATTN=mma selects the mma.sync kernel of
 // attention.cu (kept as the independent implementation the tensor-memory kernel is unit-tested against)

@@ -18,7 +18,14 @@ void VaeModel::release() {
     for (void* p : allocs) cudaFree(p);
     allocs.clear();
     blocks.clear();
+    enc_blocks.clear();
+    has_encoder = false;
     weight_bytes = 0;
+}
+void VaeEncWorkspace::release() {
+    for (void* p : allocs) cudaFree(p);
+    allocs.clear();
+    *this = VaeEncWorkspace();
 }
 void VaeWorkspace::release() {
     for (void* p : allocs) cudaFree(p);
@@ -142,6 +149,56 @@ struct VLoader {
         if (!c.w.dev) return false;
         return bias_vec(prefix + ".bias", c.c_out, stride, c.bias);
     }
+    // plain conv whose input channels are zero-padded to c_pad (encoder.conv1: 2 audio channels -> 8, the GEMM's row granule)
+    bool conv_padded(const std::string& prefix, int c_pad, VaeConv& c) {
+        std::vector<float> w;
+        std::vector<int64_t> sh;
+        if (!folded(prefix, w, sh)) return false;
+        c.c_out = (int)sh[0];
+        const int cin = (int)sh[1];
+        c.c_in = c_pad;
+        c.k = (int)sh[2];
+        c.dilation = 1;
+        c.stride = 1;
+        c.pad = (c.k - 1) / 2;
+        if (cin > c_pad) return fail(4, "unsupported channel count in " + prefix);
+        std::vector<float> r((size_t)c.c_out * c.k * c_pad, 0.f);
+        for (int co = 0; co < c.c_out; ++co)
+            for (int ci = 0; ci < cin; ++ci)
+                for (int t = 0; t < c.k; ++t) r[((size_t)co * c.k + t) * c_pad + ci] = w[((size_t)co * cin + ci) * c.k + t];
+        std::vector<uint8_t> img;
+        std::string e;
+        if (!pack_tiles_f32(r.data(), c.c_out, c.k, c_pad, W_F16, img, c.w, e)) return fail(1, e);
+        c.w.dev = dev_upload(img.data(), img.size());
+        return c.w.dev && bias_vec(prefix + ".bias", c.c_out, 1, c.bias);
+    }
+    // strided conv (k = 2*stride, stride s, pad ceil(s/2)): weight_v [Cout, Cin, K].  With the padded input viewed as rows of s
+    // consecutive positions ([L', s*Cin]) it is a 2-tap GEMM: W'[co][T][j*Cin + ci] = w[co][ci][T*s + j]
+    bool conv_strided(const std::string& prefix, int stride, VaeConv& c) {
+        std::vector<float> w;
+        std::vector<int64_t> sh;
+        if (!folded(prefix, w, sh)) return false;
+        c.c_out = (int)sh[0];
+        c.c_in = (int)sh[1];
+        c.k = (int)sh[2];
+        c.stride = stride;
+        c.dilation = 1;
+        c.pad = (stride + 1) / 2;
+        if (c.k != 2 * stride) return fail(4, "unsupported strided-conv kernel size (expected 2*stride) in " + prefix);
+        if (c.c_in % 8 != 0) return fail(4, "unsupported channel count in " + prefix);
+        const int K = stride * c.c_in;
+        std::vector<float> r((size_t)c.c_out * 2 * K);
+        for (int co = 0; co < c.c_out; ++co)
+            for (int T = 0; T < 2; ++T)
+                for (int j = 0; j < stride; ++j)
+                    for (int ci = 0; ci < c.c_in; ++ci)
+                        r[((size_t)co * 2 + T) * K + (size_t)j * c.c_in + ci] = w[((size_t)co * c.c_in + ci) * c.k + T * stride + j];
+        std::vector<uint8_t> img;
+        std::string e;
+        if (!pack_tiles_f32(r.data(), c.c_out, 2, K, W_F16, img, c.w, e)) return fail(1, e);
+        c.w.dev = dev_upload(img.data(), img.size());
+        return c.w.dev && bias_vec(prefix + ".bias", c.c_out, 1, c.bias);
+    }
     bool res_unit(const std::string& prefix, int C, int dilation, VaeResUnit& ru) {
         return snake(prefix + ".snake1", C, ru.snake1) && conv(prefix + ".conv1", dilation, true, ru.conv1) &&
                snake(prefix + ".snake2", C, ru.snake2) && conv(prefix + ".conv2", 1, true, ru.conv2);
@@ -242,12 +299,174 @@ int vae_load(const std::string& model_dir_in, VaeModel& m, std::string& err) {
             }
         } else ok = false;
     }
+    // ---- encoder (acestep_vae_model.cpp:913-929): conv1 k7 -> blocks [3 res units, snake, strided conv] -> snake -> conv2 k3
+    if (ok && tf->find("encoder.conv1.weight_v")) {
+        std::vector<int> ech;  // encoder_hidden_size * ([1] + multiples)
+        for (int x : mult) ech.push_back(c.encoder_hidden_size * x);
+        const int ne = (int)c.downsampling_ratios.size();
+        ok = (int)ech.size() >= ne + 1 || L.fail(3, "invalid VAE config: channel_multiples shorter than ratios");
+        ok = ok && L.conv_padded("encoder.conv1", 8, m.enc_conv1);
+        if (ok && (m.enc_conv1.c_out != ech[0] || m.enc_conv1.k != 7)) ok = L.fail(3, "unexpected encoder.conv1 shape");
+        m.enc_blocks.resize((size_t)ne);
+        for (int i = 0; ok && i < ne; ++i) {
+            VaeEncBlock& b = m.enc_blocks[(size_t)i];
+            const std::string p = "encoder.block." + std::to_string(i);
+            for (int j = 0; ok && j < 3; ++j) {
+                ok = L.res_unit(p + ".res_unit" + std::to_string(j + 1), ech[(size_t)i], dil[j], b.res[j]);
+                if (ok && (b.res[j].conv1.c_out != ech[(size_t)i] || b.res[j].conv1.k != 7 || b.res[j].conv2.k != 1)) ok = L.fail(3, "unexpected residual-unit shape in " + p);
+            }
+            ok = ok && L.snake(p + ".snake1", ech[(size_t)i], b.snake1);
+            ok = ok && L.conv_strided(p + ".conv1", c.downsampling_ratios[(size_t)i], b.conv);
+            if (ok && (b.conv.c_in != ech[(size_t)i] || b.conv.c_out != ech[(size_t)i + 1])) ok = L.fail(3, "unexpected shape for " + p + ".conv1");
+        }
+        ok = ok && L.snake("encoder.snake1", ech[(size_t)ne], m.enc_snake);
+        ok = ok && L.conv("encoder.conv2", 1, true, m.enc_conv2);
+        if (ok && (m.enc_conv2.c_in != ech[(size_t)ne] || m.enc_conv2.c_out < c.decoder_input_channels || m.enc_conv2.k != 3))
+            ok = L.fail(3, "unexpected encoder.conv2 shape");
+        m.has_encoder = ok;
+    }
     if (!ok) {
         err = L.err;
         m.release();
         return L.status ? L.status : 1;
     }
     return 0;
+}
+
+// ------------------------------------------------------------------------------------------------ encoder
+long vae_encode_out_frames(const VaeModel& m, long n_samples) {
+    long L = n_samples;
+    for (const VaeEncBlock& b : m.enc_blocks) {
+        const long s = b.conv.stride, p = b.conv.pad;
+        if (L + 2 * p < 2 * s) return 0;
+        L = (L + 2 * p - 2 * s) / s + 1;
+    }
+    return L;
+}
+
+bool vae_encode_workspace_reserve(const VaeModel& m, VaeEncWorkspace& ws, long n_samples, std::string& err) {
+    if ((size_t)n_samples <= ws.cap_samples && !ws.allocs.empty()) return true;
+    const size_t S = std::max<size_t>((size_t)n_samples, ws.cap_samples);
+    ws.release();
+    // widest level in elements: channels x positions never grows along the encoder (channels x2, positions / stride >= 2)
+    size_t lvl = (size_t)m.enc_conv1.c_out * S, widest = lvl, L = S;
+    for (const VaeEncBlock& b : m.enc_blocks) {
+        widest = std::max(widest, (size_t)b.conv.c_in * (L + 4 * (size_t)b.conv.stride));  // padded copy of the level
+        L = L / (size_t)b.conv.stride + 2;
+        widest = std::max(widest, (size_t)b.conv.c_out * L);
+    }
+    bool ok = true;
+    auto alloc = [&](auto*& ptr, size_t count) {
+        if (!ok) return;
+        void* p = nullptr;
+        if (cudaMalloc(&p, count * sizeof(*ptr) + 256) != cudaSuccess) {
+            err = std::string("VAE encoder workspace cudaMalloc failed: ") + cudaGetErrorString(cudaGetLastError());
+            ok = false;
+            return;
+        }
+        ws.allocs.push_back(p);
+        ptr = reinterpret_cast<decltype(ptr)>(p);
+    };
+    alloc(ws.a16, S * 8);
+    alloc(ws.x, widest);
+    alloc(ws.xs, widest);
+    alloc(ws.h, widest);
+    alloc(ws.xp, widest);
+    alloc(ws.y, (L + 2) * (size_t)m.enc_conv2.c_out);
+    if (!ok) {
+        ws.release();
+        return false;
+    }
+    ws.cap_samples = S;
+    return true;
+}
+
+cudaError_t vae_encode_device(const VaeModel& m, VaeEncWorkspace& ws, const float* d_audio, long n_samples, float* d_latents,
+                              cudaStream_t st) {
+    const VaeConfig& c = m.cfg;
+    cudaError_t rc = cudaSuccess;
+    auto run = [&](const __half* A, long L, long l_out, int C, const VaeConv& cv, int tap_stride, int tap_offset, GemmEpilogue e) {
+        if (rc != cudaSuccess) return;
+        GemmProblem g;
+        g.A = A;
+        g.B = 1;
+        g.L = (int)L;
+        g.C = C;
+        g.a_lstride = C;
+        g.a_bstride = L * C;
+        g.l_out = (int)l_out;
+        g.tap_stride = tap_stride;
+        g.tap_offset = tap_offset;
+        g.W = &cv.w;
+        g.epi = e;
+        if (g.epi.out_bstride == 0) g.epi.out_bstride = l_out * g.epi.ld_out;
+        rc = gemm_launch(g, st);
+    };
+    auto with_snake = [](GemmEpilogue e, const VaeSnake& s) {
+        e.snake_alpha = s.alpha;
+        e.snake_invbeta = s.inv_beta;
+        return e;
+    };
+    long L = n_samples;
+    launch_pad_channels_f16(d_audio, ws.a16, L, c.audio_channels, 8, st);
+    const int ne = (int)m.enc_blocks.size();
+    {  // conv1 k7: epilogue = bias -> x (fp32) and block0.res1.snake1 -> xs
+        GemmEpilogue e;
+        e.bias = m.enc_conv1.bias;
+        e.out_f32 = ws.x;
+        e.out_f16 = ws.xs;
+        e.ld_out = m.enc_conv1.c_out;
+        run(ws.a16, L, L, 8, m.enc_conv1, 1, -m.enc_conv1.pad, with_snake(e, ne ? m.enc_blocks[0].res[0].snake1 : m.enc_snake));
+    }
+    for (int i = 0; i < ne; ++i) {
+        const VaeEncBlock& b = m.enc_blocks[(size_t)i];
+        const int C = b.conv.c_in, s = b.conv.stride, p = b.conv.pad;
+        for (int j = 0; j < 3; ++j) {
+            const VaeResUnit& ru = b.res[j];
+            {
+                GemmEpilogue e;
+                e.bias = ru.conv1.bias;
+                e.out_f16 = ws.h;
+                e.ld_out = C;
+                run(ws.xs, L, L, C, ru.conv1, ru.conv1.dilation, -ru.conv1.pad, with_snake(e, ru.snake2));
+            }
+            {
+                GemmEpilogue e;
+                e.bias = ru.conv2.bias;
+                e.resid = ws.x;
+                e.ld_out = C;
+                e.out_f16 = ws.xs;
+                if (j < 2) e.out_f32 = ws.x;
+                run(ws.h, L, L, C, ru.conv2, 1, 0, with_snake(e, j < 2 ? b.res[j + 1].snake1 : b.snake1));
+            }
+        }
+        // strided conv: xp = [p zero rows | snake(x) | zero tail], read as rows of s positions; out[l] = xp'[l] W0 + xp'[l+1] W1
+        const long Lout = (L + 2 * p - 2 * s) / s + 1;
+        const long rows = Lout + 1;
+        if (rc == cudaSuccess) rc = cudaMemsetAsync(ws.xp, 0, (size_t)p * C * 2, st);
+        if (rc == cudaSuccess) rc = cudaMemcpyAsync(ws.xp + (size_t)p * C, ws.xs, (size_t)L * C * 2, cudaMemcpyDeviceToDevice, st);
+        const long used = (long)p + L, total = rows * s;
+        if (rc == cudaSuccess && total > used) rc = cudaMemsetAsync(ws.xp + (size_t)used * C, 0, (size_t)(total - used) * C * 2, st);
+        {
+            GemmEpilogue e;
+            e.bias = b.conv.bias;
+            e.ld_out = b.conv.c_out;
+            e.out_f16 = ws.xs;
+            if (i + 1 < ne) e.out_f32 = ws.x;
+            run(ws.xp, rows, Lout, s * C, b.conv, 1, 0, with_snake(e, i + 1 < ne ? m.enc_blocks[(size_t)i + 1].res[0].snake1 : m.enc_snake));
+        }
+        L = Lout;
+    }
+    {  // conv2 k3 pad 1 -> [L, encoder_hidden_size]; the posterior mean is the first latent_ch channels (:1039-1043)
+        GemmEpilogue e;
+        e.bias = m.enc_conv2.bias;
+        e.out_f32 = ws.y;
+        e.ld_out = m.enc_conv2.c_out;
+        run(ws.xs, L, L, m.enc_conv2.c_in, m.enc_conv2, 1, -m.enc_conv2.pad, e);
+    }
+    if (rc != cudaSuccess) return rc;
+    launch_take_channels_f32(ws.y, d_latents, L, m.enc_conv2.c_out, c.decoder_input_channels, st);
+    return cudaGetLastError();
 }
 
 bool vae_workspace_reserve(const VaeModel& m, VaeWorkspace& ws, int B, int n_frames, std::string& err) {

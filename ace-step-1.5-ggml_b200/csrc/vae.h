@@ -41,10 +41,23 @@ struct VaeBlock {
     VaeResUnit res[3];
 };
 
+// encoder block: 3 residual units (dilations 1, 3, 9) at C_in, Snake, strided conv k = 2*stride (acestep_vae_model.cpp:643-668)
+struct VaeEncBlock {
+    VaeResUnit res[3];
+    VaeSnake snake1;
+    VaeConv conv;  // packed as a 2-tap GEMM over rows of `stride` consecutive positions: K = stride * C_in per tap
+};
+
 struct VaeModel {
     VaeConfig cfg;
     VaeConv conv1;
     std::vector<VaeBlock> blocks;
+    // encoder (acestep_vae_model.cpp:913-929, 1004-1044); present when the file holds the encoder.* tensors
+    bool has_encoder = false;
+    VaeConv enc_conv1;             // k7, audio channels zero-padded to 8 input channels
+    std::vector<VaeEncBlock> enc_blocks;
+    VaeSnake enc_snake;
+    VaeConv enc_conv2;             // k3 -> encoder_hidden_size (mean | scale)
     VaeSnake snake_out;
     __half* conv2_w = nullptr;  // [audio_channels, 7, C] fp16 (tiny-N tail conv)
     int conv2_cin = 0;
@@ -68,6 +81,23 @@ struct VaeWorkspace {
 };
 
 bool vae_workspace_reserve(const VaeModel& m, VaeWorkspace& ws, int B, int n_frames, std::string& err);
+
+// number of latent frames the encoder produces for n_samples audio samples (floor at every strided conv, PyTorch rule)
+long vae_encode_out_frames(const VaeModel& m, long n_samples);
+// audio (device, [n_samples, audio_channels] fp32 interleaved) -> posterior mean latents (device, [frames, latent_ch] fp32).
+// One clip per call (the reference ABI's shape, acestep_ggml.cpp:975-1072).  Scratch comes from `ws` (grown on demand).
+struct VaeEncWorkspace {
+    size_t cap_samples = 0;
+    __half* a16 = nullptr;   // padded audio
+    float* x = nullptr;      // fp32 residual stream
+    __half *xs = nullptr, *h = nullptr, *xp = nullptr;
+    float* y = nullptr;      // conv2 output [frames, encoder_hidden_size]
+    std::vector<void*> allocs;
+    void release();
+};
+bool vae_encode_workspace_reserve(const VaeModel& m, VaeEncWorkspace& ws, long n_samples, std::string& err);
+cudaError_t vae_encode_device(const VaeModel& m, VaeEncWorkspace& ws, const float* d_audio, long n_samples, float* d_latents,
+                              cudaStream_t st);
 
 // latents in ws.d_lat [B, n_frames, latent_ch] -> audio [B, n_frames*hop, audio_ch] (device pointer `audio`)
 cudaError_t vae_decode_device(const VaeModel& m, VaeWorkspace& ws, int B, int n_frames, float* audio, cudaStream_t st);

@@ -53,6 +53,24 @@ ACE_GGML_API ace_ggml_status ace_b200_generate_audio(
     int32_t enc_len, const float * schedule, int32_t n_steps, float guidance, float * out_latents,
     float * out_audio, size_t out_audio_size);
 
+/* The sampler the reference runs behind ace_ggml_generate_audio_* once the condition is encoded (static
+ * ace_generate_audio_from_encoder, acestep_ggml.cpp:1901-2238), exposed for callers that already hold encoder states:
+ * context_latents = [silence latent | chunk mask] (ACE_GGML_SILENCE_LATENT_F32 file, else VAE-encoded digital silence),
+ * x_T from std::mt19937(seed) + std::normal_distribution<float> in frame-major order, the 8-step table nearest to `shift`,
+ * device-resident Euler loop, VAE decode.  out_audio [seq_len*hop, audio_ch]. */
+ACE_GGML_API ace_ggml_status ace_b200_generate_audio_from_encoder(
+    ace_ggml_context * ctx, const float * encoder_hidden_states, const int32_t * encoder_attention_mask, int32_t enc_len,
+    int32_t seq_len, float shift, int32_t seed, float * out_audio, size_t out_size, int32_t * out_audio_samples,
+    int32_t * out_audio_channels);
+
+/* The two condition encoders of the DiT checkpoint on their own (acestep_dit_model.cpp:1562-1739):
+ * lyric: token embeddings [n_tokens, text_hidden_dim] -> [n_tokens, hidden]; timbre: reference-audio latents
+ * [refer_len, timbre_hidden_dim] -> [hidden] (first time step of the encoded sequence). */
+ACE_GGML_API ace_ggml_status ace_b200_lyric_encoder_forward(ace_ggml_context * ctx, const float * lyric_embeds,
+                                                            int32_t n_tokens, float * out, size_t out_size);
+ACE_GGML_API ace_ggml_status ace_b200_timbre_encoder_forward(ace_ggml_context * ctx, const float * refer_states,
+                                                             int32_t refer_len, float * out, size_t out_size);
+
 /* the reference's shift schedules (acestep_ggml.cpp:1484-1500): t_i = s*u/(1+(s-1)*u), u = 1 - i/n_steps.
  * For n_steps == 8 and shift in {1,2,3} this reproduces the three hard-coded tables. */
 ACE_GGML_API ace_ggml_status ace_b200_shift_schedule(float shift, int32_t n_steps, float * out_schedule);

@@ -47,6 +47,16 @@ def bind(lib):
     lib.ace_ggml_vae_decode.argtypes = [P, F, ctypes.c_int32, F, ctypes.c_size_t]
     lib.ace_ggml_dit_forward.argtypes = [P, F, F, F, I, I, ctypes.c_int32, ctypes.c_int32,
                                          ctypes.c_float, ctypes.c_float, F, ctypes.c_size_t]
+    i32, f32, sz = ctypes.c_int32, ctypes.c_float, ctypes.c_size_t
+    lib.ace_ggml_load_text_encoder.argtypes = [P, ctypes.c_char_p]
+    lib.ace_ggml_vae_encode.argtypes = [P, F, i32, F, sz]
+    lib.ace_ggml_text_encoder_forward.argtypes = [P, I, i32, F, sz]
+    lib.ace_ggml_text_encoder_forward_masked.argtypes = [P, I, I, i32, F, sz]
+    lib.ace_ggml_text_encoder_forward_embeddings.argtypes = [P, I, i32, F, sz]
+    lib.ace_ggml_text_encoder_forward_layers.argtypes = [P, I, I, i32, i32, i32, F, sz]
+    lib.ace_ggml_generate_audio_simple.argtypes = [P, I, i32, i32, f32, i32, F, sz, I, I]
+    lib.ace_ggml_generate_audio_style_lyric_simple.argtypes = [P, I, i32, I, i32, i32, f32, i32, F, sz, I, I]
+    lib.ace_ggml_generate_audio_style_lyric_timbre_simple.argtypes = [P, I, i32, I, i32, F, I, i32, i32, i32, f32, i32, F, sz, I, I]
 
 
 def main():
@@ -67,6 +77,8 @@ def main():
         check(lib.ace_ggml_load_dit(ctx, job["dit_dir"].encode()), "load_dit")
     if job.get("vae_dir"):
         check(lib.ace_ggml_load_vae(ctx, job["vae_dir"].encode()), "load_vae")
+    if job.get("text_dir"):
+        check(lib.ace_ggml_load_text_encoder(ctx, job["text_dir"].encode()), "load_text_encoder")
     timings["load_s"] = time.perf_counter() - t0
 
     inp = dict(np.load(job["inputs"])) if job.get("inputs") else {}
@@ -139,6 +151,52 @@ def main():
                 s0 = (core0 - w0) * hop
                 parts.append(a[s0: s0 + (core1 - core0) * hop])
             outs[c["out"]] = np.concatenate(parts, axis=0)
+        elif op == "vae_encode":
+            audio = get(c["audio"])
+            lc, _, hop = vae_info()
+            out = np.zeros((audio.shape[0] // hop + 2, lc), dtype=np.float32)
+            check(lib.ace_ggml_vae_encode(ctx, fptr(audio), audio.shape[0], fptr(out), out.nbytes), "vae_encode")
+            outs[c["out"]] = out[: audio.shape[0] // hop]
+        elif op == "text_encoder":
+            ids = get(c["ids"]).astype(np.int32)
+            am = get(c.get("mask")) if c.get("mask") else None
+            out = np.zeros((ids.shape[0], int(c["hidden"])), dtype=np.float32)
+            mode = c.get("mode", "forward")
+            if mode == "forward":
+                rc = lib.ace_ggml_text_encoder_forward(ctx, iptr(ids), ids.shape[0], fptr(out), out.nbytes)
+            elif mode == "masked":
+                rc = lib.ace_ggml_text_encoder_forward_masked(ctx, iptr(ids), iptr(am), ids.shape[0], fptr(out), out.nbytes)
+            elif mode == "embeddings":
+                rc = lib.ace_ggml_text_encoder_forward_embeddings(ctx, iptr(ids), ids.shape[0], fptr(out), out.nbytes)
+            else:
+                rc = lib.ace_ggml_text_encoder_forward_layers(ctx, iptr(ids), iptr(am), ids.shape[0], int(c["n_layers"]),
+                                                              int(c.get("final_norm", 1)), fptr(out), out.nbytes)
+            check(rc, "text_encoder " + mode)
+            outs[c["out"]] = out
+        elif op == "generate":
+            _, ac, hop = vae_info()
+            seq_len = int(c["seq_len"])
+            out = np.zeros((seq_len * hop, ac), dtype=np.float32)
+            ns, nc = ctypes.c_int32(), ctypes.c_int32()
+            style = get(c.get("style")) if c.get("style") else None
+            lyric = get(c.get("lyric")) if c.get("lyric") else None
+            refer = get(c.get("refer")) if c.get("refer") else None
+            shift, seed = float(c.get("shift", 3.0)), int(c.get("seed", 0))
+            if c.get("mode", "simple") == "simple":
+                rc = lib.ace_ggml_generate_audio_simple(ctx, iptr(style), style.shape[0], seq_len, shift, seed, fptr(out), out.nbytes,
+                                                        ctypes.byref(ns), ctypes.byref(nc))
+            elif refer is None:
+                rc = lib.ace_ggml_generate_audio_style_lyric_simple(ctx, iptr(style), 0 if style is None else style.shape[0], iptr(lyric),
+                                                                    0 if lyric is None else lyric.shape[0], seq_len, shift, seed, fptr(out),
+                                                                    out.nbytes, ctypes.byref(ns), ctypes.byref(nc))
+            else:
+                order = np.zeros((refer.shape[0],), np.int32)
+                rc = lib.ace_ggml_generate_audio_style_lyric_timbre_simple(ctx, iptr(style), 0 if style is None else style.shape[0], iptr(lyric),
+                                                                           0 if lyric is None else lyric.shape[0], fptr(refer), iptr(order),
+                                                                           refer.shape[0], refer.shape[1], seq_len, shift, seed, fptr(out), out.nbytes,
+                                                                           ctypes.byref(ns), ctypes.byref(nc))
+            check(rc, "generate")
+            outs[c["out"]] = out[: ns.value]
         else:
             raise ValueError(op)
         timings[op + "_" + c["out"] + "_s"] = time.perf_counter() - t1

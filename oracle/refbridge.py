@@ -41,7 +41,7 @@ def ref_available() -> bool:
 
 
 def run_ref(calls: List[dict], inputs: Dict[str, np.ndarray], *, dit_dir: Optional[str] = None,
-            vae_dir: Optional[str] = None, threads: int = 4, compute_buffer_bytes: int = 1 << 30,
+            vae_dir: Optional[str] = None, text_dir: Optional[str] = None, threads: int = 4, compute_buffer_bytes: int = 1 << 30,
             env: Optional[Dict[str, str]] = None, timeout: float = 3600.0, isa: Optional[str] = None):
     """Run the reference. Returns (outputs dict, timings dict)."""
     if not ref_available():
@@ -50,7 +50,7 @@ def run_ref(calls: List[dict], inputs: Dict[str, np.ndarray], *, dit_dir: Option
         inp = os.path.join(td, "in.npz")
         out = os.path.join(td, "out.npz")
         np.savez(inp, **inputs)
-        job = {"lib": ref_lib(isa), "dit_dir": dit_dir, "vae_dir": vae_dir, "threads": threads,
+        job = {"lib": ref_lib(isa), "dit_dir": dit_dir, "vae_dir": vae_dir, "text_dir": text_dir, "threads": threads,
                "compute_buffer_bytes": int(compute_buffer_bytes), "inputs": inp, "out": out, "calls": calls}
         jp = os.path.join(td, "job.json")
         json.dump(job, open(jp, "w"))

@@ -251,5 +251,5 @@ def test_error_behaviour(br, root, tmp_path):
     st = b2.lib.ace_ggml_dit_forward(b2.ctx, hs.ctypes.data_as(F), None, None, None, None, 4, 0, 0.5, 0.5, out.ctypes.data_as(F), out.nbytes)
     assert st == 2 and b2._last_error() == "output buffer too small"
     assert b2.lib.ace_ggml_dit_forward(b2.ctx, hs.ctypes.data_as(F), None, None, None, None, 0, 0, 0.5, 0.5, out.ctypes.data_as(F), out.nbytes) == 2
-    assert b2.lib.ace_ggml_load_text_encoder(b2.ctx, b"/tmp") == 4
+    assert b2.lib.ace_ggml_load_text_encoder(b2.ctx, b"/tmp") == 3  # ACE_GGML_ERR_IO: no config.json (acestep_ggml.cpp:238-244)
     b2.close()

@@ -47,6 +47,11 @@ class DitDims:
     audio_acoustic_hidden_dim: int = 64
     use_sliding_window: bool = True
     sliding_window: int = 128
+    # condition encoders (`encoder.*` tensors, acestep_dit_model.cpp:885-994); 0 layers = not written
+    text_hidden_dim: int = 1024
+    num_lyric_encoder_hidden_layers: int = 0
+    timbre_hidden_dim: int = 64
+    num_timbre_encoder_hidden_layers: int = 0
 
     def layer_types(self) -> List[str]:
         # even layers sliding, odd layers full (R/acestep/mlx_dit/model.py:421-425)
@@ -67,6 +72,35 @@ TOY = DitDims(hidden_size=256, intermediate_size=512, num_hidden_layers=4,
               num_attention_heads=2, num_key_value_heads=1, sliding_window=8)
 MID = DitDims(hidden_size=512, intermediate_size=1536, num_hidden_layers=4,
               num_attention_heads=4, num_key_value_heads=2, sliding_window=16)
+# toy DiT that also carries the condition side: text projector, 2-layer lyric encoder, 2-layer timbre encoder
+TOY_COND = DitDims(hidden_size=256, intermediate_size=512, num_hidden_layers=4,
+                   num_attention_heads=2, num_key_value_heads=1, sliding_window=8,
+                   text_hidden_dim=256, num_lyric_encoder_hidden_layers=2, num_timbre_encoder_hidden_layers=2)
+
+
+@dataclass
+class QwenDims:
+    """Qwen3 text encoder (qwen_config.cpp:52-62)."""
+    vocab_size: int = 151669
+    hidden_size: int = 1024
+    num_hidden_layers: int = 28
+    num_attention_heads: int = 16
+    num_key_value_heads: int = 8
+    intermediate_size: int = 3072
+    head_dim: int = 128
+    max_position_embeddings: int = 32768
+    rms_norm_eps: float = 1e-6
+    rope_theta: float = 1000000.0
+
+    def config_json(self) -> dict:
+        d = asdict(self)
+        d["dtype"] = "float32"
+        return d
+
+
+QWEN_FULL = QwenDims()
+QWEN_TOY = QwenDims(vocab_size=512, hidden_size=256, num_hidden_layers=3, num_attention_heads=2,
+                    num_key_value_heads=1, intermediate_size=512)
 
 
 @dataclass
@@ -92,7 +126,7 @@ class VaeDims:
 
 VAE_FULL = VaeDims()
 # toy VAE: channels 128 -> 64 -> 32 (every level a multiple of 32, like the real 2048..128 plan)
-VAE_TOY = VaeDims(decoder_channels=32, encoder_hidden_size=16,
+VAE_TOY = VaeDims(decoder_channels=32, encoder_hidden_size=128,
                   downsampling_ratios=[2, 4, 6], channel_multiples=[1, 2, 4])
 
 
@@ -194,7 +228,69 @@ def dit_tensors(d: DitDims, seed: int = 0, fast: bool = False) -> Dict[str, np.n
         tab[0, 2] += 1.0
         tab[0, 5] += 1.0
         T[p + "scale_shift_table"] = tab
+
+    def enc_layers(prefix, n):
+        for i in range(n):
+            q = f"{prefix}layers.{i}."
+            norm(q + "input_layernorm.weight", H)
+            norm(q + "post_attention_layernorm.weight", H)
+            lin(q + "self_attn.q_proj", nq * hd, H)
+            lin(q + "self_attn.k_proj", nkv * hd, H)
+            lin(q + "self_attn.v_proj", nkv * hd, H)
+            lin(q + "self_attn.o_proj", H, nq * hd)
+            norm(q + "self_attn.q_norm.weight", hd)
+            norm(q + "self_attn.k_norm.weight", hd)
+            lin(q + "mlp.gate_proj", I, H)
+            lin(q + "mlp.up_proj", I, H)
+            lin(q + "mlp.down_proj", H, I)
+
+    if d.num_lyric_encoder_hidden_layers > 0 or d.num_timbre_encoder_hidden_layers > 0:
+        lin("encoder.text_projector", H, d.text_hidden_dim)
+    if d.num_lyric_encoder_hidden_layers > 0:
+        lin("encoder.lyric_encoder.embed_tokens", H, d.text_hidden_dim, bias=True)
+        norm("encoder.lyric_encoder.norm.weight", H)
+        enc_layers("encoder.lyric_encoder.", d.num_lyric_encoder_hidden_layers)
+    if d.num_timbre_encoder_hidden_layers > 0:
+        lin("encoder.timbre_encoder.embed_tokens", H, d.timbre_hidden_dim, bias=True)
+        norm("encoder.timbre_encoder.norm.weight", H)
+        enc_layers("encoder.timbre_encoder.", d.num_timbre_encoder_hidden_layers)
     return T
+
+
+def qwen_tensors(d: QwenDims, seed: int = 0, fast: bool = False) -> Dict[str, np.ndarray]:
+    """Qwen3 tensors under the names the reference loader reads (qwen_model.cpp:425-470)."""
+    r = _Rng(seed, fast)
+    H, I, hd = d.hidden_size, d.intermediate_size, d.head_dim
+    nq, nkv = d.num_attention_heads, d.num_key_value_heads
+    T: Dict[str, np.ndarray] = {}
+    T["embed_tokens.weight"] = r.normal((d.vocab_size, H), 1.0)
+    T["norm.weight"] = (1.0 + r.normal((H,), 0.05)).astype(np.float32)
+    for i in range(d.num_hidden_layers):
+        p = f"layers.{i}."
+        for nm, n in (("input_layernorm.weight", H), ("post_attention_layernorm.weight", H),
+                      ("self_attn.q_norm.weight", hd), ("self_attn.k_norm.weight", hd)):
+            T[p + nm] = (1.0 + r.normal((n,), 0.05)).astype(np.float32)
+        T[p + "self_attn.q_proj.weight"] = r.normal((nq * hd, H), H ** -0.5)
+        T[p + "self_attn.k_proj.weight"] = r.normal((nkv * hd, H), H ** -0.5)
+        T[p + "self_attn.v_proj.weight"] = r.normal((nkv * hd, H), H ** -0.5)
+        T[p + "self_attn.o_proj.weight"] = r.normal((H, nq * hd), (nq * hd) ** -0.5)
+        T[p + "mlp.gate_proj.weight"] = r.normal((I, H), H ** -0.5)
+        T[p + "mlp.up_proj.weight"] = r.normal((I, H), H ** -0.5)
+        T[p + "mlp.down_proj.weight"] = r.normal((H, I), I ** -0.5)
+    return T
+
+
+def make_qwen_fixture(out_dir: str, dims: QwenDims = QWEN_TOY, seed: int = 0, *, safetensors: bool = True,
+                      gguf_quant: Optional[str] = None, ggml_lib: Optional[str] = None, fast: bool = False) -> str:
+    os.makedirs(out_dir, exist_ok=True)
+    with open(os.path.join(out_dir, "config.json"), "w") as f:
+        json.dump(dims.config_json(), f, indent=1)
+    T = qwen_tensors(dims, seed, fast)
+    if safetensors:
+        save_safetensors(os.path.join(out_dir, "model.safetensors"), T)
+    if gguf_quant:
+        save_gguf(os.path.join(out_dir, "model.gguf"), T, gguf_quant, ggml_lib, arch="qwen3", fast=fast)
+    return out_dir
 
 
 # --------------------------------------------------------------------------- GGUF export

@@ -74,6 +74,12 @@ SIGNATURES = {
                                                             ctypes.c_int32, _F, ctypes.c_size_t, _I, _I]),
     "ace_b200_lyric_encoder_forward": (ctypes.c_int, [_P, _F, ctypes.c_int32, _F, ctypes.c_size_t]),
     "ace_b200_timbre_encoder_forward": (ctypes.c_int, [_P, _F, ctypes.c_int32, _F, ctypes.c_size_t]),
+    "ace_b200_create_on_device": (ctypes.c_int, [ctypes.POINTER(AceInitParams), ctypes.c_int32, ctypes.POINTER(_P)]),
+    "ace_b200_peer_buffer_create": (ctypes.c_int, [_P, ctypes.c_size_t, _P]),
+    "ace_b200_peer_buffer_open": (ctypes.c_int, [_P, _P, ctypes.c_size_t]),
+    "ace_b200_peer_buffer_attach": (ctypes.c_int, [_P, _P]),
+    "ace_b200_vae_decode_window": (ctypes.c_int, [_P, _F, ctypes.c_int32, ctypes.c_int32, ctypes.c_int32, ctypes.c_int64]),
+    "ace_b200_peer_buffer_read": (ctypes.c_int, [_P, _F, ctypes.c_size_t]),
     "ace_b200_shift_schedule": (ctypes.c_int, [ctypes.c_float, ctypes.c_int32, _F]),
     "ace_b200_last_device_ms": (ctypes.c_double, [_P]),
     "ace_b200_kernel_launches": (ctypes.c_uint64, []),
@@ -130,11 +136,16 @@ class B200Bridge:
     """Same surface as the reference ``GGMLCAPIBridge`` (run_non_ggml_real_case.py:135-354)."""
 
     def __init__(self, lib_path: Optional[os.PathLike] = None, n_threads: int = 1, compute_buffer_mb: int = 0,
-                 use_metal: bool = False):
+                 use_metal: bool = False, device: Optional[int] = None):
+        """device=None: ACE_B200_DEVICE, else the current CUDA device (ace_ggml_create); an int names the GPU explicitly
+        (ace_b200_create_on_device) — several bridges on several GPUs can live in one process."""
         self.lib = load_library(lib_path)
         self.ctx = _P()
         prm = AceInitParams(int(n_threads), 1 if use_metal else 0, int(compute_buffer_mb) * 1024 * 1024)
-        st = self.lib.ace_ggml_create(ctypes.byref(prm), ctypes.byref(self.ctx))
+        if device is None:
+            st = self.lib.ace_ggml_create(ctypes.byref(prm), ctypes.byref(self.ctx))
+        else:
+            st = self.lib.ace_b200_create_on_device(ctypes.byref(prm), int(device), ctypes.byref(self.ctx))
         if st != 0 or not self.ctx:
             self.ctx = _P()
             raise RuntimeError(f"ace_ggml_create failed with status {st} ({STATUS_NAMES.get(st, '?')}): "
@@ -358,6 +369,32 @@ class B200Bridge:
         audio = self.vae_decode_tfirst(lat[w0:w1])
         s0 = (c0 - w0) * self.hop_length
         return np.ascontiguousarray(audio[s0:s0 + (c1 - c0) * self.hop_length])
+
+    # ---- time-split decode with peer stores (include/acestep_b200.h): the assembled clip lives on the owner's GPU
+    def peer_buffer_create(self, n_frames: int) -> bytes:
+        """owner: allocate the assembled-clip buffer for n_frames latent frames; returns its 64-byte CUDA IPC handle"""
+        h = (ctypes.c_ubyte * 64)()
+        nbytes = int(n_frames) * self.hop_length * self.audio_channels * 4
+        self._ensure_ok(self.lib.ace_b200_peer_buffer_create(self.ctx, nbytes, ctypes.cast(h, _P)), "ace_b200_peer_buffer_create")
+        return bytes(h)
+
+    def peer_buffer_open(self, handle: bytes, n_frames: int) -> None:
+        h = (ctypes.c_ubyte * 64).from_buffer_copy(handle)
+        nbytes = int(n_frames) * self.hop_length * self.audio_channels * 4
+        self._ensure_ok(self.lib.ace_b200_peer_buffer_open(self.ctx, ctypes.cast(h, _P), nbytes), "ace_b200_peer_buffer_open")
+
+    def peer_buffer_attach(self, owner: "B200Bridge") -> None:
+        self._ensure_ok(self.lib.ace_b200_peer_buffer_attach(self.ctx, owner.ctx), "ace_b200_peer_buffer_attach")
+
+    def vae_decode_window(self, latents_window: np.ndarray, core_frame0: int, core_frames: int, dst_frame: int) -> None:
+        lat = _f32(latents_window, 2)
+        self._ensure_ok(self.lib.ace_b200_vae_decode_window(self.ctx, _f(lat), int(lat.shape[0]), int(core_frame0), int(core_frames),
+                                                            int(dst_frame)), "ace_b200_vae_decode_window")
+
+    def peer_buffer_read(self, n_frames: int) -> np.ndarray:
+        out = np.empty((int(n_frames) * self.hop_length, self.audio_channels), dtype=np.float32)
+        self._ensure_ok(self.lib.ace_b200_peer_buffer_read(self.ctx, _f(out), out.nbytes), "ace_b200_peer_buffer_read")
+        return out
 
     def vae_decode_batched(self, latents) -> np.ndarray:
         lat = _f32(latents, 3)

@@ -89,3 +89,35 @@ def gather_results(local: np.ndarray, n_songs: int, dist=None) -> Optional[np.nd
     for r in range(world):
         out[r::world] = bufs[r].cpu().numpy()[: counts[r]]
     return out
+
+
+class PeerSplitDecode:
+    """Time-split VAE decode of ONE clip over the ranks of a torch.distributed job (one process per GPU), with the exchange step
+    fused into the decode: rank 0 owns the assembled clip on its GPU and hands its CUDA IPC handle to the other ranks once; each
+    rank's decode then stores its core samples straight into that buffer over NVLink (the last conv kernel's own stores), and the
+    only collective left is the barrier that tells rank 0 the clip is complete."""
+
+    def __init__(self, bridge, n_frames: int, rank: int, world: int, dist, halo: int = 16):
+        import torch
+        self.br, self.n, self.rank, self.world, self.dist, self.halo = bridge, int(n_frames), rank, world, dist, halo
+        dev = torch.device("cuda", torch.cuda.current_device()) if dist.get_backend() == "nccl" else torch.device("cpu")
+        if rank == 0:
+            handle = bridge.peer_buffer_create(self.n)
+            t = torch.frombuffer(bytearray(handle), dtype=torch.uint8).to(dev)
+        else:
+            t = torch.empty(64, dtype=torch.uint8, device=dev)
+        dist.broadcast(t, src=0)
+        if rank != 0:
+            bridge.peer_buffer_open(bytes(t.cpu().numpy().tobytes()), self.n)
+        self.plan = time_split_plan(self.n, rank, world, halo)
+
+    def decode(self, latents: np.ndarray, fetch: bool = False) -> Optional[np.ndarray]:
+        """every rank passes the same full latents [n_frames, C] (3.8 MB for 600 s: replicating it is cheaper than a halo exchange);
+        returns the assembled clip on rank 0 when fetch is set"""
+        w0, w1, c0, c1 = self.plan
+        if c1 > c0:
+            self.br.vae_decode_window(np.ascontiguousarray(latents[w0:w1]), c0 - w0, c1 - c0, c0)
+        self.dist.barrier()  # every rank's stores have landed (vae_decode_window synchronises its stream before returning)
+        if fetch and self.rank == 0:
+            return self.br.peer_buffer_read(self.n)
+        return None

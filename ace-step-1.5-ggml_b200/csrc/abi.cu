@@ -230,13 +230,7 @@ ace_ggml_status sample_latents_device(ace_ggml_context* ctx, const float* noise,
     return ACE_GGML_OK;
 }
 
-}  // namespace ace_abi
-
-using namespace ace_abi;
-
-extern "C" {
-
-ace_ggml_status ace_ggml_create(const ace_ggml_init_params* params, ace_ggml_context** out_ctx) {
+ace_ggml_status create_context(const ace_ggml_init_params* params, int dev, ace_ggml_context** out_ctx) {
     if (!out_ctx) return ACE_GGML_ERR_INVALID_ARG;
     *out_ctx = nullptr;
     int n_dev = 0;
@@ -245,10 +239,8 @@ ace_ggml_status ace_ggml_create(const ace_ggml_init_params* params, ace_ggml_con
                      cudaGetErrorString(cudaGetLastError()));
         return ACE_GGML_ERR;
     }
-    int dev = 0;
-    if (const char* v = std::getenv("ACE_B200_DEVICE")) dev = std::atoi(v);
-    else cudaGetDevice(&dev);
-    if (dev < 0 || dev >= n_dev) return ACE_GGML_ERR_INVALID_ARG;
+    if (dev < 0) cudaGetDevice(&dev);
+    if (dev < 0 || dev >= n_dev || dev >= ACE_MAX_DEVICES) return ACE_GGML_ERR_INVALID_ARG;
     cudaDeviceProp prop;
     if (cudaGetDeviceProperties(&prop, dev) != cudaSuccess) return ACE_GGML_ERR;
     if (prop.major != 10) {
@@ -269,6 +261,30 @@ ace_ggml_status ace_ggml_create(const ace_ggml_init_params* params, ace_ggml_con
     return ACE_GGML_OK;
 }
 
+void release_peer_buffer(ace_ggml_context* ctx) {
+    if (ctx->peer_buf) {
+        if (ctx->peer_kind == 1) cudaFree(ctx->peer_buf);
+        else if (ctx->peer_kind == 2) cudaIpcCloseMemHandle(ctx->peer_buf);
+    }
+    ctx->peer_buf = nullptr;
+    ctx->peer_bytes = 0;
+    ctx->peer_kind = 0;
+}
+
+}  // namespace ace_abi
+
+using namespace ace_abi;
+
+extern "C" {
+
+ace_ggml_status ace_ggml_create(const ace_ggml_init_params* params, ace_ggml_context** out_ctx) {
+    // device of the context: ACE_B200_DEVICE if set, else the calling thread's current CUDA device (ace_b200_create_on_device
+    // names it explicitly, which is what a process that drives several GPUs from several threads should use)
+    int dev = -1;
+    if (const char* v = std::getenv("ACE_B200_DEVICE")) dev = std::atoi(v);
+    return create_context(params, dev, out_ctx);
+}
+
 void ace_ggml_destroy(ace_ggml_context* ctx) {
     if (!ctx) return;
     {
@@ -282,6 +298,7 @@ void ace_ggml_destroy(ace_ggml_context* ctx) {
         ctx->text.release();
         ctx->ews.release();
         ctx->io.release();
+        release_peer_buffer(ctx);
         if (ctx->d_x) cudaFree(ctx->d_x);
         if (ctx->d_v) cudaFree(ctx->d_v);
         for (void* p : ctx->dbg_allocs) cudaFree(p);

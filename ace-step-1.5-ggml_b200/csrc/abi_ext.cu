@@ -84,6 +84,107 @@ ace_ggml_status ace_b200_generate_audio(ace_ggml_context* ctx, const float* nois
     return ACE_GGML_OK;
 }
 
+ace_ggml_status ace_b200_create_on_device(const ace_ggml_init_params* params, int32_t device, ace_ggml_context** out_ctx) {
+    if (device < 0) return ACE_GGML_ERR_INVALID_ARG;
+    return create_context(params, device, out_ctx);
+}
+
+// ---- time-split VAE decode of one clip over several GPUs: the assembled clip lives on ONE device; every rank's final conv
+// kernel stores its core samples straight into it (peer stores over NVLink / NVSwitch), so the split needs no gather pass.
+ace_ggml_status ace_b200_peer_buffer_create(ace_ggml_context* ctx, size_t bytes, void* ipc_handle_out) {
+    if (!ctx || bytes == 0) return ACE_GGML_ERR_INVALID_ARG;
+    DeviceGuard guard(ctx->device);
+    cudaStreamSynchronize(ctx->stream);
+    if (!(ctx->peer_kind == 1 && ctx->peer_bytes >= bytes)) {
+        release_peer_buffer(ctx);
+        void* p = nullptr;
+        if (cudaMalloc(&p, bytes) != cudaSuccess) return cuda_fail(ctx, "peer buffer cudaMalloc failed", cudaGetLastError());
+        ctx->peer_buf = static_cast<float*>(p);
+        ctx->peer_bytes = bytes;
+        ctx->peer_kind = 1;
+    }
+    if (ipc_handle_out) {
+        cudaIpcMemHandle_t h;
+        const cudaError_t e = cudaIpcGetMemHandle(&h, ctx->peer_buf);
+        if (e != cudaSuccess) return cuda_fail(ctx, "cudaIpcGetMemHandle failed", e);
+        static_assert(sizeof(h) == 64, "CUDA IPC handles are 64 bytes");
+        std::memcpy(ipc_handle_out, &h, sizeof(h));
+    }
+    return ACE_GGML_OK;
+}
+
+ace_ggml_status ace_b200_peer_buffer_open(ace_ggml_context* ctx, const void* ipc_handle, size_t bytes) {
+    if (!ctx || !ipc_handle || bytes == 0) return ACE_GGML_ERR_INVALID_ARG;
+    DeviceGuard guard(ctx->device);
+    cudaStreamSynchronize(ctx->stream);
+    release_peer_buffer(ctx);
+    cudaIpcMemHandle_t h;
+    std::memcpy(&h, ipc_handle, sizeof(h));
+    void* p = nullptr;
+    const cudaError_t e = cudaIpcOpenMemHandle(&p, h, cudaIpcMemLazyEnablePeerAccess);
+    if (e != cudaSuccess) return cuda_fail(ctx, "cudaIpcOpenMemHandle failed (no peer access between the two GPUs?)", e);
+    ctx->peer_buf = static_cast<float*>(p);
+    ctx->peer_bytes = bytes;
+    ctx->peer_kind = 2;
+    return ACE_GGML_OK;
+}
+
+ace_ggml_status ace_b200_peer_buffer_attach(ace_ggml_context* ctx, ace_ggml_context* owner) {
+    if (!ctx || !owner || owner->peer_kind != 1 || !owner->peer_buf) return ACE_GGML_ERR_INVALID_ARG;
+    DeviceGuard guard(ctx->device);
+    cudaStreamSynchronize(ctx->stream);
+    release_peer_buffer(ctx);
+    if (owner->device != ctx->device) {
+        int can = 0;
+        cudaDeviceCanAccessPeer(&can, ctx->device, owner->device);
+        if (!can) return set_error(ctx, ACE_GGML_ERR_UNSUPPORTED, "no peer access between the two GPUs");
+        const cudaError_t e = cudaDeviceEnablePeerAccess(owner->device, 0);
+        if (e != cudaSuccess && e != cudaErrorPeerAccessAlreadyEnabled) return cuda_fail(ctx, "cudaDeviceEnablePeerAccess failed", e);
+        cudaGetLastError();
+    }
+    ctx->peer_buf = owner->peer_buf;
+    ctx->peer_bytes = owner->peer_bytes;
+    ctx->peer_kind = 3;
+    return ACE_GGML_OK;
+}
+
+ace_ggml_status ace_b200_vae_decode_window(ace_ggml_context* ctx, const float* latents_window, int32_t n_window_frames,
+                                           int32_t core_frame0, int32_t core_frames, int64_t dst_frame) {
+    if (!ctx || !latents_window || n_window_frames <= 0 || core_frame0 < 0 || core_frames < 0 || core_frame0 + core_frames > n_window_frames ||
+        dst_frame < 0)
+        return ACE_GGML_ERR_INVALID_ARG;
+    if (!ctx->vae_loaded) return set_error(ctx, ACE_GGML_ERR, "vae not loaded");
+    if (!ctx->peer_buf) return set_error(ctx, ACE_GGML_ERR, "no peer buffer bound (ace_b200_peer_buffer_create / _open / _attach)");
+    DeviceGuard guard(ctx->device);
+    const VaeConfig& c = ctx->vae.cfg;
+    const size_t end = (size_t)(dst_frame + core_frames) * c.hop_length * c.audio_channels * 4;
+    if (end > ctx->peer_bytes) return set_error(ctx, ACE_GGML_ERR_INVALID_ARG, "output buffer too small");
+    std::string err;
+    if (!vae_workspace_reserve(ctx->vae, ctx->vws, 1, n_window_frames, err)) return set_error(ctx, ACE_GGML_ERR, err);
+    cudaError_t e = cudaMemcpyAsync(ctx->vws.d_lat, latents_window, (size_t)n_window_frames * c.decoder_input_channels * 4, cudaMemcpyHostToDevice, ctx->stream);
+    if (e != cudaSuccess) return cuda_fail(ctx, "latent upload failed", e);
+    cudaEventRecord(ctx->ev0, ctx->stream);
+    VaeOutWindow win{core_frame0, core_frame0 + core_frames, dst_frame};
+    e = vae_decode_device(ctx->vae, ctx->vws, 1, n_window_frames, ctx->peer_buf, ctx->stream, &win);
+    cudaEventRecord(ctx->ev1, ctx->stream);
+    if (e == cudaSuccess) e = cudaStreamSynchronize(ctx->stream);  // the peer stores have landed when this returns
+    if (e != cudaSuccess) return cuda_fail(ctx, "vae decode failed", e);
+    float ms = 0.f;
+    cudaEventElapsedTime(&ms, ctx->ev0, ctx->ev1);
+    ctx->last_device_ms = ms;
+    return ACE_GGML_OK;
+}
+
+ace_ggml_status ace_b200_peer_buffer_read(ace_ggml_context* ctx, float* out, size_t bytes) {
+    if (!ctx || !out) return ACE_GGML_ERR_INVALID_ARG;
+    if (!ctx->peer_buf || bytes > ctx->peer_bytes) return set_error(ctx, ACE_GGML_ERR_INVALID_ARG, "output buffer too small");
+    DeviceGuard guard(ctx->device);
+    cudaError_t e = cudaMemcpyAsync(out, ctx->peer_buf, bytes, cudaMemcpyDeviceToHost, ctx->stream);
+    if (e == cudaSuccess) e = cudaStreamSynchronize(ctx->stream);
+    if (e != cudaSuccess) return cuda_fail(ctx, "audio download failed", e);
+    return ACE_GGML_OK;
+}
+
 ace_ggml_status ace_b200_shift_schedule(float shift, int32_t n_steps, float* out) {
     if (!out || n_steps <= 0 || !(shift > 0.f)) return ACE_GGML_ERR_INVALID_ARG;
     for (int i = 0; i < n_steps; ++i) {

@@ -65,6 +65,11 @@ struct ace_ggml_context {
     float* d_x = nullptr;   // [B, T, A] latents being integrated
     float* d_v = nullptr;   // [2B, T, A] velocities
     size_t sampler_cap = 0;
+    // assembled-clip buffer of a time-split VAE decode (abi_ext.cu): owned here, IPC-mapped from another process, or borrowed from
+    // another context of this process (peer access)
+    float* peer_buf = nullptr;
+    size_t peer_bytes = 0;
+    int peer_kind = 0;  // 0 none, 1 owned, 2 IPC-mapped, 3 borrowed
     // debug scratch (unit-test hooks)
     std::vector<void*> dbg_allocs;
 };
@@ -115,6 +120,8 @@ ace_ggml_status sample_latents_device(ace_ggml_context* ctx, const float* noise,
                                       const float* uncond_enc, const int32_t* mask, const int32_t* enc_mask, int B, int T,
                                       int E, const float* schedule, int n_steps, float guidance);
 int env_max_layers();
+void release_peer_buffer(ace_ggml_context* ctx);
+ace_ggml_status create_context(const ace_ggml_init_params* params, int device, ace_ggml_context** out_ctx);
 cudaError_t vae_decode_grouped(ace_ggml_context* ctx, const float* d_latents, int B, int n_frames, float* d_audio, std::string& err);
 
 }  // namespace ace_abi

@@ -245,14 +245,15 @@ constexpr int CSO_THREADS = 128;  // 4 warps x 32 positions
 
 __global__ void __launch_bounds__(CSO_THREADS)
 conv_small_out_kernel(const __half* __restrict__ xs, const __half* __restrict__ w, const float* __restrict__ bias,
-                      float* __restrict__ out, long L, int C, int Cout, int taps, int pad) {
+                      float* __restrict__ out, long L, int C, int Cout, int taps, int pad, long l_lo, long l_hi, long out_shift,
+                      long out_bstride) {
     extern __shared__ __align__(16) uint8_t cso_smem[];
     const int rs = C + 8;                       // padded row stride (halves)
     const int rows = CSO_TL + taps - 1;
     __half* sx = reinterpret_cast<__half*>(cso_smem);            // [rows][rs]
     __half* sw = sx + (size_t)rows * rs;                         // [8][taps*C] (rows >= Cout are zero)
     const int K = taps * C;
-    const long l0 = (long)blockIdx.x * CSO_TL;
+    const long l0 = (l_lo / CSO_TL + (long)blockIdx.x) * CSO_TL;  // only the tiles that overlap [l_lo, l_hi) are launched
     const int b = blockIdx.y;
     const __half* xb = xs + (long)b * L * C;
     const int cpr = C / 8;                      // 16-byte chunks per row
@@ -308,8 +309,8 @@ conv_small_out_kernel(const __half* __restrict__ xs, const __half* __restrict__ 
 #pragma unroll
             for (int hrow = 0; hrow < 2; ++hrow) {
                 const long l = l0 + warp * 32 + m * 16 + g + hrow * 8;
-                if (l >= L) continue;
-                float* o = out + ((long)b * L + l) * Cout + c0;
+                if (l < l_lo || l >= l_hi) continue;
+                float* o = out + ((long)b * out_bstride + l + out_shift) * Cout + c0;  // may be peer memory (time-split decode)
                 const float v0 = acc[m][2 * hrow] + bz0, v1 = acc[m][2 * hrow + 1] + bz1;
                 if (c0 + 1 < Cout && (Cout & 1) == 0) *reinterpret_cast<float2*>(o) = make_float2(v0, v1);
                 else {
@@ -424,7 +425,12 @@ void launch_euler_step(float* x, const float* vc, const float* vu, float g, floa
     euler_step_kernel<<<blocks_for(n, 256), 256, 0, st>>>(x, vc, vu, g, dt, n);
 }
 void launch_conv_small_out(const __half* xs, const __half* w, const float* bias, float* out, int B, long L, int C,
-                           int Cout, int taps, int pad, cudaStream_t st) {
+                           int Cout, int taps, int pad, cudaStream_t st, long l_lo, long l_hi, long out_shift, long out_bstride) {
+    if (l_hi < 0) l_hi = L;
+    if (out_bstride < 0) out_bstride = L;
+    l_lo = l_lo < 0 ? 0 : l_lo;
+    if (l_hi > L) l_hi = L;
+    if (l_hi <= l_lo) return;
     note_launch();
     ProfScope prof_scope(PROF_VAE_TAIL, 2.0 * B * L * C * Cout * taps, (double)B * L * (C * 2.0 + Cout * 4.0), st);
     // loaders guarantee C % 16 == 0 (vae.cu: channel levels are multiples of 32) and Cout <= 8
@@ -435,8 +441,8 @@ void launch_conv_small_out(const __half* xs, const __half* w, const float* bias,
         std::fprintf(stderr, "[ace_b200] conv_small_out: %zu bytes of shared memory needed, 200 KB available\n", smem);
         return;
     }
-    dim3 grid((unsigned)((L + CSO_TL - 1) / CSO_TL), (unsigned)B);
-    conv_small_out_kernel<<<grid, CSO_THREADS, smem, st>>>(xs, w, bias, out, L, C, Cout, taps, pad);
+    dim3 grid((unsigned)((l_hi + CSO_TL - 1) / CSO_TL - l_lo / CSO_TL), (unsigned)B);
+    conv_small_out_kernel<<<grid, CSO_THREADS, smem, st>>>(xs, w, bias, out, L, C, Cout, taps, pad, l_lo, l_hi, out_shift, out_bstride);
 }
 
 }  // namespace ace

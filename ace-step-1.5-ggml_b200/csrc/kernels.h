@@ -149,7 +149,11 @@ void launch_euler_step(float* x, const float* v_cond, const float* v_uncond, flo
 // ---- VAE tail ------------------------------------------------------------------------------------
 // final conv: out[b, l, co] = sum_{tap, c} xs[b, l + tap - pad, c] * w[co, tap, c]  (+bias) for tiny C_out (audio channels)
 // reference: acestep_vae_model.cpp:999-1000 (conv2 k7, no bias)
+// Only positions l in [l_lo, l_hi) are computed and stored, at out[b*out_bstride + l + out_shift] (defaults: the whole clip in place).
+// A time-split decode passes its core range and a pointer into the assembled clip — which may be PEER memory of another GPU: the
+// stores then travel over NVLink and the gather of the split costs no extra pass.
 void launch_conv_small_out(const __half* xs, const __half* w /*[Cout, taps, C]*/, const float* bias, float* out, int B,
-                           long L, int C, int Cout, int taps, int pad, cudaStream_t st);
+                           long L, int C, int Cout, int taps, int pad, cudaStream_t st, long l_lo = 0, long l_hi = -1,
+                           long out_shift = 0, long out_bstride = -1);
 
 }  // namespace ace

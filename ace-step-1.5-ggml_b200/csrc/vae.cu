@@ -514,7 +514,8 @@ bool vae_workspace_reserve(const VaeModel& m, VaeWorkspace& ws, int B, int n_fra
     return true;
 }
 
-cudaError_t vae_decode_device(const VaeModel& m, VaeWorkspace& ws, int B, int n_frames, float* audio, cudaStream_t st) {
+cudaError_t vae_decode_device(const VaeModel& m, VaeWorkspace& ws, int B, int n_frames, float* audio, cudaStream_t st,
+                              const VaeOutWindow* win) {
     const VaeConfig& c = m.cfg;
     __half* blk_in = static_cast<__half*>(ws.allocs.back());
     cudaError_t rc = cudaSuccess;
@@ -601,7 +602,13 @@ cudaError_t vae_decode_device(const VaeModel& m, VaeWorkspace& ws, int B, int n_
         }
     }
     if (rc != cudaSuccess) return rc;
-    launch_conv_small_out(ws.xs, m.conv2_w, nullptr, audio, B, L, m.conv2_cin, c.audio_channels, 7, 3, st);
+    if (win) {
+        const long hop = c.hop_length;
+        launch_conv_small_out(ws.xs, m.conv2_w, nullptr, audio, B, L, m.conv2_cin, c.audio_channels, 7, 3, st, win->frame_lo * hop,
+                              win->frame_hi * hop, (win->dst_frame - win->frame_lo) * hop, 0);
+    } else {
+        launch_conv_small_out(ws.xs, m.conv2_w, nullptr, audio, B, L, m.conv2_cin, c.audio_channels, 7, 3, st);
+    }
     return cudaGetLastError();
 }
 

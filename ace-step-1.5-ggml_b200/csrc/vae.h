@@ -100,6 +100,12 @@ cudaError_t vae_encode_device(const VaeModel& m, VaeEncWorkspace& ws, const floa
                               cudaStream_t st);
 
 // latents in ws.d_lat [B, n_frames, latent_ch] -> audio [B, n_frames*hop, audio_ch] (device pointer `audio`)
-cudaError_t vae_decode_device(const VaeModel& m, VaeWorkspace& ws, int B, int n_frames, float* audio, cudaStream_t st);
+// `win` (optional, B = 1): keep only the samples of latent frames [frame_lo, frame_hi) of this window and store them at sample
+// offset dst_frame * hop of `audio` (the assembled clip, possibly peer memory) instead of in place.
+struct VaeOutWindow {
+    long frame_lo = 0, frame_hi = 0, dst_frame = 0;
+};
+cudaError_t vae_decode_device(const VaeModel& m, VaeWorkspace& ws, int B, int n_frames, float* audio, cudaStream_t st,
+                              const VaeOutWindow* win = nullptr);
 
 }  // namespace ace

@@ -71,6 +71,27 @@ ACE_GGML_API ace_ggml_status ace_b200_lyric_encoder_forward(ace_ggml_context * c
 ACE_GGML_API ace_ggml_status ace_b200_timbre_encoder_forward(ace_ggml_context * ctx, const float * refer_states,
                                                              int32_t refer_len, float * out, size_t out_size);
 
+/* ace_ggml_create on an explicitly named CUDA device (ace_ggml_create itself takes ACE_B200_DEVICE, else the calling thread's
+ * current device).  Contexts on different devices are independent and may be driven from different host threads. */
+ACE_GGML_API ace_ggml_status ace_b200_create_on_device(const ace_ggml_init_params * params, int32_t device,
+                                                       ace_ggml_context ** out_ctx);
+
+/* Time-split VAE decode of ONE long clip over several GPUs (BASELINE configs[3]; replaces the reference's chunk / overlap loop,
+ * acestep_ggml.cpp:2114-2229).  The assembled clip lives on one device:
+ *   owner:  ace_b200_peer_buffer_create(ctx, bytes, handle[64])  allocates it and returns its CUDA IPC handle (handle may be NULL);
+ *   other processes: ace_b200_peer_buffer_open(ctx, handle, bytes);   other contexts of the same process: ace_b200_peer_buffer_attach;
+ *   every rank: ace_b200_vae_decode_window decodes its halo'd window [n_window_frames, latent_ch] and the LAST kernel of the decode
+ *     stores the samples of window frames [core_frame0, core_frame0 + core_frames) at frame offset dst_frame of the clip — plain
+ *     stores into peer memory over NVLink, no gather pass; the call returns when they have landed;
+ *   owner, after the ranks have synchronised: ace_b200_peer_buffer_read copies the clip to the host. */
+ACE_GGML_API ace_ggml_status ace_b200_peer_buffer_create(ace_ggml_context * ctx, size_t bytes, void * ipc_handle_out);
+ACE_GGML_API ace_ggml_status ace_b200_peer_buffer_open(ace_ggml_context * ctx, const void * ipc_handle, size_t bytes);
+ACE_GGML_API ace_ggml_status ace_b200_peer_buffer_attach(ace_ggml_context * ctx, ace_ggml_context * owner);
+ACE_GGML_API ace_ggml_status ace_b200_vae_decode_window(ace_ggml_context * ctx, const float * latents_window,
+                                                        int32_t n_window_frames, int32_t core_frame0, int32_t core_frames,
+                                                        int64_t dst_frame);
+ACE_GGML_API ace_ggml_status ace_b200_peer_buffer_read(ace_ggml_context * ctx, float * out, size_t bytes);
+
 /* the reference's shift schedules (acestep_ggml.cpp:1484-1500): t_i = s*u/(1+(s-1)*u), u = 1 - i/n_steps.
  * For n_steps == 8 and shift in {1,2,3} this reproduces the three hard-coded tables. */
 ACE_GGML_API ace_ggml_status ace_b200_shift_schedule(float shift, int32_t n_steps, float * out_schedule);

@@ -48,8 +48,34 @@ def _worker(rank, world, port, q):
     w0, w1, c0, c1 = shard.time_split_plan(T, rank, world, 4)
     win = np.repeat(lat[w0:w1], hop)[:, None]
     stitched = shard.gather_time_slices(win[(c0 - w0) * hop:(c0 - w0) * hop + (c1 - c0) * hop], T, hop, dist)
+    # PeerSplitDecode host logic with a stand-in bridge: the "peer buffer" is a file both ranks map, the "decode" repeats x hop
+    class FakeBridge:
+        hop_length, audio_channels = hop, 1
+
+        def __init__(self, path):
+            self.path, self.buf = path, None
+
+        def peer_buffer_create(self, n_frames):
+            np.zeros((n_frames * hop, 1), np.float32).tofile(self.path)
+            self.buf = np.memmap(self.path, np.float32, "r+", shape=(n_frames * hop, 1))
+            return os.path.basename(self.path).encode().ljust(64, b"\0")
+
+        def peer_buffer_open(self, handle, n_frames):
+            assert handle.rstrip(b"\0") == os.path.basename(self.path).encode() and len(handle) == 64
+            self.buf = np.memmap(self.path, np.float32, "r+", shape=(n_frames * hop, 1))
+
+        def vae_decode_window(self, lat_win, core0, core_frames, dst_frame):
+            audio = np.repeat(lat_win[:, 0], hop)
+            self.buf[dst_frame * hop:(dst_frame + core_frames) * hop, 0] = audio[core0 * hop:(core0 + core_frames) * hop]
+            self.buf.flush()
+
+        def peer_buffer_read(self, n_frames):
+            return np.array(np.memmap(self.path, np.float32, "r", shape=(n_frames * hop, 1)))
+
+    split = shard.PeerSplitDecode(FakeBridge(os.path.join(os.environ["ACE_TEST_TMP"], "peer.bin")), T, rank, world, dist, halo=4)
+    peer = split.decode(lat[:, None], fetch=True)
     if rank == 0:
-        q.put((out, stitched))
+        q.put((out, stitched, peer))
     dist.barrier()
     dist.destroy_process_group()
 
@@ -60,13 +86,16 @@ def test_two_rank_gloo_shard_and_gather():
     s.bind(("127.0.0.1", 0))
     port = s.getsockname()[1]
     s.close()
+    import tempfile
+    os.environ["ACE_TEST_TMP"] = tempfile.mkdtemp(prefix="ace_peer_")
     ctx = mp.get_context("spawn")
     q = ctx.Queue()
     procs = [ctx.Process(target=_worker, args=(r, 2, port, q)) for r in range(2)]
     for p in procs:
         p.start()
-    out, stitched = q.get(timeout=120)
+    out, stitched, peer = q.get(timeout=120)
     assert np.array_equal(stitched[:, 0], np.repeat(np.arange(37, dtype=np.float32), 3))
+    assert np.array_equal(peer[:, 0], np.repeat(np.arange(37, dtype=np.float32), 3))  # peer-store split == un-split
     for p in procs:
         p.join(timeout=60)
         assert p.exitcode == 0

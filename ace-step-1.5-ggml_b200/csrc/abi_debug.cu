@@ -1,6 +1,9 @@
 // Unit-test hooks of the C ABI (include/acestep_b200.h, "debug_*"): direct access to the tap-GEMM and attention
 // kernels and to the weight packer, so tests/ can compare each against the oracle through the shared library.
 #include "abi_internal.h"
+#include "tensor_file.h"
+
+#include <memory>
 
 using namespace ace_abi;
 
@@ -157,6 +160,26 @@ ace_ggml_status ace_b200_debug_attention(ace_ggml_context* ctx, const float* Q, 
     cudaEventElapsedTime(&ms, ctx->ev0, ctx->ev1);
     ctx->last_device_ms = ms;
     return ACE_GGML_OK;
+}
+
+// CPU-only: open a weight file with the library's own readers and report the number of tensors (or -1 + message).
+int64_t ace_b200_debug_probe_tensor_file(const char* path, int32_t is_gguf, char* err_out, size_t err_size) {
+    if (!path) return -1;
+    std::string err;
+    std::unique_ptr<TensorFile> tf = is_gguf ? TensorFile::open_gguf(path, err) : TensorFile::open_safetensors(path, err);
+    if (err_out && err_size) {
+        std::snprintf(err_out, err_size, "%s", err.c_str());
+    }
+    if (!tf) return -1;
+    std::vector<float> tmp;
+    for (const TensorInfo& t : tf->tensors()) {  // every tensor must be decodable without leaving the mapping
+        std::string e;
+        if (t.numel() <= (1 << 22) && !tf->read_f32(t.name, tmp, nullptr, e)) {
+            if (err_out && err_size) std::snprintf(err_out, err_size, "%s", e.c_str());
+            return -1;
+        }
+    }
+    return (int64_t)tf->tensors().size();
 }
 
 }  // extern "C"

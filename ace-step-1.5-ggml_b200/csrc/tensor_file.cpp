@@ -245,6 +245,18 @@ bool TensorFile::read_f32(const std::string& name, std::vector<float>& out, std:
     return true;
 }
 
+// every dim in [0, 2^40] and the element count below 2^46 (crafted headers must not wrap size arithmetic)
+static bool checked_numel(const std::vector<int64_t>& shape, uint64_t* out) {
+    uint64_t n = 1;
+    for (int64_t d : shape) {
+        if (d < 0 || d > (int64_t)1 << 40) return false;
+        if (d != 0 && n > ((uint64_t)1 << 46) / (uint64_t)d) return false;
+        n *= (uint64_t)d;
+    }
+    if (out) *out = n;
+    return true;
+}
+
 std::unique_ptr<TensorFile> TensorFile::open_safetensors(const std::string& path, std::string& err) {
     std::unique_ptr<TensorFile> f(new TensorFile());
     if (!f->map_file(path, err)) return nullptr;
@@ -285,6 +297,7 @@ std::unique_ptr<TensorFile> TensorFile::open_safetensors(const std::string& path
             return nullptr;
         }
         for (const auto& d : sh->arr) ti.shape.push_back((int64_t)d.num);
+        if (!checked_numel(ti.shape, nullptr)) { err = "safetensors: bad shape for " + kv.first; return nullptr; }
         const uint64_t o0 = (uint64_t)off->arr[0].num, o1 = (uint64_t)off->arr[1].num;
         if (o1 < o0 || o1 > data_size) { err = "safetensors: offsets out of range for " + kv.first; return nullptr; }
         ti.data = data0 + o0;
@@ -340,7 +353,8 @@ bool gguf_skip_value(Cursor& c, uint32_t type, uint64_t* u32_out) {
         if (et == 8) { for (uint64_t i = 0; i < n && c.ok; ++i) c.str(); return c.ok; }
         const size_t es = gguf_scalar_size(et);
         if (es == 0) return false;
-        c.skip(es * n);
+        if (n > (uint64_t)(c.end - c.p) / es) { c.ok = false; return false; }  // es * n must not wrap
+        c.skip(es * (size_t)n);
         return c.ok;
     }
     const size_t s = gguf_scalar_size(type);
@@ -363,6 +377,7 @@ std::unique_ptr<TensorFile> TensorFile::open_gguf(const std::string& path, std::
     if (version < 2 || version > 3) { err = "gguf: unsupported version"; return nullptr; }
     const uint64_t n_tensors = c.rd<uint64_t>();
     const uint64_t n_kv = c.rd<uint64_t>();
+    if (!c.ok || n_tensors > f->map_size_ / 24 || n_kv > f->map_size_ / 12) { err = "gguf: implausible tensor / KV count"; return nullptr; }
     uint64_t alignment = 32;
     for (uint64_t i = 0; i < n_kv && c.ok; ++i) {
         const std::string key = c.str();
@@ -370,7 +385,7 @@ std::unique_ptr<TensorFile> TensorFile::open_gguf(const std::string& path, std::
         uint64_t u = 0;
         const bool want = (key == "general.alignment");
         if (!gguf_skip_value(c, type, want ? &u : nullptr)) { err = "gguf: bad KV " + key; return nullptr; }
-        if (want && type == 4 && u > 0) alignment = u;
+        if (want && type == 4 && u > 0 && u <= (1u << 20) && (u & (u - 1)) == 0) alignment = u;
     }
     struct Pending { TensorInfo ti; uint64_t offset; };
     std::vector<Pending> pend;
@@ -389,13 +404,19 @@ std::unique_ptr<TensorFile> TensorFile::open_gguf(const std::string& path, std::
     if (!c.ok) { err = "gguf: truncated header"; return nullptr; }
     size_t data_off = (size_t)(c.p - base);
     data_off = (data_off + alignment - 1) / alignment * alignment;
+    if (data_off > f->map_size_) { err = "gguf: truncated header"; return nullptr; }
+    const size_t data_size = f->map_size_ - data_off;
     for (auto& pd : pend) {
         TensorInfo& ti = pd.ti;
+        uint64_t numel = 0;
+        if (!checked_numel(ti.shape, &numel)) { err = std::string("gguf: bad shape for ") + ti.name; return nullptr; }
         const int64_t row = ti.shape.empty() ? 1 : ti.shape.back();
-        const size_t rb = ggml_row_bytes(ti.ggml_type, row);
+        const size_t rb = row > 0 ? ggml_row_bytes(ti.ggml_type, row) : 0;
         if (rb == 0) { err = std::string("gguf: unsupported type/shape for ") + ti.name; return nullptr; }
-        ti.nbytes = rb * (size_t)(ti.numel() / (row ? row : 1));
-        if (data_off + pd.offset + ti.nbytes > f->map_size_) { err = "gguf: tensor out of file range: " + ti.name; return nullptr; }
+        const uint64_t rows = numel / (uint64_t)row;
+        if (rows > data_size / rb) { err = "gguf: tensor out of file range: " + ti.name; return nullptr; }  // rb * rows cannot wrap now
+        ti.nbytes = rb * (size_t)rows;
+        if (pd.offset > data_size || ti.nbytes > data_size - pd.offset) { err = "gguf: tensor out of file range: " + ti.name; return nullptr; }
         ti.data = base + data_off + pd.offset;
         f->index_[ti.name] = f->tensors_.size();
         f->tensors_.push_back(std::move(ti));

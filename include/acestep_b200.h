@@ -127,6 +127,10 @@ ACE_GGML_API ace_ggml_status ace_b200_debug_attention(ace_ggml_context * ctx, co
 ACE_GGML_API ace_ggml_status ace_b200_debug_pack_roundtrip(const void * W, int32_t w_ggml_type, int32_t N, int32_t K,
                                                            float * unpacked, float * ref);
 
+/* CPU-only: parse a .gguf (is_gguf != 0) or .safetensors file with the library's readers and decode every small tensor; returns the
+ * tensor count, or -1 with the reader's message in err_out.  Used by the malformed-file tests. */
+ACE_GGML_API int64_t ace_b200_debug_probe_tensor_file(const char * path, int32_t is_gguf, char * err_out, size_t err_size);
+
 #ifdef __cplusplus
 }
 #endif

@@ -204,6 +204,20 @@ def test_vae_decode_matches_reference(br, root, n_frames):
     assert m["cos"] >= 0.9999 and m["snr_db"] >= 40.0, m
 
 
+def test_vae_decode_vs_reference_with_f32_conv_transpose(br, root, monkeypatch):
+    """ACE_GGML_VAE_TRANSPOSE_CONV_F32=1 (default in the reference's run.sh:39) keeps the conv-transpose weights and inputs in F32 on the
+    CPU (acestep_vae_model.cpp:567-572).  This library always feeds the tensor cores fp16 operands with fp32 accumulation; the switch is
+    accepted and changes nothing.  Measured deviation against the reference run WITH the switch: the same waveform bound holds."""
+    need_ref()
+    d = make_vae_dir(root)
+    lat = fx.vae_latents(fx.VAE_TOY, 45, seed=7)
+    outs, _ = refbridge.run_ref([{"op": "vae_decode", "latents": "lat", "out": "audio"}], {"lat": lat}, vae_dir=d, env={"ACE_GGML_VAE_TRANSPOSE_CONV_F32": "1"})
+    monkeypatch.setenv("ACE_GGML_VAE_TRANSPOSE_CONV_F32", "1")
+    br.load_vae(d)
+    m = metrics(br.vae_decode_tfirst(lat), outs["audio"])
+    assert m["cos"] >= 0.9999 and m["snr_db"] >= 40.0, m
+
+
 def test_vae_tiled_reference_policy_equals_untiled(br, root):
     """the reference's chunk 128 / overlap 32 tiling (acestep_ggml.cpp:2114-2215) has halo >= receptive field, so an
     un-tiled decode reproduces it; checked on the toy VAE with chunk 24 / overlap 12"""

@@ -2,7 +2,7 @@
 # One parameterised GPU-box script (replaces round 1's sixteen gpu_*.sh): every stage writes under gpurun_out/<tag>_*.
 #   gpurun --timeout 1500 -- 'bash scripts/gpu_run.sh <tag> <stage> [<stage> ...]'
 # stages: tests[:<pytest -k expr>]  smoke  bench[:<extra bench.py args>]  bench_ref  launches[:<bench args>]  ncu:<kernel regex>[:<bench args>]
-#         torchrun:<N>[:<bench args>]   probe:<perf_probe.py args>   sass
+#         sh:<shell command>   torchrun:<N>[:<bench args>]   probe:<perf_probe.py args>   sass
 OUT=gpurun_out; TAG=${1:-run}; shift
 mkdir -p $OUT
 export PYTHONUNBUFFERED=1
@@ -24,6 +24,7 @@ for st in "$@"; do
              timeout 1500 ncu --set full --clock-control none --import-source on -k regex:$kre -s 40 -c 12 -o $OUT/${TAG}_ncu_$(echo $kre | tr -c 'A-Za-z0-9\n' '_') -f \
                  python bench.py --steps 2 --warmup 3 --no-cpu-baseline --no-song $bargs > $OUT/${TAG}_ncu.log 2>&1; rc=$? ;;
     probe)   timeout 900 python scripts/perf_probe.py $arg > $OUT/${TAG}_probe.log 2>&1; rc=$?; tail -20 $OUT/${TAG}_probe.log ;;
+    sh)      name=$(echo "sh_${arg}" | tr -c 'A-Za-z0-9\n' '_' | cut -c1-60); timeout 1200 bash -c "$arg" > $OUT/${TAG}_${name}.log 2>&1; rc=$?; tail -12 $OUT/${TAG}_${name}.log ;;
     sass)    bash scripts/sass_summary.sh > $OUT/${TAG}_sass.txt 2>&1; rc=$? ;;
     *)       echo "unknown stage $st"; rc=99 ;;
   esac

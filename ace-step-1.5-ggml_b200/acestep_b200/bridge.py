@@ -93,6 +93,7 @@ SIGNATURES = {
                                            ctypes.c_size_t]),
     "ace_b200_debug_attention": (ctypes.c_int, [_P, _F, _F, _F, _I, ctypes.c_int32, ctypes.c_int32, ctypes.c_int32,
                                                 ctypes.c_int32, ctypes.c_int32, ctypes.c_int32, _F, ctypes.c_size_t]),
+    "ace_b200_debug_quantize_rows": (ctypes.c_int, [_F, ctypes.c_int32, ctypes.c_int32, ctypes.c_int32, _P, ctypes.c_size_t]),
     "ace_b200_debug_probe_tensor_file": (ctypes.c_int64, [ctypes.c_char_p, ctypes.c_int32, ctypes.c_char_p, ctypes.c_size_t]),
     "ace_b200_debug_pack_roundtrip": (ctypes.c_int, [_P, ctypes.c_int32, ctypes.c_int32, ctypes.c_int32, _F, _F]),
 }

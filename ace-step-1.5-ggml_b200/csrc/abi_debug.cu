@@ -182,4 +182,19 @@ int64_t ace_b200_debug_probe_tensor_file(const char* path, int32_t is_gguf, char
     return (int64_t)tf->tensors().size();
 }
 
+// CPU-only: quantise fp32 rows [N, K] to raw ggml rows of w_ggml_type (8 Q8_0 / 12 Q4_K / 14 Q6_K) with the library's own quantisers
+ace_ggml_status ace_b200_debug_quantize_rows(const float* src, int32_t w_ggml_type, int32_t N, int32_t K, void* dst, size_t dst_size) {
+    if (!src || !dst || N <= 0 || K <= 0) return ACE_GGML_ERR_INVALID_ARG;
+    const size_t rb = ggml_row_bytes(w_ggml_type, K);
+    if (rb == 0 || dst_size < rb * (size_t)N) return ACE_GGML_ERR_INVALID_ARG;
+    for (int r = 0; r < N; ++r) {
+        uint8_t* d = static_cast<uint8_t*>(dst) + (size_t)r * rb;
+        if (w_ggml_type == GGML_Q8_0) quantize_row_q8_0(src + (size_t)r * K, d, K);
+        else if (w_ggml_type == GGML_Q4_K) quantize_row_q4_k(src + (size_t)r * K, d, K);
+        else if (w_ggml_type == GGML_Q6_K) quantize_row_q6_k(src + (size_t)r * K, d, K);
+        else return ACE_GGML_ERR_UNSUPPORTED;
+    }
+    return ACE_GGML_OK;
+}
+
 }  // extern "C"

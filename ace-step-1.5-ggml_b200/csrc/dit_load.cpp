@@ -82,10 +82,9 @@ int parse_online_qtype(std::string& unsupported) {
         std::string s(v);
         std::transform(s.begin(), s.end(), s.begin(), [](unsigned char ch) { return (char)std::toupper(ch); });
         if (s == "Q8" || s == "Q8_0") return W_Q8_0;
-        if (s == "Q6" || s == "Q6_K" || s == "Q4" || s == "Q4_K" || s == "Q4_K_M") {
-            unsupported = s;
-            return -2;
-        }
+        if (s == "Q6" || s == "Q6_K") return W_Q6_K;
+        if (s == "Q4" || s == "Q4_K" || s == "Q4_K_M") return W_Q4_K;
+        (void)unsupported;
         return -1;  // unknown strings are ignored by the reference too
     }
     return -1;
@@ -136,12 +135,6 @@ int dit_load(const std::string& model_dir, DitModel& m, std::string& err) {
     Loader L{tf.get(), &m.allocs, &m.weight_bytes, {}, 0, -1};
     std::string unsup;
     L.online_q = parse_online_qtype(unsup);
-    if (L.online_q == -2 && !tf->is_gguf()) {
-        err = "on-the-fly " + unsup + " quantisation of safetensors weights is not provided; export a pre-quantised GGUF "
-              "(tools/export_safetensors_to_gguf.py) and point ACE_GGML_DIT_GGUF at it";
-        m.release();
-        return 4;
-    }
 
     const int H = c.hidden_size, I = c.intermediate_size, hd = c.head_dim;
     const int nq = c.num_attention_heads * hd, nkv = c.num_key_value_heads * hd;

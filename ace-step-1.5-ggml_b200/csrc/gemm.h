@@ -67,13 +67,12 @@ struct GemmProblem {
 // (same operands, same epilogue) that the tensor-core kernel is unit-tested against.
 cudaError_t gemm_launch(const GemmProblem& p, cudaStream_t stream, bool simt = false);
 
-// Decode a quantised packed weight ONCE into the F16 tile image (n_tiles * taps*kb_per_tap * 16 KB at `dst`), with the
-// same device decoders the GEMM runs in shared memory, so both routes feed the tensor cores bit-identical operands.
-// Policy (gemm_launch): a quantised weight with a decoded twin (PackedWeight::dev_f16) uses the twin when the problem
-// has >= predecode_min_rows() activation rows: there the GEMM is compute-bound, every weight tile would be re-decoded
-// by each of the M/128 row tiles, and 3 GB of HBM (of 180) for the twin buys F16-kernel speed.  Below the threshold
-// (time-embedding GEMVs, short clips) the GEMM is HBM-bound on the weight stream and decodes the 4.5-8.5 bit codes
-// in shared memory.  ACE_B200_PREDECODE=0 disables the twins, ACE_B200_PREDECODE_MIN_M moves the threshold.
+// Quantised weights are decoded IN THE GEMM: packed codes land in shared memory by TMA bulk copy, decoder warps expand them to
+// the fp16 UMMA tile, tcgen05 consumes it (single-CTA kernel for one row tile, CTA-pair kernel — one sub-tile decoded per CTA
+// per k-block — beyond).  The decoded F16 twin of round 1 survives as an opt-in A/B route: ACE_B200_PREDECODE=1 decodes every
+// quantised weight once at load (gemm_predecode, same decoder code, +3.15 GB for the turbo DiT) and GEMMs with
+// >= predecode_min_rows() rows (ACE_B200_PREDECODE_MIN_M, default 256) read it through the F16 kernels.  Both routes feed the
+// tensor cores bit-identical operands (tests/test_kernels_gpu.py).
 size_t      gemm_predecode_bytes(const PackedWeight& w);
 cudaError_t gemm_predecode(const PackedWeight& w, void* dst, cudaStream_t stream);
 bool        predecode_enabled();

@@ -1008,24 +1008,42 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
 constexpr int STAGES2 = 6;
 constexpr int STAGE2_BYTES = A_STAGE_BYTES + W_SUB_BYTES;  // 32 KB
 constexpr int SMEM2_BYTES = STAGES2 * STAGE2_BYTES + 8 * STG_WARP_BYTES + 2 * 256 * 4 + 512;
+// QUANT variant (packed Q8_0 / Q4_K / Q6_K tiles decoded in shared memory): the pair shape is what makes in-kernel decoding
+// affordable at large M — a CTA decodes ONE 128 x 64 sub-tile per k-block (its half of the weight tile) while the pair's
+// tensor cores spend 512 cycles on it (M = 256 x N = 256), instead of two sub-tiles per 512 cycles in the single-CTA kernel,
+// which ran decode-bound at 1444 cycles per k-block (profiles/r2_quant_trace_d.log).  Two decoder groups of 4 warps take
+// alternate k-blocks (one warp per scheduler decodes at ~0.25 IPC: latency-, not issue-bound), 4 epilogue warps, 14 warps.
+constexpr int NUM_THREADS2Q = 448;
+constexpr int STAGES2Q = 5;
+constexpr int RAW2_BYTES = 8704;  // largest packed tile (Q8_0), 16-byte multiple
+constexpr int SMEM2Q_BYTES = STAGES2Q * (STAGE2_BYTES + RAW2_BYTES) + 4 * STG_WARP_BYTES + 2 * 256 * 4 + 512;
+static_assert(SMEM2Q_BYTES <= 227 * 1024, "pair QUANT layout exceeds shared memory");
 
-template <bool WARM>
-__global__ void __launch_bounds__(NUM_THREADS, 1)
+template <bool WARM, bool QUANT>
+__global__ void __launch_bounds__(QUANT ? NUM_THREADS2Q : NUM_THREADS, 1)
 gemm_tc2_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmOut, const KParams p) {
     constexpr int BN = 256;
     constexpr int TMEM_COLS = 2 * BN;
+    constexpr int NS = QUANT ? STAGES2Q : STAGES2;
+    constexpr int EPI_WARPS = QUANT ? 4 : 8;
+    constexpr int NPARTS = EPI_WARPS / 4;
+    constexpr int TMA_WARP = QUANT ? 12 : 8;
+    constexpr int MMA_WARP = QUANT ? 13 : 9;
     extern __shared__ __align__(1024) uint8_t smem[];
     if (threadIdx.x == 0 && (ptx::smem_u32(smem) & 1023u) != 0) __trap();
-    uint8_t* sA = smem;                            // [STAGES2][16 KB]
-    uint8_t* sB = sA + STAGES2 * A_STAGE_BYTES;    // [STAGES2][16 KB]  this CTA's half of the weight tile
-    float* sStg = reinterpret_cast<float*>(sB + STAGES2 * W_SUB_BYTES);  // [8][32 x 32 fp32] epilogue transpose buffers
-    float* sCol = sStg + 8 * (STG_WARP_BYTES / 4);  // [2][256]: bias, gate of the current tile
+    uint8_t* sA = smem;                       // [NS][16 KB]
+    uint8_t* sB = sA + NS * A_STAGE_BYTES;    // [NS][16 KB]  this CTA's half of the weight tile (fp16 UMMA image)
+    uint8_t* sR = sB + NS * W_SUB_BYTES;      // QUANT: [NS][RAW2_BYTES] packed codes as they land
+    float* sStg = reinterpret_cast<float*>(sR + (QUANT ? NS * RAW2_BYTES : 0));  // [EPI_WARPS][32 x 32 fp32] epilogue transpose buffers
+    float* sCol = sStg + EPI_WARPS * (STG_WARP_BYTES / 4);  // [2][256]: bias, gate of the current tile
     uint64_t* bars = reinterpret_cast<uint64_t*>(sCol + 2 * 256);
-    uint64_t* full = bars;                    // [S] local operands landed
-    uint64_t* empty = bars + STAGES2;         // [S] MMAs reading this CTA's stage completed (multicast commit)
-    uint64_t* peer_full = bars + 2 * STAGES2; // [S] leader only: CTA 1's stage landed
-    uint64_t* acc_full = bars + 3 * STAGES2;  // [2] local (multicast commit)
-    uint64_t* acc_empty = acc_full + 2;       // [2] leader only: 16 epilogue warps of the pair
+    uint64_t* full = bars;               // [S] local operands landed (QUANT: A landed + this CTA's sub-tile decoded)
+    uint64_t* empty = bars + NS;         // [S] MMAs reading this CTA's stage completed (multicast commit)
+    uint64_t* peer_full = bars + 2 * NS; // [S] leader only: CTA 1's stage landed
+    uint64_t* raw_full = bars + 3 * NS;  // [S] QUANT: packed codes landed
+    uint64_t* raw_empty = bars + 4 * NS; // [S] QUANT: decoders done with the packed codes
+    uint64_t* acc_full = bars + 5 * NS;  // [2] local (multicast commit)
+    uint64_t* acc_empty = acc_full + 2;  // [2] leader only: the epilogue warps of the pair
     uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(acc_empty + 2);
 
     const int warp = threadIdx.x >> 5;
@@ -1040,19 +1058,21 @@ gemm_tc2_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__
     const int total_tiles = n_tiles * p.split_k * m_tiles;
 
     if (threadIdx.x == 0) {
-        for (int s = 0; s < STAGES2; ++s) {
-            ptx::mbar_init(&full[s], 1);
+        for (int s = 0; s < NS; ++s) {
+            ptx::mbar_init(&full[s], QUANT ? 1 + 4 : 1);
             ptx::mbar_init(&empty[s], 1);
             ptx::mbar_init(&peer_full[s], 1);
+            ptx::mbar_init(&raw_full[s], 1);
+            ptx::mbar_init(&raw_empty[s], 4);
         }
         for (int a = 0; a < 2; ++a) {
             ptx::mbar_init(&acc_full[a], 1);
-            ptx::mbar_init(&acc_empty[a], 16);
+            ptx::mbar_init(&acc_empty[a], 2 * EPI_WARPS);
         }
         ptx::fence_mbar_init();
     }
-    if (warp == 9) ptx::tmem_alloc_2cta<TMEM_COLS>(tmem_slot);
-    if (warp == 8 && lane == 0) ptx::prefetch_tmap(&tmA);
+    if (warp == MMA_WARP) ptx::tmem_alloc_2cta<TMEM_COLS>(tmem_slot);
+    if (warp == TMA_WARP && lane == 0) ptx::prefetch_tmap(&tmA);
     ptx::tc_fence_before();
     __syncthreads();
     ptx::cluster_sync();
@@ -1074,11 +1094,12 @@ gemm_tc2_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__
         kb1 = (int)((long)p.kb_total * (sp + 1) / p.split_k);
     };
 
-    if (warp == 8) {
+    if (warp == TMA_WARP) {
         // ===================== TMA producer (both CTAs): whole warp, elected lane issues =====================
         {
             uint32_t s = 0, ph = 0;
-            const size_t sub_stride = (size_t)p.kb_total * W_SUB_BYTES;
+            const size_t w_tile = QUANT ? (size_t)p.tile_bytes : (size_t)W_SUB_BYTES;
+            const size_t sub_stride = (size_t)p.kb_total * w_tile;
             for (int t = cluster_id; t < total_tiles; t += n_clusters) {
                 int nt, sp, b, l0, kb0, kb1;
                 decode_tile_index(t, nt, sp, b, l0);
@@ -1086,28 +1107,38 @@ gemm_tc2_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__
                 int tap = kb0 / p.kb_per_tap;
                 int kc = kb0 - tap * p.kb_per_tap;
                 int row = l0 + tap * p.tap_stride + p.tap_offset;
-                const uint8_t* wptr = p.W + (size_t)(nt * 2 + (int)rank) * sub_stride + (size_t)kb0 * W_SUB_BYTES;
+                const uint8_t* wptr = p.W + (size_t)(nt * 2 + (int)rank) * sub_stride + (size_t)kb0 * w_tile;
                 for (int kb = kb0; kb < kb1; ++kb) {
                     ptx::mbar_wait(&empty[s], ph ^ 1);
-                    if (ptx::elect_one()) {
-                        ptx::mbar_expect_tx(&full[s], STAGE2_BYTES);
-                        ptx::tma_load_3d(sA + s * A_STAGE_BYTES, &tmA, &full[s], kc * BK, row, b);
-                        ptx::bulk_load(sB + s * W_SUB_BYTES, wptr, W_SUB_BYTES, &full[s]);
+                    if (QUANT) {
+                        ptx::mbar_wait(&raw_empty[s], ph ^ 1);
+                        if (ptx::elect_one()) {
+                            ptx::mbar_expect_tx(&full[s], A_STAGE_BYTES);
+                            ptx::tma_load_3d(sA + s * A_STAGE_BYTES, &tmA, &full[s], kc * BK, row, b);
+                            ptx::mbar_expect_tx(&raw_full[s], (uint32_t)p.tile_bytes);
+                            ptx::bulk_load(sR + s * RAW2_BYTES, wptr, p.tile_bytes, &raw_full[s]);
+                        }
+                    } else {
+                        if (ptx::elect_one()) {
+                            ptx::mbar_expect_tx(&full[s], STAGE2_BYTES);
+                            ptx::tma_load_3d(sA + s * A_STAGE_BYTES, &tmA, &full[s], kc * BK, row, b);
+                            ptx::bulk_load(sB + s * W_SUB_BYTES, wptr, W_SUB_BYTES, &full[s]);
+                        }
                     }
                     __syncwarp();
-                    wptr += W_SUB_BYTES;
+                    wptr += w_tile;
                     if (++kc == p.kb_per_tap) {
                         kc = 0;
                         row += p.tap_stride;
                     }
-                    if (++s == (uint32_t)STAGES2) {
+                    if (++s == (uint32_t)NS) {
                         s = 0;
                         ph ^= 1;
                     }
                 }
             }
         }
-    } else if (warp == 9) {
+    } else if (warp == MMA_WARP) {
         if (rank == 0) {
             // ===================== MMA issuer (leader CTA): whole warp on uniform values, elected lane issues =====================
             constexpr uint32_t idesc = ptx::umma_idesc_f16(2 * BM, BN);
@@ -1137,7 +1168,7 @@ gemm_tc2_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__
                     }
                     __syncwarp();
                     acc_flag = 1;
-                    if (++s == (uint32_t)STAGES2) {
+                    if (++s == (uint32_t)NS) {
                         s = 0;
                         ph ^= 1;
                     }
@@ -1156,7 +1187,7 @@ gemm_tc2_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__
                     for (int kb = kb0; kb < kb1; ++kb) {
                         ptx::mbar_wait(&full[s], ph);
                         ptx::mbar_arrive_cluster(ptx::mapa(&peer_full[s], 0));
-                        if (++s == (uint32_t)STAGES2) {
+                        if (++s == (uint32_t)NS) {
                             s = 0;
                             ph ^= 1;
                         }
@@ -1164,10 +1195,37 @@ gemm_tc2_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__
                 }
             }
         }
+    } else if (QUANT && warp >= 4) {
+        // ===================== weight decoders (both CTAs): warps 4..7 take the even k-blocks of the ring, 8..11 the odd ones =====
+        // thread = one row of the CTA's 128 x 64 sub-tile; the decoded tile is written with generic stores, published to the
+        // tensor-core (async) proxy with fence.proxy.async, then counted on full[s] next to the TMA's A box.
+        const int grp = (warp - 4) >> 2;
+        const int row = (int)threadIdx.x - 128 - grp * 128;  // 0..127
+        uint32_t g = 0;
+        for (int t = cluster_id; t < total_tiles; t += n_clusters) {
+            int nt, sp, b, l0, kb0, kb1;
+            decode_tile_index(t, nt, sp, b, l0);
+            k_range(sp, kb0, kb1);
+            for (int kb = kb0; kb < kb1; ++kb, ++g) {
+                if ((int)(g & 1u) != grp) continue;
+                const uint32_t s = g % (uint32_t)NS;
+                const uint32_t ph = (g / (uint32_t)NS) & 1u;
+                ptx::mbar_wait(&raw_full[s], ph);
+                ptx::mbar_wait(&empty[s], ph ^ 1);
+                decode_tile(p.wtype, sR + s * RAW2_BYTES, sB + s * W_SUB_BYTES, row);
+                ptx::fence_proxy_async_smem();
+                __syncwarp();
+                if (lane == 0) {
+                    ptx::mbar_arrive(&full[s]);
+                    ptx::mbar_arrive(&raw_empty[s]);
+                }
+            }
+        }
     } else {
-        // ===================== epilogue: warps 0..7 of both CTAs, two groups on alternate column chunks =====================
+        // ===================== epilogue: warps 0..EPI_WARPS-1 of both CTAs, NPARTS groups on alternate column chunks ==========
         const int q = warp & 3;
         const int part = warp >> 2;
+        constexpr int EPI_THREADS = EPI_WARPS * 32;
         int it = 0;
         bool dry = WARM;  // instruction-cache warm-up pass, see gemm_tc_kernel
         for (int t = cluster_id; t < total_tiles;) {
@@ -1178,13 +1236,13 @@ gemm_tc2_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__
             const uint32_t aph = (it >> 1) & 1;
             if (!dry) {
                 if (p.epi.mode == EPI_STORE) {
-                    epi_bar_sync(256);
-                    stage_column_terms<BN, 256>(p, b, nt * BN, sp == 0, (int)threadIdx.x, sCol, sCol + BN);
-                    epi_bar_sync(256);
+                    epi_bar_sync(EPI_THREADS);
+                    stage_column_terms<BN, EPI_THREADS>(p, b, nt * BN, sp == 0, (int)threadIdx.x, sCol, sCol + BN);
+                    epi_bar_sync(EPI_THREADS);
                 } else if (p.epi.mode == EPI_HEADNORM) {
-                    epi_bar_sync(256);
-                    stage_head_weights<BN, 256>(p, nt * BN, (int)threadIdx.x, sCol);
-                    epi_bar_sync(256);
+                    epi_bar_sync(EPI_THREADS);
+                    stage_head_weights<BN, EPI_THREADS>(p, nt * BN, (int)threadIdx.x, sCol);
+                    epi_bar_sync(EPI_THREADS);
                 }
                 ptx::mbar_wait(&acc_full[a], aph);
                 ptx::tc_fence_after();
@@ -1193,14 +1251,14 @@ gemm_tc2_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__
             const uint32_t taddr = tmem_base + ((uint32_t)(q * 32) << 16) + (uint32_t)(a * BN);
             if (p.epi.mode == EPI_HEADNORM) {
 #pragma unroll 1
-                for (int hh = part; hh < BN / 128; hh += 2) {
+                for (int hh = part; hh < BN / 128; hh += NPARTS) {
                     const int n0 = nt * BN + hh * 128;
                     if (n0 >= p.N) break;
                     if (kb1 > kb0) epilogue_head128<WARM>(p, taddr + hh * 128, b, !dry, l0 + q * 32, lane, n0, sStg + warp * (STG_WARP_BYTES / 4), sCol + hh * 128, 0, 1);
                 }
             } else
 #pragma unroll 1
-            for (int c = part; c < BN / 32; c += 2) {
+            for (int c = part; c < BN / 32; c += NPARTS) {
                 const int n0 = nt * BN + c * 32;
                 if (n0 >= p.N) break;
                 uint32_t r[32];
@@ -1231,7 +1289,7 @@ gemm_tc2_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__
     ptx::tc_fence_before();
     __syncthreads();
     ptx::cluster_sync();  // the peer's smem / barriers stay alive until every MMA and remote arrive has landed
-    if (warp == 9) {
+    if (warp == MMA_WARP) {
         ptx::tc_fence_after();
         ptx::tmem_dealloc_2cta<TMEM_COLS>(tmem_base);
     }
@@ -1335,13 +1393,9 @@ cudaError_t gemm_predecode(const PackedWeight& w, void* dst, cudaStream_t stream
     return cudaGetLastError();
 }
 
-bool predecode_enabled() {
-    static int v = -1;
-    if (v < 0) {
-        const char* e = std::getenv("ACE_B200_PREDECODE");
-        v = (e && e[0] == '0') ? 0 : 1;
-    }
-    return v == 1;
+bool predecode_enabled() {  // opt-in since the CTA-pair kernel decodes in shared memory at full speed (read per call: tests flip it)
+    const char* e = std::getenv("ACE_B200_PREDECODE");
+    return e && e[0] && e[0] != '0';
 }
 
 int predecode_min_rows() {
@@ -1390,8 +1444,10 @@ int max_active_pairs() {
     int result = 0;
     once.run([](int& n) {
         n = 0;
-        if (cudaFuncSetAttribute(gemm_tc2_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, SMEM2_BYTES) == cudaSuccess &&
-            cudaFuncSetAttribute(gemm_tc2_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, SMEM2_BYTES) == cudaSuccess) {
+        if (cudaFuncSetAttribute(gemm_tc2_kernel<false, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, SMEM2_BYTES) == cudaSuccess &&
+            cudaFuncSetAttribute(gemm_tc2_kernel<true, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, SMEM2_BYTES) == cudaSuccess &&
+            cudaFuncSetAttribute(gemm_tc2_kernel<false, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, SMEM2Q_BYTES) == cudaSuccess &&
+            cudaFuncSetAttribute(gemm_tc2_kernel<true, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, SMEM2Q_BYTES) == cudaSuccess) {
             cudaLaunchConfig_t cfg = {};
             cfg.gridDim = dim3(2 * 148);
             cfg.blockDim = dim3(NUM_THREADS);
@@ -1404,8 +1460,13 @@ int max_active_pairs() {
             cfg.attrs = at;
             cfg.numAttrs = 1;
             int c = 0;
-            if (cudaOccupancyMaxActiveClusters(&c, gemm_tc2_kernel<false>, &cfg) == cudaSuccess) n = c;
+            if (cudaOccupancyMaxActiveClusters(&c, gemm_tc2_kernel<false, false>, &cfg) == cudaSuccess) n = c;
             else cudaGetLastError();
+            cfg.blockDim = dim3(NUM_THREADS2Q);  // the QUANT variant (more threads, more shared memory) must fit as often
+            cfg.dynamicSmemBytes = SMEM2Q_BYTES;
+            int cq = 0;
+            if (cudaOccupancyMaxActiveClusters(&cq, gemm_tc2_kernel<false, true>, &cfg) == cudaSuccess) n = std::min(n, cq);
+            else { cudaGetLastError(); n = 0; }
             if (std::getenv("ACE_B200_DEBUG")) std::fprintf(stderr, "[ace_b200] max active CTA pairs: %d\n", n);
         } else cudaGetLastError();
         return cudaSuccess;
@@ -1415,9 +1476,10 @@ int max_active_pairs() {
 
 cudaError_t launch_tc2(const CUtensorMap& tm, const CUtensorMap& tmo, const KParams& kp, int clusters, cudaStream_t stream) {
     cudaLaunchConfig_t cfg = {};
+    const bool quant = kp.wtype != W_F16;
     cfg.gridDim = dim3((unsigned)(2 * clusters));
-    cfg.blockDim = dim3(NUM_THREADS);
-    cfg.dynamicSmemBytes = SMEM2_BYTES;
+    cfg.blockDim = dim3(quant ? NUM_THREADS2Q : NUM_THREADS);
+    cfg.dynamicSmemBytes = quant ? SMEM2Q_BYTES : SMEM2_BYTES;
     cfg.stream = stream;
     cudaLaunchAttribute at[2];
     at[0].id = cudaLaunchAttributeClusterDimension;
@@ -1428,7 +1490,8 @@ cudaError_t launch_tc2(const CUtensorMap& tm, const CUtensorMap& tmo, const KPar
     at[1].val.programmaticStreamSerializationAllowed = 1;
     cfg.attrs = at;
     cfg.numAttrs = pdl_enabled() ? 2 : 1;
-    return kp.warm_epi ? cudaLaunchKernelEx(&cfg, gemm_tc2_kernel<true>, tm, tmo, kp) : cudaLaunchKernelEx(&cfg, gemm_tc2_kernel<false>, tm, tmo, kp);
+    if (quant) return kp.warm_epi ? cudaLaunchKernelEx(&cfg, gemm_tc2_kernel<true, true>, tm, tmo, kp) : cudaLaunchKernelEx(&cfg, gemm_tc2_kernel<false, true>, tm, tmo, kp);
+    return kp.warm_epi ? cudaLaunchKernelEx(&cfg, gemm_tc2_kernel<true, false>, tm, tmo, kp) : cudaLaunchKernelEx(&cfg, gemm_tc2_kernel<false, false>, tm, tmo, kp);
 }
 
 }  // namespace
@@ -1561,12 +1624,16 @@ cudaError_t gemm_launch(const GemmProblem& g, cudaStream_t stream, bool simt) {
     const int m_pairs = kp.B * ((g.l_out + 2 * BM - 1) / (2 * BM));
     // Measured (profiles/r1_gemm_sweep_pair2.log): the pair wins once a cluster runs several tiles (M = 6000: +6..17 %),
     // and loses at M = 750 where its longer per-tile ramp (relay hop, cluster syncs) is not amortised -> rows >= 2048.
-    const bool pair_ok = kp.wtype == W_F16 && (kp.n_tiles128 & 1) == 0 && kp.n_tiles128 >= 2;
+    // (packed quantised tiles too: gemm_tc2_kernel<., true> decodes them in shared memory; taps == 1 by construction)
+    const bool pair_ok = (kp.n_tiles128 & 1) == 0 && kp.n_tiles128 >= 2;
     const long tiles_pair = (long)(kp.n_tiles128 / 2) * m_pairs;
     // ... and below that when every cluster still gets >= ~28 k-blocks of work (M = 750: MLP up-projection N = 12288 792 vs
     // 647 TFLOP/s, down-projection K = 6144 612 vs 526; QKV / o-proj stay single-CTA: profiles/r1_gemm_sweep_issue1.log)
     const int pairs_avail = std::max(1, max_active_pairs());
     bool pair = pair_ok && ((long)g.B * g.l_out >= 2048 || tiles_pair * (long)kp.kb_total >= 28L * pairs_avail);
+    // packed quantised tiles: the pair halves the decode work per tensor-core cycle (one sub-tile per CTA per k-block), so it is
+    // the route whenever there are two row tiles to pair; one row tile (M <= 128: the HBM-bound GEMVs) stays on the single CTA
+    if (kp.wtype != W_F16) pair = pair_ok && (long)g.B * g.l_out > BM;
     if (const char* fp = std::getenv("ACE_B200_GEMM_2CTA")) pair = pair_ok && std::atoi(fp) != 0;
     if (pair && max_active_pairs() < 8) pair = false;
     const int units = pair ? max_active_pairs() : sms;  // schedulable units: clusters or CTAs

@@ -19,7 +19,7 @@ struct WeightLoader {
     size_t* weight_bytes;
     std::string err;
     int status = 0;
-    int online_q = -1;  // W_Q8_0 when ACE_GGML_*_WEIGHT_QTYPE asks for it (safetensors only)
+    int online_q = -1;  // W_Q8_0 / W_Q4_K / W_Q6_K when ACE_GGML_*_WEIGHT_QTYPE asks for it (safetensors only)
 
     bool fail(int st, const std::string& e) {
         if (status == 0) {
@@ -129,7 +129,10 @@ struct WeightLoader {
     }
     bool pack_f32(const std::vector<float>& w, int N, int K, std::vector<uint8_t>& img, PackedWeight& out) {
         std::string e;
-        const int wt = (online_q == W_Q8_0 && !tf->is_gguf() && K % 32 == 0 && K % TILE_K == 0) ? W_Q8_0 : W_F16;
+        // quantise when the input dim is a whole number of blocks, else keep the tensor unquantised (acestep_dit_model.cpp:165-173)
+        int wt = W_F16;
+        if (!tf->is_gguf() && online_q == W_Q8_0 && K % TILE_K == 0) wt = W_Q8_0;
+        if (!tf->is_gguf() && (online_q == W_Q4_K || online_q == W_Q6_K) && K % 256 == 0) wt = online_q;
         if (!pack_tiles_f32(w.data(), N, 1, K, wt, img, out, e)) return fail(1, e);
         return true;
     }

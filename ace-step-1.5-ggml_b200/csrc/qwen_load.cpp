@@ -59,7 +59,7 @@ std::string resolve_qwen_gguf(const std::string& dir) {
     return "";
 }
 
-// W_Q8_0, -2 (a K-quant was asked for: not provided on line), -1 (nothing)
+// W_Q8_0 / W_Q4_K / W_Q6_K, or -1 (nothing asked for)
 int qwen_online_qtype(std::string& unsupported) {
     for (const char* key : {"ACE_GGML_QWEN_WEIGHT_QTYPE", "ACE_GGML_WEIGHT_QTYPE"}) {
         const char* v = std::getenv(key);
@@ -67,10 +67,9 @@ int qwen_online_qtype(std::string& unsupported) {
         std::string s(v);
         std::transform(s.begin(), s.end(), s.begin(), [](unsigned char ch) { return (char)std::toupper(ch); });
         if (s == "Q8" || s == "Q8_0") return W_Q8_0;
-        if (s == "Q6" || s == "Q6_K" || s == "Q4" || s == "Q4_K" || s == "Q4_K_M") {
-            unsupported = s;
-            return -2;
-        }
+        if (s == "Q6" || s == "Q6_K") return W_Q6_K;
+        if (s == "Q4" || s == "Q4_K" || s == "Q4_K_M") return W_Q4_K;
+        (void)unsupported;
     }
     return -1;
 }
@@ -105,11 +104,6 @@ int qwen_load(const std::string& model_dir, QwenModel& m, std::string& err) {
     WeightLoader L{tf.get(), &m.allocs, &m.weight_bytes, {}, 0, -1};
     std::string unsup;
     L.online_q = qwen_online_qtype(unsup);
-    if (L.online_q == -2 && !tf->is_gguf()) {
-        err = "on-the-fly " + unsup + " quantisation of safetensors weights is not provided; export a pre-quantised GGUF";
-        m.release();
-        return 4;
-    }
     EncStack& st = m.stack;
     st.H = c.hidden_size;
     st.I = c.intermediate_size;
@@ -129,12 +123,17 @@ int qwen_load(const std::string& model_dir, QwenModel& m, std::string& err) {
         else if (sh.size() != 2 || sh[1] != c.hidden_size || sh[0] < 1) ok = L.fail(3, "invalid tensor shape for embed_tokens.weight");
         else {
             if (sh[0] < c.vocab_size) m.cfg.vocab_size = (int)sh[0];
-            if (L.online_q == W_Q8_0 && !tf->is_gguf() && c.hidden_size % 32 == 0) {
+            const int oq = tf->is_gguf() ? -1 : L.online_q;
+            if ((oq == W_Q8_0 && c.hidden_size % 32 == 0) || ((oq == W_Q4_K || oq == W_Q6_K) && c.hidden_size % 256 == 0)) {
                 // the reference quantises the table too when the on-line switch is set (qwen_model.cpp:124-146): round-trip it
-                std::vector<uint8_t> q(ggml_row_bytes(GGML_Q8_0, c.hidden_size));
+                const int gt = oq == W_Q8_0 ? GGML_Q8_0 : (oq == W_Q4_K ? GGML_Q4_K : GGML_Q6_K);
+                std::vector<uint8_t> q(ggml_row_bytes(gt, c.hidden_size));
                 for (int64_t r = 0; r < sh[0]; ++r) {
-                    quantize_row_q8_0(tab.data() + r * c.hidden_size, q.data(), c.hidden_size);
-                    dequant_row(GGML_Q8_0, q.data(), tab.data() + r * c.hidden_size, c.hidden_size);
+                    float* row = tab.data() + r * c.hidden_size;
+                    if (gt == GGML_Q8_0) quantize_row_q8_0(row, q.data(), c.hidden_size);
+                    else if (gt == GGML_Q4_K) quantize_row_q4_k(row, q.data(), c.hidden_size);
+                    else quantize_row_q6_k(row, q.data(), c.hidden_size);
+                    dequant_row(gt, q.data(), row, c.hidden_size);
                 }
             }
             m.table = L.upload_f32(tab);

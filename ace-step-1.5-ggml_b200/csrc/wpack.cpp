@@ -381,23 +381,266 @@ bool pack_tiles_ggml(const void* rows_v, int ggml_type, int N, int K, std::vecto
     return true;
 }
 
+// ------------------------------------------------------------------ K-quant row quantisers (on-line ACE_GGML_*_WEIGHT_QTYPE)
+// Restatement of ggml's reference quantisers — quantize_row_q4_K_ref / quantize_row_q6_K_ref with make_qkx2_quants /
+// make_qx_quants (third_party/ggml/src/ggml-quants.c:444-518, 622-701, 1280-1350, 1692-1760) — with the float operations in
+// the same order, so the blocks are bit-identical to what ggml_quantize_chunk writes (tests/test_wpack_cpu.py checks that
+// against the reference library).  The reference runs them at load when the env switch names a K-quant
+// (acestep_dit_model.cpp:156-192); this library does the same.
+namespace {
+
+inline int round_magic(float v) {  // ggml's nearest_int: round-to-nearest-even through the 1.5 * 2^23 trick
+    const float t = v + 12582912.f;
+    int i;
+    std::memcpy(&i, &t, sizeof(i));
+    return (i & 0x007fffff) - 0x00400000;
+}
+
+// asymmetric 4-bit group fit: codes in [0, nmax], returns the scale, *neg_min = -offset (weighted least squares over a
+// small grid of inverse scales)
+float fit_scale_min(int n, int nmax, const float* x, const float* wgt, uint8_t* L, float* neg_min, uint8_t* trial, float rmin,
+                    float rdelta, int nstep) {
+    float lo = x[0], hi = x[0], sum_w = wgt[0], sum_x = sum_w * x[0];
+    for (int i = 1; i < n; ++i) {
+        if (x[i] < lo) lo = x[i];
+        if (x[i] > hi) hi = x[i];
+        const float w = wgt[i];
+        sum_w += w;
+        sum_x += w * x[i];
+    }
+    if (lo > 0) lo = 0;
+    if (hi == lo) {
+        for (int i = 0; i < n; ++i) L[i] = 0;
+        *neg_min = -lo;
+        return 0.f;
+    }
+    float iscale = nmax / (hi - lo);
+    float scale = 1 / iscale;
+    float best = 0;
+    for (int i = 0; i < n; ++i) {
+        const int l = round_magic(iscale * (x[i] - lo));
+        L[i] = (uint8_t)std::max(0, std::min(nmax, l));
+        float diff = scale * L[i] + lo - x[i];
+        diff = diff * diff;
+        best += wgt[i] * diff;
+    }
+    for (int is = 0; is <= nstep; ++is) {
+        iscale = (rmin + rdelta * is + nmax) / (hi - lo);
+        float sl = 0, sl2 = 0, sxl = 0;
+        for (int i = 0; i < n; ++i) {
+            int l = round_magic(iscale * (x[i] - lo));
+            l = std::max(0, std::min(nmax, l));
+            trial[i] = (uint8_t)l;
+            const float w = wgt[i];
+            sl += w * l;
+            sl2 += w * l * l;
+            sxl += w * l * x[i];
+        }
+        const float D = sum_w * sl2 - sl * sl;
+        if (D > 0) {
+            float sc = (sum_w * sxl - sum_x * sl) / D;
+            float mn = (sl2 * sum_x - sl * sxl) / D;
+            if (mn > 0) {
+                mn = 0;
+                sc = sxl / sl2;
+            }
+            float cur = 0;
+            for (int i = 0; i < n; ++i) {
+                float diff = sc * trial[i] + mn - x[i];
+                diff = diff * diff;
+                cur += wgt[i] * diff;
+            }
+            if (cur < best) {
+                for (int i = 0; i < n; ++i) L[i] = trial[i];
+                best = cur;
+                scale = sc;
+                lo = mn;
+            }
+        }
+    }
+    *neg_min = -lo;
+    return scale;
+}
+
+// symmetric group fit used by Q6_K (x^2 weights, 18 trial scales around -nmax / max)
+float fit_scale_sym(int n, int nmax, const float* x, int8_t* L) {
+    float mx = 0, amax = 0;
+    for (int i = 0; i < n; ++i) {
+        const float ax = std::fabs(x[i]);
+        if (ax > amax) {
+            amax = ax;
+            mx = x[i];
+        }
+    }
+    if (amax < 1e-15f) {
+        for (int i = 0; i < n; ++i) L[i] = 0;
+        return 0.f;
+    }
+    float iscale = -nmax / mx;
+    float sumlx = 0, suml2 = 0;
+    for (int i = 0; i < n; ++i) {
+        int l = round_magic(iscale * x[i]);
+        l = std::max(-nmax, std::min(nmax - 1, l));
+        L[i] = (int8_t)(l + nmax);
+        const float w = x[i] * x[i];
+        sumlx += w * x[i] * l;
+        suml2 += w * l * l;
+    }
+    float scale = suml2 ? sumlx / suml2 : 0.0f;
+    float best = scale * sumlx;
+    for (int is = -9; is <= 9; ++is) {
+        if (is == 0) continue;
+        iscale = -(nmax + 0.1f * is) / mx;
+        sumlx = suml2 = 0;
+        for (int i = 0; i < n; ++i) {
+            int l = round_magic(iscale * x[i]);
+            l = std::max(-nmax, std::min(nmax - 1, l));
+            const float w = x[i] * x[i];
+            sumlx += w * x[i] * l;
+            suml2 += w * l * l;
+        }
+        if (suml2 > 0 && sumlx * sumlx > best * suml2) {
+            for (int i = 0; i < n; ++i) {
+                const int l = round_magic(iscale * x[i]);
+                L[i] = (int8_t)(nmax + std::max(-nmax, std::min(nmax - 1, l)));
+            }
+            scale = sumlx / suml2;
+            best = scale * sumlx;
+        }
+    }
+    return scale;
+}
+
+}  // namespace
+
+// block_q4_K: fp16 d, fp16 dmin, 12 bytes of packed 6-bit (scale, min) pairs, 128 bytes of nibbles  (ggml-common.h:291-305)
+void quantize_row_q4_k(const float* x, void* dst, int64_t n) {
+    uint8_t* out = static_cast<uint8_t*>(dst);
+    uint8_t L[256], trial[32];
+    float wgt[32], mins[8], scales[8];
+    for (int64_t b = 0; b < n / 256; ++b, x += 256, out += 144) {
+        float max_scale = 0, max_min = 0;
+        for (int j = 0; j < 8; ++j) {
+            float sum_x2 = 0;
+            for (int l = 0; l < 32; ++l) sum_x2 += x[32 * j + l] * x[32 * j + l];
+            const float av = std::sqrt(sum_x2 / 32);
+            for (int l = 0; l < 32; ++l) wgt[l] = av + std::fabs(x[32 * j + l]);
+            scales[j] = fit_scale_min(32, 15, x + 32 * j, wgt, L + 32 * j, &mins[j], trial, -1.f, 0.1f, 20);
+            if (scales[j] > max_scale) max_scale = scales[j];
+            if (mins[j] > max_min) max_min = mins[j];
+        }
+        const float inv_scale = max_scale > 0 ? 63.f / max_scale : 0.f;
+        const float inv_min = max_min > 0 ? 63.f / max_min : 0.f;
+        uint8_t* sc = out + 4;
+        std::memset(sc, 0, 12);
+        for (int j = 0; j < 8; ++j) {
+            uint8_t ls = (uint8_t)round_magic(inv_scale * scales[j]);
+            uint8_t lm = (uint8_t)round_magic(inv_min * mins[j]);
+            ls = std::min<uint8_t>(63, ls);
+            lm = std::min<uint8_t>(63, lm);
+            if (j < 4) {
+                sc[j] = ls;
+                sc[j + 4] = lm;
+            } else {
+                sc[j + 4] = (uint8_t)((ls & 0xF) | ((lm & 0xF) << 4));
+                sc[j - 4] |= (uint8_t)((ls >> 4) << 6);
+                sc[j] |= (uint8_t)((lm >> 4) << 6);
+            }
+        }
+        const uint16_t dh = f32_to_f16(max_scale / 63.f), mh = f32_to_f16(max_min / 63.f);
+        std::memcpy(out, &dh, 2);
+        std::memcpy(out + 2, &mh, 2);
+        const float d_all = f16_to_f32(dh), m_all = f16_to_f32(mh);
+        for (int j = 0; j < 8; ++j) {
+            uint8_t s6, m6;
+            q4k_scale_min(j, sc, s6, m6);
+            const float d = d_all * s6;
+            if (!d) continue;
+            const float dm = m_all * m6;
+            for (int i = 0; i < 32; ++i) {
+                const int l = round_magic((x[32 * j + i] + dm) / d);
+                L[32 * j + i] = (uint8_t)std::max(0, std::min(15, l));
+            }
+        }
+        uint8_t* q = out + 16;
+        for (int j = 0; j < 256; j += 64, q += 32)
+            for (int l = 0; l < 32; ++l) q[l] = (uint8_t)(L[j + l] | (L[j + l + 32] << 4));
+    }
+}
+
+// block_q6_K: 128 bytes low nibbles, 64 bytes high 2-bit planes, 16 int8 scales, fp16 d  (ggml-common.h:326-335)
+void quantize_row_q6_k(const float* x, void* dst, int64_t n) {
+    uint8_t* out = static_cast<uint8_t*>(dst);
+    int8_t L[256];
+    float scales[16];
+    for (int64_t b = 0; b < n / 256; ++b, x += 256, out += 210) {
+        float max_scale = 0, max_abs = 0;
+        for (int ib = 0; ib < 16; ++ib) {
+            const float sc = fit_scale_sym(16, 32, x + 16 * ib, L + 16 * ib);
+            scales[ib] = sc;
+            const float a = std::fabs(sc);
+            if (a > max_abs) {
+                max_abs = a;
+                max_scale = sc;
+            }
+        }
+        if (max_abs < 1e-15f) {
+            std::memset(out, 0, 210);
+            continue;
+        }
+        const float iscale = -128.f / max_scale;
+        const uint16_t dh = f32_to_f16(1 / iscale);
+        std::memcpy(out + 208, &dh, 2);
+        int8_t* sc8 = reinterpret_cast<int8_t*>(out + 192);
+        for (int ib = 0; ib < 16; ++ib) sc8[ib] = (int8_t)std::min(127, round_magic(iscale * scales[ib]));
+        const float d_all = f16_to_f32(dh);
+        for (int j = 0; j < 16; ++j) {
+            const float d = d_all * sc8[j];
+            if (!d) continue;
+            for (int i = 0; i < 16; ++i) {
+                int l = round_magic(x[16 * j + i] / d);
+                l = std::max(-32, std::min(31, l));
+                L[16 * j + i] = (int8_t)(l + 32);
+            }
+        }
+        uint8_t* ql = out;
+        uint8_t* qh = out + 128;
+        for (int j = 0; j < 256; j += 128, ql += 64, qh += 32) {
+            for (int l = 0; l < 32; ++l) {
+                const uint8_t q1 = L[j + l] & 0xF, q2 = L[j + l + 32] & 0xF, q3 = L[j + l + 64] & 0xF, q4 = L[j + l + 96] & 0xF;
+                ql[l] = (uint8_t)(q1 | (q3 << 4));
+                ql[l + 32] = (uint8_t)(q2 | (q4 << 4));
+                qh[l] = (uint8_t)((L[j + l] >> 4) | ((L[j + l + 32] >> 4) << 2) | ((L[j + l + 64] >> 4) << 4) | ((L[j + l + 96] >> 4) << 6));
+            }
+        }
+    }
+}
+
+
 bool pack_tiles_f32(const float* w, int N, int taps, int K, int wtype, std::vector<uint8_t>& out, PackedWeight& meta,
                     std::string& err) {
-    if (wtype == W_Q8_0) {
-        if (taps != 1 || K % TILE_K != 0) {
-            err = "pack_tiles_f32: Q8_0 needs taps == 1 and K % 64 == 0";
+    if (wtype == W_Q8_0 || wtype == W_Q4_K || wtype == W_Q6_K) {
+        const int blk_elems = wtype == W_Q8_0 ? TILE_K : 256;
+        if (taps != 1 || K % blk_elems != 0) {
+            err = "pack_tiles_f32: on-line quantisation needs taps == 1 and K % 64 == 0 (K % 256 for the K-quants)";
             return false;
         }
-        const size_t rb = ggml_row_bytes(GGML_Q8_0, K);
+        const int gt = wtype == W_Q8_0 ? GGML_Q8_0 : (wtype == W_Q4_K ? GGML_Q4_K : GGML_Q6_K);
+        const size_t rb = ggml_row_bytes(gt, K);
         std::vector<uint8_t> q((size_t)N * rb);
-        parallel_for((N + 63) / 64, [&](int blk) {
-            for (int r = blk * 64; r < std::min(N, blk * 64 + 64); ++r)
-                quantize_row_q8_0(w + (size_t)r * K, q.data() + (size_t)r * rb, K);
+        parallel_for((N + 15) / 16, [&](int blk) {
+            for (int r = blk * 16; r < std::min(N, blk * 16 + 16); ++r) {
+                const float* src = w + (size_t)r * K;
+                uint8_t* dst = q.data() + (size_t)r * rb;
+                if (wtype == W_Q8_0) quantize_row_q8_0(src, dst, K);
+                else if (wtype == W_Q4_K) quantize_row_q4_k(src, dst, K);
+                else quantize_row_q6_k(src, dst, K);
+            }
         });
-        return pack_tiles_ggml(q.data(), GGML_Q8_0, N, K, out, meta, err);
+        return pack_tiles_ggml(q.data(), gt, N, K, out, meta, err);
     }
     if (wtype != W_F16) {
-        err = "pack_tiles_f32: only F16 and Q8_0 can be produced from fp32 data";
+        err = "pack_tiles_f32: unknown weight type";
         return false;
     }
     init_meta(meta, W_F16, N, taps, K);

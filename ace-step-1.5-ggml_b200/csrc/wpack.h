@@ -52,6 +52,9 @@ const char* ggml_type_name(int ggml_type);
 bool dequant_row(int ggml_type, const void* src, float* dst, int64_t n);
 // fp32 row -> Q8_0 blocks (ggml quantize_row_q8_0_ref: d = amax/127 as fp16, q = round(x/d))
 void quantize_row_q8_0(const float* src, void* dst, int64_t n);
+// fp32 row -> Q4_K / Q6_K super-blocks, bit-identical to ggml's quantize_row_q4_K_ref / quantize_row_q6_K_ref (n % 256 == 0)
+void quantize_row_q4_k(const float* src, void* dst, int64_t n);
+void quantize_row_q6_k(const float* src, void* dst, int64_t n);
 
 float    f16_to_f32(uint16_t h);
 uint16_t f32_to_f16(float f);  // round-to-nearest-even, same as the hardware cvt.rn.f16.f32
@@ -76,8 +79,8 @@ struct PackedWeight {
 
 // Build the host image of a packed weight.
 //  * pack_tiles_f32: W given as fp32 [N, taps, K] (row-major) -> F16 tiles (values rounded to fp16), or,
-//    with wtype == W_Q8_0 and taps == 1 and K % 64 == 0, quantised on the fly like the reference's
-//    ACE_GGML_*_WEIGHT_QTYPE=Q8_0 path (acestep_dit_model.cpp:156-192).
+//    with wtype == W_Q8_0 / W_Q4_K / W_Q6_K and taps == 1 and K a whole number of blocks, quantised on the fly like the
+//    reference's ACE_GGML_*_WEIGHT_QTYPE path (acestep_dit_model.cpp:156-192).
 //  * pack_tiles_ggml: W given as raw ggml rows [N][row_bytes] of type Q8_0 / Q4_K / Q6_K, K % 64 == 0 (K % 256
 //    for the K-quants); the codes are carried over unchanged.
 bool pack_tiles_f32(const float* w, int N, int taps, int K, int wtype, std::vector<uint8_t>& out, PackedWeight& meta,

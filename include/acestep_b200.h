@@ -127,6 +127,11 @@ ACE_GGML_API ace_ggml_status ace_b200_debug_attention(ace_ggml_context * ctx, co
 ACE_GGML_API ace_ggml_status ace_b200_debug_pack_roundtrip(const void * W, int32_t w_ggml_type, int32_t N, int32_t K,
                                                            float * unpacked, float * ref);
 
+/* CPU-only: fp32 rows [N, K] -> raw ggml rows of w_ggml_type (8 Q8_0 / 12 Q4_K / 14 Q6_K) with the library's own quantisers, the ones
+ * ACE_GGML_*_WEIGHT_QTYPE runs at load; bit-identical to ggml_quantize_chunk (tests/test_wpack_cpu.py). */
+ACE_GGML_API ace_ggml_status ace_b200_debug_quantize_rows(const float * src, int32_t w_ggml_type, int32_t N, int32_t K,
+                                                          void * dst, size_t dst_size);
+
 /* CPU-only: parse a .gguf (is_gguf != 0) or .safetensors file with the library's readers and decode every small tensor; returns the
  * tensor count, or -1 with the reader's message in err_out.  Used by the malformed-file tests. */
 ACE_GGML_API int64_t ace_b200_debug_probe_tensor_file(const char * path, int32_t is_gguf, char * err_out, size_t err_size);

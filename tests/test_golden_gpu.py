@@ -40,13 +40,17 @@ def vae_gold():
 
 
 @pytest.mark.parametrize("q", ["f32", "F16", "Q8_0", "Q4_K", "Q6_K"])
-@pytest.mark.parametrize("route", ["in_kernel_decode", "f16_twin"])
+@pytest.mark.parametrize("route", ["in_kernel_decode", "single_cta_decode", "f16_twin"])
 def test_dit_forward_vs_golden(br, root, dit_gold, q, route, monkeypatch):
     if q in ("Q4_K", "Q6_K") and not refbridge.ref_available():
         pytest.fail("K-quant GGUF export needs ggml_quantize_chunk from oracle/_ref")
-    if route == "f16_twin" and q in ("f32", "F16"):
-        pytest.skip("unquantised weights have no twin")
-    monkeypatch.setenv("ACE_B200_PREDECODE_MIN_M", "1" if route == "f16_twin" else "1000000")
+    if route != "in_kernel_decode" and q in ("f32", "F16"):
+        pytest.skip("unquantised weights have one route")
+    if route == "f16_twin":  # opt-in decoded twin, forced for every row count
+        monkeypatch.setenv("ACE_B200_PREDECODE", "1")
+        monkeypatch.setenv("ACE_B200_PREDECODE_MIN_M", "1")
+    elif route == "single_cta_decode":
+        monkeypatch.setenv("ACE_B200_GEMM_2CTA", "0")
     d = make_dit_dir(root, fx.TOY, 0, None if q == "f32" else q)
     inp = fx.dit_inputs(fx.TOY, 33, 7, seed=1234)
     br.load_dit(d)

@@ -238,20 +238,47 @@ def test_attention(br, ql, kl, window, masked, impl, monkeypatch):
 
 
 @pytest.mark.parametrize("gt", [8, 12, 14])
-def test_gemm_predecoded_twin_is_bit_identical(br, gt, monkeypatch):
-    """quantised weight, two routes (gemm.h policy): decoded in shared memory inside the GEMM vs decoded once to the F16
-    twin and run through the F16 kernel.  Same decoder arithmetic, same MMA order -> identical fp32 results."""
-    g = np.random.default_rng(gt)
-    L, K, N = 640, 512, 384
+@pytest.mark.parametrize("shape", [(640, 512, 384), (129, 2048, 256), (1500, 1024, 1024), (3000, 512, 512)])
+def test_gemm_quantised_routes_agree(br, gt, shape, monkeypatch):
+    """quantised weight, three routes (gemm.h): decoded in shared memory by the single-CTA kernel, decoded in shared memory by the
+    CTA-pair kernel (the default beyond one row tile; N = 384 has an odd tile count and falls back to the single CTA), and
+    decoded once to the F16 twin (ACE_B200_PREDECODE=1) and run through the F16 kernels.  Same decoder arithmetic and the same K
+    order per output element: the single-CTA route and the twin are bit-identical, the pair agrees to fp32 rounding."""
+    L, K, N = shape
+    g = np.random.default_rng(gt + L)
     A = g.standard_normal((1, L, K), dtype=np.float32)
     rows = random_rows(gt, N, K, seed=gt + 1)
-    monkeypatch.setenv("ACE_B200_PREDECODE_MIN_M", "1000000")
-    in_kernel = br.debug_gemm(A, rows, w_type=gt, N=N)
+    monkeypatch.setenv("ACE_B200_GEMM_2CTA", "0")
+    single = br.debug_gemm(A, rows, w_type=gt, N=N)
+    monkeypatch.delenv("ACE_B200_GEMM_2CTA")
+    default = br.debug_gemm(A, rows, w_type=gt, N=N)
+    monkeypatch.setenv("ACE_B200_PREDECODE", "1")
     monkeypatch.setenv("ACE_B200_PREDECODE_MIN_M", "1")
+    monkeypatch.setenv("ACE_B200_GEMM_2CTA", "0")
     twin = br.debug_gemm(A, rows, w_type=gt, N=N)
-    assert np.array_equal(in_kernel, twin)
+    assert np.array_equal(single, twin)
     ref = tap_gemm_ref(h16(A), dequant_ref(rows, gt, N, K).astype(np.float64)[:, None, :], 1, 0, 0, L)
     assert rel_err(twin, ref) < 2e-3
+    assert np.isfinite(default).all() and np.abs(default - single).max() <= 1e-5 * np.abs(ref).max(), np.abs(default - single).max()
+
+
+@pytest.mark.parametrize("gt", [8, 12, 14])
+def test_gemm_quantised_pair_epilogues(br, gt, monkeypatch):
+    """CTA-pair in-kernel decode through the fused epilogues the DiT uses: bias, SwiGLU over interleaved rows, split-K residual
+    accumulate (TMA reduce-add); each against the single-CTA route"""
+    g = np.random.default_rng(100 + gt)
+    L, K, N = 700, 1024, 512
+    A = g.standard_normal((1, L, K), dtype=np.float32)
+    rows = random_rows(gt, N, K, seed=gt + 7)
+    bias = g.standard_normal((N,), dtype=np.float32)
+    R = g.standard_normal((1, L, N), dtype=np.float32)
+    for kw in (dict(bias=bias), dict(swiglu=True), dict(resid=R), dict(resid=R, split_k=True)):
+        monkeypatch.setenv("ACE_B200_GEMM_2CTA", "0")
+        single = br.debug_gemm(A, rows, w_type=gt, N=N, **kw)
+        monkeypatch.setenv("ACE_B200_GEMM_2CTA", "1")
+        pair = br.debug_gemm(A, rows, w_type=gt, N=N, **kw)
+        assert np.isfinite(pair).all()
+        assert np.abs(pair - single).max() <= 2e-3 * max(1.0, np.abs(single).max()), (sorted(kw), np.abs(pair - single).max())
 
 
 @pytest.mark.parametrize("shape", [(1, 700, 2048, 1024, 1), (2, 333, 128, 256, 7), (1, 128 * 20, 256, 2048, 1), (1, 100, 512, 512, 1)])

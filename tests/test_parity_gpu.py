@@ -55,6 +55,24 @@ def test_dit_forward_matches_reference(br, root, quant):
     assert m["rel_l2"] <= rl and m["cos"] >= cs, (quant, m, br.model_info())
 
 
+@pytest.mark.parametrize("qtype", ["Q8_0", "Q6_K", "Q4_K"])
+def test_dit_online_quantisation_matches_reference(br, root, qtype, monkeypatch):
+    """ACE_GGML_DIT_WEIGHT_QTYPE on a safetensors directory: both sides quantise the 2-D weights at load (the reference with
+    ggml_quantize_chunk, acestep_dit_model.cpp:156-192; this library with its own bit-identical row quantisers, wpack.cpp) and run the
+    quantised network"""
+    need_ref()
+    d = make_dit_dir(root, fx.TOY, 0, None)
+    inp = fx.dit_inputs(fx.TOY, 33, 7, seed=1234)
+    calls = [{"op": "dit_forward", "t": 0.6, "t_r": 0.6, "out": "v"}]
+    ref, _ = refbridge.run_ref(calls, inp, dit_dir=d, env={"ACE_GGML_DIT_WEIGHT_QTYPE": qtype})
+    monkeypatch.setenv("ACE_GGML_DIT_WEIGHT_QTYPE", qtype)
+    br.load_dit(d)
+    assert qtype in br.model_info()
+    out = br.dit_forward_tfirst(inp["hidden_states"], inp["context_latents"], inp["encoder_hidden_states"], None, None, 0.6, 0.6)
+    m = metrics(out, ref["v"])
+    assert m["rel_l2"] <= TOL[qtype][0] and m["cos"] >= TOL[qtype][1], (qtype, m, br.model_info())
+
+
 @pytest.mark.parametrize("k", [1, 2, 3, 4])
 def test_dit_per_block_parity(br, root, k, monkeypatch):
     """depth-truncated network (ACE_GGML_DIT_MAX_LAYERS, acestep_dit_model.cpp:1457-1464) after k = 1..L blocks"""

@@ -66,10 +66,12 @@ struct SmemLayout {
     static constexpr int EPI_WARPS  = QUANT ? 4 : 8;
     static constexpr int STG_BYTES  = EPI_WARPS * STG_WARP_BYTES;  // epilogue transpose buffers
     static constexpr int COL_BYTES  = 2 * BN * 4;                  // staged bias + gate of one tile
-    static constexpr int BUDGET     = 227 * 1024 - 256 /*barriers*/ - STG_BYTES - COL_BYTES;
+    static constexpr int BUDGET     = 227 * 1024 - 256 /*barriers*/ - STG_BYTES - COL_BYTES - (QUANT ? 1024 : 0) /*raw-region padding*/;
     static constexpr int STAGES_RAW = BUDGET / (STAGE + RAW_STAGE);
     static constexpr int STAGES     = STAGES_RAW > 6 ? 6 : STAGES_RAW;
-    static constexpr int BYTES      = STAGES * (STAGE + RAW_STAGE) + STG_BYTES + COL_BYTES + 256;
+    // the epilogue transpose buffers double as the source of TMA reduce-add boxes (128-byte-swizzle image): 1 KB aligned
+    static constexpr int RAW_TOTAL  = (STAGES * RAW_STAGE + 1023) / 1024 * 1024;
+    static constexpr int BYTES      = STAGES * STAGE + RAW_TOTAL + STG_BYTES + COL_BYTES + 256;
 };
 
 // ---------------------------------------------------------------- weight decoders (one thread = one tile row)
@@ -617,7 +619,7 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
     uint8_t* sA = smem;                                  // [STAGES][16 KB]   |  SLAB: [2][SLAB_BYTES]
     uint8_t* sB = sA + (SLAB ? 2 * SLAB_BYTES : STAGES * A_STAGE_BYTES);  // [STAGES][SUBS*16 KB]
     uint8_t* sR = sB + STAGES * SL::B_STAGE;             // [STAGES][SUBS*RAW_MAX] (QUANT only)
-    float* sStg = reinterpret_cast<float*>(sR + STAGES * SL::RAW_STAGE);  // [EPI_WARPS][32 x 32 fp32]
+    float* sStg = reinterpret_cast<float*>(sR + SL::RAW_TOTAL);  // [EPI_WARPS][32 x 32 fp32], 1 KB aligned
     float* sCol = sStg + SL::STG_BYTES / 4;  // [2][BN]: bias, gate of the current tile
     uint64_t* bars = reinterpret_cast<uint64_t*>(reinterpret_cast<uint8_t*>(sCol) + SL::COL_BYTES);
     uint64_t* full = bars;                  // [STAGES] operands of stage s are in smem
@@ -1016,7 +1018,8 @@ constexpr int SMEM2_BYTES = STAGES2 * STAGE2_BYTES + 8 * STG_WARP_BYTES + 2 * 25
 constexpr int NUM_THREADS2Q = 448;
 constexpr int STAGES2Q = 5;
 constexpr int RAW2_BYTES = 8704;  // largest packed tile (Q8_0), 16-byte multiple
-constexpr int SMEM2Q_BYTES = STAGES2Q * (STAGE2_BYTES + RAW2_BYTES) + 4 * STG_WARP_BYTES + 2 * 256 * 4 + 512;
+constexpr int RAW2_TOTAL = (STAGES2Q * RAW2_BYTES + 1023) / 1024 * 1024;  // keeps the transpose buffers behind it 1 KB aligned
+constexpr int SMEM2Q_BYTES = STAGES2Q * STAGE2_BYTES + RAW2_TOTAL + 4 * STG_WARP_BYTES + 2 * 256 * 4 + 512;
 static_assert(SMEM2Q_BYTES <= 227 * 1024, "pair QUANT layout exceeds shared memory");
 
 template <bool WARM, bool QUANT>
@@ -1034,7 +1037,8 @@ gemm_tc2_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__
     uint8_t* sA = smem;                       // [NS][16 KB]
     uint8_t* sB = sA + NS * A_STAGE_BYTES;    // [NS][16 KB]  this CTA's half of the weight tile (fp16 UMMA image)
     uint8_t* sR = sB + NS * W_SUB_BYTES;      // QUANT: [NS][RAW2_BYTES] packed codes as they land
-    float* sStg = reinterpret_cast<float*>(sR + (QUANT ? NS * RAW2_BYTES : 0));  // [EPI_WARPS][32 x 32 fp32] epilogue transpose buffers
+    float* sStg = reinterpret_cast<float*>(sR + (QUANT ? RAW2_TOTAL : 0));  // [EPI_WARPS][32 x 32 fp32] epilogue transpose buffers (1 KB aligned:
+                                                                          // they are the 128-byte-swizzle source image of the TMA reduce-add boxes)
     float* sCol = sStg + EPI_WARPS * (STG_WARP_BYTES / 4);  // [2][256]: bias, gate of the current tile
     uint64_t* bars = reinterpret_cast<uint64_t*>(sCol + 2 * 256);
     uint64_t* full = bars;               // [S] local operands landed (QUANT: A landed + this CTA's sub-tile decoded)

@@ -201,7 +201,9 @@ cudaError_t dit_forward_device(const DitModel& m, DitWorkspace& ws, int B, int T
         const float* c_gate = mod + 5 * H;
 
         // self-attention
-        launch_rmsnorm_mod(ws.x, ly.self_norm, scale_msa, shift_msa, mod_bs, ws.xn, B, S, H, eps, st);
+        // early_mod: the tables were written by build_modulation ahead of the patch-embed GEMM, and every kernel since waits before
+        // it triggers its dependents, so no rmsnorm can start before that writer has completed
+        launch_rmsnorm_mod(ws.x, ly.self_norm, scale_msa, shift_msa, mod_bs, ws.xn, B, S, H, eps, st, nullptr, true);
         {
             GemmEpilogue e;  // fused: per-head RMSNorm(q, k) + NEOX RoPE at position l; V stored as is
             e.mode = EPI_HEADNORM;
@@ -251,7 +253,7 @@ cudaError_t dit_forward_device(const DitModel& m, DitWorkspace& ws, int B, int T
             }
         }
         // MLP
-        launch_rmsnorm_mod(ws.x, ly.mlp_norm, c_scale, c_shift, mod_bs, ws.xn, B, S, H, eps, st);
+        launch_rmsnorm_mod(ws.x, ly.mlp_norm, c_scale, c_shift, mod_bs, ws.xn, B, S, H, eps, st, nullptr, true);
         {
             GemmEpilogue e;
             e.mode = EPI_SWIGLU;
@@ -271,7 +273,7 @@ cudaError_t dit_forward_device(const DitModel& m, DitWorkspace& ws, int B, int T
     }
 
     // ---- output head: AdaLN(norm_out) -> proj_out (un-patch) -> crop to T
-    launch_rmsnorm_mod(ws.x, m.norm_out, ws.out_mod + H, ws.out_mod, 2L * H, ws.xn, B, S, H, eps, st);
+    launch_rmsnorm_mod(ws.x, m.norm_out, ws.out_mod + H, ws.out_mod, 2L * H, ws.xn, B, S, H, eps, st, nullptr, n_layers > 0);
     {
         GemmEpilogue e;
         e.bias = m.proj_out_b;

@@ -185,7 +185,16 @@ int dit_load(const std::string& model_dir, DitModel& m, std::string& err) {
     ok = ok && L.linear({"decoder.condition_embedder.weight"}, false, H, m.condition);
     ok = ok && L.vec("decoder.condition_embedder.bias", H, m.condition_b);
     ok = ok && L.vec("decoder.norm_out.weight", H, m.norm_out);
-    ok = ok && L.vec("decoder.scale_shift_table", 2L * H, m.out_table);
+    if (ok) {
+        std::vector<float> t;
+        if (!tf->read_f32("decoder.scale_shift_table", t, nullptr, e)) ok = L.fail(3, e);
+        else if ((int64_t)t.size() != 2L * H) ok = L.fail(3, "unexpected size for decoder.scale_shift_table");
+        else {
+            L.online_roundtrip(t, H);
+            m.out_table = L.upload_f32(t);
+            ok = m.out_table != nullptr;
+        }
+    }
     auto load_te = [&](const std::string& p, DitTimeEmbed& te) {
         return L.linear({p + ".linear_1.weight"}, false, 256, te.w1) && L.vec(p + ".linear_1.bias", H, te.b1) &&
                L.linear({p + ".linear_2.weight"}, false, H, te.w2) && L.vec(p + ".linear_2.bias", H, te.b2) &&
@@ -214,7 +223,10 @@ int dit_load(const std::string& model_dir, DitModel& m, std::string& err) {
             std::vector<float> t;
             if (!tf->read_f32(p + "scale_shift_table", t, nullptr, e)) ok = L.fail(3, e);
             else if ((int64_t)t.size() != 6L * H) ok = L.fail(3, "unexpected size for " + p + "scale_shift_table");
-            else std::memcpy(tables.data() + (size_t)i * 6 * H, t.data(), t.size() * 4);
+            else {
+                L.online_roundtrip(t, H);
+                std::memcpy(tables.data() + (size_t)i * 6 * H, t.data(), t.size() * 4);
+            }
         }
         if (ok && (ly.self_qkv.N != nq + 2 * nkv || ly.self_o.N != H || ly.cross_q.N != nq || ly.cross_kv.N != 2 * nkv ||
                    ly.mlp_gate_up.N != 2 * I || ly.mlp_down.N != H))

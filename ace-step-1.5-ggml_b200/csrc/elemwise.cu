@@ -113,7 +113,7 @@ __global__ void build_modulation_kernel(const float* __restrict__ tables, const 
 __global__ void __launch_bounds__(128)
 rmsnorm_mod_kernel(const float* __restrict__ x, const float* __restrict__ w, const float* __restrict__ scale1,
                    const float* __restrict__ shift, long mod_bstride, __half* __restrict__ y, long rows, int rows_per_b,
-                   int H, float eps, float* __restrict__ y32) {
+                   int H, float eps, float* __restrict__ y32, int early_mod) {
     __shared__ float red[4];
     const long row = blockIdx.x;
     const int tid = threadIdx.x;
@@ -121,8 +121,10 @@ rmsnorm_mod_kernel(const float* __restrict__ x, const float* __restrict__ w, con
     const float* s1 = scale1 ? scale1 + (long)b * mod_bstride : nullptr;
     const float* sh = shift ? shift + (long)b * mod_bstride : nullptr;
     constexpr int MAXV = 4;  // up to H = 2048 held in registers; wider rows re-read from L1/L2
-    // norm weight and AdaLN scale / shift do not depend on the previous kernel: fetch them before the PDL wait so their L2
-    // round trip overlaps its tail instead of following the reduction
+    // The norm weight is a constant of the model: fetch it before the PDL wait so its L2 round trip overlaps the previous kernel's
+    // tail.  The AdaLN scale / shift are rewritten every step: they are fetched early only when the caller vouches (early_mod) that
+    // their writer is NOT the immediately preceding kernel and that every kernel in between waited before triggering its dependents
+    // (dit_forward_device builds the tables ahead of the patch-embed GEMM); otherwise they are read after the wait.
     float4 ww[MAXV], sc[MAXV], sf[MAXV];
 #pragma unroll
     for (int i = 0; i < MAXV; ++i) {
@@ -130,12 +132,24 @@ rmsnorm_mod_kernel(const float* __restrict__ x, const float* __restrict__ w, con
         ww[i] = sc[i] = sf[i] = make_float4(0.f, 0.f, 0.f, 0.f);
         if (c < H) {
             ww[i] = __ldg(reinterpret_cast<const float4*>(w + c));
-            if (s1) sc[i] = __ldg(reinterpret_cast<const float4*>(s1 + c));
-            if (sh) sf[i] = __ldg(reinterpret_cast<const float4*>(sh + c));
+            if (early_mod) {
+                if (s1) sc[i] = __ldg(reinterpret_cast<const float4*>(s1 + c));
+                if (sh) sf[i] = __ldg(reinterpret_cast<const float4*>(sh + c));
+            }
         }
     }
     asm volatile("griddepcontrol.wait;" ::: "memory");             // PDL: the residual stream comes from the previous GEMM
     asm volatile("griddepcontrol.launch_dependents;" ::: "memory");
+    if (!early_mod) {
+#pragma unroll
+        for (int i = 0; i < MAXV; ++i) {
+            const int c = (i * 128 + tid) * 4;
+            if (c < H) {
+                if (s1) sc[i] = *reinterpret_cast<const float4*>(s1 + c);
+                if (sh) sf[i] = *reinterpret_cast<const float4*>(sh + c);
+            }
+        }
+    }
     const float* xr = x + row * H;
     float4 v[MAXV];
     float ss = 0.f;
@@ -400,11 +414,12 @@ void launch_build_modulation(const float* tables, const float* proj, float* mod,
                                                                     B, layers, H);
 }
 void launch_rmsnorm_mod(const float* x, const float* w, const float* scale1, const float* shift, long mod_bstride,
-                        __half* y, int B, int rows_per_b, int H, float eps, cudaStream_t st, float* y32) {
+                        __half* y, int B, int rows_per_b, int H, float eps, cudaStream_t st, float* y32, bool early_mod) {
     note_launch();
     const long rows = (long)B * rows_per_b;
     ProfScope prof_scope(PROF_ELEM, 0.0, (double)rows * H * (4.0 + (y ? 2.0 : 0.0) + (y32 ? 4.0 : 0.0)), st);  // weight / scale / shift are L2-resident vectors
-    launch_pdl(rmsnorm_mod_kernel, dim3((unsigned)rows), dim3(128), 0, st, x, w, scale1, shift, mod_bstride, y, rows, rows_per_b, H, eps, y32);
+    launch_pdl(rmsnorm_mod_kernel, dim3((unsigned)rows), dim3(128), 0, st, x, w, scale1, shift, mod_bstride, y, rows, rows_per_b, H, eps, y32,
+               early_mod ? 1 : 0);
 }
 void launch_headnorm_rope(__half* buf, long row_stride, int col0, int n_heads, const float* w, const float2* rope_tab,
                           int B, int rows_per_b, float eps, cudaStream_t st) {

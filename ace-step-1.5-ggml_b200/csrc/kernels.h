@@ -111,7 +111,8 @@ void launch_build_modulation(const float* tables /*[layers,6,H]*/, const float* 
 // reference: ggml_rms_norm (ggml-cpu/ops.cpp:3646-3697) + acestep_dit_model.cpp:1097-1106, 1477-1481
 // y32 (optional) receives the same result unrounded (final norms of the condition / text encoders, whose output is fp32)
 void launch_rmsnorm_mod(const float* x, const float* w, const float* scale1, const float* shift, long mod_bstride,
-                        __half* y, int B, int rows_per_b, int H, float eps, cudaStream_t st, float* y32 = nullptr);
+                        __half* y, int B, int rows_per_b, int H, float eps, cudaStream_t st, float* y32 = nullptr,
+                        bool early_mod = false);  // early_mod: scale1 / shift may be read before the PDL wait (see the kernel)
 // out[i, :] = table[ids[i], :]  (fp32 rows; ggml_get_rows + cast, qwen_model.cpp:553-554); ids outside [0, vocab) give zeros
 void launch_gather_rows(const float* table, const int32_t* ids, float* out, int n, int width, int vocab, cudaStream_t st);
 // dst[l, 0..c_dst) = fp16(src[l, 0..c_src)) zero-padded (VAE encoder input: 2 audio channels -> 8, acestep_vae_model.cpp:1018-1027)

@@ -60,6 +60,20 @@ struct WeightLoader {
         }
         return d;
     }
+    // The reference's on-line switch also quantises the [1, rows, row_len] tables it loads as 2-D tensors (scale_shift_table:
+    // acestep_dit_model.cpp:279-332) and dequantises them again at run time (ggml_cast); the equivalent here is a round trip.
+    void online_roundtrip(std::vector<float>& v, int64_t row_len) const {
+        if (tf->is_gguf() || online_q < 0 || row_len <= 0) return;
+        const int gt = online_q == W_Q8_0 ? GGML_Q8_0 : (online_q == W_Q4_K ? GGML_Q4_K : GGML_Q6_K);
+        if (row_len % ggml_block_elems(gt) != 0) return;
+        std::vector<uint8_t> q(ggml_row_bytes(gt, row_len));
+        for (size_t r = 0; r + (size_t)row_len <= v.size(); r += (size_t)row_len) {
+            if (gt == GGML_Q8_0) quantize_row_q8_0(v.data() + r, q.data(), row_len);
+            else if (gt == GGML_Q4_K) quantize_row_q4_k(v.data() + r, q.data(), row_len);
+            else quantize_row_q6_k(v.data() + r, q.data(), row_len);
+            dequant_row(gt, q.data(), v.data() + r, row_len);
+        }
+    }
     bool vec(const std::string& name, int64_t expect, float*& out) {
         std::vector<float> v;
         std::string e;

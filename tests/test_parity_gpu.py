@@ -56,13 +56,14 @@ def test_dit_forward_matches_reference(br, root, quant):
 
 
 @pytest.mark.parametrize("qtype", ["Q8_0", "Q6_K", "Q4_K"])
-def test_dit_online_quantisation_matches_reference(br, root, qtype, monkeypatch):
-    """ACE_GGML_DIT_WEIGHT_QTYPE on a safetensors directory: both sides quantise the 2-D weights at load (the reference with
-    ggml_quantize_chunk, acestep_dit_model.cpp:156-192; this library with its own bit-identical row quantisers, wpack.cpp) and run the
-    quantised network"""
+def test_dit_online_quantisation_matches_reference(br, root, qtype, monkeypatch, tmp_path):
+    """ACE_GGML_DIT_WEIGHT_QTYPE on a safetensors directory: both sides quantise the 2-D weights (and the [1, n, H] AdaLN tables) at
+    load — the reference with ggml_quantize_chunk (acestep_dit_model.cpp:156-192, 279-332), this library with its own bit-identical
+    row quantisers (wpack.cpp) — and run the quantised network.  MID dims (hidden 512: two Q8_K activation blocks per row on the
+    reference side).  Also: the on-line load equals a load of the GGUF the in-tree exporter writes from the same file."""
     need_ref()
-    d = make_dit_dir(root, fx.TOY, 0, None)
-    inp = fx.dit_inputs(fx.TOY, 33, 7, seed=1234)
+    d = make_dit_dir(root, fx.MID, 0, None)
+    inp = fx.dit_inputs(fx.MID, 64, 9, seed=1234)
     calls = [{"op": "dit_forward", "t": 0.6, "t_r": 0.6, "out": "v"}]
     ref, _ = refbridge.run_ref(calls, inp, dit_dir=d, env={"ACE_GGML_DIT_WEIGHT_QTYPE": qtype})
     monkeypatch.setenv("ACE_GGML_DIT_WEIGHT_QTYPE", qtype)
@@ -71,6 +72,17 @@ def test_dit_online_quantisation_matches_reference(br, root, qtype, monkeypatch)
     out = br.dit_forward_tfirst(inp["hidden_states"], inp["context_latents"], inp["encoder_hidden_states"], None, None, 0.6, 0.6)
     m = metrics(out, ref["v"])
     assert m["rel_l2"] <= TOL[qtype][0] and m["cos"] >= TOL[qtype][1], (qtype, m, br.model_info())
+    monkeypatch.delenv("ACE_GGML_DIT_WEIGHT_QTYPE")
+    from tools import export_safetensors_to_gguf as exporter
+    import shutil
+    g = str(tmp_path / "exported")
+    os.makedirs(g)
+    shutil.copy(os.path.join(d, "config.json"), g)
+    exporter.export(os.path.join(d, "model.safetensors"), os.path.join(g, "model.gguf"), qtype)
+    br.load_dit(g)
+    out_g = br.dit_forward_tfirst(inp["hidden_states"], inp["context_latents"], inp["encoder_hidden_states"], None, None, 0.6, 0.6)
+    # same quantised blocks on both loads; the exported file additionally rounds biases / norm weights / proj_in to F16
+    assert metrics(out_g, out)["rel_l2"] <= 2e-3, metrics(out_g, out)
 
 
 @pytest.mark.parametrize("k", [1, 2, 3, 4])

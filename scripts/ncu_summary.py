@@ -1,7 +1,8 @@
 #!/usr/bin/env python
 """Markdown table + roofline_traffic.json from `ncu --set full` reports (read with `ncu -i … --page raw --csv`).
 
-usage: ncu_summary.py <tag> <gemm.ncu-rep> [<attention.ncu-rep>]   -> stdout = markdown; rewrites profiles/roofline_traffic.json
+usage: ncu_summary.py <tag> <gemm.ncu-rep> [<attention.ncu-rep>] [--workload config2]
+       -> stdout = markdown; updates key gemm_bytes_per_launch_<workload> of profiles/roofline_traffic.json
 """
 import csv
 import io
@@ -59,16 +60,26 @@ def table(rep):
 
 
 def main():
+    workload = "config2"
+    if "--workload" in sys.argv:
+        i = sys.argv.index("--workload")
+        workload = sys.argv[i + 1]
+        del sys.argv[i:i + 2]
     tag, gemm_rep = sys.argv[1], sys.argv[2]
     t, traffic = table(gemm_rep)
     print(f"## tap-GEMM launches ({os.path.basename(gemm_rep)})\n\n{t}\n")
     if traffic:
         mean = sum(traffic) / len(traffic)
         print(f"Mean DRAM traffic per launch: {mean / 1e6:.1f} MB over {len(traffic)} launches.\n")
-        json.dump({"gemm_bytes_per_launch": mean, "launches": len(traffic),
-                   "source": f"profiles/r1_ncu_{tag}.md: mean of dram__bytes_read.sum + dram__bytes_write.sum over {len(traffic)} consecutive gemm_tc* "
-                             "launches of `bench.py --steps 2 --warmup 3` (ncu --set full, one transformer layer + neighbours)"},
-                  open(os.path.join(ROOT, "profiles", "roofline_traffic.json"), "w"), indent=1)
+        path = os.path.join(ROOT, "profiles", "roofline_traffic.json")
+        try:
+            doc = json.load(open(path))
+        except Exception:
+            doc = {}
+        doc[f"gemm_bytes_per_launch_{workload}"] = mean
+        doc[f"source_{workload}"] = (f"profiles/{tag}.md: mean of dram__bytes_read.sum + dram__bytes_write.sum over {len(traffic)} consecutive gemm_tc* launches of "
+                                     f"`bench.py --workload {workload} --steps 2 --warmup 3` (ncu --set full)")
+        json.dump(doc, open(path, "w"), indent=1)
     if len(sys.argv) > 3:
         t, _ = table(sys.argv[3])
         print(f"## attention launches ({os.path.basename(sys.argv[3])})\n\n{t}\n")

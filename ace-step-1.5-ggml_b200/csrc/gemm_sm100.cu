@@ -1013,31 +1013,37 @@ constexpr int SMEM2_BYTES = STAGES2 * STAGE2_BYTES + 8 * STG_WARP_BYTES + 2 * 25
 // QUANT variant (packed Q8_0 / Q4_K / Q6_K tiles decoded in shared memory): the pair shape is what makes in-kernel decoding
 // affordable at large M — a CTA decodes ONE 128 x 64 sub-tile per k-block (its half of the weight tile) while the pair's
 // tensor cores spend 512 cycles on it (M = 256 x N = 256), instead of two sub-tiles per 512 cycles in the single-CTA kernel,
-// which ran decode-bound at 1444 cycles per k-block (profiles/r2_quant_trace_d.log).  Two decoder groups of 4 warps take
-// alternate k-blocks (one warp per scheduler decodes at ~0.25 IPC: latency-, not issue-bound), 4 epilogue warps, 14 warps.
+// whose 3-stage ring (48 KB + 17 KB of codes per stage) left the MMA thread waiting 966 of 1444 cycles per k-block
+// (profiles/r2_quant_trace_d.log).
+// Warp budget of the QUANT variants: 14 warps = 12 workers + TMA + MMA.  DEC_GROUPS = 1: 8 epilogue warps + one decoder group
+// (the epilogue keeps the F16 kernel's width; decode must fit the 512-cycle k-block by itself); DEC_GROUPS = 2: 4 epilogue warps
+// + two decoder groups on alternate k-blocks.  NSQ = ring depth: the packed-code slots are sized by the weight type at run time
+// (Q4_K 5120 B, Q6_K 7168 B, Q8_0 8704 B), so Q4_K affords 5 stages next to 8 transpose buffers, the others 4.
 constexpr int NUM_THREADS2Q = 448;
-constexpr int STAGES2Q = 5;
-constexpr int RAW2_BYTES = 8704;  // largest packed tile (Q8_0), 16-byte multiple
-constexpr int RAW2_TOTAL = (STAGES2Q * RAW2_BYTES + 1023) / 1024 * 1024;  // keeps the transpose buffers behind it 1 KB aligned
-constexpr int SMEM2Q_BYTES = STAGES2Q * STAGE2_BYTES + RAW2_TOTAL + 4 * STG_WARP_BYTES + 2 * 256 * 4 + 512;
-static_assert(SMEM2Q_BYTES <= 227 * 1024, "pair QUANT layout exceeds shared memory");
+inline __host__ __device__ int raw2_stride(int tile_bytes) { return (tile_bytes + 127) & ~127; }
+inline __host__ __device__ int raw2_total(int ns, int tile_bytes) { return (ns * raw2_stride(tile_bytes) + 1023) / 1024 * 1024; }
+inline int smem2q_bytes(int ns, int dec_groups, int tile_bytes) {
+    return ns * STAGE2_BYTES + raw2_total(ns, tile_bytes) + (12 - 4 * dec_groups) * STG_WARP_BYTES + 2 * 256 * 4 + 512;
+}
 
-template <bool WARM, bool QUANT>
+template <bool WARM, bool QUANT, int NSQ = 5, int DEC_GROUPS = 2>
 __global__ void __launch_bounds__(QUANT ? NUM_THREADS2Q : NUM_THREADS, 1)
 gemm_tc2_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmOut, const KParams p) {
     constexpr int BN = 256;
     constexpr int TMEM_COLS = 2 * BN;
-    constexpr int NS = QUANT ? STAGES2Q : STAGES2;
-    constexpr int EPI_WARPS = QUANT ? 4 : 8;
+    constexpr int NS = QUANT ? NSQ : STAGES2;
+    constexpr int EPI_WARPS = QUANT ? 12 - 4 * DEC_GROUPS : 8;
     constexpr int NPARTS = EPI_WARPS / 4;
+    constexpr int DEC0 = EPI_WARPS;  // first decoder warp
     constexpr int TMA_WARP = QUANT ? 12 : 8;
     constexpr int MMA_WARP = QUANT ? 13 : 9;
+    const int raw_stride = QUANT ? raw2_stride(p.tile_bytes) : 0;
     extern __shared__ __align__(1024) uint8_t smem[];
     if (threadIdx.x == 0 && (ptx::smem_u32(smem) & 1023u) != 0) __trap();
     uint8_t* sA = smem;                       // [NS][16 KB]
     uint8_t* sB = sA + NS * A_STAGE_BYTES;    // [NS][16 KB]  this CTA's half of the weight tile (fp16 UMMA image)
-    uint8_t* sR = sB + NS * W_SUB_BYTES;      // QUANT: [NS][RAW2_BYTES] packed codes as they land
-    float* sStg = reinterpret_cast<float*>(sR + (QUANT ? RAW2_TOTAL : 0));  // [EPI_WARPS][32 x 32 fp32] epilogue transpose buffers (1 KB aligned:
+    uint8_t* sR = sB + NS * W_SUB_BYTES;      // QUANT: [NS][raw_stride] packed codes as they land
+    float* sStg = reinterpret_cast<float*>(sR + (QUANT ? raw2_total(NS, p.tile_bytes) : 0));  // [EPI_WARPS][32 x 32 fp32] epilogue transpose buffers (1 KB aligned:
                                                                           // they are the 128-byte-swizzle source image of the TMA reduce-add boxes)
     float* sCol = sStg + EPI_WARPS * (STG_WARP_BYTES / 4);  // [2][256]: bias, gate of the current tile
     uint64_t* bars = reinterpret_cast<uint64_t*>(sCol + 2 * 256);
@@ -1120,7 +1126,7 @@ gemm_tc2_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__
                             ptx::mbar_expect_tx(&full[s], A_STAGE_BYTES);
                             ptx::tma_load_3d(sA + s * A_STAGE_BYTES, &tmA, &full[s], kc * BK, row, b);
                             ptx::mbar_expect_tx(&raw_full[s], (uint32_t)p.tile_bytes);
-                            ptx::bulk_load(sR + s * RAW2_BYTES, wptr, p.tile_bytes, &raw_full[s]);
+                            ptx::bulk_load(sR + s * raw_stride, wptr, p.tile_bytes, &raw_full[s]);
                         }
                     } else {
                         if (ptx::elect_one()) {
@@ -1199,24 +1205,24 @@ gemm_tc2_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__
                 }
             }
         }
-    } else if (QUANT && warp >= 4) {
-        // ===================== weight decoders (both CTAs): warps 4..7 take the even k-blocks of the ring, 8..11 the odd ones =====
+    } else if (QUANT && warp >= DEC0) {
+        // ===================== weight decoders (both CTAs): DEC_GROUPS groups of 4 warps on alternate k-blocks of the ring =====
         // thread = one row of the CTA's 128 x 64 sub-tile; the decoded tile is written with generic stores, published to the
         // tensor-core (async) proxy with fence.proxy.async, then counted on full[s] next to the TMA's A box.
-        const int grp = (warp - 4) >> 2;
-        const int row = (int)threadIdx.x - 128 - grp * 128;  // 0..127
+        const int grp = (warp - DEC0) >> 2;
+        const int row = (int)threadIdx.x - DEC0 * 32 - grp * 128;  // 0..127
         uint32_t g = 0;
         for (int t = cluster_id; t < total_tiles; t += n_clusters) {
             int nt, sp, b, l0, kb0, kb1;
             decode_tile_index(t, nt, sp, b, l0);
             k_range(sp, kb0, kb1);
             for (int kb = kb0; kb < kb1; ++kb, ++g) {
-                if ((int)(g & 1u) != grp) continue;
+                if (DEC_GROUPS == 2 && (int)(g & 1u) != grp) continue;
                 const uint32_t s = g % (uint32_t)NS;
                 const uint32_t ph = (g / (uint32_t)NS) & 1u;
                 ptx::mbar_wait(&raw_full[s], ph);
                 ptx::mbar_wait(&empty[s], ph ^ 1);
-                decode_tile(p.wtype, sR + s * RAW2_BYTES, sB + s * W_SUB_BYTES, row);
+                decode_tile(p.wtype, sR + s * raw_stride, sB + s * W_SUB_BYTES, row);
                 ptx::fence_proxy_async_smem();
                 __syncwarp();
                 if (lane == 0) {
@@ -1442,6 +1448,25 @@ bool make_tmap_a(const GemmProblem& g, CUtensorMap* tm, int box_rows = BM) {
     return r == CUDA_SUCCESS;
 }
 
+template <int NSQ, int DG>
+cudaError_t set_tc2q_attr_one() {
+    cudaError_t e = cudaFuncSetAttribute(gemm_tc2_kernel<false, true, NSQ, DG>, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024);
+    if (e == cudaSuccess) e = cudaFuncSetAttribute(gemm_tc2_kernel<true, true, NSQ, DG>, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024);
+    return e;
+}
+cudaError_t set_tc2q_attrs() {
+    cudaError_t e = set_tc2q_attr_one<5, 1>();
+    if (e == cudaSuccess) e = set_tc2q_attr_one<4, 1>();
+    if (e == cudaSuccess) e = set_tc2q_attr_one<5, 2>();
+    if (e == cudaSuccess) e = set_tc2q_attr_one<4, 2>();
+    return e;
+}
+template <int NSQ, int DG>
+cudaError_t launch_tc2q(cudaLaunchConfig_t& cfg, const CUtensorMap& tm, const CUtensorMap& tmo, const KParams& kp) {
+    return kp.warm_epi ? cudaLaunchKernelEx(&cfg, gemm_tc2_kernel<true, true, NSQ, DG>, tm, tmo, kp)
+                       : cudaLaunchKernelEx(&cfg, gemm_tc2_kernel<false, true, NSQ, DG>, tm, tmo, kp);
+}
+
 // co-resident CTA pairs on this device (a GPC with an odd SM count cannot pair its last SM); 0 = pairs unavailable
 int max_active_pairs() {
     static DeviceOnce once;
@@ -1450,8 +1475,7 @@ int max_active_pairs() {
         n = 0;
         if (cudaFuncSetAttribute(gemm_tc2_kernel<false, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, SMEM2_BYTES) == cudaSuccess &&
             cudaFuncSetAttribute(gemm_tc2_kernel<true, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, SMEM2_BYTES) == cudaSuccess &&
-            cudaFuncSetAttribute(gemm_tc2_kernel<false, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, SMEM2Q_BYTES) == cudaSuccess &&
-            cudaFuncSetAttribute(gemm_tc2_kernel<true, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, SMEM2Q_BYTES) == cudaSuccess) {
+            set_tc2q_attrs() == cudaSuccess) {
             cudaLaunchConfig_t cfg = {};
             cfg.gridDim = dim3(2 * 148);
             cfg.blockDim = dim3(NUM_THREADS);
@@ -1466,10 +1490,10 @@ int max_active_pairs() {
             int c = 0;
             if (cudaOccupancyMaxActiveClusters(&c, gemm_tc2_kernel<false, false>, &cfg) == cudaSuccess) n = c;
             else cudaGetLastError();
-            cfg.blockDim = dim3(NUM_THREADS2Q);  // the QUANT variant (more threads, more shared memory) must fit as often
-            cfg.dynamicSmemBytes = SMEM2Q_BYTES;
+            cfg.blockDim = dim3(NUM_THREADS2Q);  // the QUANT variants (more threads, more shared memory) must fit as often
+            cfg.dynamicSmemBytes = 227 * 1024;
             int cq = 0;
-            if (cudaOccupancyMaxActiveClusters(&cq, gemm_tc2_kernel<false, true>, &cfg) == cudaSuccess) n = std::min(n, cq);
+            if (cudaOccupancyMaxActiveClusters(&cq, gemm_tc2_kernel<false, true, 5, 1>, &cfg) == cudaSuccess) n = std::min(n, cq);
             else { cudaGetLastError(); n = 0; }
             if (std::getenv("ACE_B200_DEBUG")) std::fprintf(stderr, "[ace_b200] max active CTA pairs: %d\n", n);
         } else cudaGetLastError();
@@ -1482,8 +1506,13 @@ cudaError_t launch_tc2(const CUtensorMap& tm, const CUtensorMap& tmo, const KPar
     cudaLaunchConfig_t cfg = {};
     const bool quant = kp.wtype != W_F16;
     cfg.gridDim = dim3((unsigned)(2 * clusters));
+    // QUANT variant: one decoder group + 8 epilogue warps by default (ACE_B200_GEMM_QDEC=2: two groups + 4 epilogue warps);
+    // the deepest ring (5, else 4 stages) that fits next to the type's packed-code slots
+    int dec_groups = 1;
+    if (const char* e = std::getenv("ACE_B200_GEMM_QDEC")) dec_groups = std::atoi(e) == 2 ? 2 : 1;
+    const int ns = quant && smem2q_bytes(5, dec_groups, kp.tile_bytes) <= 227 * 1024 ? 5 : 4;
     cfg.blockDim = dim3(quant ? NUM_THREADS2Q : NUM_THREADS);
-    cfg.dynamicSmemBytes = quant ? SMEM2Q_BYTES : SMEM2_BYTES;
+    cfg.dynamicSmemBytes = quant ? smem2q_bytes(ns, dec_groups, kp.tile_bytes) : SMEM2_BYTES;
     cfg.stream = stream;
     cudaLaunchAttribute at[2];
     at[0].id = cudaLaunchAttributeClusterDimension;
@@ -1494,7 +1523,10 @@ cudaError_t launch_tc2(const CUtensorMap& tm, const CUtensorMap& tmo, const KPar
     at[1].val.programmaticStreamSerializationAllowed = 1;
     cfg.attrs = at;
     cfg.numAttrs = pdl_enabled() ? 2 : 1;
-    if (quant) return kp.warm_epi ? cudaLaunchKernelEx(&cfg, gemm_tc2_kernel<true, true>, tm, tmo, kp) : cudaLaunchKernelEx(&cfg, gemm_tc2_kernel<false, true>, tm, tmo, kp);
+    if (quant) {
+        if (dec_groups == 1) return ns == 5 ? launch_tc2q<5, 1>(cfg, tm, tmo, kp) : launch_tc2q<4, 1>(cfg, tm, tmo, kp);
+        return ns == 5 ? launch_tc2q<5, 2>(cfg, tm, tmo, kp) : launch_tc2q<4, 2>(cfg, tm, tmo, kp);
+    }
     return kp.warm_epi ? cudaLaunchKernelEx(&cfg, gemm_tc2_kernel<true, false>, tm, tmo, kp) : cudaLaunchKernelEx(&cfg, gemm_tc2_kernel<false, false>, tm, tmo, kp);
 }
 

@@ -142,6 +142,27 @@ def test_dit_masks_and_tr(br, root):
     assert metrics(out0, ref0)["rel_l2"] <= 5e-3
 
 
+@pytest.mark.parametrize("quant", [None, "Q8_0"])
+def test_dit_outlier_activations(br, root, quant):
+    """operand range (known limit): GEMM operands are fp16 here, fp32 / int8-with-fp32-scale in the reference.  A few
+    latent / context / encoder channels carry |x| ~ 1e4 (the scale of outlier channels in trained transformers, still inside fp16):
+    the residual stream (fp32) then holds outliers the RMSNorms must absorb.  Same tolerance as the ordinary inputs."""
+    need_ref()
+    d = make_dit_dir(root, fx.TOY, 0, quant)
+    T, E = 40, 9
+    inp = fx.dit_inputs(fx.TOY, T, E, seed=31)
+    inp["hidden_states"][:, [3, 17]] *= np.float32(4000.0)
+    inp["context_latents"][:, 5] *= np.float32(2500.0)
+    inp["encoder_hidden_states"][:, [7, 100]] *= np.float32(3000.0)
+    assert 5e3 < np.abs(inp["hidden_states"]).max() < 6e4
+    ref, _ = ref_dit_forward(d, inp, 0.6, 0.6)
+    br.load_dit(d)
+    out = br.dit_forward_tfirst(inp["hidden_states"], inp["context_latents"], inp["encoder_hidden_states"], None, None, 0.6, 0.6)
+    m = metrics(out, ref)
+    assert np.isfinite(out).all()
+    assert m["rel_l2"] <= TOL[quant][0] and m["cos"] >= TOL[quant][1], (quant, m)
+
+
 def test_dit_batched_equals_single(br, root):
     d = make_dit_dir(root, fx.TOY, 0, None)
     br.load_dit(d)

@@ -1015,9 +1015,9 @@ constexpr int SMEM2_BYTES = STAGES2 * STAGE2_BYTES + 8 * STG_WARP_BYTES + 2 * 25
 // tensor cores spend 512 cycles on it (M = 256 x N = 256), instead of two sub-tiles per 512 cycles in the single-CTA kernel,
 // whose 3-stage ring (48 KB + 17 KB of codes per stage) left the MMA thread waiting 966 of 1444 cycles per k-block
 // (profiles/r2_quant_trace_d.log).
-// Warp budget of the QUANT variants: 14 warps = 12 workers + TMA + MMA.  DEC_GROUPS = 1: 8 epilogue warps + one decoder group
-// (the epilogue keeps the F16 kernel's width; decode must fit the 512-cycle k-block by itself); DEC_GROUPS = 2: 4 epilogue warps
-// + two decoder groups on alternate k-blocks.  NSQ = ring depth: the packed-code slots are sized by the weight type at run time
+// Warp budget of the QUANT variants: 14 warps = 12 workers + TMA + MMA.  DEC_GROUPS = 2 (default): 4 epilogue warps + two decoder
+// groups on alternate k-blocks — one group of 4 warps does not finish a 128 x 64 sub-tile inside the 512-cycle k-block (measured);
+// DEC_GROUPS = 1: 8 epilogue warps + one decoder group (A/B variant).  NSQ = ring depth: the packed-code slots are sized by the weight type at run time
 // (Q4_K 5120 B, Q6_K 7168 B, Q8_0 8704 B), so Q4_K affords 5 stages next to 8 transpose buffers, the others 4.
 constexpr int NUM_THREADS2Q = 448;
 inline __host__ __device__ int raw2_stride(int tile_bytes) { return (tile_bytes + 127) & ~127; }
@@ -1506,10 +1506,11 @@ cudaError_t launch_tc2(const CUtensorMap& tm, const CUtensorMap& tmo, const KPar
     cudaLaunchConfig_t cfg = {};
     const bool quant = kp.wtype != W_F16;
     cfg.gridDim = dim3((unsigned)(2 * clusters));
-    // QUANT variant: one decoder group + 8 epilogue warps by default (ACE_B200_GEMM_QDEC=2: two groups + 4 epilogue warps);
-    // the deepest ring (5, else 4 stages) that fits next to the type's packed-code slots
-    int dec_groups = 1;
-    if (const char* e = std::getenv("ACE_B200_GEMM_QDEC")) dec_groups = std::atoi(e) == 2 ? 2 : 1;
+    // QUANT variant: two decoder groups + 4 epilogue warps by default; ACE_B200_GEMM_QDEC=1: one group + 8 epilogue warps (measured
+    // decode-bound: gate_up at M = 12 000 1057 vs 1308 TFLOP/s, profiles/r2_quant_sweep_decgroups_i.log).  Ring: the deepest (5, else 4
+    // stages) that fits next to the type's packed-code slots
+    int dec_groups = 2;
+    if (const char* e = std::getenv("ACE_B200_GEMM_QDEC")) dec_groups = std::atoi(e) == 1 ? 1 : 2;
     const int ns = quant && smem2q_bytes(5, dec_groups, kp.tile_bytes) <= 227 * 1024 ? 5 : 4;
     cfg.blockDim = dim3(quant ? NUM_THREADS2Q : NUM_THREADS);
     cfg.dynamicSmemBytes = quant ? smem2q_bytes(ns, dec_groups, kp.tile_bytes) : SMEM2_BYTES;

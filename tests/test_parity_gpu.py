@@ -81,8 +81,10 @@ def test_dit_online_quantisation_matches_reference(br, root, qtype, monkeypatch,
     exporter.export(os.path.join(d, "model.safetensors"), os.path.join(g, "model.gguf"), qtype)
     br.load_dit(g)
     out_g = br.dit_forward_tfirst(inp["hidden_states"], inp["context_latents"], inp["encoder_hidden_states"], None, None, 0.6, 0.6)
-    # same quantised blocks on both loads; the exported file additionally rounds biases / norm weights / proj_in to F16
-    assert metrics(out_g, out)["rel_l2"] <= 2e-3, metrics(out_g, out)
+    # same quantised blocks for every 2-D weight; they differ where the two rules differ: the exporter leaves the 3-D conv weights
+    # proj_in / proj_out in F16 (last dim = patch size) while the on-line switch quantises proj_out after its relayout to [P*A, H]
+    # (acestep_dit_model.cpp:445-456), and the exported file rounds biases / norm weights to F16
+    assert metrics(out_g, out)["rel_l2"] <= 2e-2, metrics(out_g, out)
 
 
 @pytest.mark.parametrize("k", [1, 2, 3, 4])

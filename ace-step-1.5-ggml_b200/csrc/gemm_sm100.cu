@@ -1019,24 +1019,26 @@ constexpr int SMEM2_BYTES = STAGES2 * STAGE2_BYTES + 8 * STG_WARP_BYTES + 2 * 25
 // groups on alternate k-blocks — one group of 4 warps does not finish a 128 x 64 sub-tile inside the 512-cycle k-block (measured);
 // DEC_GROUPS = 1: 8 epilogue warps + one decoder group (A/B variant).  NSQ = ring depth: the packed-code slots are sized by the weight type at run time
 // (Q4_K 5120 B, Q6_K 7168 B, Q8_0 8704 B), so Q4_K affords 5 stages next to 8 transpose buffers, the others 4.
-constexpr int NUM_THREADS2Q = 448;
 inline __host__ __device__ int raw2_stride(int tile_bytes) { return (tile_bytes + 127) & ~127; }
 inline __host__ __device__ int raw2_total(int ns, int tile_bytes) { return (ns * raw2_stride(tile_bytes) + 1023) / 1024 * 1024; }
-inline int smem2q_bytes(int ns, int dec_groups, int tile_bytes) {
-    return ns * STAGE2_BYTES + raw2_total(ns, tile_bytes) + (12 - 4 * dec_groups) * STG_WARP_BYTES + 2 * 256 * 4 + 512;
+inline int smem2q_bytes(int ns, int epi_warps, int tile_bytes) {
+    return ns * STAGE2_BYTES + raw2_total(ns, tile_bytes) + epi_warps * STG_WARP_BYTES + 2 * 256 * 4 + 512;
 }
+// EPIW = 8 with two decoder groups makes 18 warps (576 threads, 112 registers per thread: the epilogue spills a little more, but
+// twice as many warps share it — the K = 2048 shapes with heavy epilogues (QKV head-norm, SwiGLU) were epilogue-bound with 4)
+constexpr int tc2q_threads(int epiw, int dg) { return (epiw + 4 * dg + 2) * 32; }
 
-template <bool WARM, bool QUANT, int NSQ = 5, int DEC_GROUPS = 2>
-__global__ void __launch_bounds__(QUANT ? NUM_THREADS2Q : NUM_THREADS, 1)
+template <bool WARM, bool QUANT, int NSQ = 5, int DEC_GROUPS = 2, int EPIW = 4>
+__global__ void __launch_bounds__(QUANT ? tc2q_threads(EPIW, DEC_GROUPS) : NUM_THREADS, 1)
 gemm_tc2_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmOut, const KParams p) {
     constexpr int BN = 256;
     constexpr int TMEM_COLS = 2 * BN;
     constexpr int NS = QUANT ? NSQ : STAGES2;
-    constexpr int EPI_WARPS = QUANT ? 12 - 4 * DEC_GROUPS : 8;
+    constexpr int EPI_WARPS = QUANT ? EPIW : 8;
     constexpr int NPARTS = EPI_WARPS / 4;
     constexpr int DEC0 = EPI_WARPS;  // first decoder warp
-    constexpr int TMA_WARP = QUANT ? 12 : 8;
-    constexpr int MMA_WARP = QUANT ? 13 : 9;
+    constexpr int TMA_WARP = QUANT ? EPIW + 4 * DEC_GROUPS : 8;
+    constexpr int MMA_WARP = TMA_WARP + 1;
     const int raw_stride = QUANT ? raw2_stride(p.tile_bytes) : 0;
     extern __shared__ __align__(1024) uint8_t smem[];
     if (threadIdx.x == 0 && (ptx::smem_u32(smem) & 1023u) != 0) __trap();
@@ -1448,23 +1450,26 @@ bool make_tmap_a(const GemmProblem& g, CUtensorMap* tm, int box_rows = BM) {
     return r == CUDA_SUCCESS;
 }
 
-template <int NSQ, int DG>
+template <int NSQ, int DG, int EW>
 cudaError_t set_tc2q_attr_one() {
-    cudaError_t e = cudaFuncSetAttribute(gemm_tc2_kernel<false, true, NSQ, DG>, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024);
-    if (e == cudaSuccess) e = cudaFuncSetAttribute(gemm_tc2_kernel<true, true, NSQ, DG>, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024);
+    cudaError_t e = cudaFuncSetAttribute(gemm_tc2_kernel<false, true, NSQ, DG, EW>, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024);
+    if (e == cudaSuccess) e = cudaFuncSetAttribute(gemm_tc2_kernel<true, true, NSQ, DG, EW>, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024);
     return e;
 }
 cudaError_t set_tc2q_attrs() {
-    cudaError_t e = set_tc2q_attr_one<5, 1>();
-    if (e == cudaSuccess) e = set_tc2q_attr_one<4, 1>();
-    if (e == cudaSuccess) e = set_tc2q_attr_one<5, 2>();
-    if (e == cudaSuccess) e = set_tc2q_attr_one<4, 2>();
+    cudaError_t e = set_tc2q_attr_one<5, 1, 8>();
+    if (e == cudaSuccess) e = set_tc2q_attr_one<4, 1, 8>();
+    if (e == cudaSuccess) e = set_tc2q_attr_one<5, 2, 4>();
+    if (e == cudaSuccess) e = set_tc2q_attr_one<4, 2, 4>();
+    if (e == cudaSuccess) e = set_tc2q_attr_one<5, 2, 8>();
+    if (e == cudaSuccess) e = set_tc2q_attr_one<4, 2, 8>();
     return e;
 }
-template <int NSQ, int DG>
+template <int NSQ, int DG, int EW>
 cudaError_t launch_tc2q(cudaLaunchConfig_t& cfg, const CUtensorMap& tm, const CUtensorMap& tmo, const KParams& kp) {
-    return kp.warm_epi ? cudaLaunchKernelEx(&cfg, gemm_tc2_kernel<true, true, NSQ, DG>, tm, tmo, kp)
-                       : cudaLaunchKernelEx(&cfg, gemm_tc2_kernel<false, true, NSQ, DG>, tm, tmo, kp);
+    cfg.blockDim = dim3(tc2q_threads(EW, DG));
+    return kp.warm_epi ? cudaLaunchKernelEx(&cfg, gemm_tc2_kernel<true, true, NSQ, DG, EW>, tm, tmo, kp)
+                       : cudaLaunchKernelEx(&cfg, gemm_tc2_kernel<false, true, NSQ, DG, EW>, tm, tmo, kp);
 }
 
 // co-resident CTA pairs on this device (a GPC with an odd SM count cannot pair its last SM); 0 = pairs unavailable
@@ -1490,10 +1495,10 @@ int max_active_pairs() {
             int c = 0;
             if (cudaOccupancyMaxActiveClusters(&c, gemm_tc2_kernel<false, false>, &cfg) == cudaSuccess) n = c;
             else cudaGetLastError();
-            cfg.blockDim = dim3(NUM_THREADS2Q);  // the QUANT variants (more threads, more shared memory) must fit as often
+            cfg.blockDim = dim3(tc2q_threads(8, 2));  // the QUANT variants (more threads, more shared memory) must fit as often
             cfg.dynamicSmemBytes = 227 * 1024;
             int cq = 0;
-            if (cudaOccupancyMaxActiveClusters(&cq, gemm_tc2_kernel<false, true, 5, 1>, &cfg) == cudaSuccess) n = std::min(n, cq);
+            if (cudaOccupancyMaxActiveClusters(&cq, gemm_tc2_kernel<false, true, 5, 2, 8>, &cfg) == cudaSuccess) n = std::min(n, cq);
             else { cudaGetLastError(); n = 0; }
             if (std::getenv("ACE_B200_DEBUG")) std::fprintf(stderr, "[ace_b200] max active CTA pairs: %d\n", n);
         } else cudaGetLastError();
@@ -1509,11 +1514,13 @@ cudaError_t launch_tc2(const CUtensorMap& tm, const CUtensorMap& tmo, const KPar
     // QUANT variant: two decoder groups + 4 epilogue warps by default; ACE_B200_GEMM_QDEC=1: one group + 8 epilogue warps (measured
     // decode-bound: gate_up at M = 12 000 1057 vs 1308 TFLOP/s, profiles/r2_quant_sweep_decgroups_i.log).  Ring: the deepest (5, else 4
     // stages) that fits next to the type's packed-code slots
-    int dec_groups = 2;
+    int dec_groups = 2, epi_warps = 4;
     if (const char* e = std::getenv("ACE_B200_GEMM_QDEC")) dec_groups = std::atoi(e) == 1 ? 1 : 2;
-    const int ns = quant && smem2q_bytes(5, dec_groups, kp.tile_bytes) <= 227 * 1024 ? 5 : 4;
-    cfg.blockDim = dim3(quant ? NUM_THREADS2Q : NUM_THREADS);
-    cfg.dynamicSmemBytes = quant ? smem2q_bytes(ns, dec_groups, kp.tile_bytes) : SMEM2_BYTES;
+    if (const char* e = std::getenv("ACE_B200_GEMM_QEPI")) epi_warps = std::atoi(e) == 8 ? 8 : 4;
+    if (dec_groups == 1) epi_warps = 8;
+    const int ns = quant && smem2q_bytes(5, epi_warps, kp.tile_bytes) <= 227 * 1024 ? 5 : 4;
+    cfg.blockDim = dim3(NUM_THREADS);
+    cfg.dynamicSmemBytes = quant ? smem2q_bytes(ns, epi_warps, kp.tile_bytes) : SMEM2_BYTES;
     cfg.stream = stream;
     cudaLaunchAttribute at[2];
     at[0].id = cudaLaunchAttributeClusterDimension;
@@ -1525,8 +1532,9 @@ cudaError_t launch_tc2(const CUtensorMap& tm, const CUtensorMap& tmo, const KPar
     cfg.attrs = at;
     cfg.numAttrs = pdl_enabled() ? 2 : 1;
     if (quant) {
-        if (dec_groups == 1) return ns == 5 ? launch_tc2q<5, 1>(cfg, tm, tmo, kp) : launch_tc2q<4, 1>(cfg, tm, tmo, kp);
-        return ns == 5 ? launch_tc2q<5, 2>(cfg, tm, tmo, kp) : launch_tc2q<4, 2>(cfg, tm, tmo, kp);
+        if (dec_groups == 1) return ns == 5 ? launch_tc2q<5, 1, 8>(cfg, tm, tmo, kp) : launch_tc2q<4, 1, 8>(cfg, tm, tmo, kp);
+        if (epi_warps == 8) return ns == 5 ? launch_tc2q<5, 2, 8>(cfg, tm, tmo, kp) : launch_tc2q<4, 2, 8>(cfg, tm, tmo, kp);
+        return ns == 5 ? launch_tc2q<5, 2, 4>(cfg, tm, tmo, kp) : launch_tc2q<4, 2, 4>(cfg, tm, tmo, kp);
     }
     return kp.warm_epi ? cudaLaunchKernelEx(&cfg, gemm_tc2_kernel<true, false>, tm, tmo, kp) : cudaLaunchKernelEx(&cfg, gemm_tc2_kernel<false, false>, tm, tmo, kp);
 }

@@ -1514,7 +1514,12 @@ cudaError_t launch_tc2(const CUtensorMap& tm, const CUtensorMap& tmo, const KPar
     // QUANT variant: two decoder groups + 4 epilogue warps by default; ACE_B200_GEMM_QDEC=1: one group + 8 epilogue warps (measured
     // decode-bound: gate_up at M = 12 000 1057 vs 1308 TFLOP/s, profiles/r2_quant_sweep_decgroups_i.log).  Ring: the deepest (5, else 4
     // stages) that fits next to the type's packed-code slots
-    int dec_groups = 2, epi_warps = 4;
+    // Epilogue width: 8 warps (18-warp CTA, 96 registers) where the epilogue is the critical resource — the head-norm epilogue of
+    // the Q/K/V projections, and launches of <= 6144 rows where few tiles per cluster leave it exposed — else 4 warps (14-warp CTA,
+    // 128 registers).  Measured per shape: profiles/r2_quant_sweep_epi_j.log (QKV +7..16 %, M = 3000 o-proj / down +13..20 %,
+    // gate_up at M = 12 000 -5 %).  ACE_B200_GEMM_QEPI=4/8 forces one.
+    int dec_groups = 2;
+    int epi_warps = (kp.epi.mode == EPI_HEADNORM || (long)kp.B * kp.l_out <= 6144) ? 8 : 4;
     if (const char* e = std::getenv("ACE_B200_GEMM_QDEC")) dec_groups = std::atoi(e) == 1 ? 1 : 2;
     if (const char* e = std::getenv("ACE_B200_GEMM_QEPI")) epi_warps = std::atoi(e) == 8 ? 8 : 4;
     if (dec_groups == 1) epi_warps = 8;

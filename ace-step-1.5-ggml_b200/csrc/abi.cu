@@ -207,6 +207,9 @@ ace_ggml_status sample_latents_device(ace_ggml_context* ctx, const float* noise,
     o.has_enc_mask = enc_mask != nullptr && E > 0;
     ws.cross_kv_valid = false;
     std::vector<float> tt((size_t)2 * EB);
+    // time embeddings of the whole schedule in one pass (every sample of the batch shares the step's t; t_r == t)
+    const bool sched_ok = !env_on("ACE_B200_NO_SCHED_TEMB") && dit_time_embed_schedule(ctx->dit, ws, schedule, n_steps, st) == cudaSuccess;
+    if (!sched_ok) cudaGetLastError();
     cudaEventRecord(ctx->ev0, st);
     for (int i = 0; i < n_steps; ++i) {
         const float t = schedule[i];
@@ -219,6 +222,7 @@ ace_ggml_status sample_latents_device(ace_ggml_context* ctx, const float* noise,
         chk(cudaMemcpyAsync(ws.d_hidden, ctx->d_x, n_lat * 4, cudaMemcpyDeviceToDevice, st));
         if (cfg) chk(cudaMemcpyAsync(ws.d_hidden + n_lat, ctx->d_x, n_lat * 4, cudaMemcpyDeviceToDevice, st));
         o.reuse_cross_kv = i > 0;  // condition_embedder output and cross K/V do not depend on the step
+        o.sched_step = sched_ok ? i : -1;
         chk(dit_forward_device(ctx->dit, ws, EB, T, E, ctx->d_v, o, st));
         const float dt = (i == n_steps - 1) ? t : (t - schedule[i + 1]);
         launch_euler_step(ctx->d_x, ctx->d_v, cfg ? ctx->d_v + n_lat : nullptr, guidance, dt, (long)n_lat, st);

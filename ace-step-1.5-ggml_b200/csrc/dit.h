@@ -86,6 +86,11 @@ struct DitWorkspace {
     float* x = nullptr;
     __half *tfreq = nullptr, *th1 = nullptr, *th2 = nullptr;
     float *temb = nullptr, *temb_r = nullptr, *tproj = nullptr, *mod = nullptr, *out_mod = nullptr;
+    // schedule-wide time embeddings (device-resident sampler): [n_steps, H], [n_steps, H], [n_steps, 6H]
+    float *sched_temb = nullptr, *sched_temb_r = nullptr, *sched_tproj = nullptr;
+    __half *sched_freq = nullptr, *sched_h1 = nullptr, *sched_h2 = nullptr;
+    float* sched_t = nullptr;
+    int sched_cap = 0;
     float2* rope = nullptr;
     int rope_len = 0;
     bool cross_kv_valid = false;  // set by the device-resident sampler to reuse step-invariant K/V
@@ -97,10 +102,18 @@ struct DitForwardOpts {
     int max_layers = 0;           // 0 = all (ACE_GGML_DIT_MAX_LAYERS, acestep_dit_model.cpp:1457-1464)
     bool reuse_cross_kv = false;  // skip condition_embedder + cross K/V projection (cached from a previous call)
     bool has_mask = false, has_enc_mask = false;
+    // time embeddings precomputed for the whole schedule (dit_time_embed_schedule): row `step` of ws.sched_* is this call's, shared
+    // by every sample of the batch; the six M = 1 GEMVs are then skipped
+    int sched_step = -1;
 };
 
 // grows `ws` to hold (B, T, E); returns false + err on allocation failure
 bool dit_workspace_reserve(const DitModel& m, DitWorkspace& ws, int B, int T, int E, std::string& err);
+
+// Time-embedding MLPs of a whole schedule in one pass (every caller of the sampler has timestep_r == timestep, so the second embedder
+// sees 0 at every step): the six weight-streaming M = 1 GEMVs per step become six launches with M = n_steps rows before the loop.
+// t_host: [n_steps] timesteps.  reference: acestep_dit_model.cpp:1286-1308, 1420-1424
+cudaError_t dit_time_embed_schedule(const DitModel& m, DitWorkspace& ws, const float* t_host, int n_steps, cudaStream_t st);
 
 // Batched forward on device-resident inputs already placed in ws.d_hidden [B,T,A], ws.d_context [B,T,ctx],
 // ws.d_enc [B,E,H], ws.d_mask [B,T], ws.d_enc_mask [B,E], ws.d_t [2,B]. Writes velocity to `out` [B,T,A] (device).

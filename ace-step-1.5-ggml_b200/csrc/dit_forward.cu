@@ -105,7 +105,66 @@ struct Fwd {
     }
 };
 
+// both embedders (t, then t - t_r) on `rows` rows of sinusoidal features laid out [2, rows, 256]: temb / temb_r [rows, H], tproj = sum
+void time_embed_rows(Fwd& f, const __half* freq, __half* h1, __half* h2, float* temb, float* temb_r, float* tproj, int rows) {
+    const DitModel& m = f.m;
+    const int H = m.cfg.hidden_size;
+    for (int which = 0; which < 2; ++which) {
+        const DitTimeEmbed& te = which == 0 ? m.te : m.te_r;
+        GemmEpilogue e1;
+        e1.bias = te.b1;
+        e1.out_f16 = h1;
+        e1.silu_f16 = 1;
+        e1.ld_out = H;
+        f.gemm(freq + (size_t)which * rows * 256, 256, 1, rows, te.w1, e1, false);
+        GemmEpilogue e2;
+        e2.bias = te.b2;
+        e2.out_f32 = which == 0 ? temb : temb_r;
+        e2.out_f16 = h2;
+        e2.silu_f16 = 1;
+        e2.ld_out = H;
+        f.gemm(h1, H, 1, rows, te.w2, e2, false);
+        GemmEpilogue e3;
+        e3.bias = te.b_proj;
+        e3.out_f32 = tproj;
+        e3.resid = which == 0 ? nullptr : tproj;  // proj = proj_t + proj_r
+        e3.ld_out = 6 * H;
+        f.gemm(h2, H, 1, rows, te.w_proj, e3, false);
+    }
+}
+
 }  // namespace
+
+cudaError_t dit_time_embed_schedule(const DitModel& m, DitWorkspace& ws, const float* t_host, int n_steps, cudaStream_t st) {
+    const int H = m.cfg.hidden_size;
+    if (n_steps > ws.sched_cap) {
+        // grown separately from the (B, T, E) workspace: freed with it
+        auto alloc = [&](auto*& ptr, size_t count) {
+            void* p = nullptr;
+            if (cudaMalloc(&p, count * sizeof(*ptr) + 64) != cudaSuccess) return false;
+            ws.allocs.push_back(p);
+            ptr = reinterpret_cast<decltype(ptr)>(p);
+            return true;
+        };
+        const size_t n = (size_t)n_steps;
+        if (!alloc(ws.sched_temb, n * H) || !alloc(ws.sched_temb_r, n * H) || !alloc(ws.sched_tproj, n * 6 * H) || !alloc(ws.sched_freq, 2 * n * 256) ||
+            !alloc(ws.sched_h1, n * H) || !alloc(ws.sched_h2, n * H) || !alloc(ws.sched_t, 2 * n)) {
+            ws.sched_cap = 0;
+            return cudaErrorMemoryAllocation;
+        }
+        ws.sched_cap = n_steps;
+    }
+    std::vector<float> tt((size_t)2 * n_steps, 0.f);  // [t_0 .. t_{n-1} | 0 .. 0]: timestep_r == timestep in every caller
+    for (int i = 0; i < n_steps; ++i) tt[(size_t)i] = t_host[i];
+    cudaError_t e = cudaMemcpyAsync(ws.sched_t, tt.data(), tt.size() * 4, cudaMemcpyHostToDevice, st);
+    if (e != cudaSuccess) return e;
+    e = cudaStreamSynchronize(st);  // `tt` is pageable and goes out of scope
+    if (e != cudaSuccess) return e;
+    launch_timestep_features(ws.sched_t, ws.sched_freq, 2 * n_steps, st);
+    Fwd f{m, ws, st, cudaSuccess, device_sm_count()};
+    time_embed_rows(f, ws.sched_freq, ws.sched_h1, ws.sched_h2, ws.sched_temb, ws.sched_temb_r, ws.sched_tproj, n_steps);
+    return f.rc != cudaSuccess ? f.rc : cudaGetLastError();
+}
 
 cudaError_t dit_forward_device(const DitModel& m, DitWorkspace& ws, int B, int T, int E, float* out,
                                const DitForwardOpts& opts, cudaStream_t st) {
@@ -130,31 +189,15 @@ cudaError_t dit_forward_device(const DitModel& m, DitWorkspace& ws, int B, int T
     launch_pack_dit_input(ws.d_hidden, ws.d_context, ws.x0, B, T, S, P, ctx, A, st);
     launch_patch_mask(opts.has_mask ? ws.d_mask : nullptr, ws.d_pmask, B, T, S, P, st);
     // ---- timestep embeddings -> AdaLN tables   (M = B rows; HBM-bound GEMVs through the same kernel)
-    launch_timestep_features(ws.d_t, ws.tfreq, 2 * B, st);
-    for (int which = 0; which < 2; ++which) {
-        const DitTimeEmbed& te = which == 0 ? m.te : m.te_r;
-        float* temb = which == 0 ? ws.temb : ws.temb_r;
-        GemmEpilogue e1;
-        e1.bias = te.b1;
-        e1.out_f16 = ws.th1;
-        e1.silu_f16 = 1;
-        e1.ld_out = H;
-        f.gemm(ws.tfreq + (size_t)which * B * 256, 256, 1, B, te.w1, e1, false);
-        GemmEpilogue e2;
-        e2.bias = te.b2;
-        e2.out_f32 = temb;
-        e2.out_f16 = ws.th2;
-        e2.silu_f16 = 1;
-        e2.ld_out = H;
-        f.gemm(ws.th1, H, 1, B, te.w2, e2, false);
-        GemmEpilogue e3;
-        e3.bias = te.b_proj;
-        e3.out_f32 = ws.tproj;
-        e3.resid = which == 0 ? nullptr : ws.tproj;  // proj = proj_t + proj_r
-        e3.ld_out = 6 * H;
-        f.gemm(ws.th2, H, 1, B, te.w_proj, e3, false);
+    if (opts.sched_step >= 0 && opts.sched_step < ws.sched_cap) {
+        const size_t r = (size_t)opts.sched_step;
+        launch_build_modulation(m.layer_tables, ws.sched_tproj + r * 6 * H, ws.mod, m.out_table, ws.sched_temb + r * H, ws.sched_temb_r + r * H,
+                                ws.out_mod, B, layers_all, H, st, /*shared_t=*/true);
+    } else {
+        launch_timestep_features(ws.d_t, ws.tfreq, 2 * B, st);
+        time_embed_rows(f, ws.tfreq, ws.th1, ws.th2, ws.temb, ws.temb_r, ws.tproj, B);
+        launch_build_modulation(m.layer_tables, ws.tproj, ws.mod, m.out_table, ws.temb, ws.temb_r, ws.out_mod, B, layers_all, H, st);
     }
-    launch_build_modulation(m.layer_tables, ws.tproj, ws.mod, m.out_table, ws.temb, ws.temb_r, ws.out_mod, B, layers_all, H, st);
     const long mod_bs = (long)layers_all * 6 * H;
 
     // ---- patch-embed and condition embedder.  They run AFTER the modulation tables on purpose: rmsnorm_mod reads its scale /

@@ -83,7 +83,7 @@ __global__ void timestep_features_kernel(const float* __restrict__ t, __half* __
 __global__ void build_modulation_kernel(const float* __restrict__ tables, const float* __restrict__ proj,
                                         float* __restrict__ mod, const float* __restrict__ out_table,
                                         const float* __restrict__ temb_a, const float* __restrict__ temb_b,
-                                        float* __restrict__ out_mod, int B, int layers, int H) {
+                                        float* __restrict__ out_mod, int B, int layers, int H, long t_bstride) {
     const long n_mod = (long)B * layers * 6 * H;
     const long n_out = (long)B * 2 * H;
     const long idx = (long)blockIdx.x * blockDim.x + threadIdx.x;
@@ -94,7 +94,7 @@ __global__ void build_modulation_kernel(const float* __restrict__ tables, const 
         r /= 6;
         const int layer = (int)(r % layers);
         const int b = (int)(r / layers);
-        float v = tables[((long)layer * 6 + j) * H + c] + proj[((long)b * 6 + j) * H + c];
+        float v = tables[((long)layer * 6 + j) * H + c] + proj[(long)b * 6 * t_bstride + (long)j * H + c];
         if (j == 1 || j == 4) v += 1.0f;
         mod[idx] = v;
     } else if (idx < n_mod + n_out) {
@@ -102,7 +102,7 @@ __global__ void build_modulation_kernel(const float* __restrict__ tables, const 
         const int c = (int)(k % H);
         const int j = (int)((k / H) % 2);
         const int b = (int)(k / (2 * H));
-        float v = out_table[(long)j * H + c] + temb_a[(long)b * H + c] + (temb_b ? temb_b[(long)b * H + c] : 0.f);
+        float v = out_table[(long)j * H + c] + temb_a[(long)b * t_bstride + c] + (temb_b ? temb_b[(long)b * t_bstride + c] : 0.f);
         if (j == 1) v += 1.0f;
         out_mod[k] = v;
     }
@@ -406,12 +406,12 @@ void launch_timestep_features(const float* t, __half* out, int n, cudaStream_t s
 }
 void launch_build_modulation(const float* tables, const float* proj, float* mod, const float* out_table,
                              const float* temb_a, const float* temb_b, float* out_mod, int B, int layers, int H,
-                             cudaStream_t st) {
+                             cudaStream_t st, bool shared_t) {
     note_launch();
     const long total = (long)B * layers * 6 * H + (long)B * 2 * H;
     ProfScope prof_scope(PROF_ELEM, 0.0, total * 4.0 + ((double)layers * 6 * H + 2.0 * H + 8.0 * B * H) * 4.0, st);
     build_modulation_kernel<<<blocks_for(total, 256), 256, 0, st>>>(tables, proj, mod, out_table, temb_a, temb_b, out_mod,
-                                                                    B, layers, H);
+                                                                    B, layers, H, shared_t ? 0L : (long)H);
 }
 void launch_rmsnorm_mod(const float* x, const float* w, const float* scale1, const float* shift, long mod_bstride,
                         __half* y, int B, int rows_per_b, int H, float eps, cudaStream_t st, float* y32, bool early_mod) {

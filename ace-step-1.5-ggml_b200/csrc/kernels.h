@@ -104,7 +104,8 @@ void launch_timestep_features(const float* t, __half* out, int n, cudaStream_t s
 // reference: acestep_dit_model.cpp:1469-1481, 1522-1526, 1537-1549
 void launch_build_modulation(const float* tables /*[layers,6,H]*/, const float* proj /*[B,6,H]*/, float* mod,
                              const float* out_table /*[2,H]*/, const float* temb_a, const float* temb_b,
-                             float* out_mod /*[B,2,H]*/, int B, int layers, int H, cudaStream_t st);
+                             float* out_mod /*[B,2,H]*/, int B, int layers, int H, cudaStream_t st, bool shared_t = false);
+// shared_t: every sample of the batch is at the same timestep, proj / temb_a / temb_b hold ONE row that all B samples read
 
 // ---- normalisation -------------------------------------------------------------------------------
 // y = fp16( x / sqrt(mean(x^2)+eps) * w * scale1[b] + shift[b] );  scale1/shift may be null (plain RMSNorm)

@@ -42,6 +42,7 @@ struct KParams {
     int  tap_stride, tap_offset;
     int  B, l_out, m_tiles_per_b;
     int  split_k;
+    int  band_m;                 // tile rasterisation: row tiles per band (see tile_coords); >= m_tiles = one band = column-major order
     GemmEpilogue epi;
     int  tma_reduce;             // accumulate epilogue goes out as TMA reduce-add tiles through tmOut
     int  slab_rows;              // SLAB kernel: rows of the activation slab of one tile = 128 + (taps-1) * tap_stride
@@ -55,6 +56,23 @@ enum { TR_START = 0, TR_SETUP = 1, TR_FIRST_FULL = 2, TR_LAST_MMA = 3, TR_ACC_RE
        TR_T8_MMA_WAIT = 9, TR_T8_MMA_GO = 10, TR_T8_MMA_DONE = 11, TR_T8_EPI_WAIT = 12, TR_T8_EPI_GO = 13, TR_T8_EPI_DONE = 14, TR_N = 16 };  // T8_*: the CTA's 9th tile (steady state)
 __device__ __forceinline__ void trace_stamp(const KParams& p, int slot) {
     if (p.trace) p.trace[(size_t)blockIdx.x * TR_N + slot] = clock64();
+}
+
+// Tile rasterisation.  Work item t -> (row tile mt, K split sp, weight tile nt).  Row tiles are grouped in BANDS of band_m: inside a
+// band the order is row tile fastest, then split, then weight tile, so the CTAs of a wave share one weight tile and walk the band's
+// rows, and the NEXT wave re-reads the SAME activation rows against the next weight tile while they are still in L2.  Without
+// bands (one band = all rows) a GEMM whose activations exceed the 126 MB L2 re-streams them from HBM once per weight tile: ncu
+// showed 7.5 GB of DRAM reads for the 211 MB of operands of the MLP up-projection at M = 48 000 (profiles/r2_ncu_gemm_config2_k.md).
+__device__ __forceinline__ void tile_coords(int t, int m_tiles, int band_m, int nt_sk, int split_k, int& mt, int& sp, int& nt) {
+    const int per_band = band_m * nt_sk;
+    const int band = t / per_band;
+    const int m0 = band * band_m;
+    const int bm = min(band_m, m_tiles - m0);   // only the last band can be short
+    const int r = t - band * per_band;
+    mt = m0 + r % bm;
+    const int rest = r / bm;
+    sp = rest % split_k;
+    nt = rest / split_k;
 }
 
 template <int BN, bool QUANT>
@@ -667,10 +685,8 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
     if (threadIdx.x == 0) trace_stamp(p, TR_SETUP);
 
     auto decode_tile_index = [&](int t, int& nt, int& sp, int& b, int& l0) {
-        const int mt = t % m_tiles;
-        const int rest = t / m_tiles;
-        sp = rest % p.split_k;
-        nt = rest / p.split_k;
+        int mt;
+        tile_coords(t, m_tiles, p.band_m, n_tiles * p.split_k, p.split_k, mt, sp, nt);
         b = mt / p.m_tiles_per_b;
         l0 = (mt % p.m_tiles_per_b) * BM;
     };
@@ -1094,10 +1110,8 @@ gemm_tc2_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__
     ptx::pdl_launch();
 
     auto decode_tile_index = [&](int t, int& nt, int& sp, int& b, int& l0) {
-        const int mt = t % m_tiles;
-        const int rest = t / m_tiles;
-        sp = rest % p.split_k;
-        nt = rest / p.split_k;
+        int mt;
+        tile_coords(t, m_tiles, p.band_m, n_tiles * p.split_k, p.split_k, mt, sp, nt);
         b = mt / m_pairs_per_b;
         l0 = (mt % m_pairs_per_b) * (2 * BM) + (int)rank * BM;  // this CTA's 128 rows
     };
@@ -1700,6 +1714,16 @@ cudaError_t gemm_launch(const GemmProblem& g, cudaStream_t stream, bool simt) {
     }
     if (sk > 1 && !accumulate) return cudaErrorInvalidValue;
     kp.split_k = std::min(sk, kp.kb_total);
+    {  // bands of row tiles whose activations (~32 MB) stay L2-resident across the weight tiles (tile_coords); ACE_B200_GEMM_BAND_MB=0: off
+        double band_mb = 32.0;
+        if (const char* eb = std::getenv("ACE_B200_GEMM_BAND_MB")) band_mb = std::atof(eb);
+        const int mt_all = pair ? m_pairs : m_tiles;
+        const double tile_bytes_a = (double)(pair ? 2 * BM : BM) * g.C * 2.0;
+        long bm = band_mb > 0 ? (long)(band_mb * 1048576.0 / tile_bytes_a) : (long)mt_all;
+        // (a band may be narrower than a wave: the wave then spans several weight tiles of the same rows, all L2 hits; the weights
+        // themselves — <= 50 MB per matrix — stay L2-resident next to the band)
+        kp.band_m = (int)std::max<long>(2, std::min<long>(bm, mt_all));
+    }
     {  // the dry-run epilogue pass pays off only where a CTA runs a handful of tiles (it costs one extra epilogue per CTA)
         const long work_tiles = tiles_nosplit * kp.split_k;
         kp.warm_epi = work_tiles <= 4L * units ? 1 : 0;

@@ -85,7 +85,7 @@ def test_dit_online_quantisation_matches_reference(br, root, qtype, monkeypatch,
     # proj_in / proj_out in F16 (last dim = patch size) while the on-line switch quantises proj_out after its relayout to [P*A, H]
     # (acestep_dit_model.cpp:445-456), and the exported file rounds biases / norm weights to F16
     # (Q4_K / Q6_K error of proj_out alone — the last projection — is 2-7 % of the output, so the bound is the quantisation's own)
-    assert metrics(out_g, out)["rel_l2"] <= {"Q8_0": 5e-3, "Q6_K": 3e-2, "Q4_K": 1.5e-1}[qtype], metrics(out_g, out)
+    assert metrics(out_g, out)["rel_l2"] <= {"Q8_0": 2e-2, "Q6_K": 3e-2, "Q4_K": 1.5e-1}[qtype], metrics(out_g, out)
 
 
 @pytest.mark.parametrize("k", [1, 2, 3, 4])

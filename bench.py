@@ -307,17 +307,25 @@ def run_dit_workload(a, wl, world, rank, local, dist):
     for i in range(2):
         br.dit_forward_batched(hid2, ctx2, enc2, None, None, one, one, out=vout)
     barrier()
+    # host side of a step (what the caller's pipeline does between two library calls): CFG combine + Euler update, on torch CPU views
+    # of the pinned buffers (multi-threaded, in place)
+    t_hid, t_v = torch.from_numpy(hid2), torch.from_numpy(vout)
+    t_x = torch.from_numpy(noise.copy())
+    t_tmp = torch.empty_like(t_x)
     t0 = time.perf_counter()
-    x = noise.copy()
     for i in range(a.steps):
-        hid2[:B] = x
+        t_hid[:B].copy_(t_x)
         if wl["cfg"]:
-            hid2[B:] = x
+            t_hid[B:].copy_(t_x)
         t = float(sched[i])
         br.dit_forward_batched(hid2, ctx2, enc2, None, None, one * t, one * t, out=vout)
-        v = vout[B:] + np.float32(g) * (vout[:B] - vout[B:]) if wl["cfg"] else vout
-        dt = sched[i] if i == a.steps - 1 else sched[i] - sched[i + 1]
-        x = x - v * np.float32(dt)
+        dt = float(sched[i] if i == a.steps - 1 else sched[i] - sched[i + 1])
+        if wl["cfg"]:  # v = v_u + g (v_c - v_u)
+            torch.sub(t_v[:B], t_v[B:], out=t_tmp)
+            t_tmp.mul_(g).add_(t_v[B:])
+            t_x.sub_(t_tmp, alpha=dt)
+        else:
+            t_x.sub_(t_v, alpha=dt)
     barrier()
     e2e_ms = (time.perf_counter() - t0) * 1e3
     clocks = sampler.stop()

@@ -63,7 +63,28 @@ ace_ggml_status dit_forward_impl(ace_ggml_context* ctx, const float* hidden, con
     std::string err;
     if (!dit_workspace_reserve(ctx->dit, ctx->dws, B, T, E, err)) return set_error(ctx, ACE_GGML_ERR, err);
     const auto t_init = Clock::now();
-    ace_ggml_status s = stage_dit_inputs(ctx, hidden, context, enc, mask, enc_mask, B, T, E);
+    // step-invariant conditioning: same bytes as the previous call -> keep the device copies and the cached cross K/V
+    DitForwardOpts o;
+    o.max_layers = env_max_layers();
+    const size_t enc_n = (size_t)B * E * c.hidden_size;
+    bool same_cond = E > 0 && enc != nullptr && ctx->dws.cross_kv_valid && ctx->enc_cache_B == B && ctx->enc_cache_E == E &&
+                     ctx->enc_cache_layers == o.max_layers && ctx->enc_cache.size() == enc_n && ctx->enc_cache_has_mask == (enc_mask != nullptr) &&
+                     !env_on("ACE_B200_NO_COND_CACHE");
+    if (same_cond) same_cond = std::memcmp(ctx->enc_cache.data(), enc, enc_n * 4) == 0;
+    if (same_cond && enc_mask) same_cond = std::memcmp(ctx->enc_mask_cache.data(), enc_mask, (size_t)B * E * 4) == 0;
+    if (!same_cond) {
+        ctx->dws.cross_kv_valid = false;
+        ctx->enc_cache_B = 0;
+        if (E > 0 && enc != nullptr && !env_on("ACE_B200_NO_COND_CACHE")) {
+            ctx->enc_cache.assign(enc, enc + enc_n);
+            if (enc_mask) ctx->enc_mask_cache.assign(enc_mask, enc_mask + (size_t)B * E);
+            ctx->enc_cache_has_mask = enc_mask != nullptr;
+            ctx->enc_cache_B = B;
+            ctx->enc_cache_E = E;
+            ctx->enc_cache_layers = o.max_layers;
+        }
+    }
+    ace_ggml_status s = stage_dit_inputs(ctx, hidden, context, same_cond ? nullptr : enc, mask, same_cond ? nullptr : enc_mask, B, T, same_cond ? 0 : E);
     if (s != ACE_GGML_OK) return s;
     std::vector<float> tt((size_t)2 * B);
     for (int b = 0; b < B; ++b) {
@@ -72,10 +93,9 @@ ace_ggml_status dit_forward_impl(ace_ggml_context* ctx, const float* hidden, con
     }
     cudaError_t e = cudaMemcpyAsync(ctx->dws.d_t, tt.data(), tt.size() * 4, cudaMemcpyHostToDevice, ctx->stream);
     if (e != cudaSuccess) return cuda_fail(ctx, "timestep upload failed", e);
-    DitForwardOpts o;
-    o.max_layers = env_max_layers();
     o.has_mask = mask != nullptr;
     o.has_enc_mask = enc_mask != nullptr && E > 0;
+    o.reuse_cross_kv = same_cond;
     cudaEventRecord(ctx->ev0, ctx->stream);
     e = dit_forward_device(ctx->dit, ctx->dws, B, T, E, ctx->dws.d_out, o, ctx->stream);
     cudaEventRecord(ctx->ev1, ctx->stream);

@@ -61,6 +61,13 @@ struct ace_ggml_context {
     std::string last_error;
     std::string info;
     double last_device_ms = 0.0;
+    // conditioning of the previous ace_ggml_dit_forward call (host copy): a sampler that drives the single-call ABI passes the SAME
+    // encoder states at every step, so an identical (bytes, mask, shape, depth) call skips the 4 MB upload and the step-invariant
+    // condition_embedder + 24 cross-K/V GEMMs (the reference recomputes them every step: acestep_dit_model.cpp:1412, 1195-1196)
+    std::vector<float> enc_cache;
+    std::vector<int32_t> enc_mask_cache;
+    int enc_cache_B = 0, enc_cache_E = 0, enc_cache_layers = -1;
+    bool enc_cache_has_mask = false;
     // sampler scratch
     float* d_x = nullptr;   // [B, T, A] latents being integrated
     float* d_v = nullptr;   // [2B, T, A] velocities

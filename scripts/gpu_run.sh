@@ -21,7 +21,7 @@ for st in "$@"; do
     launches) timeout 1200 ncu --metrics gpu__time_duration.sum --clock-control none -c 6000 --csv --log-file $OUT/${TAG}_launches.csv \
                  python bench.py --steps 2 --warmup 3 --no-cpu-baseline --no-song $arg > $OUT/${TAG}_launches.log 2>&1; rc=$? ;;
     ncu)     kre=${arg%%:*}; bargs=""; [[ "$arg" == *:* ]] && bargs=${arg#*:}
-             timeout 1500 ncu --set full --clock-control none -k regex:$kre -s 40 -c 6 -o $OUT/${TAG}_ncu_$(echo $kre | tr -c 'A-Za-z0-9\n' '_') -f \
+             timeout 1500 ncu --set full --clock-control none -k regex:$kre -s 40 -c 3 -o $OUT/${TAG}_ncu_$(echo $kre | tr -c 'A-Za-z0-9\n' '_') -f \
                  python bench.py --steps 2 --warmup 3 --no-cpu-baseline --no-song $bargs > $OUT/${TAG}_ncu.log 2>&1; rc=$? ;;
     probe)   timeout 900 python scripts/perf_probe.py $arg > $OUT/${TAG}_probe.log 2>&1; rc=$?; tail -20 $OUT/${TAG}_probe.log ;;
     sh)      name=$(echo "sh_${arg}" | tr -c 'A-Za-z0-9\n' '_' | cut -c1-60); timeout 1200 bash -c "$arg" > $OUT/${TAG}_${name}.log 2>&1; rc=$?; tail -12 $OUT/${TAG}_${name}.log ;;

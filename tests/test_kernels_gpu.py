@@ -262,6 +262,33 @@ def test_gemm_quantised_routes_agree(br, gt, shape, monkeypatch):
     assert np.isfinite(default).all() and np.abs(default - single).max() <= 1e-5 * np.abs(ref).max(), np.abs(default - single).max()
 
 
+@pytest.mark.parametrize("route", ["single", "pair"])
+@pytest.mark.parametrize("wt", [0, 12])
+def test_gemm_banded_rasterisation_is_a_permutation(br, route, wt, monkeypatch):
+    """tile order in L2-sized bands of row tiles (tile_coords): with the band shrunk to a few row tiles — several bands, a short
+    last one, two samples, K split — every output tile is still computed exactly once: bit-identical to the one-band order for
+    plain stores, and to fp32 reduction order for the split-K accumulate epilogue."""
+    g = np.random.default_rng(5)
+    B, L, K, N = 2, 1100, 512, 768
+    A = g.standard_normal((B, L, K), dtype=np.float32)
+    W = (g.standard_normal((N, K), dtype=np.float32) * K ** -0.5) if wt == 0 else random_rows(wt, N, K, seed=3)
+    R = g.standard_normal((B, L, N), dtype=np.float32)
+    bias = g.standard_normal((N,), dtype=np.float32)
+    monkeypatch.setenv("ACE_B200_GEMM_2CTA", "1" if route == "pair" else "0")
+    for kw, exact in ((dict(bias=bias), True), (dict(resid=R), False), (dict(resid=R, split_k=True), False)):
+        monkeypatch.setenv("ACE_B200_GEMM_BAND_MB", "0")
+        one_band = br.debug_gemm(A, W, w_type=wt, N=N, **kw)
+        outs = []
+        for mb in ("0.3", "0.8"):   # 128-row tiles of 128 KB / 256-row pairs of 256 KB: bands of 2..6 row tiles out of 9..18
+            monkeypatch.setenv("ACE_B200_GEMM_BAND_MB", mb)
+            outs.append(br.debug_gemm(A, W, w_type=wt, N=N, **kw))
+        for o in outs:
+            if exact:
+                assert np.array_equal(o, one_band)
+            else:
+                assert np.abs(o - one_band).max() <= 1e-5 * max(1.0, np.abs(one_band).max())
+
+
 @pytest.mark.parametrize("gt", [8, 12, 14])
 def test_gemm_quantised_pair_epilogues(br, gt, monkeypatch):
     """CTA-pair in-kernel decode through the fused epilogues the DiT uses: bias, SwiGLU over interleaved rows, split-K residual

@@ -279,7 +279,7 @@ def test_gemm_banded_rasterisation_is_a_permutation(br, route, wt, monkeypatch):
         monkeypatch.setenv("ACE_B200_GEMM_BAND_MB", "0")
         one_band = br.debug_gemm(A, W, w_type=wt, N=N, **kw)
         outs = []
-        for mb in ("0.3", "0.8"):   # 128-row tiles of 128 KB / 256-row pairs of 256 KB: bands of 2..6 row tiles out of 9..18
+        for mb in ("0.3", "0.55", "0.8"):   # 128-row tiles of 128 KB / 256-row pairs of 256 KB: bands of 2..6 row tiles out of 10..18, short last bands
             monkeypatch.setenv("ACE_B200_GEMM_BAND_MB", mb)
             outs.append(br.debug_gemm(A, W, w_type=wt, N=N, **kw))
         for o in outs:

@@ -8,11 +8,12 @@ import numpy as np
 ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 sys.path[:0] = [ROOT, os.path.join(ROOT, "ace-step-1.5-ggml_b200"), os.path.join(ROOT, "tests")]
 import bench  # noqa: E402
+from parity_common import full_vae_dir, turbo_dit_dir  # noqa: E402
 from acestep_b200.bridge import B200Bridge  # noqa: E402
 
 T = int(sys.argv[1]) if len(sys.argv) > 1 else 1500
 br = B200Bridge()
-br.load_dit(bench.ensure_dit_fixture())
+br.load_dit(turbo_dit_dir("F16"))
 noise, ctx, enc = bench.synth_inputs(T, 512)
 for _ in range(3):
     br.dit_forward_tfirst(noise[0], ctx[0], enc[0], None, None, 1.0, 1.0)

@@ -7,12 +7,12 @@ import numpy as np
 
 ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 sys.path[:0] = [ROOT, os.path.join(ROOT, "ace-step-1.5-ggml_b200"), os.path.join(ROOT, "tests")]
-import bench  # noqa: E402
+from parity_common import full_vae_dir, turbo_dit_dir  # noqa: E402
 from acestep_b200.bridge import B200Bridge  # noqa: E402
 
 secs = int(sys.argv[1]) if len(sys.argv) > 1 else 60
 br = B200Bridge()
-br.load_vae(bench.ensure_vae_fixture())
+br.load_vae(full_vae_dir())
 lat = np.random.default_rng(0).standard_normal((secs * 25, 64), dtype=np.float32)
 for _ in range(2):
     br.vae_decode_tfirst(lat)

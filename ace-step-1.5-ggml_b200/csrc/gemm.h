@@ -33,7 +33,9 @@ struct GemmEpilogue {
     const float* gate          = nullptr;  // [B, gate_bstride] per-sample column scale (AdaLN gate)
     long         gate_bstride  = 0;
     const float* resid         = nullptr;  // fp32, same indexing as out_f32 (may alias it)
+    const __half* resid16      = nullptr;  // 16-bit residual stream (VAE): same indexing; exclusive with resid
     float*       out_f32       = nullptr;
+    __half*      out_x16       = nullptr;  // v (after bias / residual, BEFORE Snake) rounded to fp16: the 16-bit residual stream
     __half*      out_f16       = nullptr;
     long         ld_out        = 0;        // elements between consecutive l rows of the outputs
     long         out_bstride   = 0;        // elements between samples

@@ -288,6 +288,21 @@ __device__ __forceinline__ void epilogue_row32(const KParams& p, const float (&a
                 v[4 * i] += t.x; v[4 * i + 1] += t.y; v[4 * i + 2] += t.z; v[4 * i + 3] += t.w;
             }
         }
+        if (e.resid16) {
+            const uint2* r = reinterpret_cast<const uint2*>(e.resid16 + base);
+#pragma unroll
+            for (int i = 0; i < 8; ++i) {
+                const uint2 t = r[i];
+                const float2 a = __half22float2(u2h(t.x)), b2 = __half22float2(u2h(t.y));
+                v[4 * i] += a.x; v[4 * i + 1] += a.y; v[4 * i + 2] += b2.x; v[4 * i + 3] += b2.y;
+            }
+        }
+        if (e.out_x16) {
+            uint2* o = reinterpret_cast<uint2*>(e.out_x16 + base);
+#pragma unroll
+            for (int i = 0; i < 8; ++i)
+                o[i] = make_uint2(h2u(__floats2half2_rn(v[4 * i], v[4 * i + 1])), h2u(__floats2half2_rn(v[4 * i + 2], v[4 * i + 3])));
+        }
         if (e.out_f32) {
             float4* o = reinterpret_cast<float4*>(e.out_f32 + base);
 #pragma unroll
@@ -323,6 +338,8 @@ __device__ __forceinline__ void epilogue_row32(const KParams& p, const float (&a
         if (f < 0 || f >= e.out_valid) continue;
         float x = v[i];
         if (e.resid) x += e.resid[base + i];
+        if (e.resid16) x += __half2float(e.resid16[base + i]);
+        if (e.out_x16) e.out_x16[base + i] = __float2half_rn(x);
         if (e.out_f32) e.out_f32[base + i] = x;
         if (e.out_f16) {
             if (e.snake_alpha) {
@@ -340,14 +357,23 @@ __device__ __forceinline__ void epilogue_row32(const KParams& p, const float (&a
 // no run-time feature tests in the loop).  ncu on the last-level VAE convolutions showed the generic code at ~1200 warp
 // instructions per 32x32 chunk — issue-bound, 8.5 k cycles of epilogue per 128x128 tile against 3.6 k of MMAs
 // (profiles/r1_vae_conv_ncu.md); this form needs ~350.
-enum { SV_GENERIC = 0, SV_F16 = 1, SV_F16_SNAKE = 2, SV_F16_SILU = 3, SV_F32 = 4, SV_RES_F32_F16SNAKE = 5, SV_RES_F16SNAKE = 6, SV_F32_F16SNAKE = 7 };
-template <bool W, int ACT, bool RESID, bool OUT32, bool OUT16>
+enum { SV_GENERIC = 0, SV_F16 = 1, SV_F16_SNAKE = 2, SV_F16_SILU = 3, SV_F32 = 4, SV_RES_F32_F16SNAKE = 5, SV_RES_F16SNAKE = 6, SV_F32_F16SNAKE = 7,
+       SV_RES16_X16_F16SNAKE = 8, SV_RES16_F16SNAKE = 9, SV_X16_F16SNAKE = 10 };  // 8..10: 16-bit residual stream (resid16 / out_x16)
+// RESID: 0 none, 1 fp32 `resid`, 2 fp16 `resid16`.  OUTX: 0 none, 1 fp32 `out_f32`, 2 fp16 `out_x16`.
+template <bool W, int ACT, int RESID, int OUTX, bool OUT16>
 __device__ __forceinline__ void staged_phase2_fast(const GemmEpilogue& e, const float4* s4, long off0, long step, int lane, int n0, bool live) {
     const int seg = lane & 7, r0 = lane >> 3;
     float4 res[8];
-    if (RESID) {
+    if (RESID == 1) {
 #pragma unroll
         for (int k = 0; k < 8; ++k) res[k] = __ldcg(reinterpret_cast<const float4*>(e.resid + off0 + k * step));
+    } else if (RESID == 2) {
+#pragma unroll
+        for (int k = 0; k < 8; ++k) {
+            const uint2 t = __ldcg(reinterpret_cast<const uint2*>(e.resid16 + off0 + k * step));
+            const float2 a = __half22float2(u2h(t.x)), b2 = __half22float2(u2h(t.y));
+            res[k] = make_float4(a.x, a.y, b2.x, b2.y);
+        }
     }
     float4 sa = make_float4(0.f, 0.f, 0.f, 0.f), sb = sa;
     if (ACT == 1) {
@@ -360,7 +386,8 @@ __device__ __forceinline__ void staged_phase2_fast(const GemmEpilogue& e, const 
         const int rr = 4 * k + r0;
         float4 t = s4[rr * 8 + (seg ^ (rr & 7))];
         if (RESID) { t.x += res[k].x; t.y += res[k].y; t.z += res[k].z; t.w += res[k].w; }
-        if (OUT32) st_v4_f32_if<W>(live, e.out_f32 + off0 + k * step, t);
+        if (OUTX == 1) st_v4_f32_if<W>(live, e.out_f32 + off0 + k * step, t);
+        if (OUTX == 2) st_v2_b32_if<W>(live, e.out_x16 + off0 + k * step, h2u(__floats2half2_rn(t.x, t.y)), h2u(__floats2half2_rn(t.z, t.w)));
         if (OUT16) {
             if (ACT == 1) {
                 t.x = snake_f(t.x, sa.x, sb.x); t.y = snake_f(t.y, sa.y, sb.y);
@@ -430,13 +457,16 @@ __device__ __forceinline__ bool epilogue_store_staged(const KParams& p, const CU
             const long step = 4 * e.ld_out;
             const bool live = !(W && dry);
             switch (p.epi_variant) {
-                case SV_F16:              staged_phase2_fast<W, 0, false, false, true>(e, s4, off0, step, lane, n0, live); break;
-                case SV_F16_SNAKE:        staged_phase2_fast<W, 1, false, false, true>(e, s4, off0, step, lane, n0, live); break;
-                case SV_F16_SILU:         staged_phase2_fast<W, 2, false, false, true>(e, s4, off0, step, lane, n0, live); break;
-                case SV_F32:              staged_phase2_fast<W, 0, false, true, false>(e, s4, off0, step, lane, n0, live); break;
-                case SV_RES_F32_F16SNAKE: staged_phase2_fast<W, 1, true, true, true>(e, s4, off0, step, lane, n0, live); break;
-                case SV_RES_F16SNAKE:     staged_phase2_fast<W, 1, true, false, true>(e, s4, off0, step, lane, n0, live); break;
-                default:                  staged_phase2_fast<W, 1, false, true, true>(e, s4, off0, step, lane, n0, live); break;
+                case SV_F16:              staged_phase2_fast<W, 0, 0, 0, true>(e, s4, off0, step, lane, n0, live); break;
+                case SV_F16_SNAKE:        staged_phase2_fast<W, 1, 0, 0, true>(e, s4, off0, step, lane, n0, live); break;
+                case SV_F16_SILU:         staged_phase2_fast<W, 2, 0, 0, true>(e, s4, off0, step, lane, n0, live); break;
+                case SV_F32:              staged_phase2_fast<W, 0, 0, 1, false>(e, s4, off0, step, lane, n0, live); break;
+                case SV_RES_F32_F16SNAKE: staged_phase2_fast<W, 1, 1, 1, true>(e, s4, off0, step, lane, n0, live); break;
+                case SV_RES_F16SNAKE:     staged_phase2_fast<W, 1, 1, 0, true>(e, s4, off0, step, lane, n0, live); break;
+                case SV_RES16_X16_F16SNAKE: staged_phase2_fast<W, 1, 2, 2, true>(e, s4, off0, step, lane, n0, live); break;
+                case SV_RES16_F16SNAKE:   staged_phase2_fast<W, 1, 2, 0, true>(e, s4, off0, step, lane, n0, live); break;
+                case SV_X16_F16SNAKE:     staged_phase2_fast<W, 1, 0, 2, true>(e, s4, off0, step, lane, n0, live); break;
+                default:                  staged_phase2_fast<W, 1, 0, 1, true>(e, s4, off0, step, lane, n0, live); break;
             }
             __syncwarp();  // buffer is reused by the next chunk
             return true;
@@ -468,6 +498,16 @@ __device__ __forceinline__ bool epilogue_store_staged(const KParams& p, const CU
     if (e.resid) {  // all eight row segments in flight before the first use
 #pragma unroll
         for (int k = 0; k < 8; ++k) res[k] = ok[k] ? __ldcg(reinterpret_cast<const float4*>(e.resid + off[k])) : make_float4(0.f, 0.f, 0.f, 0.f);
+    } else if (e.resid16) {
+#pragma unroll
+        for (int k = 0; k < 8; ++k) {
+            res[k] = make_float4(0.f, 0.f, 0.f, 0.f);
+            if (ok[k]) {
+                const uint2 t = __ldcg(reinterpret_cast<const uint2*>(e.resid16 + off[k]));
+                const float2 a = __half22float2(u2h(t.x)), b2 = __half22float2(u2h(t.y));
+                res[k] = make_float4(a.x, a.y, b2.x, b2.y);
+            }
+        }
     }
     float4 sa = make_float4(0.f, 0.f, 0.f, 0.f), sb = sa;
     if (e.out_f16 && e.snake_alpha) {
@@ -480,8 +520,9 @@ __device__ __forceinline__ bool epilogue_store_staged(const KParams& p, const CU
         const int rr = 4 * k + (lane >> 3);
         float4 t = s4[rr * 8 + (seg ^ (rr & 7))];
         if (!ok[k]) continue;
-        if (e.resid) { t.x += res[k].x; t.y += res[k].y; t.z += res[k].z; t.w += res[k].w; }
+        if (e.resid || e.resid16) { t.x += res[k].x; t.y += res[k].y; t.z += res[k].z; t.w += res[k].w; }
         if (e.out_f32) *reinterpret_cast<float4*>(e.out_f32 + off[k]) = t;
+        if (e.out_x16) *reinterpret_cast<uint2*>(e.out_x16 + off[k]) = make_uint2(h2u(__floats2half2_rn(t.x, t.y)), h2u(__floats2half2_rn(t.z, t.w)));
         if (e.out_f16) {
             if (e.snake_alpha) {
                 t.x = snake_f(t.x, sa.x, sb.x); t.y = snake_f(t.y, sa.y, sb.y);
@@ -1662,7 +1703,10 @@ cudaError_t gemm_launch(const GemmProblem& g, cudaStream_t stream, bool simt) {
         const GemmEpilogue& e = kp.epi;
         int v = SV_GENERIC;
         const bool snake = e.snake_alpha != nullptr, plain = e.mode == EPI_STORE && !e.atomic && !e.gate && e.ld_out > 0;
-        if (plain && !e.resid) {
+        if (e.resid16 || e.out_x16) {  // 16-bit residual stream (VAE)
+            if (plain && snake && e.out_f16 && !e.resid && !e.out_f32)
+                v = e.resid16 ? (e.out_x16 ? SV_RES16_X16_F16SNAKE : SV_RES16_F16SNAKE) : SV_X16_F16SNAKE;
+        } else if (plain && !e.resid) {
             if (e.out_f16 && !e.out_f32) v = snake ? SV_F16_SNAKE : (e.silu_f16 ? SV_F16_SILU : SV_F16);
             else if (e.out_f32 && !e.out_f16) v = SV_F32;
             else if (e.out_f32 && e.out_f16 && snake) v = SV_F32_F16SNAKE;

@@ -542,6 +542,13 @@ cudaError_t vae_decode_device(const VaeModel& m, VaeWorkspace& ws, int B, int n_
         return e;
     };
 
+    // Residual stream between the convolutions: 16-bit by default (the k1 convolutions of the last levels are HBM-bound on it:
+    // fp32 in + fp32 out + fp16 Snake'd copy = 10 of their 12 bytes per element; fp16 in / out makes it 8), fp32 with
+    // ACE_B200_VAE_X32=1 (round 1's layout).  The reference adds in F32 and rounds every conv INPUT to F16 (ggml im2col), so the extra
+    // rounding sits on values that are rounded one op later anyway; the waveform bound (cos >= 0.9999, SNR >= 40 dB) holds with margin.
+    const char* x32_env = std::getenv("ACE_B200_VAE_X32");
+    const bool x16 = !(x32_env && x32_env[0] && x32_env[0] != '0');
+    __half* xh = reinterpret_cast<__half*>(ws.x);
     launch_f32_to_f16(ws.d_lat, ws.lat16, (long)B * n_frames * c.decoder_input_channels, st);
     long L = n_frames;
     {  // conv1 k7: latents -> C0 channels, epilogue = bias + block0.snake1
@@ -560,7 +567,8 @@ cudaError_t vae_decode_device(const VaeModel& m, VaeWorkspace& ws, int B, int n_
         {  // conv-transpose as `s` phase-GEMMs in one launch: D[i, (r, co)] = out_full[i*s + r, co]; crop = flat shift
             GemmEpilogue e;
             e.bias = b.conv_t.bias;
-            e.out_f32 = ws.x;
+            if (x16) e.out_x16 = xh;
+            else e.out_f32 = ws.x;
             e.out_f16 = ws.xs;
             e.ld_out = (long)s * Co;
             e.out_bstride = Lout * Co;
@@ -582,12 +590,14 @@ cudaError_t vae_decode_device(const VaeModel& m, VaeWorkspace& ws, int B, int n_
             {  // k1 conv, epilogue = bias + skip, then the NEXT consumer's snake
                 GemmEpilogue e;
                 e.bias = ru.conv2.bias;
-                e.resid = ws.x;
+                if (x16) e.resid16 = xh;
+                else e.resid = ws.x;
                 e.ld_out = Co;
                 e.out_bstride = L * Co;
                 const VaeSnake* next;
                 if (j < 2) {
-                    e.out_f32 = ws.x;
+                    if (x16) e.out_x16 = xh;
+                    else e.out_f32 = ws.x;
                     e.out_f16 = ws.xs;
                     next = &b.res[j + 1].snake1;
                 } else if (i + 1 < nb) {

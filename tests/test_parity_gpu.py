@@ -297,6 +297,23 @@ def test_vae_decode_vs_reference_with_f32_conv_transpose(br, root, monkeypatch):
     assert m["cos"] >= 0.9999 and m["snr_db"] >= 40.0, m
 
 
+def test_vae_residual_stream_widths_agree(br, root, monkeypatch):
+    """the 16-bit residual stream (default) against the fp32 one (ACE_B200_VAE_X32=1): both inside the waveform bound against the
+    reference, and close to each other"""
+    need_ref()
+    d = make_vae_dir(root)
+    lat = fx.vae_latents(fx.VAE_TOY, 45, seed=7)
+    outs, _ = refbridge.run_ref([{"op": "vae_decode", "latents": "lat", "out": "audio"}], {"lat": lat}, vae_dir=d)
+    br.load_vae(d)
+    a16 = br.vae_decode_tfirst(lat)
+    monkeypatch.setenv("ACE_B200_VAE_X32", "1")
+    a32 = br.vae_decode_tfirst(lat)
+    for a in (a16, a32):
+        m = metrics(a, outs["audio"])
+        assert m["cos"] >= 0.9999 and m["snr_db"] >= 40.0, m
+    assert metrics(a16, a32)["snr_db"] >= 45.0
+
+
 def test_vae_tiled_reference_policy_equals_untiled(br, root):
     """the reference's chunk 128 / overlap 32 tiling (acestep_ggml.cpp:2114-2215) has halo >= receptive field, so an
     un-tiled decode reproduces it; checked on the toy VAE with chunk 24 / overlap 12"""

@@ -1674,8 +1674,12 @@ bool gemm_force_simt() {
 cudaError_t gemm_launch(const GemmProblem& g, cudaStream_t stream, bool simt) {
     const PackedWeight& w = *g.W;
     note_launch();
+    // algorithmic HBM bytes: packed weights once + activations once + every output / residual stream the epilogue touches
+    const double out_elems = (double)g.B * g.l_out * (g.epi.mode == EPI_SWIGLU ? w.N / 2 : w.N);
+    const double out_bytes = out_elems * ((g.epi.out_f32 ? 4.0 : 0.0) + (g.epi.out_f16 ? 2.0 : 0.0) + (g.epi.out_x16 ? 2.0 : 0.0) +
+                                          (g.epi.resid ? 4.0 : 0.0) + (g.epi.resid16 ? 2.0 : 0.0));
     ProfScope prof_scope(PROF_GEMM, 2.0 * g.B * (double)g.l_out * w.N * (double)w.K * w.taps,
-                         (double)w.bytes + (double)g.B * g.L * g.C * 2.0, stream);
+                         (double)w.bytes + (double)g.B * g.L * g.C * 2.0 + out_bytes, stream);
     KParams kp;
     kp.tma_reduce = 0;
     kp.trace = nullptr;

@@ -379,7 +379,8 @@ def run_dit_workload(a, wl, world, rank, local, dist):
         roofline = {"bound": "tensor", "kernel": "gemm_tc2_kernel / gemm_tc_kernel (tcgen05 tap-GEMM family)", "achieved": ach, "peak": peak, "unit": "TFLOP/s",
                     "frac": ach / peak, "traffic": traffic, "peak_source": f"{peak_kind}: bf16_tflops_sustained (kernel timed inside a long step)",
                     "avg_launch_us": 1e3 * gm["ms"] / max(gm["launches"], 1), "launches": gm["launches"],
-                    "flops_per_launch": gm["flops"] / max(gm["launches"], 1), "share_of_step": gm["ms"] / total_prof if total_prof else None,
+                    "flops_per_launch": gm["flops"] / max(gm["launches"], 1),
+                    "algorithmic_bytes_per_launch": gm["bytes"] / max(gm["launches"], 1), "share_of_step": gm["ms"] / total_prof if total_prof else None,
                     "families_ms": {k: v["ms"] for k, v in prof.items()},
                     "attention": {"bound": "tensor", "achieved": at["flops"] / (at["ms"] * 1e-3) / 1e12 if at["ms"] > 0 else 0.0, "peak": peak, "unit": "TFLOP/s",
                                   "frac": (at["flops"] / (at["ms"] * 1e-3) / 1e12 / peak) if at["ms"] > 0 else 0.0, "share_of_step": at["ms"] / total_prof if total_prof else None},

@@ -328,6 +328,26 @@ def test_gemm_cta_pair_matches_single_cta(br, shape, monkeypatch):
     assert np.abs(pair - single).max() <= 1e-5 * np.abs(ref).max()
 
 
+@pytest.mark.parametrize("wt", [0, 12])
+def test_gemm_cta_pair_stress_is_deterministic(br, wt, monkeypatch):
+    """the CTA-pair kernels publish "CTA 1's stage landed" to the leader with a RELAXED remote mbarrier arrive (ptx.cuh: a release at
+    cluster scope cost ~1 us per k-block) — for the QUANT variant the stage was written by generic stores + fence.proxy.async.  A lost
+    ordering would show as run-to-run differences: 25 repetitions x 3 shapes must be bit-identical to the first run of the same
+    route, and agree with the single-CTA route."""
+    g = np.random.default_rng(77)
+    for (L, K, N) in ((2100, 2048, 1024), (900, 6144, 512), (5000, 512, 2048)):
+        A = g.standard_normal((1, L, K), dtype=np.float32)
+        W = (g.standard_normal((N, K), dtype=np.float32) * K ** -0.5) if wt == 0 else random_rows(wt, N, K, seed=L)
+        monkeypatch.setenv("ACE_B200_GEMM_2CTA", "0")
+        single = br.debug_gemm(A, W, w_type=wt, N=N)
+        monkeypatch.setenv("ACE_B200_GEMM_2CTA", "1")
+        first = br.debug_gemm(A, W, w_type=wt, N=N)
+        assert np.abs(first - single).max() <= 1e-5 * np.abs(single).max()
+        for it in range(24):
+            again = br.debug_gemm(A, W, w_type=wt, N=N)
+            assert np.array_equal(again, first), (L, K, N, it)
+
+
 def test_gemm_cta_pair_splitk_residual(br, monkeypatch):
     g = np.random.default_rng(21)
     L, K, N = 260, 1024, 512

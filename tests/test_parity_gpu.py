@@ -260,6 +260,23 @@ def test_cfg_sampler_matches_composed_reference(br, root, batch):
         assert metrics(plain[b], refs[b])["rel_l2"] > 4 * max(m["rel_l2"], 1e-3)  # guidance changes the result: the test can fail
 
 
+def test_sampler_50_step_base_schedule(br, root):
+    """BASELINE configs[4] shape of the loop: 50 Euler steps on the closed-form shift-3 schedule (ace_b200_shift_schedule; the reference
+    ABI only has the three 8-step tables, so the reference is driven step by step through ace_ggml_dit_forward with the same t_i).
+    The device-resident sampler precomputes the time embeddings of all 50 steps in one pass and caches cross K/V."""
+    need_ref()
+    d = make_dit_dir(root, fx.TOY, 0, None)
+    T, E = 24, 6
+    inp = fx.dit_inputs(fx.TOY, T, E, seed=13)
+    sched = [float(x) for x in br.shift_schedule(3.0, 50)]
+    assert abs(sched[0] - 1.0) < 1e-7 and all(a > b for a, b in zip(sched, sched[1:]))
+    outs, _ = refbridge.run_ref([{"op": "dit_sample", "steps": sched, "out": "x_final", "trace": "x_steps"}], inp, dit_dir=d)
+    br.load_dit(d)
+    lat = br.generate_latents(inp["hidden_states"][None], inp["context_latents"][None], inp["encoder_hidden_states"][None], schedule=sched)
+    m = metrics(lat[0], outs["x_final"])
+    assert np.isfinite(lat).all() and m["rel_l2"] <= 2e-2, m
+
+
 def test_shift_schedule_tables(br):
     """closed form reproduces the three hard-coded 8-step tables (acestep_ggml.cpp:1485-1487)"""
     s1 = [1.0, 0.875, 0.75, 0.625, 0.5, 0.375, 0.25, 0.125]

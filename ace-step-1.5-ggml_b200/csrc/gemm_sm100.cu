@@ -83,7 +83,7 @@ struct SmemLayout {
     static constexpr int STAGE      = A_STAGE_BYTES + B_STAGE;
     static constexpr int EPI_WARPS  = QUANT ? 4 : 8;
     static constexpr int STG_BYTES  = EPI_WARPS * STG_WARP_BYTES;  // epilogue transpose buffers
-    static constexpr int COL_BYTES  = 2 * BN * 4;                  // staged bias + gate of one tile
+    static constexpr int COL_BYTES  = 4 * BN * 4;                  // staged bias, gate, Snake alpha, Snake 1/beta of one tile's columns
     static constexpr int BUDGET     = 227 * 1024 - 256 /*barriers*/ - STG_BYTES - COL_BYTES - (QUANT ? 1024 : 0) /*raw-region padding*/;
     static constexpr int STAGES_RAW = BUDGET / (STAGE + RAW_STAGE);
     static constexpr int STAGES     = STAGES_RAW > 6 ? 6 : STAGES_RAW;
@@ -361,7 +361,8 @@ enum { SV_GENERIC = 0, SV_F16 = 1, SV_F16_SNAKE = 2, SV_F16_SILU = 3, SV_F32 = 4
        SV_RES16_X16_F16SNAKE = 8, SV_RES16_F16SNAKE = 9, SV_X16_F16SNAKE = 10 };  // 8..10: 16-bit residual stream (resid16 / out_x16)
 // RESID: 0 none, 1 fp32 `resid`, 2 fp16 `resid16`.  OUTX: 0 none, 1 fp32 `out_f32`, 2 fp16 `out_x16`.
 template <bool W, int ACT, int RESID, int OUTX, bool OUT16>
-__device__ __forceinline__ void staged_phase2_fast(const GemmEpilogue& e, const float4* s4, long off0, long step, int lane, int n0, bool live) {
+__device__ __forceinline__ void staged_phase2_fast(const GemmEpilogue& e, const float4* s4, long off0, long step, int lane, int n0, bool live,
+                                                   const float* s_sa, const float* s_sb) {
     const int seg = lane & 7, r0 = lane >> 3;
     float4 res[8];
     if (RESID == 1) {
@@ -377,9 +378,14 @@ __device__ __forceinline__ void staged_phase2_fast(const GemmEpilogue& e, const 
     }
     float4 sa = make_float4(0.f, 0.f, 0.f, 0.f), sb = sa;
     if (ACT == 1) {
-        const int c0 = (e.snake_period ? (n0 % e.snake_period) : n0) + 4 * seg;
-        sa = __ldg(reinterpret_cast<const float4*>(e.snake_alpha + c0));
-        sb = __ldg(reinterpret_cast<const float4*>(e.snake_invbeta + c0));
+        if (s_sa) {  // staged in shared memory with the tile's bias (single-CTA kernel)
+            sa = *reinterpret_cast<const float4*>(s_sa + 4 * seg);
+            sb = *reinterpret_cast<const float4*>(s_sb + 4 * seg);
+        } else {
+            const int c0 = (e.snake_period ? (n0 % e.snake_period) : n0) + 4 * seg;
+            sa = __ldg(reinterpret_cast<const float4*>(e.snake_alpha + c0));
+            sb = __ldg(reinterpret_cast<const float4*>(e.snake_invbeta + c0));
+        }
     }
 #pragma unroll
     for (int k = 0; k < 8; ++k) {
@@ -411,7 +417,8 @@ __device__ __forceinline__ void staged_phase2_fast(const GemmEpilogue& e, const 
 // both phases are bank-conflict free.  Returns false (nothing done) when the chunk does not qualify: caller falls back.
 template <bool W>
 __device__ __forceinline__ bool epilogue_store_staged(const KParams& p, const CUtensorMap* tmOut, const float (&acc)[32], int b, int l_base,
-                                                      int lane, int n0, const float* s_bias, const float* s_gate, float* stg, bool dry) {
+                                                      int lane, int n0, const float* s_bias, const float* s_gate, float* stg, bool dry,
+                                                      const float* s_sa = nullptr, const float* s_sb = nullptr) {
     const GemmEpilogue& e = p.epi;
     if (n0 + 32 > p.N) return false;                                     // warp-uniform
     const long col0 = (long)n0 + e.out_shift;
@@ -457,16 +464,16 @@ __device__ __forceinline__ bool epilogue_store_staged(const KParams& p, const CU
             const long step = 4 * e.ld_out;
             const bool live = !(W && dry);
             switch (p.epi_variant) {
-                case SV_F16:              staged_phase2_fast<W, 0, 0, 0, true>(e, s4, off0, step, lane, n0, live); break;
-                case SV_F16_SNAKE:        staged_phase2_fast<W, 1, 0, 0, true>(e, s4, off0, step, lane, n0, live); break;
-                case SV_F16_SILU:         staged_phase2_fast<W, 2, 0, 0, true>(e, s4, off0, step, lane, n0, live); break;
-                case SV_F32:              staged_phase2_fast<W, 0, 0, 1, false>(e, s4, off0, step, lane, n0, live); break;
-                case SV_RES_F32_F16SNAKE: staged_phase2_fast<W, 1, 1, 1, true>(e, s4, off0, step, lane, n0, live); break;
-                case SV_RES_F16SNAKE:     staged_phase2_fast<W, 1, 1, 0, true>(e, s4, off0, step, lane, n0, live); break;
-                case SV_RES16_X16_F16SNAKE: staged_phase2_fast<W, 1, 2, 2, true>(e, s4, off0, step, lane, n0, live); break;
-                case SV_RES16_F16SNAKE:   staged_phase2_fast<W, 1, 2, 0, true>(e, s4, off0, step, lane, n0, live); break;
-                case SV_X16_F16SNAKE:     staged_phase2_fast<W, 1, 0, 2, true>(e, s4, off0, step, lane, n0, live); break;
-                default:                  staged_phase2_fast<W, 1, 0, 1, true>(e, s4, off0, step, lane, n0, live); break;
+                case SV_F16:              staged_phase2_fast<W, 0, 0, 0, true>(e, s4, off0, step, lane, n0, live, s_sa, s_sb); break;
+                case SV_F16_SNAKE:        staged_phase2_fast<W, 1, 0, 0, true>(e, s4, off0, step, lane, n0, live, s_sa, s_sb); break;
+                case SV_F16_SILU:         staged_phase2_fast<W, 2, 0, 0, true>(e, s4, off0, step, lane, n0, live, s_sa, s_sb); break;
+                case SV_F32:              staged_phase2_fast<W, 0, 0, 1, false>(e, s4, off0, step, lane, n0, live, s_sa, s_sb); break;
+                case SV_RES_F32_F16SNAKE: staged_phase2_fast<W, 1, 1, 1, true>(e, s4, off0, step, lane, n0, live, s_sa, s_sb); break;
+                case SV_RES_F16SNAKE:     staged_phase2_fast<W, 1, 1, 0, true>(e, s4, off0, step, lane, n0, live, s_sa, s_sb); break;
+                case SV_RES16_X16_F16SNAKE: staged_phase2_fast<W, 1, 2, 2, true>(e, s4, off0, step, lane, n0, live, s_sa, s_sb); break;
+                case SV_RES16_F16SNAKE:   staged_phase2_fast<W, 1, 2, 0, true>(e, s4, off0, step, lane, n0, live, s_sa, s_sb); break;
+                case SV_X16_F16SNAKE:     staged_phase2_fast<W, 1, 0, 2, true>(e, s4, off0, step, lane, n0, live, s_sa, s_sb); break;
+                default:                  staged_phase2_fast<W, 1, 0, 1, true>(e, s4, off0, step, lane, n0, live, s_sa, s_sb); break;
             }
             __syncwarp();  // buffer is reused by the next chunk
             return true;
@@ -511,9 +518,14 @@ __device__ __forceinline__ bool epilogue_store_staged(const KParams& p, const CU
     }
     float4 sa = make_float4(0.f, 0.f, 0.f, 0.f), sb = sa;
     if (e.out_f16 && e.snake_alpha) {
-        const int c0 = (e.snake_period ? (n0 % e.snake_period) : n0) + 4 * seg;
-        sa = __ldg(reinterpret_cast<const float4*>(e.snake_alpha + c0));
-        sb = __ldg(reinterpret_cast<const float4*>(e.snake_invbeta + c0));
+        if (s_sa) {
+            sa = *reinterpret_cast<const float4*>(s_sa + 4 * seg);
+            sb = *reinterpret_cast<const float4*>(s_sb + 4 * seg);
+        } else {
+            const int c0 = (e.snake_period ? (n0 % e.snake_period) : n0) + 4 * seg;
+            sa = __ldg(reinterpret_cast<const float4*>(e.snake_alpha + c0));
+            sb = __ldg(reinterpret_cast<const float4*>(e.snake_invbeta + c0));
+        }
     }
 #pragma unroll
     for (int k = 0; k < 8; ++k) {
@@ -542,13 +554,19 @@ __device__ __forceinline__ bool epilogue_store_staged(const KParams& p, const CU
 // Column vectors of one tile for the staged epilogue: bias (0 when absent / not this split's job) and AdaLN gate (1 when
 // absent) of the tile's BN columns, fetched by the epilogue warps while the tile's MMAs are still running.
 template <int BN, int NTHREADS>
-__device__ __forceinline__ void stage_column_terms(const KParams& p, int b, int n_base, bool add_bias, int tid, float* s_bias, float* s_gate) {
+__device__ __forceinline__ void stage_column_terms(const KParams& p, int b, int n_base, bool add_bias, int tid, float* s_bias, float* s_gate,
+                                                   float* s_snake = nullptr) {
     const GemmEpilogue& e = p.epi;
     for (int j = tid; j < BN; j += NTHREADS) {
         const int n = n_base + j;
         const bool in = n < p.N;
         s_bias[j] = (in && e.bias && add_bias) ? __ldg(e.bias + n) : 0.f;
         s_gate[j] = (in && e.gate) ? __ldg(e.gate + (long)b * e.gate_bstride + n) : 1.f;
+        if (s_snake && e.snake_alpha) {  // per-channel Snake constants: ncu had the phase-2 loads of these at 9 % of all stall samples
+            const int ch = e.snake_period ? (n % e.snake_period) : n;
+            s_snake[j] = in ? __ldg(e.snake_alpha + ch) : 0.f;
+            s_snake[BN + j] = in ? __ldg(e.snake_invbeta + ch) : 0.f;
+        }
     }
 }
 // EPI_HEADNORM: q/k norm weights of the tile's heads (128 floats per head, zeros for V heads) into smem, under the MMAs.
@@ -679,7 +697,7 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
     uint8_t* sB = sA + (SLAB ? 2 * SLAB_BYTES : STAGES * A_STAGE_BYTES);  // [STAGES][SUBS*16 KB]
     uint8_t* sR = sB + STAGES * SL::B_STAGE;             // [STAGES][SUBS*RAW_MAX] (QUANT only)
     float* sStg = reinterpret_cast<float*>(sR + SL::RAW_TOTAL);  // [EPI_WARPS][32 x 32 fp32], 1 KB aligned
-    float* sCol = sStg + SL::STG_BYTES / 4;  // [2][BN]: bias, gate of the current tile
+    float* sCol = sStg + SL::STG_BYTES / 4;  // [4][BN]: bias, gate, Snake alpha, Snake 1/beta of the current tile's columns
     uint64_t* bars = reinterpret_cast<uint64_t*>(reinterpret_cast<uint8_t*>(sCol) + SL::COL_BYTES);
     uint64_t* full = bars;                  // [STAGES] operands of stage s are in smem
     uint64_t* empty = bars + STAGES;        // [STAGES] MMAs reading stage s have completed
@@ -985,7 +1003,7 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
             if (!dry) {
                 if (p.epi.mode == EPI_STORE) {  // column terms of this tile, fetched under the tile's MMAs
                     epi_bar_sync(EPI_THREADS);  // every warp is done reading the previous tile's terms
-                    stage_column_terms<BN, EPI_THREADS>(p, b, nt * BN, sp == 0, QUANT ? (int)threadIdx.x - 128 : (int)threadIdx.x, sCol, sCol + BN);
+                    stage_column_terms<BN, EPI_THREADS>(p, b, nt * BN, sp == 0, QUANT ? (int)threadIdx.x - 128 : (int)threadIdx.x, sCol, sCol + BN, sCol + 2 * BN);
                     epi_bar_sync(EPI_THREADS);
                 } else if (p.epi.mode == EPI_HEADNORM) {
                     epi_bar_sync(EPI_THREADS);
@@ -1027,7 +1045,8 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
                 for (int i = 0; i < 32; ++i) acc[i] = __uint_as_float(r[i]);
                 if (kb1 > kb0) {
                     float* stg = sStg + (QUANT ? q : warp) * (STG_WARP_BYTES / 4);
-                    if (p.epi.mode != EPI_STORE || !epilogue_store_staged<WARM>(p, &tmOut, acc, b, l0 + q * 32, lane, n0, sCol + c * 32, sCol + BN + c * 32, stg, dry))
+                    if (p.epi.mode != EPI_STORE || !epilogue_store_staged<WARM>(p, &tmOut, acc, b, l0 + q * 32, lane, n0, sCol + c * 32, sCol + BN + c * 32, stg, dry,
+                                                                                sCol + 2 * BN + c * 32, sCol + 3 * BN + c * 32))
                         epilogue_row32<WARM>(p, acc, b, l, n0, sp == 0, dry);
                 }
                 if (warp == 4 && lane == 0 && c == part) trace_stamp(p, TR_EPI_CHUNK0);

@@ -6,12 +6,13 @@
  * dlopen()s / links `libacestep_ggml` can be pointed at `libacestep_b200.so`
  * without source changes.  Only plain pointers and sizes cross the boundary.
  *
- *   hot path (implemented on sm_100a):       ace_ggml_create / destroy / last_error,
- *     ace_ggml_load_dit, ace_ggml_load_vae, ace_ggml_vae_get_info,
- *     ace_ggml_dit_forward, ace_ggml_vae_decode
- *   link-compatible, ACE_GGML_ERR_UNSUPPORTED: the text-encoder / LM entry points,
- *     ace_ggml_vae_encode and the three ace_ggml_generate_audio_* wrappers
- *     (SURVEY.md §8f "next" rows).
+ *   hot path:   ace_ggml_create / destroy / last_error, ace_ggml_load_dit,
+ *     ace_ggml_load_vae, ace_ggml_vae_get_info, ace_ggml_dit_forward, ace_ggml_vae_decode
+ *   callers either side (§8f):    ace_ggml_load_text_encoder / load_lm, the four
+ *     ace_ggml_text_encoder_forward* entry points, ace_ggml_vae_encode and the three
+ *     ace_ggml_generate_audio_* wrappers (csrc/abi_gen.cu)
+ *   Every entry point runs on sm_100a; none has a CPU fallback (a missing device or a
+ *   failed launch is ACE_GGML_ERR with the reason in ace_ggml_last_error).
  *
  * Additive extensions (batched / device-resident sampler) live in acestep_b200.h.
  */
@@ -72,7 +73,7 @@ ACE_GGML_API ace_ggml_status ace_ggml_vae_decode(ace_ggml_context * ctx, const f
 ACE_GGML_API ace_ggml_status ace_ggml_vae_encode(ace_ggml_context * ctx, const float * audio, int32_t n_samples,
                                                  float * out, size_t out_size);
 
-/* text encoder (unsupported here) — reference: acestep_ggml.h:63-94 */
+/* text encoder (Qwen3 stack, csrc/abi_gen.cu) — reference: acestep_ggml.h:63-94 */
 ACE_GGML_API ace_ggml_status ace_ggml_text_encoder_forward(ace_ggml_context * ctx, const int32_t * token_ids,
                                                            int32_t n_tokens, float * out, size_t out_size);
 ACE_GGML_API ace_ggml_status ace_ggml_text_encoder_forward_masked(ace_ggml_context * ctx, const int32_t * token_ids,
@@ -99,7 +100,7 @@ ACE_GGML_API ace_ggml_status ace_ggml_dit_forward(ace_ggml_context * ctx, const 
                                                   int32_t enc_len, float timestep, float timestep_r, float * out,
                                                   size_t out_size);
 
-/* token-to-audio wrappers (unsupported here: they need the text / lyric / timbre encoders) —
+/* token-to-audio wrappers (text / lyric / timbre encoders -> seed-exact noise -> sampler -> VAE) —
  * reference: acestep_ggml.h:110-152 */
 ACE_GGML_API ace_ggml_status ace_ggml_generate_audio_simple(ace_ggml_context * ctx, const int32_t * token_ids,
                                                             int32_t n_tokens, int32_t seq_len, float shift,

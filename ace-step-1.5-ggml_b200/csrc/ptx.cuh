@@ -84,6 +84,14 @@ __device__ __forceinline__ void tma_reduce_add_3d(const void* tmap, const void* 
         "r"(smem_u32(src)), "r"(c0), "r"(c1), "r"(c2)
         : "memory");
 }
+// tile store shared -> global through the TMA (same completion mechanism; rows / columns outside the tensor are clipped)
+__device__ __forceinline__ void tma_store_3d(const void* tmap, const void* src, int c0, int c1, int c2) {
+    asm volatile(
+        "cp.async.bulk.tensor.3d.global.shared::cta.tile.bulk_group [%0, {%2, %3, %4}], [%1];" ::"l"(
+            reinterpret_cast<uint64_t>(tmap)),
+        "r"(smem_u32(src)), "r"(c0), "r"(c1), "r"(c2)
+        : "memory");
+}
 __device__ __forceinline__ void bulk_commit() { asm volatile("cp.async.bulk.commit_group;" ::: "memory"); }
 __device__ __forceinline__ void bulk_wait_read0() { asm volatile("cp.async.bulk.wait_group.read 0;" ::: "memory"); }
 __device__ __forceinline__ void bulk_wait0() { asm volatile("cp.async.bulk.wait_group 0;" ::: "memory"); }

@@ -560,6 +560,9 @@ cudaError_t vae_decode_device(const VaeModel& m, VaeWorkspace& ws, int B, int n_
         run(ws.lat16, (int)L, (int)L, m.conv1, 1, -m.conv1.pad, with_snake(e, m.blocks[0].snake1, 0));
     }
     const int nb = (int)m.blocks.size();
+    const char* fuse_env = std::getenv("ACE_B200_VAE_FUSE");   // 0 = every unit as two GEMM launches (A/B and bisecting aid)
+    const bool fuse_units = !(fuse_env && fuse_env[0] == '0');
+    const __half* tail_in = ws.xs;  // input of the final k7 convolution
     for (int i = 0; i < nb; ++i) {
         const VaeBlock& b = m.blocks[(size_t)i];
         const int s = b.conv_t.stride, Co = b.conv_t.c_out, p = b.conv_t.pad;
@@ -577,8 +580,22 @@ cudaError_t vae_decode_device(const VaeModel& m, VaeWorkspace& ws, int B, int n_
             run(blk_in, (int)L, (int)L + 1, b.conv_t, -1, 0, with_snake(e, b.res[0].snake1, Co));
         }
         L = Lout;
+        // Fused residual units (vae_resunit.cu) at 128 channels with the 16-bit residual stream: the Snake'd copy ping-pongs between
+        // ws.xs and ws.h (a tile's k7 taps read its neighbours' rows, so a unit cannot overwrite its own input).
+        const bool fuse = fuse_units && x16 && vae_resunit128_supported(b.res[0]) && vae_resunit128_supported(b.res[1]) &&
+                          vae_resunit128_supported(b.res[2]);
         for (int j = 0; j < 3; ++j) {
             const VaeResUnit& ru = b.res[j];
+            if (fuse) {
+                if (rc != cudaSuccess) break;
+                const __half* in = (j & 1) ? ws.h : ws.xs;
+                __half* out = (j & 1) ? ws.xs : ws.h;
+                const VaeSnake* next = j < 2 ? &b.res[j + 1].snake1 : (i + 1 < nb ? &m.blocks[(size_t)i + 1].snake1 : &m.snake_out);
+                if (j == 2 && i + 1 < nb) out = blk_in;
+                rc = launch_vae_resunit128(in, xh, j < 2 ? xh : nullptr, out, B, L, ru, *next, st);
+                if (j == 2 && i + 1 == nb) tail_in = out;
+                continue;
+            }
             {  // k7 dilated conv, epilogue = bias + snake2 -> h
                 GemmEpilogue e;
                 e.bias = ru.conv1.bias;
@@ -614,10 +631,10 @@ cudaError_t vae_decode_device(const VaeModel& m, VaeWorkspace& ws, int B, int n_
     if (rc != cudaSuccess) return rc;
     if (win) {
         const long hop = c.hop_length;
-        launch_conv_small_out(ws.xs, m.conv2_w, nullptr, audio, B, L, m.conv2_cin, c.audio_channels, 7, 3, st, win->frame_lo * hop,
+        launch_conv_small_out(tail_in, m.conv2_w, nullptr, audio, B, L, m.conv2_cin, c.audio_channels, 7, 3, st, win->frame_lo * hop,
                               win->frame_hi * hop, (win->dst_frame - win->frame_lo) * hop, 0);
     } else {
-        launch_conv_small_out(ws.xs, m.conv2_w, nullptr, audio, B, L, m.conv2_cin, c.audio_channels, 7, 3, st);
+        launch_conv_small_out(tail_in, m.conv2_w, nullptr, audio, B, L, m.conv2_cin, c.audio_channels, 7, 3, st);
     }
     return cudaGetLastError();
 }

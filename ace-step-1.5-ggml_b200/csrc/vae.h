@@ -108,4 +108,11 @@ struct VaeOutWindow {
 cudaError_t vae_decode_device(const VaeModel& m, VaeWorkspace& ws, int B, int n_frames, float* audio, cudaStream_t st,
                               const VaeOutWindow* win = nullptr);
 
+// One residual unit at 128 channels in ONE launch (vae_resunit.cu): k7 dilated conv -> Snake -> k1 conv -> + x -> next Snake, the
+// intermediate h staying in shared memory.  xs_in: Snake'd input [B, L, 128] fp16; x_in: residual stream (fp16); x_out (may be
+// null, may alias x_in): new residual stream; xs_out (must not alias xs_in: neighbouring tiles read its halo): next Snake'd copy.
+bool vae_resunit128_supported(const VaeResUnit& ru);
+cudaError_t launch_vae_resunit128(const __half* xs_in, const __half* x_in, __half* x_out, __half* xs_out, int B, long L,
+                                  const VaeResUnit& ru, const VaeSnake& next, cudaStream_t st);
+
 }  // namespace ace

@@ -1,0 +1,406 @@
+// One Oobleck residual unit at 128 channels in ONE launch (sm_100a): the two last decoder levels, 63 % of a VAE decode.
+//
+//     h   = snake2( conv_k7_dilated(xs) + b1 )         tap-GEMM, 14 k-blocks, A from an activation slab (as gemm_tc_kernel<SLAB>)
+//     x'  = x + conv_k1(h) + b2                         second MMA: h goes registers -> shared memory -> tensor core, never to HBM
+//     out_x  = fp16(x')        (the 16-bit residual stream, optional)
+//     out_xs = fp16(snake_next(x'))                     (input of the next unit / block)
+// reference: acestep_vae_model.cpp:682-742 (snake, dilated conv, k1 conv, residual add of one unit)
+//
+// Unfused, the k1 convolution is a pure HBM stream (h and x in, x' and xs out: 8 bytes per element at 128 channels against 256 FLOPs)
+// running at 0.49 of the copy bandwidth (profiles/r2_vae240_launches_p.md) — 36 % of the decode.  Fused, h (a quarter of that
+// traffic plus the k7 kernel's store) disappears and the remaining three streams ride under the k7 MMAs.
+// The arithmetic is the unfused kernels' to the bit: same MMA order, h rounded to fp16 before the second MMA, (acc + bias) + x in fp32.
+//
+// CTA = 10 warps, persistent over 128-row tiles, one CTA per SM:
+//   warps 0-7  epilogue: warp w owns TMEM lanes 32 (w & 3).. and the 64-column half (w >> 2) of both accumulators
+//   warp  8    TMA producer: activation slab per tile (double-buffered), weight ring (slot = the two 64-channel k-blocks of a tap;
+//              the k1 weights travel through the same ring, one slot per tile)
+//   warp  9    TMEM allocator + tcgen05.mma issuer.  Issue order  MMA1(0) | MMA1(1) MMA2(0) | MMA1(2) MMA2(1) | ... : the second
+//              MMA of a tile is issued one tile late, so the tensor pipe never waits for the epilogue pass that produces h.
+// Epilogue order per iteration i:  pass 2 of tile i-1 (acc2 -> x', xs -> TMA stores), residual prefetch of tile i (registers),
+// pass 1 of tile i (acc1 -> h in shared memory).  A warp's 32 x 64 block of h is one contiguous 4 KB piece of the K-major
+// SWIZZLE_128B operand image AND exactly a {64, 32} TMA store box, so the same 4 KB stages x' and xs on their way out.
+#include "vae.h"
+#include "gemm.h"
+#include "kernels.h"
+#include "ptx.cuh"
+#include "tmap.h"
+
+#include <cuda.h>
+#include <cstdlib>
+
+namespace ace {
+
+namespace {
+
+constexpr int RU_C = 128;                      // channels in = out
+constexpr int RU_BM = 128;                     // rows per tile
+constexpr int RU_TAPS = 7;
+constexpr int RU_THREADS = 320;
+constexpr int RU_SLAB_MAX_ROWS = 184;          // 128 + 6 x dilation 9 = 182 -> whole 8-row swizzle atoms
+constexpr int RU_PANEL = RU_SLAB_MAX_ROWS * 128;   // one 64-channel panel of a slab (23 KB)
+constexpr int RU_SLAB = 2 * RU_PANEL;
+constexpr int RU_WTILE = 128 * 64 * 2;         // one packed F16 weight tile: 128 output channels x 64 input channels (16 KB)
+constexpr int RU_SLOT = 2 * RU_WTILE;          // ring slot = both k-blocks of a tap
+constexpr int RU_NSLOT = 3;
+constexpr int RU_HTILE = 2 * RU_BM * 128;      // h as MMA operand: two 64-channel panels of 128 rows (32 KB)
+constexpr int RU_COLS = 6 * RU_C * 4;          // bias1, snake2 a, snake2 1/b, bias2, next a, next 1/b
+constexpr int RU_OFF_W = 2 * RU_SLAB;
+constexpr int RU_OFF_H = RU_OFF_W + RU_NSLOT * RU_SLOT;
+constexpr int RU_OFF_COL = RU_OFF_H + RU_HTILE;
+constexpr int RU_OFF_BAR = RU_OFF_COL + RU_COLS;
+constexpr int RU_SMEM = RU_OFF_BAR + 256;
+static_assert(RU_SMEM <= 227 * 1024, "residual-unit kernel exceeds shared memory");
+static_assert(RU_PANEL % 1024 == 0 && RU_OFF_W % 1024 == 0 && RU_OFF_H % 1024 == 0, "swizzled tiles need 1 KB alignment");
+
+struct RuParams {
+    const uint8_t* W1;       // 14 packed tiles (tap-major, two k-blocks per tap)
+    const uint8_t* W2;       // 2 packed tiles
+    const float* cols[6];    // bias1, snake2 alpha, snake2 1/beta, bias2, next alpha, next 1/beta   [128] each
+    const __half* x_in;      // residual stream [B, L, 128]
+    int B, L, m_tiles_per_b, dilation, slab_rows, store_x;
+};
+
+__device__ __forceinline__ float snake_f(float v, float a, float inv_b) {  // gemm_sm100.cu's, to the instruction
+    const float s = __sinf(a * v);
+    return fmaf(s * s, inv_b, v);
+}
+__device__ __forceinline__ uint32_t pack_h2(float a, float b) {
+    const __half2 h = __floats2half2_rn(a, b);
+    return *reinterpret_cast<const uint32_t*>(&h);
+}
+
+__global__ void __launch_bounds__(RU_THREADS, 1)
+vae_resunit128_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmX,
+                      const __grid_constant__ CUtensorMap tmXS, const RuParams p) {
+    extern __shared__ __align__(1024) uint8_t smem[];
+    uint8_t* sSlab = smem;                     // [2][2 panels][184 rows x 128 B]
+    uint8_t* sW = smem + RU_OFF_W;             // [RU_NSLOT][2 x 16 KB]
+    uint8_t* sH = smem + RU_OFF_H;             // [2 panels][128 rows x 128 B]: h, then x' / xs on their way out
+    float* sCol = reinterpret_cast<float*>(smem + RU_OFF_COL);
+    uint64_t* bars = reinterpret_cast<uint64_t*>(smem + RU_OFF_BAR);
+    uint64_t* full = bars;              // [3] weight slot landed
+    uint64_t* empty = bars + 3;         // [3] MMAs reading the slot have completed
+    uint64_t* slab_full = bars + 6;     // [2]
+    uint64_t* slab_empty = bars + 8;    // [2]
+    uint64_t* acc1_full = bars + 10;    // [2]
+    uint64_t* acc1_empty = bars + 12;   // [2] 8 epilogue warps
+    uint64_t* h_ready = bars + 14;      //     8 epilogue warps: h of the tile is in shared memory
+    uint64_t* acc2_full = bars + 15;
+    uint64_t* acc2_empty = bars + 16;   //     8 epilogue warps
+    uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + 17);
+
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    const int total_tiles = p.B * p.m_tiles_per_b;
+
+    if (threadIdx.x == 0) {
+        if ((ptx::smem_u32(smem) & 1023u) != 0) __trap();
+        for (int s = 0; s < RU_NSLOT; ++s) {
+            ptx::mbar_init(&full[s], 1);
+            ptx::mbar_init(&empty[s], 1);
+        }
+        for (int a = 0; a < 2; ++a) {
+            ptx::mbar_init(&slab_full[a], 1);
+            ptx::mbar_init(&slab_empty[a], 1);
+            ptx::mbar_init(&acc1_full[a], 1);
+            ptx::mbar_init(&acc1_empty[a], 8);
+        }
+        ptx::mbar_init(h_ready, 8);
+        ptx::mbar_init(acc2_full, 1);
+        ptx::mbar_init(acc2_empty, 8);
+        ptx::fence_mbar_init();
+    }
+    if (warp == 9) ptx::tmem_alloc<512>(tmem_slot);
+    if (warp == 8 && lane == 0) {
+        ptx::prefetch_tmap(&tmA);
+        ptx::prefetch_tmap(&tmX);
+        ptx::prefetch_tmap(&tmXS);
+    }
+    if (threadIdx.x < RU_C) {  // per-channel constants (weights: not produced by the previous kernel, safe before pdl_wait)
+#pragma unroll
+        for (int k = 0; k < 6; ++k) sCol[k * RU_C + threadIdx.x] = __ldg(p.cols[k] + threadIdx.x);
+    }
+    ptx::tc_fence_before();
+    __syncthreads();
+    ptx::tc_fence_after();
+    const uint32_t tmem_base = *tmem_slot;
+    ptx::pdl_wait();
+    ptx::pdl_launch();
+
+    if (warp == 8) {
+        // ===================== TMA producer =====================
+        uint32_t s = 0, ph = 0;
+        auto ring_load = [&](const uint8_t* src) {
+            ptx::mbar_wait(&empty[s], ph ^ 1);
+            if (ptx::elect_one()) {
+                ptx::mbar_expect_tx(&full[s], RU_SLOT);
+                ptx::bulk_load(sW + s * RU_SLOT, src, RU_WTILE, &full[s]);
+                ptx::bulk_load(sW + s * RU_SLOT + RU_WTILE, src + RU_WTILE, RU_WTILE, &full[s]);
+            }
+            __syncwarp();
+            if (++s == (uint32_t)RU_NSLOT) {
+                s = 0;
+                ph ^= 1;
+            }
+        };
+        const uint32_t panel_bytes = (uint32_t)p.slab_rows * 128u;
+        int it = 0;
+        for (int t = blockIdx.x; t < total_tiles; t += gridDim.x, ++it) {
+            const int b = t / p.m_tiles_per_b, l0 = (t % p.m_tiles_per_b) * RU_BM;
+            const int buf = it & 1;
+            ptx::mbar_wait(&slab_empty[buf], ((it >> 1) & 1) ^ 1);
+            if (ptx::elect_one()) {
+                ptx::mbar_expect_tx(&slab_full[buf], 2 * panel_bytes);
+                ptx::tma_load_3d(sSlab + buf * RU_SLAB, &tmA, &slab_full[buf], 0, l0 - 3 * p.dilation, b);
+                ptx::tma_load_3d(sSlab + buf * RU_SLAB + RU_PANEL, &tmA, &slab_full[buf], 64, l0 - 3 * p.dilation, b);
+            }
+            __syncwarp();
+            for (int tap = 0; tap < RU_TAPS; ++tap) ring_load(p.W1 + (size_t)tap * RU_SLOT);
+            if (it > 0) ring_load(p.W2);   // consumed by MMA2 of the previous tile, issued after this tile's MMA1
+        }
+        if (it > 0) ring_load(p.W2);
+    } else if (warp == 9) {
+        // ===================== MMA issuer (whole warp on uniform values, one elected lane issues) =====================
+        constexpr uint32_t idesc = ptx::umma_idesc_f16(RU_BM, RU_C);
+        const uint32_t tmem_u = __shfl_sync(0xffffffffu, tmem_base, 0);
+        const uint64_t desc_slab0 = ptx::umma_desc_sw128(ptx::smem_u32(sSlab));
+        const uint64_t desc_w0 = ptx::umma_desc_sw128(ptx::smem_u32(sW));
+        const uint64_t desc_h0 = ptx::umma_desc_sw128(ptx::smem_u32(sH));
+        uint32_t s = 0, ph = 0;
+        auto ring_next = [&]() {
+            if (++s == (uint32_t)RU_NSLOT) {
+                s = 0;
+                ph ^= 1;
+            }
+        };
+        auto mma2 = [&](int j) {  // acc2 = h_j . W2^T
+            ptx::mbar_wait(&full[s], ph);
+            ptx::mbar_wait(h_ready, (uint32_t)(j & 1));
+            ptx::mbar_wait(acc2_empty, (uint32_t)((j & 1) ^ 1));
+            ptx::tc_fence_after();
+            const uint64_t db = desc_w0 + (uint64_t)(s * (RU_SLOT >> 4));
+            if (ptx::elect_one()) {
+#pragma unroll
+                for (int kc = 0; kc < 2; ++kc)
+#pragma unroll
+                    for (int k = 0; k < 4; ++k)
+                        ptx::umma_f16(tmem_u + 256u, desc_h0 + (uint64_t)(kc * ((RU_BM * 128) >> 4) + 2 * k),
+                                      db + (uint64_t)(kc * (RU_WTILE >> 4) + 2 * k), idesc, (kc | k) ? 1u : 0u);
+                ptx::umma_commit(&empty[s]);
+                ptx::umma_commit(acc2_full);
+            }
+            __syncwarp();
+            ring_next();
+        };
+        int it = 0;
+        for (int t = blockIdx.x; t < total_tiles; t += gridDim.x, ++it) {
+            const int a = it & 1;
+            ptx::mbar_wait(&acc1_empty[a], (uint32_t)(((it >> 1) & 1) ^ 1));
+            ptx::mbar_wait(&slab_full[a], (uint32_t)((it >> 1) & 1));
+            ptx::tc_fence_after();
+            const uint32_t d_tmem = tmem_u + (uint32_t)(a * RU_C);
+            const uint64_t da0 = desc_slab0 + (uint64_t)(a * (RU_SLAB >> 4));
+            for (int tap = 0; tap < RU_TAPS; ++tap) {
+                ptx::mbar_wait(&full[s], ph);
+                ptx::tc_fence_after();
+                const uint64_t da = da0 + (uint64_t)(tap * p.dilation * 8);   // `dilation` rows of 128 bytes per tap
+                const uint64_t db = desc_w0 + (uint64_t)(s * (RU_SLOT >> 4));
+                if (ptx::elect_one()) {
+#pragma unroll
+                    for (int kc = 0; kc < 2; ++kc)
+#pragma unroll
+                        for (int k = 0; k < 4; ++k)
+                            ptx::umma_f16(d_tmem, da + (uint64_t)(kc * (RU_PANEL >> 4) + 2 * k), db + (uint64_t)(kc * (RU_WTILE >> 4) + 2 * k), idesc,
+                                          (tap | kc | k) ? 1u : 0u);
+                    ptx::umma_commit(&empty[s]);
+                }
+                __syncwarp();
+                ring_next();
+            }
+            if (ptx::elect_one()) {
+                ptx::umma_commit(&acc1_full[a]);
+                ptx::umma_commit(&slab_empty[a]);
+            }
+            __syncwarp();
+            if (it > 0) mma2(it - 1);
+        }
+        if (it > 0) mma2(it - 1);
+    } else {
+        // ===================== epilogue: warps 0..7 =====================
+        const int q = warp & 3, hf = warp >> 2;
+        const int r = q * 32 + lane;
+        uint8_t* slice = sH + hf * (RU_BM * 128) + q * (32 * 128);   // this warp's 32 rows x 64 channels: 4 KB, 1 KB aligned
+        uint8_t* my_row = slice + lane * 128;
+        const int sw = lane & 7;
+        const uint32_t lane_taddr = tmem_base + ((uint32_t)(q * 32) << 16) + (uint32_t)(hf * 64);
+        const float* cB1 = sCol + 0 * RU_C + hf * 64;
+        const float* cA2 = sCol + 1 * RU_C + hf * 64;
+        const float* cI2 = sCol + 2 * RU_C + hf * 64;
+        const float* cB2 = sCol + 3 * RU_C + hf * 64;
+        const float* cAn = sCol + 4 * RU_C + hf * 64;
+        const float* cIn = sCol + 5 * RU_C + hf * 64;
+        uint4 R[8];   // residual x of the tile in flight: this thread's row, 64 channels
+
+        auto pass2 = [&](int j, int b, int l0) {
+            ptx::mbar_wait(acc2_full, (uint32_t)(j & 1));
+            ptx::tc_fence_after();
+            uint32_t v[2][32];
+            ptx::tmem_ld32(lane_taddr + 256u, v[0]);
+            ptx::tmem_ld32(lane_taddr + 256u + 32u, v[1]);
+            ptx::tmem_ld_wait();
+            ptx::tc_fence_before();
+            __syncwarp();
+            if (lane == 0) ptx::mbar_arrive(acc2_empty);
+            uint4 XS[8];
+#pragma unroll
+            for (int g = 0; g < 8; ++g) {   // 16-byte group g: channels 8 g .. 8 g + 7 of this warp's half
+                const uint32_t* vv = &v[g >> 2][(g & 3) * 8];
+                const float4 b0 = *reinterpret_cast<const float4*>(cB2 + 8 * g), b1 = *reinterpret_cast<const float4*>(cB2 + 8 * g + 4);
+                const float4 a0 = *reinterpret_cast<const float4*>(cAn + 8 * g), a1 = *reinterpret_cast<const float4*>(cAn + 8 * g + 4);
+                const float4 i0 = *reinterpret_cast<const float4*>(cIn + 8 * g), i1 = *reinterpret_cast<const float4*>(cIn + 8 * g + 4);
+                const float2 r0 = __half22float2(*reinterpret_cast<const __half2*>(&R[g].x)), r1 = __half22float2(*reinterpret_cast<const __half2*>(&R[g].y));
+                const float2 r2 = __half22float2(*reinterpret_cast<const __half2*>(&R[g].z)), r3 = __half22float2(*reinterpret_cast<const __half2*>(&R[g].w));
+                const float x0 = (__uint_as_float(vv[0]) + b0.x) + r0.x, x1 = (__uint_as_float(vv[1]) + b0.y) + r0.y;
+                const float x2 = (__uint_as_float(vv[2]) + b0.z) + r1.x, x3 = (__uint_as_float(vv[3]) + b0.w) + r1.y;
+                const float x4 = (__uint_as_float(vv[4]) + b1.x) + r2.x, x5 = (__uint_as_float(vv[5]) + b1.y) + r2.y;
+                const float x6 = (__uint_as_float(vv[6]) + b1.z) + r3.x, x7 = (__uint_as_float(vv[7]) + b1.w) + r3.y;
+                if (p.store_x)
+                    *reinterpret_cast<uint4*>(my_row + ((g ^ sw) << 4)) = make_uint4(pack_h2(x0, x1), pack_h2(x2, x3), pack_h2(x4, x5), pack_h2(x6, x7));
+                XS[g] = make_uint4(pack_h2(snake_f(x0, a0.x, i0.x), snake_f(x1, a0.y, i0.y)), pack_h2(snake_f(x2, a0.z, i0.z), snake_f(x3, a0.w, i0.w)),
+                                   pack_h2(snake_f(x4, a1.x, i1.x), snake_f(x5, a1.y, i1.y)), pack_h2(snake_f(x6, a1.z, i1.z), snake_f(x7, a1.w, i1.w)));
+            }
+            const bool rows_in = l0 + q * 32 < p.L;   // warp-uniform: a box entirely below the tensor is not issued
+            if (p.store_x) {
+                ptx::fence_proxy_async_smem();
+                __syncwarp();
+                if (lane == 0 && rows_in) {
+                    ptx::tma_store_3d(&tmX, slice, hf * 64, l0 + q * 32, b);
+                    ptx::bulk_commit();
+                    ptx::bulk_wait_read0();   // the same 4 KB carries xs next
+                }
+                __syncwarp();
+            }
+#pragma unroll
+            for (int g = 0; g < 8; ++g) *reinterpret_cast<uint4*>(my_row + ((g ^ sw) << 4)) = XS[g];
+            ptx::fence_proxy_async_smem();
+            __syncwarp();
+            if (lane == 0 && rows_in) {
+                ptx::tma_store_3d(&tmXS, slice, hf * 64, l0 + q * 32, b);
+                ptx::bulk_commit();
+            }
+        };
+
+        int it = 0, pb = 0, pl0 = 0;
+        for (int t = blockIdx.x; t < total_tiles; t += gridDim.x, ++it) {
+            const int b = t / p.m_tiles_per_b, l0 = (t % p.m_tiles_per_b) * RU_BM;
+            if (it > 0) pass2(it - 1, pb, pl0);
+            {   // residual rows of this tile: in flight under pass 1 and the second MMA
+                const int l = l0 + r;
+                if (l < p.L) {
+                    const uint4* src = reinterpret_cast<const uint4*>(p.x_in + ((long)b * p.L + l) * RU_C + hf * 64);
+#pragma unroll
+                    for (int g = 0; g < 8; ++g) R[g] = src[g];
+                } else {
+#pragma unroll
+                    for (int g = 0; g < 8; ++g) R[g] = make_uint4(0u, 0u, 0u, 0u);
+                }
+            }
+            // ---- pass 1: acc1 -> h = snake2(acc + b1) as the K-major operand of the second MMA
+            const int a = it & 1;
+            ptx::mbar_wait(&acc1_full[a], (uint32_t)((it >> 1) & 1));
+            ptx::tc_fence_after();
+            if (lane == 0) ptx::bulk_wait_read0();   // the previous tile's xs store has read this warp's 4 KB
+            __syncwarp();
+#pragma unroll 1
+            for (int c = 0; c < 2; ++c) {
+                uint32_t v[32];
+                ptx::tmem_ld32(lane_taddr + (uint32_t)(a * RU_C + c * 32), v);
+                ptx::tmem_ld_wait();
+#pragma unroll
+                for (int g = 0; g < 4; ++g) {
+                    const int ch = c * 32 + g * 8;
+                    const float4 b0 = *reinterpret_cast<const float4*>(cB1 + ch), b1 = *reinterpret_cast<const float4*>(cB1 + ch + 4);
+                    const float4 a0 = *reinterpret_cast<const float4*>(cA2 + ch), a1 = *reinterpret_cast<const float4*>(cA2 + ch + 4);
+                    const float4 i0 = *reinterpret_cast<const float4*>(cI2 + ch), i1 = *reinterpret_cast<const float4*>(cI2 + ch + 4);
+                    const uint32_t* vv = &v[g * 8];
+                    const uint4 o = make_uint4(
+                        pack_h2(snake_f(__uint_as_float(vv[0]) + b0.x, a0.x, i0.x), snake_f(__uint_as_float(vv[1]) + b0.y, a0.y, i0.y)),
+                        pack_h2(snake_f(__uint_as_float(vv[2]) + b0.z, a0.z, i0.z), snake_f(__uint_as_float(vv[3]) + b0.w, a0.w, i0.w)),
+                        pack_h2(snake_f(__uint_as_float(vv[4]) + b1.x, a1.x, i1.x), snake_f(__uint_as_float(vv[5]) + b1.y, a1.y, i1.y)),
+                        pack_h2(snake_f(__uint_as_float(vv[6]) + b1.z, a1.z, i1.z), snake_f(__uint_as_float(vv[7]) + b1.w, a1.w, i1.w)));
+                    *reinterpret_cast<uint4*>(my_row + (((c * 4 + g) ^ sw) << 4)) = o;
+                }
+            }
+            ptx::fence_proxy_async_smem();
+            ptx::tc_fence_before();
+            __syncwarp();
+            if (lane == 0) {
+                ptx::mbar_arrive(&acc1_empty[a]);
+                ptx::mbar_arrive(h_ready);
+            }
+            pb = b;
+            pl0 = l0;
+        }
+        if (it > 0) pass2(it - 1, pb, pl0);
+        if (lane == 0) ptx::bulk_wait0();   // every store this thread issued has been performed
+    }
+
+    ptx::tc_fence_before();
+    __syncthreads();
+    if (warp == 9) {
+        ptx::tc_fence_after();
+        ptx::tmem_dealloc<512>(tmem_base);
+    }
+}
+
+}  // namespace
+
+bool vae_resunit128_supported(const VaeResUnit& ru) {
+    const VaeConv &c1 = ru.conv1, &c2 = ru.conv2;
+    return c1.c_in == RU_C && c1.c_out == RU_C && c2.c_in == RU_C && c2.c_out == RU_C && c1.k == RU_TAPS && c2.k == 1 &&
+           c1.w.wtype == W_F16 && c2.w.wtype == W_F16 && c1.w.taps == RU_TAPS && c1.w.kb_per_tap == 2 && c2.w.taps == 1 &&
+           c2.w.kb_per_tap == 2 && c1.w.n_tiles == 1 && c2.w.n_tiles == 1 && c1.dilation >= 1 &&
+           RU_BM + (RU_TAPS - 1) * c1.dilation <= RU_SLAB_MAX_ROWS && c1.pad == 3 * c1.dilation && c1.bias && c2.bias &&
+           ru.snake2.alpha && ru.snake2.inv_beta;
+}
+
+cudaError_t launch_vae_resunit128(const __half* xs_in, const __half* x_in, __half* x_out, __half* xs_out, int B, long L,
+                                  const VaeResUnit& ru, const VaeSnake& next, cudaStream_t st) {
+    if (!vae_resunit128_supported(ru) || !next.alpha || !next.inv_beta || L <= 0 || L > 0x7fffffffL / RU_C || xs_in == xs_out)
+        return cudaErrorInvalidValue;
+    note_launch();
+    const double elems = (double)B * (double)L * RU_C;
+    ProfScope prof_scope(PROF_GEMM, 2.0 * elems * RU_C * (RU_TAPS + 1), (double)ru.conv1.w.bytes + (double)ru.conv2.w.bytes + elems * 2.0 * (x_out ? 4 : 3), st);
+    const int d = ru.conv1.dilation;
+    RuParams p;
+    p.W1 = static_cast<const uint8_t*>(ru.conv1.w.dev);
+    p.W2 = static_cast<const uint8_t*>(ru.conv2.w.dev);
+    p.cols[0] = ru.conv1.bias;
+    p.cols[1] = ru.snake2.alpha;
+    p.cols[2] = ru.snake2.inv_beta;
+    p.cols[3] = ru.conv2.bias;
+    p.cols[4] = next.alpha;
+    p.cols[5] = next.inv_beta;
+    p.x_in = x_in;
+    p.B = B;
+    p.L = (int)L;
+    p.m_tiles_per_b = (int)((L + RU_BM - 1) / RU_BM);
+    p.dilation = d;
+    p.slab_rows = RU_BM + (RU_TAPS - 1) * d;
+    p.store_x = x_out ? 1 : 0;
+    const uint64_t dims[3] = {(uint64_t)RU_C, (uint64_t)L, (uint64_t)B};
+    const uint64_t strides[2] = {(uint64_t)RU_C * 2, (uint64_t)L * RU_C * 2};
+    const uint32_t box_a[3] = {64, (uint32_t)p.slab_rows, 1}, box_o[3] = {64, 32, 1};
+    CUtensorMap tmA, tmX, tmXS;
+    if (!make_tmap_f16_sw128(&tmA, xs_in, 3, dims, strides, box_a) || !make_tmap_f16_sw128(&tmXS, xs_out, 3, dims, strides, box_o) ||
+        !make_tmap_f16_sw128(&tmX, x_out ? x_out : xs_out, 3, dims, strides, box_o))
+        return cudaErrorInvalidValue;
+    static DeviceOnce attr;
+    const cudaError_t ea = attr.run([](int&) { return cudaFuncSetAttribute(vae_resunit128_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, RU_SMEM); });
+    if (ea != cudaSuccess) return ea;
+    const long tiles = (long)B * p.m_tiles_per_b;
+    const int sms = device_sm_count();
+    return launch_pdl(vae_resunit128_kernel, dim3((unsigned)(tiles < sms ? tiles : sms)), dim3(RU_THREADS), (size_t)RU_SMEM, st, tmA, tmX, tmXS, p);
+}
+
+}  // namespace ace

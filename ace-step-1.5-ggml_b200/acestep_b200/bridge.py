@@ -93,6 +93,8 @@ SIGNATURES = {
                                            ctypes.c_size_t]),
     "ace_b200_debug_attention": (ctypes.c_int, [_P, _F, _F, _F, _I, ctypes.c_int32, ctypes.c_int32, ctypes.c_int32,
                                                 ctypes.c_int32, ctypes.c_int32, ctypes.c_int32, _F, ctypes.c_size_t]),
+    "ace_b200_attention_noalloc": (ctypes.c_int, [_P, _F, _F, _F, _I, ctypes.c_int32, ctypes.c_int32, ctypes.c_int32,
+                                                  ctypes.c_int32, ctypes.c_int32, ctypes.c_int32, _F, ctypes.c_size_t]),
     "ace_b200_debug_quantize_rows": (ctypes.c_int, [_F, ctypes.c_int32, ctypes.c_int32, ctypes.c_int32, _P, ctypes.c_size_t]),
     "ace_b200_debug_probe_tensor_file": (ctypes.c_int64, [ctypes.c_char_p, ctypes.c_int32, ctypes.c_char_p, ctypes.c_size_t]),
     "ace_b200_debug_pack_roundtrip": (ctypes.c_int, [_P, ctypes.c_int32, ctypes.c_int32, ctypes.c_int32, _F, _F]),
@@ -477,6 +479,20 @@ class B200Bridge:
                                                int(window), _f(out), out.nbytes)
         self._ensure_ok(st, "ace_b200_debug_attention")
         return out
+
+    def attention_noalloc(self, Q, K, V, key_mask=None, n_heads: int = 1, n_kv: int = 1, window: int = -1):
+        """same kernel and results as debug_attention; scratch = the library's static device array (no cudaMalloc)"""
+        Q, K, V = _f32(Q, 3), _f32(K, 3), _f32(V, 3)
+        km = _i32(key_mask)
+        B, ql, kl = int(Q.shape[0]), int(Q.shape[1]), int(K.shape[1])
+        out = np.empty_like(Q)
+        st = self.lib.ace_b200_attention_noalloc(self.ctx, _f(Q), _f(K), _f(V), _i(km), B, ql, kl, int(n_heads), int(n_kv),
+                                                 int(window), _f(out), out.nbytes)
+        self._ensure_ok(st, "ace_b200_attention_noalloc")
+        return out
+
+
+NOALLOC_SCRATCH_BYTES = 16 << 20  # include/acestep_b200.h: ACE_B200_NOALLOC_SCRATCH_BYTES
 
 
 def pack_roundtrip(W, w_type: int, N: int, K: int, lib: Optional[ctypes.CDLL] = None):

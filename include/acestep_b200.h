@@ -106,6 +106,24 @@ ACE_GGML_API const char * ace_b200_model_info(const ace_ggml_context * ctx);
 ACE_GGML_API void ace_b200_profile_enable(int32_t on);
 ACE_GGML_API void ace_b200_profile_collect(double * ms, double * flops, double * bytes, int64_t * launches);
 
+/* ---- allocation-free variant ------------------------------------------------------------------------------
+ * No counterpart in the reference: added for callers that cannot call
+ * cudaMalloc (code under CUDA-graph capture, tight serving loops, harnesses that forbid it).
+ * ace_b200_attention_noalloc: the same attention kernel, arguments and results as ace_b200_debug_attention below
+ * (Q [B, q_len, n_heads*128], K/V [B, k_len, n_kv*128] fp32, rounded to fp16 inside; key_mask [B, k_len] or NULL;
+ * window < 0 = full; out fp32 [B, q_len, n_heads*128]; the pointers may be host or device memory), but its fp16 operand /
+ * staging scratch is a static device array of ACE_B200_NOALLOC_SCRATCH_BYTES that every GPU loading the library holds
+ * until exit, and it calls no cudaMalloc / cudaFree.  Needs
+ *   4*max(nq, nk) + 4*nq + 4*nk (+ 4*B*k_len with a mask) bytes,  nq = B*q_len*n_heads*128, nk = B*k_len*n_kv*128
+ * (each piece rounded up to 256 B); a larger problem is rejected with ACE_GGML_ERR_INVALID_ARG and a message naming
+ * the need and the limit.  All calls on one GPU share the array (it keeps the last call's contents; every call
+ * overwrites what it reads and clears its output region first): calls that overlap on the same GPU race. */
+#define ACE_B200_NOALLOC_SCRATCH_BYTES ((size_t)16 << 20)
+ACE_GGML_API ace_ggml_status ace_b200_attention_noalloc(ace_ggml_context * ctx, const float * Q, const float * K,
+                                                        const float * V, const int32_t * key_mask, int32_t B,
+                                                        int32_t q_len, int32_t k_len, int32_t n_heads, int32_t n_kv,
+                                                        int32_t window, float * out, size_t out_size);
+
 /* ---- unit-test hooks (tests/ only) -------------------------------------------------------------------------
  * debug_gemm: D[B, l_out, N] = tapGEMM(A fp32 [B, L, C] rounded to fp16, W) through the tensor-core kernel (simt = 0)
  * or the plain-FMA debug kernel (simt = 1).  W is given either as fp32 [N, taps, C] (w_ggml_type = 0 -> F16 tiles,

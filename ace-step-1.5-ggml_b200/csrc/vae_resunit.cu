@@ -251,13 +251,14 @@ vae_resunit128_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_cons
             ptx::tc_fence_before();
             __syncwarp();
             if (lane == 0) ptx::mbar_arrive(acc2_empty);
-            uint4 XS[8];
+            // x' = (acc + b2) + x first (cheap) and on its way out through the TMA; the Snake of the 64 values (the expensive part)
+            // then runs while the TMA reads the slice, so the wait before the slice is re-used for xs is already satisfied
+            // (trace: 1450 cycles of a 9.4 k-cycle epilogue iteration were spent in that wait, another 1150 in pass 1's).
+            const bool rows_in = l0 + q * 32 < p.L;   // warp-uniform: a box entirely below the tensor is not issued
 #pragma unroll
             for (int g = 0; g < 8; ++g) {   // 16-byte group g: channels 8 g .. 8 g + 7 of this warp's half
-                const uint32_t* vv = &v[g >> 2][(g & 3) * 8];
+                uint32_t* vv = &v[g >> 2][(g & 3) * 8];
                 const float4 b0 = *reinterpret_cast<const float4*>(cB2 + 8 * g), b1 = *reinterpret_cast<const float4*>(cB2 + 8 * g + 4);
-                const float4 a0 = *reinterpret_cast<const float4*>(cAn + 8 * g), a1 = *reinterpret_cast<const float4*>(cAn + 8 * g + 4);
-                const float4 i0 = *reinterpret_cast<const float4*>(cIn + 8 * g), i1 = *reinterpret_cast<const float4*>(cIn + 8 * g + 4);
                 const float2 r0 = __half22float2(*reinterpret_cast<const __half2*>(&R[g].x)), r1 = __half22float2(*reinterpret_cast<const __half2*>(&R[g].y));
                 const float2 r2 = __half22float2(*reinterpret_cast<const __half2*>(&R[g].z)), r3 = __half22float2(*reinterpret_cast<const __half2*>(&R[g].w));
                 const float x0 = (__uint_as_float(vv[0]) + b0.x) + r0.x, x1 = (__uint_as_float(vv[1]) + b0.y) + r0.y;
@@ -266,18 +267,30 @@ vae_resunit128_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_cons
                 const float x6 = (__uint_as_float(vv[6]) + b1.z) + r3.x, x7 = (__uint_as_float(vv[7]) + b1.w) + r3.y;
                 if (p.store_x)
                     *reinterpret_cast<uint4*>(my_row + ((g ^ sw) << 4)) = make_uint4(pack_h2(x0, x1), pack_h2(x2, x3), pack_h2(x4, x5), pack_h2(x6, x7));
-                XS[g] = make_uint4(pack_h2(snake_f(x0, a0.x, i0.x), snake_f(x1, a0.y, i0.y)), pack_h2(snake_f(x2, a0.z, i0.z), snake_f(x3, a0.w, i0.w)),
-                                   pack_h2(snake_f(x4, a1.x, i1.x), snake_f(x5, a1.y, i1.y)), pack_h2(snake_f(x6, a1.z, i1.z), snake_f(x7, a1.w, i1.w)));
+                vv[0] = __float_as_uint(x0); vv[1] = __float_as_uint(x1); vv[2] = __float_as_uint(x2); vv[3] = __float_as_uint(x3);
+                vv[4] = __float_as_uint(x4); vv[5] = __float_as_uint(x5); vv[6] = __float_as_uint(x6); vv[7] = __float_as_uint(x7);
             }
-            const bool rows_in = l0 + q * 32 < p.L;   // warp-uniform: a box entirely below the tensor is not issued
             if (p.store_x) {
                 ptx::fence_proxy_async_smem();
                 __syncwarp();
                 if (lane == 0 && rows_in) {
                     ptx::tma_store_3d(&tmX, slice, hf * 64, l0 + q * 32, b);
                     ptx::bulk_commit();
-                    ptx::bulk_wait_read0();   // the same 4 KB carries xs next
                 }
+            }
+            uint4 XS[8];
+#pragma unroll
+            for (int g = 0; g < 8; ++g) {
+                const uint32_t* vv = &v[g >> 2][(g & 3) * 8];
+                const float4 a0 = *reinterpret_cast<const float4*>(cAn + 8 * g), a1 = *reinterpret_cast<const float4*>(cAn + 8 * g + 4);
+                const float4 i0 = *reinterpret_cast<const float4*>(cIn + 8 * g), i1 = *reinterpret_cast<const float4*>(cIn + 8 * g + 4);
+                XS[g] = make_uint4(pack_h2(snake_f(__uint_as_float(vv[0]), a0.x, i0.x), snake_f(__uint_as_float(vv[1]), a0.y, i0.y)),
+                                   pack_h2(snake_f(__uint_as_float(vv[2]), a0.z, i0.z), snake_f(__uint_as_float(vv[3]), a0.w, i0.w)),
+                                   pack_h2(snake_f(__uint_as_float(vv[4]), a1.x, i1.x), snake_f(__uint_as_float(vv[5]), a1.y, i1.y)),
+                                   pack_h2(snake_f(__uint_as_float(vv[6]), a1.z, i1.z), snake_f(__uint_as_float(vv[7]), a1.w, i1.w)));
+            }
+            if (p.store_x) {
+                if (lane == 0) ptx::bulk_wait_read0();   // the x' store has read the slice: the same 4 KB carries xs next
                 __syncwarp();
             }
 #pragma unroll
@@ -309,9 +322,8 @@ vae_resunit128_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_cons
             const int a = it & 1;
             ptx::mbar_wait(&acc1_full[a], (uint32_t)((it >> 1) & 1));
             ptx::tc_fence_after();
-            if (lane == 0) ptx::bulk_wait_read0();   // the previous tile's xs store has read this warp's 4 KB
-            __syncwarp();
-#pragma unroll 1
+            uint4 HP[8];   // h of this thread's row, packed: computed while the previous tile's xs store still reads the slice
+#pragma unroll
             for (int c = 0; c < 2; ++c) {
                 uint32_t v[32];
                 ptx::tmem_ld32(lane_taddr + (uint32_t)(a * RU_C + c * 32), v);
@@ -323,14 +335,17 @@ vae_resunit128_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_cons
                     const float4 a0 = *reinterpret_cast<const float4*>(cA2 + ch), a1 = *reinterpret_cast<const float4*>(cA2 + ch + 4);
                     const float4 i0 = *reinterpret_cast<const float4*>(cI2 + ch), i1 = *reinterpret_cast<const float4*>(cI2 + ch + 4);
                     const uint32_t* vv = &v[g * 8];
-                    const uint4 o = make_uint4(
+                    HP[c * 4 + g] = make_uint4(
                         pack_h2(snake_f(__uint_as_float(vv[0]) + b0.x, a0.x, i0.x), snake_f(__uint_as_float(vv[1]) + b0.y, a0.y, i0.y)),
                         pack_h2(snake_f(__uint_as_float(vv[2]) + b0.z, a0.z, i0.z), snake_f(__uint_as_float(vv[3]) + b0.w, a0.w, i0.w)),
                         pack_h2(snake_f(__uint_as_float(vv[4]) + b1.x, a1.x, i1.x), snake_f(__uint_as_float(vv[5]) + b1.y, a1.y, i1.y)),
                         pack_h2(snake_f(__uint_as_float(vv[6]) + b1.z, a1.z, i1.z), snake_f(__uint_as_float(vv[7]) + b1.w, a1.w, i1.w)));
-                    *reinterpret_cast<uint4*>(my_row + (((c * 4 + g) ^ sw) << 4)) = o;
                 }
             }
+            if (lane == 0) ptx::bulk_wait_read0();   // the previous tile's xs store has read this warp's 4 KB
+            __syncwarp();
+#pragma unroll
+            for (int g = 0; g < 8; ++g) *reinterpret_cast<uint4*>(my_row + ((g ^ sw) << 4)) = HP[g];
             ptx::fence_proxy_async_smem();
             ptx::tc_fence_before();
             __syncwarp();

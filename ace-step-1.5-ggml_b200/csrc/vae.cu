@@ -560,7 +560,7 @@ cudaError_t vae_decode_device(const VaeModel& m, VaeWorkspace& ws, int B, int n_
         run(ws.lat16, (int)L, (int)L, m.conv1, 1, -m.conv1.pad, with_snake(e, m.blocks[0].snake1, 0));
     }
     const int nb = (int)m.blocks.size();
-    const char* fuse_env = std::getenv("ACE_B200_VAE_FUSE");   // 0 = every unit as two GEMM launches (A/B and bisecting aid)
+    const char* fuse_env = std::getenv("ACE_B200_VAE_FUSE");   // 0 = every unit as two GEMM launches, 1 = fused on single CTAs (A/B and bisecting aids)
     const bool fuse_units = !(fuse_env && fuse_env[0] == '0');
     const __half* tail_in = ws.xs;  // input of the final k7 convolution
     for (int i = 0; i < nb; ++i) {

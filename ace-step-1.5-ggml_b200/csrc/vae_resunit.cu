@@ -27,7 +27,9 @@
 #include "tmap.h"
 
 #include <cuda.h>
+#include <cstdio>
 #include <cstdlib>
+#include <vector>
 
 namespace ace {
 
@@ -41,17 +43,27 @@ constexpr int RU_SLAB_MAX_ROWS = 184;          // 128 + 6 x dilation 9 = 182 -> 
 constexpr int RU_PANEL = RU_SLAB_MAX_ROWS * 128;   // one 64-channel panel of a slab (23 KB)
 constexpr int RU_SLAB = 2 * RU_PANEL;
 constexpr int RU_WTILE = 128 * 64 * 2;         // one packed F16 weight tile: 128 output channels x 64 input channels (16 KB)
-constexpr int RU_SLOT = 2 * RU_WTILE;          // ring slot = both k-blocks of a tap
-constexpr int RU_NSLOT = 3;
 constexpr int RU_HTILE = 2 * RU_BM * 128;      // h as MMA operand: two 64-channel panels of 128 rows (32 KB)
 constexpr int RU_COLS = 6 * RU_C * 4;          // bias1, snake2 a, snake2 1/b, bias2, next a, next 1/b
-constexpr int RU_OFF_W = 2 * RU_SLAB;
-constexpr int RU_OFF_H = RU_OFF_W + RU_NSLOT * RU_SLOT;
-constexpr int RU_OFF_COL = RU_OFF_H + RU_HTILE;
-constexpr int RU_OFF_BAR = RU_OFF_COL + RU_COLS;
-constexpr int RU_SMEM = RU_OFF_BAR + 256;
-static_assert(RU_SMEM <= 227 * 1024, "residual-unit kernel exceeds shared memory");
-static_assert(RU_PANEL % 1024 == 0 && RU_OFF_W % 1024 == 0 && RU_OFF_H % 1024 == 0, "swizzled tiles need 1 KB alignment");
+// PAIR = a cluster of two CTAs on cta_group::2 MMAs (M = 256 across the pair): CTA r owns rows l0 + 128 r of a 256-row super tile
+// (its own slab, accumulators, h and stores) and stages only HALF of every weight tile (output channels 64 r ..), the tensor core reads
+// the other half from the peer's shared memory.  The single-CTA kernel re-reads 229 KB of weights per 128-row tile and sits at the L2
+// throughput cap (ncu: 29.6 GB L2 -> SM per launch at 3.9 ms = 7.6 TB/s; ~330 KB per tile against 6300 B/cycle chip-wide);
+// the pair halves the weight bytes per row, and the shared memory it frees holds a separate staging buffer for the stores.
+template <bool PAIR>
+struct RuLayout {
+    static constexpr int WHALF = PAIR ? RU_WTILE / 2 : RU_WTILE;   // bytes of one k-block's weights staged by this CTA
+    static constexpr int SLOT = 2 * WHALF;                         // ring slot = both k-blocks of a tap
+    static constexpr int NSLOT = PAIR ? 4 : 3;
+    static constexpr int OFF_W = 2 * RU_SLAB;
+    static constexpr int OFF_H = OFF_W + NSLOT * SLOT;
+    static constexpr int OFF_STG = OFF_H + RU_HTILE;               // PAIR: store staging of its own (32 KB); else the h slices double as staging
+    static constexpr int OFF_COL = OFF_STG + (PAIR ? RU_HTILE : 0);
+    static constexpr int OFF_BAR = OFF_COL + RU_COLS;
+    static constexpr int SMEM = OFF_BAR + 512;
+    static_assert(SMEM <= 227 * 1024, "residual-unit kernel exceeds shared memory");
+    static_assert(RU_PANEL % 1024 == 0 && OFF_W % 1024 == 0 && OFF_H % 1024 == 0 && OFF_STG % 1024 == 0, "swizzled tiles need 1 KB alignment");
+};
 
 struct RuParams {
     const uint8_t* W1;       // 14 packed tiles (tap-major, two k-blocks per tap)
@@ -59,7 +71,13 @@ struct RuParams {
     const float* cols[6];    // bias1, snake2 alpha, snake2 1/beta, bias2, next alpha, next 1/beta   [128] each
     const __half* x_in;      // residual stream [B, L, 128]
     int B, L, m_tiles_per_b, dilation, slab_rows, store_x;
+    long long* trace;        // debug (ACE_B200_RU_TRACE=1): clock64 stamps of one steady-state tile per CTA, else null
 };
+
+constexpr int RU_TR_N = 32, RU_TR_TILE = 4;   // stamps per CTA; the CTA's 5th work item is the one traced
+__device__ __forceinline__ void ru_stamp(const RuParams& p, int it, int slot) {
+    if (p.trace && it == RU_TR_TILE) p.trace[(size_t)blockIdx.x * RU_TR_N + slot] = clock64();
+}
 
 __device__ __forceinline__ float snake_f(float v, float a, float inv_b) {  // gemm_sm100.cu's, to the instruction
     const float s = __sinf(a * v);
@@ -70,51 +88,74 @@ __device__ __forceinline__ uint32_t pack_h2(float a, float b) {
     return *reinterpret_cast<const uint32_t*>(&h);
 }
 
+template <bool PAIR>
 __global__ void __launch_bounds__(RU_THREADS, 1)
 vae_resunit128_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmX,
-                      const __grid_constant__ CUtensorMap tmXS, const RuParams p) {
+                      const __grid_constant__ CUtensorMap tmXS, const __grid_constant__ CUtensorMap tmR, const RuParams p) {
+    using LY = RuLayout<PAIR>;
+    constexpr int NSLOT = LY::NSLOT;
     extern __shared__ __align__(1024) uint8_t smem[];
     uint8_t* sSlab = smem;                     // [2][2 panels][184 rows x 128 B]
-    uint8_t* sW = smem + RU_OFF_W;             // [RU_NSLOT][2 x 16 KB]
-    uint8_t* sH = smem + RU_OFF_H;             // [2 panels][128 rows x 128 B]: h, then x' / xs on their way out
-    float* sCol = reinterpret_cast<float*>(smem + RU_OFF_COL);
-    uint64_t* bars = reinterpret_cast<uint64_t*>(smem + RU_OFF_BAR);
-    uint64_t* full = bars;              // [3] weight slot landed
-    uint64_t* empty = bars + 3;         // [3] MMAs reading the slot have completed
-    uint64_t* slab_full = bars + 6;     // [2]
-    uint64_t* slab_empty = bars + 8;    // [2]
-    uint64_t* acc1_full = bars + 10;    // [2]
-    uint64_t* acc1_empty = bars + 12;   // [2] 8 epilogue warps
-    uint64_t* h_ready = bars + 14;      //     8 epilogue warps: h of the tile is in shared memory
-    uint64_t* acc2_full = bars + 15;
-    uint64_t* acc2_empty = bars + 16;   //     8 epilogue warps
-    uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + 17);
+    uint8_t* sW = smem + LY::OFF_W;            // [NSLOT][2 k-blocks x WHALF]
+    uint8_t* sH = smem + LY::OFF_H;            // [2 panels][128 rows x 128 B]: h (single CTA: then x' / xs on their way out)
+    uint8_t* sStg = smem + LY::OFF_STG;        // PAIR: x' / xs on their way out, same geometry as sH
+    float* sCol = reinterpret_cast<float*>(smem + LY::OFF_COL);
+    uint64_t* bars = reinterpret_cast<uint64_t*>(smem + LY::OFF_BAR);
+    uint64_t* full = bars;              // [4] weight slot landed (local)
+    uint64_t* empty = bars + 4;         // [4] MMAs reading the slot have completed (PAIR: multicast commit)
+    uint64_t* peer_full = bars + 8;     // [4] leader only: CTA 1's slot landed
+    uint64_t* slab_full = bars + 12;    // [2]
+    uint64_t* slab_empty = bars + 14;   // [2]
+    uint64_t* peer_slab = bars + 16;    // [2] leader only
+    uint64_t* acc1_full = bars + 18;    // [2]
+    uint64_t* acc1_empty = bars + 20;   // [2] leader only in a pair: the epilogue warps of both CTAs
+    uint64_t* h_ready = bars + 22;      //     8 local epilogue warps: h of the tile is in shared memory
+    uint64_t* peer_h = bars + 23;       //     leader only: CTA 1's h
+    uint64_t* acc2_full = bars + 24;
+    uint64_t* acc2_empty = bars + 25;   //     leader only in a pair
+    uint64_t* r_full = bars + 26;       // [8] PAIR: the residual box of epilogue warp w has landed in its staging slice
+    uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + 34);
 
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-    const int total_tiles = p.B * p.m_tiles_per_b;
+    const uint32_t rank = PAIR ? ptx::cluster_ctarank() : 0u;
+    // work items: 128-row tiles (single CTA) or 256-row super tiles (pair; this CTA's rows start at 128 * rank)
+    const int first = PAIR ? (int)(blockIdx.x >> 1) : (int)blockIdx.x;
+    const int stride = PAIR ? (int)(gridDim.x >> 1) : (int)gridDim.x;
+    const int items_per_b = PAIR ? (p.m_tiles_per_b + 1) / 2 : p.m_tiles_per_b;
+    const int total_tiles = p.B * items_per_b;
+    constexpr int ITEM_ROWS = PAIR ? 2 * RU_BM : RU_BM;
+    constexpr int EPI_ARRIVALS = PAIR ? 16 : 8;
 
     if (threadIdx.x == 0) {
         if ((ptx::smem_u32(smem) & 1023u) != 0) __trap();
-        for (int s = 0; s < RU_NSLOT; ++s) {
+        for (int s = 0; s < NSLOT; ++s) {
             ptx::mbar_init(&full[s], 1);
             ptx::mbar_init(&empty[s], 1);
+            ptx::mbar_init(&peer_full[s], 1);
         }
         for (int a = 0; a < 2; ++a) {
             ptx::mbar_init(&slab_full[a], 1);
             ptx::mbar_init(&slab_empty[a], 1);
+            ptx::mbar_init(&peer_slab[a], 1);
             ptx::mbar_init(&acc1_full[a], 1);
-            ptx::mbar_init(&acc1_empty[a], 8);
+            ptx::mbar_init(&acc1_empty[a], EPI_ARRIVALS);
         }
         ptx::mbar_init(h_ready, 8);
+        ptx::mbar_init(peer_h, 1);
         ptx::mbar_init(acc2_full, 1);
-        ptx::mbar_init(acc2_empty, 8);
+        ptx::mbar_init(acc2_empty, EPI_ARRIVALS);
+        for (int w = 0; w < 8; ++w) ptx::mbar_init(&r_full[w], 1);
         ptx::fence_mbar_init();
     }
-    if (warp == 9) ptx::tmem_alloc<512>(tmem_slot);
+    if (warp == 9) {
+        if (PAIR) ptx::tmem_alloc_2cta<512>(tmem_slot);
+        else ptx::tmem_alloc<512>(tmem_slot);
+    }
     if (warp == 8 && lane == 0) {
         ptx::prefetch_tmap(&tmA);
         ptx::prefetch_tmap(&tmX);
         ptx::prefetch_tmap(&tmXS);
+        if (PAIR) ptx::prefetch_tmap(&tmR);
     }
     if (threadIdx.x < RU_C) {  // per-channel constants (weights: not produced by the previous kernel, safe before pdl_wait)
 #pragma unroll
@@ -122,31 +163,38 @@ vae_resunit128_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_cons
     }
     ptx::tc_fence_before();
     __syncthreads();
+    if (PAIR) ptx::cluster_sync();
     ptx::tc_fence_after();
     const uint32_t tmem_base = *tmem_slot;
     ptx::pdl_wait();
     ptx::pdl_launch();
 
+    auto item_coords = [&](int t, int& b, int& l0) {
+        b = t / items_per_b;
+        l0 = (t % items_per_b) * ITEM_ROWS + (int)rank * RU_BM;
+    };
+
     if (warp == 8) {
-        // ===================== TMA producer =====================
+        // ===================== TMA producer (both CTAs of a pair) =====================
         uint32_t s = 0, ph = 0;
-        auto ring_load = [&](const uint8_t* src) {
+        auto ring_load = [&](const uint8_t* src) {   // src: the tap's two 16 KB tiles; a pair CTA takes rows 64 r.. of each (8 KB)
             ptx::mbar_wait(&empty[s], ph ^ 1);
             if (ptx::elect_one()) {
-                ptx::mbar_expect_tx(&full[s], RU_SLOT);
-                ptx::bulk_load(sW + s * RU_SLOT, src, RU_WTILE, &full[s]);
-                ptx::bulk_load(sW + s * RU_SLOT + RU_WTILE, src + RU_WTILE, RU_WTILE, &full[s]);
+                ptx::mbar_expect_tx(&full[s], LY::SLOT);
+                ptx::bulk_load(sW + s * LY::SLOT, src + rank * LY::WHALF, LY::WHALF, &full[s]);
+                ptx::bulk_load(sW + s * LY::SLOT + LY::WHALF, src + RU_WTILE + rank * LY::WHALF, LY::WHALF, &full[s]);
             }
             __syncwarp();
-            if (++s == (uint32_t)RU_NSLOT) {
+            if (++s == (uint32_t)NSLOT) {
                 s = 0;
                 ph ^= 1;
             }
         };
         const uint32_t panel_bytes = (uint32_t)p.slab_rows * 128u;
         int it = 0;
-        for (int t = blockIdx.x; t < total_tiles; t += gridDim.x, ++it) {
-            const int b = t / p.m_tiles_per_b, l0 = (t % p.m_tiles_per_b) * RU_BM;
+        for (int t = first; t < total_tiles; t += stride, ++it) {
+            int b, l0;
+            item_coords(t, b, l0);
             const int buf = it & 1;
             ptx::mbar_wait(&slab_empty[buf], ((it >> 1) & 1) ^ 1);
             if (ptx::elect_one()) {
@@ -155,83 +203,134 @@ vae_resunit128_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_cons
                 ptx::tma_load_3d(sSlab + buf * RU_SLAB + RU_PANEL, &tmA, &slab_full[buf], 64, l0 - 3 * p.dilation, b);
             }
             __syncwarp();
-            for (int tap = 0; tap < RU_TAPS; ++tap) ring_load(p.W1 + (size_t)tap * RU_SLOT);
+            for (int tap = 0; tap < RU_TAPS; ++tap) ring_load(p.W1 + (size_t)tap * (2 * RU_WTILE));
             if (it > 0) ring_load(p.W2);   // consumed by MMA2 of the previous tile, issued after this tile's MMA1
         }
         if (it > 0) ring_load(p.W2);
-    } else if (warp == 9) {
-        // ===================== MMA issuer (whole warp on uniform values, one elected lane issues) =====================
-        constexpr uint32_t idesc = ptx::umma_idesc_f16(RU_BM, RU_C);
+    } else if (warp == 9 && rank == 0) {
+        // ===================== MMA issuer (leader; whole warp on uniform values, one elected lane issues) =====================
+        constexpr uint32_t idesc = ptx::umma_idesc_f16(PAIR ? 2 * RU_BM : RU_BM, RU_C);
         const uint32_t tmem_u = __shfl_sync(0xffffffffu, tmem_base, 0);
         const uint64_t desc_slab0 = ptx::umma_desc_sw128(ptx::smem_u32(sSlab));
         const uint64_t desc_w0 = ptx::umma_desc_sw128(ptx::smem_u32(sW));
         const uint64_t desc_h0 = ptx::umma_desc_sw128(ptx::smem_u32(sH));
+        auto mma = [&](uint32_t d, uint64_t da, uint64_t db, uint32_t acc) {
+            if (PAIR) ptx::umma_f16_2cta(d, da, db, idesc, acc);
+            else ptx::umma_f16(d, da, db, idesc, acc);
+        };
+        auto commit = [&](uint64_t* bar) {   // PAIR: arrives on the barrier at this offset in BOTH CTAs
+            if (PAIR) ptx::umma_commit_2cta(bar, 3);
+            else ptx::umma_commit(bar);
+        };
         uint32_t s = 0, ph = 0;
         auto ring_next = [&]() {
-            if (++s == (uint32_t)RU_NSLOT) {
+            if (++s == (uint32_t)NSLOT) {
                 s = 0;
                 ph ^= 1;
             }
         };
         auto mma2 = [&](int j) {  // acc2 = h_j . W2^T
             ptx::mbar_wait(&full[s], ph);
+            if (PAIR) ptx::mbar_wait(&peer_full[s], ph);
+            if (lane == 0) ru_stamp(p, j + 1, 4);
             ptx::mbar_wait(h_ready, (uint32_t)(j & 1));
+            if (PAIR) ptx::mbar_wait(peer_h, (uint32_t)(j & 1));
+            if (lane == 0) ru_stamp(p, j + 1, 5);
             ptx::mbar_wait(acc2_empty, (uint32_t)((j & 1) ^ 1));
             ptx::tc_fence_after();
-            const uint64_t db = desc_w0 + (uint64_t)(s * (RU_SLOT >> 4));
+            const uint64_t db = desc_w0 + (uint64_t)(s * (LY::SLOT >> 4));
             if (ptx::elect_one()) {
 #pragma unroll
                 for (int kc = 0; kc < 2; ++kc)
 #pragma unroll
                     for (int k = 0; k < 4; ++k)
-                        ptx::umma_f16(tmem_u + 256u, desc_h0 + (uint64_t)(kc * ((RU_BM * 128) >> 4) + 2 * k),
-                                      db + (uint64_t)(kc * (RU_WTILE >> 4) + 2 * k), idesc, (kc | k) ? 1u : 0u);
-                ptx::umma_commit(&empty[s]);
-                ptx::umma_commit(acc2_full);
+                        mma(tmem_u + 256u, desc_h0 + (uint64_t)(kc * ((RU_BM * 128) >> 4) + 2 * k), db + (uint64_t)(kc * (LY::WHALF >> 4) + 2 * k),
+                            (kc | k) ? 1u : 0u);
+                commit(&empty[s]);
+                commit(acc2_full);
             }
             __syncwarp();
             ring_next();
         };
         int it = 0;
-        for (int t = blockIdx.x; t < total_tiles; t += gridDim.x, ++it) {
+        for (int t = first; t < total_tiles; t += stride, ++it) {
             const int a = it & 1;
+            if (lane == 0) ru_stamp(p, it, 0);
             ptx::mbar_wait(&acc1_empty[a], (uint32_t)(((it >> 1) & 1) ^ 1));
+            if (lane == 0) ru_stamp(p, it, 1);
             ptx::mbar_wait(&slab_full[a], (uint32_t)((it >> 1) & 1));
+            if (PAIR) ptx::mbar_wait(&peer_slab[a], (uint32_t)((it >> 1) & 1));
             ptx::tc_fence_after();
+            if (lane == 0) ru_stamp(p, it, 2);
             const uint32_t d_tmem = tmem_u + (uint32_t)(a * RU_C);
             const uint64_t da0 = desc_slab0 + (uint64_t)(a * (RU_SLAB >> 4));
             for (int tap = 0; tap < RU_TAPS; ++tap) {
                 ptx::mbar_wait(&full[s], ph);
+                if (PAIR) ptx::mbar_wait(&peer_full[s], ph);
                 ptx::tc_fence_after();
                 const uint64_t da = da0 + (uint64_t)(tap * p.dilation * 8);   // `dilation` rows of 128 bytes per tap
-                const uint64_t db = desc_w0 + (uint64_t)(s * (RU_SLOT >> 4));
+                const uint64_t db = desc_w0 + (uint64_t)(s * (LY::SLOT >> 4));
                 if (ptx::elect_one()) {
 #pragma unroll
                     for (int kc = 0; kc < 2; ++kc)
 #pragma unroll
                         for (int k = 0; k < 4; ++k)
-                            ptx::umma_f16(d_tmem, da + (uint64_t)(kc * (RU_PANEL >> 4) + 2 * k), db + (uint64_t)(kc * (RU_WTILE >> 4) + 2 * k), idesc,
-                                          (tap | kc | k) ? 1u : 0u);
-                    ptx::umma_commit(&empty[s]);
+                            mma(d_tmem, da + (uint64_t)(kc * (RU_PANEL >> 4) + 2 * k), db + (uint64_t)(kc * (LY::WHALF >> 4) + 2 * k), (tap | kc | k) ? 1u : 0u);
+                    commit(&empty[s]);
                 }
                 __syncwarp();
                 ring_next();
             }
             if (ptx::elect_one()) {
-                ptx::umma_commit(&acc1_full[a]);
-                ptx::umma_commit(&slab_empty[a]);
+                commit(&acc1_full[a]);
+                commit(&slab_empty[a]);
             }
             __syncwarp();
+            if (lane == 0) ru_stamp(p, it, 3);
             if (it > 0) mma2(it - 1);
+            if (lane == 0) ru_stamp(p, it, 6);
         }
         if (it > 0) mma2(it - 1);
+    } else if (warp == 9) {
+        // ===================== relay (CTA 1 of a pair): local "landed / written" -> the leader's peer barriers, in the leader's order ====
+        if (lane == 0) {
+            uint32_t s = 0, ph = 0;
+            auto relay_slot = [&]() {
+                ptx::mbar_wait(&full[s], ph);
+                ptx::mbar_arrive_cluster(ptx::mapa(&peer_full[s], 0));
+                if (++s == (uint32_t)NSLOT) {
+                    s = 0;
+                    ph ^= 1;
+                }
+            };
+            auto relay_h = [&](int j) {
+                relay_slot();   // the W2 slot
+                ptx::mbar_wait(h_ready, (uint32_t)(j & 1));
+                ptx::mbar_arrive_cluster(ptx::mapa(peer_h, 0));
+            };
+            int it = 0;
+            for (int t = first; t < total_tiles; t += stride, ++it) {
+                const int a = it & 1;
+                ptx::mbar_wait(&slab_full[a], (uint32_t)((it >> 1) & 1));
+                ptx::mbar_arrive_cluster(ptx::mapa(&peer_slab[a], 0));
+                for (int tap = 0; tap < RU_TAPS; ++tap) relay_slot();
+                if (it > 0) relay_h(it - 1);
+            }
+            if (it > 0) relay_h(it - 1);
+        }
     } else {
         // ===================== epilogue: warps 0..7 =====================
         const int q = warp & 3, hf = warp >> 2;
         const int r = q * 32 + lane;
-        uint8_t* slice = sH + hf * (RU_BM * 128) + q * (32 * 128);   // this warp's 32 rows x 64 channels: 4 KB, 1 KB aligned
-        uint8_t* my_row = slice + lane * 128;
+        const int slice_off = hf * (RU_BM * 128) + q * (32 * 128);   // this warp's 32 rows x 64 channels: 4 KB, 1 KB aligned
+        uint8_t* my_row = sH + slice_off + lane * 128;               // h
+        uint8_t* slice = (PAIR ? sStg : sH) + slice_off;             // x' / xs on their way out
+        uint8_t* out_row = slice + lane * 128;
         const int sw = lane & 7;
+        auto arrive_leader = [&](uint64_t* bar) {   // barriers the MMA issuer waits on live in the leader CTA
+            if (PAIR) ptx::mbar_arrive_cluster(ptx::mapa(bar, 0));
+            else ptx::mbar_arrive(bar);
+        };
         const uint32_t lane_taddr = tmem_base + ((uint32_t)(q * 32) << 16) + (uint32_t)(hf * 64);
         const float* cB1 = sCol + 0 * RU_C + hf * 64;
         const float* cA2 = sCol + 1 * RU_C + hf * 64;
@@ -241,20 +340,32 @@ vae_resunit128_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_cons
         const float* cIn = sCol + 5 * RU_C + hf * 64;
         uint4 R[8];   // residual x of the tile in flight: this thread's row, 64 channels
 
+        const bool tr = warp == 0 && lane == 0;
         auto pass2 = [&](int j, int b, int l0) {
+            if (tr) ru_stamp(p, j + 1, 8);
             ptx::mbar_wait(acc2_full, (uint32_t)(j & 1));
             ptx::tc_fence_after();
+            if (tr) ru_stamp(p, j + 1, 9);
             uint32_t v[2][32];
             ptx::tmem_ld32(lane_taddr + 256u, v[0]);
             ptx::tmem_ld32(lane_taddr + 256u + 32u, v[1]);
             ptx::tmem_ld_wait();
             ptx::tc_fence_before();
             __syncwarp();
-            if (lane == 0) ptx::mbar_arrive(acc2_empty);
+            if (lane == 0) arrive_leader(acc2_empty);
+            if (tr) ru_stamp(p, j + 1, 10);
             // x' = (acc + b2) + x first (cheap) and on its way out through the TMA; the Snake of the 64 values (the expensive part)
             // then runs while the TMA reads the slice, so the wait before the slice is re-used for xs is already satisfied
             // (trace: 1450 cycles of a 9.4 k-cycle epilogue iteration were spent in that wait, another 1150 in pass 1's).
             const bool rows_in = l0 + q * 32 < p.L;   // warp-uniform: a box entirely below the tensor is not issued
+            if (PAIR) {
+                // the residual rows arrived as one TMA box in this warp's staging slice (issued in pass 1).  Per-thread global loads of
+                // a row each (8 x LDG.128 at a 256-byte lane stride) cost 32 LSU passes per instruction: ~2 k cycles per tile for the
+                // eight warps (trace), against 8 conflict-free LDS.128 here.  Each thread reads and later overwrites only its own row.
+                ptx::mbar_wait(&r_full[warp], (uint32_t)(j & 1));
+#pragma unroll
+                for (int g = 0; g < 8; ++g) R[g] = *reinterpret_cast<const uint4*>(out_row + ((g ^ sw) << 4));
+            }
 #pragma unroll
             for (int g = 0; g < 8; ++g) {   // 16-byte group g: channels 8 g .. 8 g + 7 of this warp's half
                 uint32_t* vv = &v[g >> 2][(g & 3) * 8];
@@ -266,11 +377,11 @@ vae_resunit128_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_cons
                 const float x4 = (__uint_as_float(vv[4]) + b1.x) + r2.x, x5 = (__uint_as_float(vv[5]) + b1.y) + r2.y;
                 const float x6 = (__uint_as_float(vv[6]) + b1.z) + r3.x, x7 = (__uint_as_float(vv[7]) + b1.w) + r3.y;
                 if (p.store_x)
-                    *reinterpret_cast<uint4*>(my_row + ((g ^ sw) << 4)) = make_uint4(pack_h2(x0, x1), pack_h2(x2, x3), pack_h2(x4, x5), pack_h2(x6, x7));
+                    *reinterpret_cast<uint4*>(out_row + ((g ^ sw) << 4)) = make_uint4(pack_h2(x0, x1), pack_h2(x2, x3), pack_h2(x4, x5), pack_h2(x6, x7));
                 vv[0] = __float_as_uint(x0); vv[1] = __float_as_uint(x1); vv[2] = __float_as_uint(x2); vv[3] = __float_as_uint(x3);
                 vv[4] = __float_as_uint(x4); vv[5] = __float_as_uint(x5); vv[6] = __float_as_uint(x6); vv[7] = __float_as_uint(x7);
             }
-            if (p.store_x) {
+            if (p.store_x && !PAIR) {
                 ptx::fence_proxy_async_smem();
                 __syncwarp();
                 if (lane == 0 && rows_in) {
@@ -278,6 +389,7 @@ vae_resunit128_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_cons
                     ptx::bulk_commit();
                 }
             }
+            if (tr) ru_stamp(p, j + 1, 11);
             uint4 XS[8];
 #pragma unroll
             for (int g = 0; g < 8; ++g) {
@@ -289,25 +401,44 @@ vae_resunit128_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_cons
                                    pack_h2(snake_f(__uint_as_float(vv[4]), a1.x, i1.x), snake_f(__uint_as_float(vv[5]), a1.y, i1.y)),
                                    pack_h2(snake_f(__uint_as_float(vv[6]), a1.z, i1.z), snake_f(__uint_as_float(vv[7]), a1.w, i1.w)));
             }
+            if (tr) ru_stamp(p, j + 1, 12);
+            if (PAIR) {
+                // x' sits in the staging slice, xs goes through the h slice (free: the second MMA of this tile has completed): one
+                // proxy fence and one bulk group for both stores; pass 1 of the next tile waits for their reads before it re-uses either
+#pragma unroll
+                for (int g = 0; g < 8; ++g) *reinterpret_cast<uint4*>(my_row + ((g ^ sw) << 4)) = XS[g];
+                ptx::fence_proxy_async_smem();
+                __syncwarp();
+                if (lane == 0 && rows_in) {
+                    if (p.store_x) ptx::tma_store_3d(&tmX, slice, hf * 64, l0 + q * 32, b);
+                    ptx::tma_store_3d(&tmXS, sH + slice_off, hf * 64, l0 + q * 32, b);
+                    ptx::bulk_commit();
+                }
+                if (tr) ru_stamp(p, j + 1, 14);
+                return;
+            }
             if (p.store_x) {
                 if (lane == 0) ptx::bulk_wait_read0();   // the x' store has read the slice: the same 4 KB carries xs next
                 __syncwarp();
             }
+            if (tr) ru_stamp(p, j + 1, 13);
 #pragma unroll
-            for (int g = 0; g < 8; ++g) *reinterpret_cast<uint4*>(my_row + ((g ^ sw) << 4)) = XS[g];
+            for (int g = 0; g < 8; ++g) *reinterpret_cast<uint4*>(out_row + ((g ^ sw) << 4)) = XS[g];
             ptx::fence_proxy_async_smem();
             __syncwarp();
             if (lane == 0 && rows_in) {
                 ptx::tma_store_3d(&tmXS, slice, hf * 64, l0 + q * 32, b);
                 ptx::bulk_commit();
             }
+            if (tr) ru_stamp(p, j + 1, 14);
         };
 
         int it = 0, pb = 0, pl0 = 0;
-        for (int t = blockIdx.x; t < total_tiles; t += gridDim.x, ++it) {
-            const int b = t / p.m_tiles_per_b, l0 = (t % p.m_tiles_per_b) * RU_BM;
+        for (int t = first; t < total_tiles; t += stride, ++it) {
+            int b, l0;
+            item_coords(t, b, l0);
             if (it > 0) pass2(it - 1, pb, pl0);
-            {   // residual rows of this tile: in flight under pass 1 and the second MMA
+            if (!PAIR) {   // residual rows of this tile: in flight under pass 1 and the second MMA
                 const int l = l0 + r;
                 if (l < p.L) {
                     const uint4* src = reinterpret_cast<const uint4*>(p.x_in + ((long)b * p.L + l) * RU_C + hf * 64);
@@ -320,8 +451,10 @@ vae_resunit128_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_cons
             }
             // ---- pass 1: acc1 -> h = snake2(acc + b1) as the K-major operand of the second MMA
             const int a = it & 1;
+            if (tr) ru_stamp(p, it, 15);
             ptx::mbar_wait(&acc1_full[a], (uint32_t)((it >> 1) & 1));
             ptx::tc_fence_after();
+            if (tr) ru_stamp(p, it, 16);
             uint4 HP[8];   // h of this thread's row, packed: computed while the previous tile's xs store still reads the slice
 #pragma unroll
             for (int c = 0; c < 2; ++c) {
@@ -342,7 +475,16 @@ vae_resunit128_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_cons
                         pack_h2(snake_f(__uint_as_float(vv[6]) + b1.z, a1.z, i1.z), snake_f(__uint_as_float(vv[7]) + b1.w, a1.w, i1.w)));
                 }
             }
-            if (lane == 0) ptx::bulk_wait_read0();   // the previous tile's xs store has read this warp's 4 KB
+            if (tr) ru_stamp(p, it, 17);
+            // the previous tile's stores have read this warp's slices (single CTA: the h slice doubles as store staging; pair: h slice = xs,
+            // staging slice = x', which now takes this tile's residual rows)
+            if (lane == 0) {
+                ptx::bulk_wait_read0();
+                if (PAIR) {
+                    ptx::mbar_expect_tx(&r_full[warp], 32 * 128);
+                    ptx::tma_load_3d(slice, &tmR, &r_full[warp], hf * 64, l0 + q * 32, b);
+                }
+            }
             __syncwarp();
 #pragma unroll
             for (int g = 0; g < 8; ++g) *reinterpret_cast<uint4*>(my_row + ((g ^ sw) << 4)) = HP[g];
@@ -350,9 +492,10 @@ vae_resunit128_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_cons
             ptx::tc_fence_before();
             __syncwarp();
             if (lane == 0) {
-                ptx::mbar_arrive(&acc1_empty[a]);
-                ptx::mbar_arrive(h_ready);
+                arrive_leader(&acc1_empty[a]);
+                ptx::mbar_arrive(h_ready);   // local: the leader's issuer waits on it directly, CTA 1's relay forwards it
             }
+            if (tr) ru_stamp(p, it, 18);
             pb = b;
             pl0 = l0;
         }
@@ -362,9 +505,11 @@ vae_resunit128_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_cons
 
     ptx::tc_fence_before();
     __syncthreads();
+    if (PAIR) ptx::cluster_sync();   // the peer's shared memory / barriers stay alive until every MMA and remote arrive has landed
     if (warp == 9) {
         ptx::tc_fence_after();
-        ptx::tmem_dealloc<512>(tmem_base);
+        if (PAIR) ptx::tmem_dealloc_2cta<512>(tmem_base);
+        else ptx::tmem_dealloc<512>(tmem_base);
     }
 }
 
@@ -406,16 +551,92 @@ cudaError_t launch_vae_resunit128(const __half* xs_in, const __half* x_in, __hal
     const uint64_t dims[3] = {(uint64_t)RU_C, (uint64_t)L, (uint64_t)B};
     const uint64_t strides[2] = {(uint64_t)RU_C * 2, (uint64_t)L * RU_C * 2};
     const uint32_t box_a[3] = {64, (uint32_t)p.slab_rows, 1}, box_o[3] = {64, 32, 1};
-    CUtensorMap tmA, tmX, tmXS;
+    CUtensorMap tmA, tmX, tmXS, tmR;
     if (!make_tmap_f16_sw128(&tmA, xs_in, 3, dims, strides, box_a) || !make_tmap_f16_sw128(&tmXS, xs_out, 3, dims, strides, box_o) ||
-        !make_tmap_f16_sw128(&tmX, x_out ? x_out : xs_out, 3, dims, strides, box_o))
+        !make_tmap_f16_sw128(&tmX, x_out ? x_out : xs_out, 3, dims, strides, box_o) || !make_tmap_f16_sw128(&tmR, x_in, 3, dims, strides, box_o))
         return cudaErrorInvalidValue;
-    static DeviceOnce attr;
-    const cudaError_t ea = attr.run([](int&) { return cudaFuncSetAttribute(vae_resunit128_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, RU_SMEM); });
+    // one-time per device: shared-memory attributes, and how many CTA pairs can be co-resident (0: clusters unavailable -> single CTA)
+    static DeviceOnce setup;
+    int max_pairs = 0;
+    const cudaError_t ea = setup.run([](int& n) {
+        cudaError_t e = cudaFuncSetAttribute(vae_resunit128_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, RuLayout<false>::SMEM);
+        if (e != cudaSuccess) return e;
+        n = 0;
+        if (cudaFuncSetAttribute(vae_resunit128_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, RuLayout<true>::SMEM) == cudaSuccess) {
+            cudaLaunchConfig_t cfg = {};
+            cfg.gridDim = dim3(2 * 148);
+            cfg.blockDim = dim3(RU_THREADS);
+            cfg.dynamicSmemBytes = RuLayout<true>::SMEM;
+            cudaLaunchAttribute at[1];
+            at[0].id = cudaLaunchAttributeClusterDimension;
+            at[0].val.clusterDim.x = 2;
+            at[0].val.clusterDim.y = 1;
+            at[0].val.clusterDim.z = 1;
+            cfg.attrs = at;
+            cfg.numAttrs = 1;
+            int c = 0;
+            if (cudaOccupancyMaxActiveClusters(&c, vae_resunit128_kernel<true>, &cfg) == cudaSuccess) n = c;
+            else cudaGetLastError();
+        } else cudaGetLastError();
+        return cudaSuccess;
+    }, &max_pairs);
     if (ea != cudaSuccess) return ea;
     const long tiles = (long)B * p.m_tiles_per_b;
     const int sms = device_sm_count();
-    return launch_pdl(vae_resunit128_kernel, dim3((unsigned)(tiles < sms ? tiles : sms)), dim3(RU_THREADS), (size_t)RU_SMEM, st, tmA, tmX, tmXS, p);
+    // ACE_B200_VAE_FUSE=1: single-CTA kernel (A/B and bisecting aid); default: CTA pairs where the device co-schedules enough of them
+    const char* fe = std::getenv("ACE_B200_VAE_FUSE");
+    const bool pair = !(fe && fe[0] == '1') && max_pairs >= 8 && tiles >= 2;
+    p.trace = nullptr;
+    struct TraceDump {   // debug aid: synchronous, prints the mean timeline of one work item of the leader CTAs
+        long long* buf = nullptr; int ctas = 0, step = 1; cudaStream_t st = nullptr; long L = 0; int d = 0, sx = 0, pair = 0;
+        ~TraceDump() {
+            if (!buf) return;
+            cudaStreamSynchronize(st);
+            std::vector<long long> h((size_t)ctas * RU_TR_N);
+            cudaMemcpy(h.data(), buf, h.size() * sizeof(long long), cudaMemcpyDeviceToHost);
+            cudaFree(buf);
+            double m[RU_TR_N] = {0};
+            int n = 0;
+            for (int c = 0; c < ctas; c += step, ++n)
+                for (int i = 0; i < RU_TR_N; ++i) m[i] += (double)(h[(size_t)c * RU_TR_N + i] - h[(size_t)c * RU_TR_N]);
+            for (double& v : m) v /= n;
+            std::fprintf(stderr, "[resunit trace] L=%ld d=%d store_x=%d pair=%d | issuer, cycles from reaching item %d: acc1 free %.0f, slab %.0f, MMA1 issued %.0f, "
+                                 "W2 slot %.0f, h ready %.0f, MMA2 issued %.0f\n", L, d, sx, pair, RU_TR_TILE, m[1], m[2], m[3], m[4], m[5], m[6]);
+            std::fprintf(stderr, "                 epilogue warp 0: pass2(prev) enters %.0f, acc2 ready %.0f, loaded %.0f, x' out %.0f, snake done %.0f, slice free %.0f, "
+                                 "xs out %.0f | pass1 enters %.0f, acc1 ready %.0f, h computed %.0f, h written %.0f\n", m[8], m[9], m[10], m[11], m[12], m[13], m[14],
+                         m[15], m[16], m[17], m[18]);
+        }
+    } trace_dump;
+    {
+        const long items = pair ? (long)B * ((p.m_tiles_per_b + 1) / 2) : tiles;
+        const int ctas = pair ? 2 * max_pairs : sms;
+        if (std::getenv("ACE_B200_RU_TRACE") && items >= (long)(RU_TR_TILE + 2) * (pair ? max_pairs : sms)) {
+            if (cudaMalloc(&trace_dump.buf, (size_t)ctas * RU_TR_N * sizeof(long long)) != cudaSuccess) return cudaErrorMemoryAllocation;
+            cudaMemsetAsync(trace_dump.buf, 0, (size_t)ctas * RU_TR_N * sizeof(long long), st);
+            p.trace = trace_dump.buf;
+            trace_dump.ctas = ctas; trace_dump.step = pair ? 2 : 1; trace_dump.st = st; trace_dump.L = L; trace_dump.d = d; trace_dump.sx = p.store_x; trace_dump.pair = pair;
+        }
+    }
+    if (pair) {
+        const long items = (long)B * ((p.m_tiles_per_b + 1) / 2);
+        cudaLaunchConfig_t cfg = {};
+        cfg.gridDim = dim3((unsigned)(2 * (items < max_pairs ? items : max_pairs)));
+        cfg.blockDim = dim3(RU_THREADS);
+        cfg.dynamicSmemBytes = RuLayout<true>::SMEM;
+        cfg.stream = st;
+        cudaLaunchAttribute at[2];
+        at[0].id = cudaLaunchAttributeClusterDimension;
+        at[0].val.clusterDim.x = 2;
+        at[0].val.clusterDim.y = 1;
+        at[0].val.clusterDim.z = 1;
+        at[1].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+        at[1].val.programmaticStreamSerializationAllowed = 1;
+        cfg.attrs = at;
+        cfg.numAttrs = pdl_enabled() ? 2 : 1;
+        return cudaLaunchKernelEx(&cfg, vae_resunit128_kernel<true>, tmA, tmX, tmXS, tmR, p);
+    }
+    return launch_pdl(vae_resunit128_kernel<false>, dim3((unsigned)(tiles < sms ? tiles : sms)), dim3(RU_THREADS), (size_t)RuLayout<false>::SMEM, st, tmA, tmX,
+                      tmXS, tmR, p);
 }
 
 }  // namespace ace

@@ -153,15 +153,20 @@ def test_vae_full_waveform(br, n_frames):
     assert m["cos"] >= 0.9999 and m["snr_db"] >= 40.0, m
 
 
-@pytest.mark.parametrize("n_frames,batch", [(9, 2), (40, 1)])
+@pytest.mark.parametrize("n_frames,batch", [(9, 2), (40, 1), (3, 1)])
 def test_vae_fused_residual_units_equal_the_two_launch_route(br, n_frames, batch, monkeypatch):
     """The 128-channel residual units run as ONE launch (vae_resunit.cu: k7 conv -> Snake -> k1 conv -> + x -> Snake, h kept in shared
-    memory); ACE_B200_VAE_FUSE=0 runs them as two tap-GEMM launches.  Same MMA order, same roundings: the waveforms are bit-identical.
-    9 frames: 8640 / 17280 positions per level (ragged last tile, one tile per CTA); 40 frames: 300 / 600 tiles (several per CTA)."""
+    memory), by default on CTA pairs (cta_group::2, each CTA stages half of every weight tile), with ACE_B200_VAE_FUSE=1 on single
+    CTAs; ACE_B200_VAE_FUSE=0 runs them as two tap-GEMM launches.  Same MMA order, same roundings: the waveforms are bit-identical.
+    9 frames: 8640 / 17280 positions per level (ragged last tile; 67.5 tiles = an odd count, so the last pair has an idle second CTA);
+    40 frames: 300 / 600 tiles (several per CTA); 3 frames: fewer super tiles than clusters."""
     br.load_vae(full_vae_dir())
     lat = np.stack([fx.vae_latents(fx.VAE_FULL, n_frames, seed=11 + b) for b in range(batch)])
-    fused = br.vae_decode_batched(lat)
+    pair = br.vae_decode_batched(lat)
+    monkeypatch.setenv("ACE_B200_VAE_FUSE", "1")
+    single = br.vae_decode_batched(lat)
     monkeypatch.setenv("ACE_B200_VAE_FUSE", "0")
     plain = br.vae_decode_batched(lat)
-    assert np.isfinite(fused).all()
-    assert np.array_equal(fused, plain), metrics(fused, plain)
+    assert np.isfinite(pair).all()
+    assert np.array_equal(single, plain), metrics(single, plain)
+    assert np.array_equal(pair, plain), metrics(pair, plain)

@@ -57,7 +57,7 @@ struct RuLayout {
     static constexpr int NSLOT = PAIR ? 4 : 3;
     static constexpr int OFF_W = 2 * RU_SLAB;
     static constexpr int OFF_H = OFF_W + NSLOT * SLOT;
-    static constexpr int OFF_STG = OFF_H + RU_HTILE;               // PAIR: store staging of its own (32 KB); else the h slices double as staging
+    static constexpr int OFF_STG = OFF_H + RU_HTILE;               // PAIR: landing buffer of the residual boxes (32 KB)
     static constexpr int OFF_COL = OFF_STG + (PAIR ? RU_HTILE : 0);
     static constexpr int OFF_BAR = OFF_COL + RU_COLS;
     static constexpr int SMEM = OFF_BAR + 512;
@@ -97,8 +97,8 @@ vae_resunit128_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_cons
     extern __shared__ __align__(1024) uint8_t smem[];
     uint8_t* sSlab = smem;                     // [2][2 panels][184 rows x 128 B]
     uint8_t* sW = smem + LY::OFF_W;            // [NSLOT][2 k-blocks x WHALF]
-    uint8_t* sH = smem + LY::OFF_H;            // [2 panels][128 rows x 128 B]: h (single CTA: then x' / xs on their way out)
-    uint8_t* sStg = smem + LY::OFF_STG;        // PAIR: x' / xs on their way out, same geometry as sH
+    uint8_t* sH = smem + LY::OFF_H;            // [2 panels][128 rows x 128 B]: single CTA: h, then x' / xs on their way out; PAIR (h lives in tensor memory): x' / xs only
+    uint8_t* sStg = smem + LY::OFF_STG;        // PAIR: residual rows as they land, same geometry as sH
     float* sCol = reinterpret_cast<float*>(smem + LY::OFF_COL);
     uint64_t* bars = reinterpret_cast<uint64_t*>(smem + LY::OFF_BAR);
     uint64_t* full = bars;              // [4] weight slot landed (local)
@@ -191,19 +191,28 @@ vae_resunit128_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_cons
             }
         };
         const uint32_t panel_bytes = (uint32_t)p.slab_rows * 128u;
-        int it = 0;
-        for (int t = first; t < total_tiles; t += stride, ++it) {
+        auto slab_load = [&](int i, int t) {   // activation slab of the CTA's i-th item
             int b, l0;
             item_coords(t, b, l0);
-            const int buf = it & 1;
-            ptx::mbar_wait(&slab_empty[buf], ((it >> 1) & 1) ^ 1);
+            const int buf = i & 1;
+            ptx::mbar_wait(&slab_empty[buf], ((i >> 1) & 1) ^ 1);
             if (ptx::elect_one()) {
                 ptx::mbar_expect_tx(&slab_full[buf], 2 * panel_bytes);
                 ptx::tma_load_3d(sSlab + buf * RU_SLAB, &tmA, &slab_full[buf], 0, l0 - 3 * p.dilation, b);
                 ptx::tma_load_3d(sSlab + buf * RU_SLAB + RU_PANEL, &tmA, &slab_full[buf], 64, l0 - 3 * p.dilation, b);
             }
             __syncwarp();
-            for (int tap = 0; tap < RU_TAPS; ++tap) ring_load(p.W1 + (size_t)tap * (2 * RU_WTILE));
+        };
+        // The slab of item i + 1 is requested in the MIDDLE of item i's weight loads: the first NSLOT of those run ahead of the tensor
+        // core, the next one waits for the first tap of item i to be consumed — by then MMA1(i - 1) has released the slab buffer.
+        // Requested after ALL of item i's weights (program order of one thread) the slab arrived 1-2 k cycles late (trace).
+        int it = 0;
+        if (first < total_tiles) slab_load(0, first);
+        for (int t = first; t < total_tiles; t += stride, ++it) {
+            for (int tap = 0; tap < RU_TAPS; ++tap) {
+                ring_load(p.W1 + (size_t)tap * (2 * RU_WTILE));
+                if (tap == NSLOT && t + stride < total_tiles) slab_load(it + 1, t + stride);
+            }
             if (it > 0) ring_load(p.W2);   // consumed by MMA2 of the previous tile, issued after this tile's MMA1
         }
         if (it > 0) ring_load(p.W2);
@@ -243,9 +252,13 @@ vae_resunit128_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_cons
 #pragma unroll
                 for (int kc = 0; kc < 2; ++kc)
 #pragma unroll
-                    for (int k = 0; k < 4; ++k)
-                        mma(tmem_u + 256u, desc_h0 + (uint64_t)(kc * ((RU_BM * 128) >> 4) + 2 * k), db + (uint64_t)(kc * (LY::WHALF >> 4) + 2 * k),
-                            (kc | k) ? 1u : 0u);
+                    for (int k = 0; k < 4; ++k) {
+                        const uint64_t dbk = db + (uint64_t)(kc * (LY::WHALF >> 4) + 2 * k);
+                        if (PAIR)   // A = h_j from tensor memory: 16 channels = 8 packed columns per step
+                            ptx::umma_f16_ts_2cta(tmem_u + 256u, tmem_u + 384u + (uint32_t)((j & 1) * 64 + (kc * 4 + k) * 8), dbk, idesc, (kc | k) ? 1u : 0u);
+                        else
+                            mma(tmem_u + 256u, desc_h0 + (uint64_t)(kc * ((RU_BM * 128) >> 4) + 2 * k), dbk, (kc | k) ? 1u : 0u);
+                    }
                 commit(&empty[s]);
                 commit(acc2_full);
             }
@@ -323,9 +336,10 @@ vae_resunit128_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_cons
         const int q = warp & 3, hf = warp >> 2;
         const int r = q * 32 + lane;
         const int slice_off = hf * (RU_BM * 128) + q * (32 * 128);   // this warp's 32 rows x 64 channels: 4 KB, 1 KB aligned
-        uint8_t* my_row = sH + slice_off + lane * 128;               // h
-        uint8_t* slice = (PAIR ? sStg : sH) + slice_off;             // x' / xs on their way out
-        uint8_t* out_row = slice + lane * 128;
+        uint8_t* slice = sH + slice_off;                             // single CTA: h, then x' / xs on their way out; pair: x' / xs only
+        uint8_t* my_row = slice + lane * 128;
+        uint8_t* r_slice = sStg + slice_off;                         // pair: landing buffer of the residual box
+        const uint8_t* r_row = r_slice + lane * 128;
         const int sw = lane & 7;
         auto arrive_leader = [&](uint64_t* bar) {   // barriers the MMA issuer waits on live in the leader CTA
             if (PAIR) ptx::mbar_arrive_cluster(ptx::mapa(bar, 0));
@@ -341,7 +355,20 @@ vae_resunit128_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_cons
         uint4 R[8];   // residual x of the tile in flight: this thread's row, 64 channels
 
         const bool tr = warp == 0 && lane == 0;
-        auto pass2 = [&](int j, int b, int l0) {
+        // residual box of an item's rows into this warp's landing slice (pair).  Per-thread global loads of a row each (8 x LDG.128 at a
+        // 256-byte lane stride) cost 32 LSU passes per instruction, ~2 k cycles per tile for the eight warps (trace); the box costs one
+        // TMA instruction and 8 conflict-free LDS.128.  It is requested a whole iteration before it is read: under the producer's
+        // slab / weight traffic a 4 KB box took ~2.5 k cycles to land.
+        auto issue_residual = [&](int b, int l0) {
+            if (lane == 0) {
+                ptx::mbar_expect_tx(&r_full[warp], 32 * 128);
+                ptx::tma_load_3d(r_slice, &tmR, &r_full[warp], hf * 64, l0 + q * 32, b);
+            }
+        };
+        // ---- pass 2 of item j: acc2 -> x' = (acc + b2) + x -> fp16 out; xs = snake_next(x') -> fp16 out.  x' is staged and handed to the
+        // TMA first, the Snake of the 64 values (the expensive part) runs while the TMA reads the slice, then xs re-uses the slice.
+        // `fetch_next`: request the residual rows of item j + 1 (coordinates nb, nl0) as soon as this item's have been read.
+        auto pass2 = [&](int j, int b, int l0, bool fetch_next, int nb, int nl0) {
             if (tr) ru_stamp(p, j + 1, 8);
             ptx::mbar_wait(acc2_full, (uint32_t)(j & 1));
             ptx::tc_fence_after();
@@ -354,17 +381,16 @@ vae_resunit128_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_cons
             __syncwarp();
             if (lane == 0) arrive_leader(acc2_empty);
             if (tr) ru_stamp(p, j + 1, 10);
-            // x' = (acc + b2) + x first (cheap) and on its way out through the TMA; the Snake of the 64 values (the expensive part)
-            // then runs while the TMA reads the slice, so the wait before the slice is re-used for xs is already satisfied
-            // (trace: 1450 cycles of a 9.4 k-cycle epilogue iteration were spent in that wait, another 1150 in pass 1's).
             const bool rows_in = l0 + q * 32 < p.L;   // warp-uniform: a box entirely below the tensor is not issued
             if (PAIR) {
-                // the residual rows arrived as one TMA box in this warp's staging slice (issued in pass 1).  Per-thread global loads of
-                // a row each (8 x LDG.128 at a 256-byte lane stride) cost 32 LSU passes per instruction: ~2 k cycles per tile for the
-                // eight warps (trace), against 8 conflict-free LDS.128 here.  Each thread reads and later overwrites only its own row.
                 ptx::mbar_wait(&r_full[warp], (uint32_t)(j & 1));
 #pragma unroll
-                for (int g = 0; g < 8; ++g) R[g] = *reinterpret_cast<const uint4*>(out_row + ((g ^ sw) << 4));
+                for (int g = 0; g < 8; ++g) R[g] = *reinterpret_cast<const uint4*>(r_row + ((g ^ sw) << 4));
+                __syncwarp();   // every lane has read its row
+                if (fetch_next) issue_residual(nb, nl0);
+                if (lane == 0) ptx::bulk_wait_read0();   // the previous item's xs store has read the slice (issued an iteration ago)
+                __syncwarp();
+                if (tr) ru_stamp(p, j + 1, 13);
             }
 #pragma unroll
             for (int g = 0; g < 8; ++g) {   // 16-byte group g: channels 8 g .. 8 g + 7 of this warp's half
@@ -377,11 +403,11 @@ vae_resunit128_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_cons
                 const float x4 = (__uint_as_float(vv[4]) + b1.x) + r2.x, x5 = (__uint_as_float(vv[5]) + b1.y) + r2.y;
                 const float x6 = (__uint_as_float(vv[6]) + b1.z) + r3.x, x7 = (__uint_as_float(vv[7]) + b1.w) + r3.y;
                 if (p.store_x)
-                    *reinterpret_cast<uint4*>(out_row + ((g ^ sw) << 4)) = make_uint4(pack_h2(x0, x1), pack_h2(x2, x3), pack_h2(x4, x5), pack_h2(x6, x7));
+                    *reinterpret_cast<uint4*>(my_row + ((g ^ sw) << 4)) = make_uint4(pack_h2(x0, x1), pack_h2(x2, x3), pack_h2(x4, x5), pack_h2(x6, x7));
                 vv[0] = __float_as_uint(x0); vv[1] = __float_as_uint(x1); vv[2] = __float_as_uint(x2); vv[3] = __float_as_uint(x3);
                 vv[4] = __float_as_uint(x4); vv[5] = __float_as_uint(x5); vv[6] = __float_as_uint(x6); vv[7] = __float_as_uint(x7);
             }
-            if (p.store_x && !PAIR) {
+            if (p.store_x) {
                 ptx::fence_proxy_async_smem();
                 __syncwarp();
                 if (lane == 0 && rows_in) {
@@ -402,28 +428,12 @@ vae_resunit128_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_cons
                                    pack_h2(snake_f(__uint_as_float(vv[6]), a1.z, i1.z), snake_f(__uint_as_float(vv[7]), a1.w, i1.w)));
             }
             if (tr) ru_stamp(p, j + 1, 12);
-            if (PAIR) {
-                // x' sits in the staging slice, xs goes through the h slice (free: the second MMA of this tile has completed): one
-                // proxy fence and one bulk group for both stores; pass 1 of the next tile waits for their reads before it re-uses either
-#pragma unroll
-                for (int g = 0; g < 8; ++g) *reinterpret_cast<uint4*>(my_row + ((g ^ sw) << 4)) = XS[g];
-                ptx::fence_proxy_async_smem();
-                __syncwarp();
-                if (lane == 0 && rows_in) {
-                    if (p.store_x) ptx::tma_store_3d(&tmX, slice, hf * 64, l0 + q * 32, b);
-                    ptx::tma_store_3d(&tmXS, sH + slice_off, hf * 64, l0 + q * 32, b);
-                    ptx::bulk_commit();
-                }
-                if (tr) ru_stamp(p, j + 1, 14);
-                return;
-            }
             if (p.store_x) {
                 if (lane == 0) ptx::bulk_wait_read0();   // the x' store has read the slice: the same 4 KB carries xs next
                 __syncwarp();
             }
-            if (tr) ru_stamp(p, j + 1, 13);
 #pragma unroll
-            for (int g = 0; g < 8; ++g) *reinterpret_cast<uint4*>(out_row + ((g ^ sw) << 4)) = XS[g];
+            for (int g = 0; g < 8; ++g) *reinterpret_cast<uint4*>(my_row + ((g ^ sw) << 4)) = XS[g];
             ptx::fence_proxy_async_smem();
             __syncwarp();
             if (lane == 0 && rows_in) {
@@ -433,29 +443,16 @@ vae_resunit128_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_cons
             if (tr) ru_stamp(p, j + 1, 14);
         };
 
-        int it = 0, pb = 0, pl0 = 0;
-        for (int t = first; t < total_tiles; t += stride, ++it) {
-            int b, l0;
-            item_coords(t, b, l0);
-            if (it > 0) pass2(it - 1, pb, pl0);
-            if (!PAIR) {   // residual rows of this tile: in flight under pass 1 and the second MMA
-                const int l = l0 + r;
-                if (l < p.L) {
-                    const uint4* src = reinterpret_cast<const uint4*>(p.x_in + ((long)b * p.L + l) * RU_C + hf * 64);
-#pragma unroll
-                    for (int g = 0; g < 8; ++g) R[g] = src[g];
-                } else {
-#pragma unroll
-                    for (int g = 0; g < 8; ++g) R[g] = make_uint4(0u, 0u, 0u, 0u);
-                }
-            }
-            // ---- pass 1: acc1 -> h = snake2(acc + b1) as the K-major operand of the second MMA
-            const int a = it & 1;
-            if (tr) ru_stamp(p, it, 15);
-            ptx::mbar_wait(&acc1_full[a], (uint32_t)((it >> 1) & 1));
+        // ---- pass 1: acc1 -> h = snake2(acc + b1), the A operand of the second MMA.  Single CTA: K-major image in shared memory.
+        // Pair: fp16 pairs in tensor memory (64 columns, double-buffered by item parity), so the pass neither waits for the second MMA
+        // of the previous item to release a buffer nor needs a proxy fence.
+        auto pass1 = [&](int i) {
+            const int a = i & 1;
+            if (tr) ru_stamp(p, i, 15);
+            ptx::mbar_wait(&acc1_full[a], (uint32_t)((i >> 1) & 1));
             ptx::tc_fence_after();
-            if (tr) ru_stamp(p, it, 16);
-            uint4 HP[8];   // h of this thread's row, packed: computed while the previous tile's xs store still reads the slice
+            if (tr) ru_stamp(p, i, 16);
+            uint32_t HP[32];   // h of this thread's row, packed: 64 channels
 #pragma unroll
             for (int c = 0; c < 2; ++c) {
                 uint32_t v[32];
@@ -468,38 +465,69 @@ vae_resunit128_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_cons
                     const float4 a0 = *reinterpret_cast<const float4*>(cA2 + ch), a1 = *reinterpret_cast<const float4*>(cA2 + ch + 4);
                     const float4 i0 = *reinterpret_cast<const float4*>(cI2 + ch), i1 = *reinterpret_cast<const float4*>(cI2 + ch + 4);
                     const uint32_t* vv = &v[g * 8];
-                    HP[c * 4 + g] = make_uint4(
-                        pack_h2(snake_f(__uint_as_float(vv[0]) + b0.x, a0.x, i0.x), snake_f(__uint_as_float(vv[1]) + b0.y, a0.y, i0.y)),
-                        pack_h2(snake_f(__uint_as_float(vv[2]) + b0.z, a0.z, i0.z), snake_f(__uint_as_float(vv[3]) + b0.w, a0.w, i0.w)),
-                        pack_h2(snake_f(__uint_as_float(vv[4]) + b1.x, a1.x, i1.x), snake_f(__uint_as_float(vv[5]) + b1.y, a1.y, i1.y)),
-                        pack_h2(snake_f(__uint_as_float(vv[6]) + b1.z, a1.z, i1.z), snake_f(__uint_as_float(vv[7]) + b1.w, a1.w, i1.w)));
+                    uint32_t* o = &HP[(c * 4 + g) * 4];
+                    o[0] = pack_h2(snake_f(__uint_as_float(vv[0]) + b0.x, a0.x, i0.x), snake_f(__uint_as_float(vv[1]) + b0.y, a0.y, i0.y));
+                    o[1] = pack_h2(snake_f(__uint_as_float(vv[2]) + b0.z, a0.z, i0.z), snake_f(__uint_as_float(vv[3]) + b0.w, a0.w, i0.w));
+                    o[2] = pack_h2(snake_f(__uint_as_float(vv[4]) + b1.x, a1.x, i1.x), snake_f(__uint_as_float(vv[5]) + b1.y, a1.y, i1.y));
+                    o[3] = pack_h2(snake_f(__uint_as_float(vv[6]) + b1.z, a1.z, i1.z), snake_f(__uint_as_float(vv[7]) + b1.w, a1.w, i1.w));
                 }
             }
-            if (tr) ru_stamp(p, it, 17);
-            // the previous tile's stores have read this warp's slices (single CTA: the h slice doubles as store staging; pair: h slice = xs,
-            // staging slice = x', which now takes this tile's residual rows)
-            if (lane == 0) {
-                ptx::bulk_wait_read0();
-                if (PAIR) {
-                    ptx::mbar_expect_tx(&r_full[warp], 32 * 128);
-                    ptx::tma_load_3d(slice, &tmR, &r_full[warp], hf * 64, l0 + q * 32, b);
-                }
-            }
-            __syncwarp();
+            if (tr) ru_stamp(p, i, 17);
+            if (PAIR) {
+                ptx::tmem_st32(tmem_base + ((uint32_t)(q * 32) << 16) + 384u + (uint32_t)(a * 64 + hf * 32), HP);
+                ptx::tmem_st_wait();
+            } else {
+                // the previous tile's xs store has read this warp's 4 KB (the h slice doubles as store staging)
+                if (lane == 0) ptx::bulk_wait_read0();
+                __syncwarp();
 #pragma unroll
-            for (int g = 0; g < 8; ++g) *reinterpret_cast<uint4*>(my_row + ((g ^ sw) << 4)) = HP[g];
-            ptx::fence_proxy_async_smem();
+                for (int g = 0; g < 8; ++g)
+                    *reinterpret_cast<uint4*>(my_row + ((g ^ sw) << 4)) = make_uint4(HP[4 * g], HP[4 * g + 1], HP[4 * g + 2], HP[4 * g + 3]);
+                ptx::fence_proxy_async_smem();
+            }
             ptx::tc_fence_before();
             __syncwarp();
             if (lane == 0) {
                 arrive_leader(&acc1_empty[a]);
                 ptx::mbar_arrive(h_ready);   // local: the leader's issuer waits on it directly, CTA 1's relay forwards it
             }
-            if (tr) ru_stamp(p, it, 18);
+            if (tr) ru_stamp(p, i, 18);
+        };
+
+        int it = 0, pb = 0, pl0 = 0;
+        if (PAIR && first < total_tiles) {
+            int b, l0;
+            item_coords(first, b, l0);
+            issue_residual(b, l0);
+        }
+        for (int t = first; t < total_tiles; t += stride, ++it) {
+            int b, l0;
+            item_coords(t, b, l0);
+            if (PAIR) {
+                // pass 1 of this item first, then pass 2 of the previous one: the second MMA of the previous item (issued when ITS pass 1
+                // finished, one iteration ago) has long completed, where the order pass 2 -> pass 1 put its ~1.5 k cycles of issue +
+                // execution latency on the epilogue's critical path every iteration (trace: acc2 wait 1470 of 7600 cycles)
+                pass1(it);
+                if (it > 0) pass2(it - 1, pb, pl0, true, b, l0);
+            } else {
+                if (it > 0) pass2(it - 1, pb, pl0, false, 0, 0);
+                {   // residual rows of this tile: in flight under pass 1 and the second MMA
+                    const int l = l0 + r;
+                    if (l < p.L) {
+                        const uint4* src = reinterpret_cast<const uint4*>(p.x_in + ((long)b * p.L + l) * RU_C + hf * 64);
+#pragma unroll
+                        for (int g = 0; g < 8; ++g) R[g] = src[g];
+                    } else {
+#pragma unroll
+                        for (int g = 0; g < 8; ++g) R[g] = make_uint4(0u, 0u, 0u, 0u);
+                    }
+                }
+                pass1(it);
+            }
             pb = b;
             pl0 = l0;
         }
-        if (it > 0) pass2(it - 1, pb, pl0);
+        if (it > 0) pass2(it - 1, pb, pl0, false, 0, 0);
         if (lane == 0) ptx::bulk_wait0();   // every store this thread issued has been performed
     }
 
@@ -602,7 +630,7 @@ cudaError_t launch_vae_resunit128(const __half* xs_in, const __half* x_in, __hal
             for (double& v : m) v /= n;
             std::fprintf(stderr, "[resunit trace] L=%ld d=%d store_x=%d pair=%d | issuer, cycles from reaching item %d: acc1 free %.0f, slab %.0f, MMA1 issued %.0f, "
                                  "W2 slot %.0f, h ready %.0f, MMA2 issued %.0f\n", L, d, sx, pair, RU_TR_TILE, m[1], m[2], m[3], m[4], m[5], m[6]);
-            std::fprintf(stderr, "                 epilogue warp 0: pass2(prev) enters %.0f, acc2 ready %.0f, loaded %.0f, x' out %.0f, snake done %.0f, slice free %.0f, "
+            std::fprintf(stderr, "                 epilogue warp 0: pass2(prev) enters %.0f, acc2 ready %.0f, loaded %.0f, x' out %.0f, snake done %.0f, slice free / residual landed %.0f, "
                                  "xs out %.0f | pass1 enters %.0f, acc1 ready %.0f, h computed %.0f, h written %.0f\n", m[8], m[9], m[10], m[11], m[12], m[13], m[14],
                          m[15], m[16], m[17], m[18]);
         }

@@ -1,0 +1,191 @@
+"""Size-independent properties at BASELINE.json's FULL sizes — the shapes the CPU reference cannot run to completion (configs[2]: Q4_K,
+240 s, 24 layers at S = 3000 needs ~90 GB of score tensors on the host; configs[3]: one 600 s clip; configs[4]: 50 steps x CFG), so the
+GPU path is held to identities that must be true whatever the numbers are.  The reference semantics each identity restates:
+
+  * samples of a batch are independent (acestep_ggml.cpp:1304-1482 evaluates one sample per call; ace_b200_dit_forward_batched must
+    therefore equal B single calls, and a sample's result must not depend on who shares its batch);
+  * CFG `v = v_u + g (v_c - v_u)` at g = 1 is the conditional velocity, and with identical branches it is that velocity
+    for EVERY g — so the 2B-sample CFG sampler must reproduce the plain sampler;
+  * the device-resident sampler is the host loop `x <- x - v dt` of acestep_ggml.cpp:2056-2086 around ace_ggml_dit_forward;
+  * masked (padded) frames do not influence unmasked ones (build_attention_mask, acestep_dit_model.cpp:1132-1173);
+  * the VAE decoder is a convolution stack with a 9.5-frame receptive field (acestep_vae_model.cpp:957-1002): a window decoded with a
+    16-frame halo equals the same frames of the whole clip — what the chunk/overlap policy of acestep_ggml.cpp:2114-2229 and the
+    8-GPU time split rely on — and clips of a batch are independent.
+
+Bounds: where both sides run the same kernels on the same rows the comparison is bit-exact or <= 1e-6; where the batch shape changes
+the launch geometry (K split of the accumulating epilogues, fp32 reduction order) the bound is 2e-5 relative (fp32 re-association
+through 24 layers), two orders of magnitude below the parity tolerance."""
+import numpy as np
+import pytest
+
+from tools import fixtures as fx
+from parity_common import full_vae_dir, metrics, shift_schedule, turbo_dit_dir
+
+pytestmark = pytest.mark.gpu
+
+REASSOC = 2e-5     # fp32 re-association across launch geometries
+T240, T120, E = 6000, 3000, 512
+
+
+@pytest.fixture(scope="module")
+def br():
+    from acestep_b200.bridge import B200Bridge
+    b = B200Bridge()
+    yield b
+    b.close()
+
+
+def batch_inputs(n, T, seed0=1234):
+    inp = [fx.dit_inputs(fx.TURBO, T, E, seed=seed0 + i) for i in range(n)]
+    return (np.stack([i["hidden_states"] for i in inp]), np.stack([i["context_latents"] for i in inp]),
+            np.stack([i["encoder_hidden_states"] for i in inp]))
+
+
+# ---------------------------------------------------------------- configs[2]: Q4_K, 240 s, full depth
+
+@pytest.fixture(scope="module")
+def q4k(br):
+    d = turbo_dit_dir("Q4_K")
+    br.load_dit(d)
+    return d
+
+
+def test_config2_batched_forward_equals_single_calls(br, q4k):
+    """3 songs at T = 6000 through ONE batched forward (M = 9000 rows per GEMM) against three ace_ggml_dit_forward calls (M = 3000)."""
+    br.load_dit(q4k)
+    h, c, e = batch_inputs(3, T240)
+    ts = [1.0, 0.7, 0.3]
+    vb = br.dit_forward_batched(h, c, e, None, None, ts, ts)
+    assert np.isfinite(vb).all() and float(np.abs(vb).mean()) > 1e-3
+    for b in range(3):
+        v1 = br.dit_forward_tfirst(h[b], c[b], e[b], None, None, ts[b], ts[b])
+        m = metrics(vb[b], v1)
+        assert m["rel_l2"] <= REASSOC, (b, m)
+    # a sample's result does not depend on its neighbours: same sample 0, different company
+    h2, c2, e2 = h.copy(), c.copy(), e.copy()
+    h2[1:] *= -3.0
+    e2[1:] = 0.0
+    vb2 = br.dit_forward_batched(h2, c2, e2, None, None, ts, ts)
+    assert np.array_equal(vb2[0], vb[0])
+
+
+def test_config2_cfg_sampler_identities(br, q4k):
+    """8-step shift-3 sampler, 2 songs at T = 6000: guidance 1 with a zero unconditional branch, and guidance 7 with the unconditional
+    branch EQUAL to the conditional one, both reduce to the plain sampler (v_u + g (v_c - v_u) = v_c)."""
+    br.load_dit(q4k)
+    h, c, e = batch_inputs(2, T240)
+    sch = br.shift_schedule(3.0, 8)
+    assert np.allclose(sch, shift_schedule(3.0, 8), rtol=0, atol=1e-7)
+    plain = br.generate_latents(h, c, e, None, schedule=sch, guidance=1.0)
+    assert np.isfinite(plain).all()
+    g1 = br.generate_latents(h, c, e, np.zeros_like(e), schedule=sch, guidance=1.0)
+    m = metrics(g1, plain)
+    assert m["rel_l2"] <= REASSOC, m            # v_u + (v_c - v_u) re-associates in fp32, nothing more
+    same = br.generate_latents(h, c, e, e.copy(), schedule=sch, guidance=7.0)
+    m = metrics(same, plain)
+    assert m["rel_l2"] <= REASSOC, m            # v_c - v_u = 0 exactly when both branches see the same rows
+    # and the guided result differs from the plain one by far more than either bound (the combine is not a no-op)
+    g7 = br.generate_latents(h, c, e, np.zeros_like(e), schedule=sch, guidance=7.0)
+    assert metrics(g7, plain)["rel_l2"] > 1e-2
+
+
+def test_config2_device_sampler_equals_host_loop(br, q4k):
+    """ace_b200_generate_latents (device-resident Euler loop) against the reference's host loop driven through ace_ggml_dit_forward
+    (acestep_ggml.cpp:2056-2086: x -= v (t_i - t_{i+1}); last step x -= v t_i)."""
+    br.load_dit(q4k)
+    h, c, e = batch_inputs(1, T240, seed0=77)
+    sch = br.shift_schedule(3.0, 8)
+    dev = br.generate_latents(h, c, e, None, schedule=sch, guidance=1.0)[0]
+    x = h[0].copy()
+    for i, t in enumerate(sch):
+        v = br.dit_forward_tfirst(x, c[0], e[0], None, None, float(t), float(t))
+        dt = np.float32(t - sch[i + 1]) if i + 1 < len(sch) else np.float32(t)
+        x = x - v * dt
+    m = metrics(dev, x)
+    assert m["rel_l2"] <= REASSOC, m
+
+
+def test_config2_padded_frames_do_not_leak(br, q4k):
+    """T = 6000 with the last 1000 frames masked out: the velocities of the kept frames do not depend on what the padded frames hold."""
+    br.load_dit(q4k)
+    h, c, e = batch_inputs(1, T240, seed0=5)
+    mask = np.ones((1, T240), np.int32)
+    mask[:, 5000:] = 0
+    va = br.dit_forward_batched(h, c, e, mask, None, [0.6], [0.6])
+    h2, c2 = h.copy(), c.copy()
+    h2[:, 5000:] = 11.0
+    c2[:, 5000:, :64] = -7.0
+    vb = br.dit_forward_batched(h2, c2, e, mask, None, [0.6], [0.6])
+    assert np.isfinite(va).all()
+    m = metrics(vb[:, :4990], va[:, :4990])   # frames 4990.. share a 2-frame patch / a conv tap with the padding
+    assert m["rel_l2"] <= 1e-6, m
+
+
+# ---------------------------------------------------------------- configs[4]: Q8_0, 120 s, 50-step closed-form schedule with CFG
+
+def test_config4_50_step_cfg_sampler_equals_host_loop(br):
+    """50 steps x (cond + uncond) at T = 3000 on the device against 100 single ace_ggml_dit_forward calls combined on the host."""
+    br.load_dit(turbo_dit_dir("Q8_0"))
+    h, c, e = batch_inputs(1, T120, seed0=21)
+    sch = br.shift_schedule(3.0, 50)
+    assert np.allclose(sch, shift_schedule(3.0, 50), rtol=0, atol=1e-7)
+    un = np.zeros_like(e)
+    dev = br.generate_latents(h, c, e, un, schedule=sch, guidance=7.0)[0]
+    x = h[0].copy()
+    for i, t in enumerate(sch):
+        vc = br.dit_forward_tfirst(x, c[0], e[0], None, None, float(t), float(t))
+        vu = br.dit_forward_tfirst(x, c[0], un[0], None, None, float(t), float(t))
+        v = vu + np.float32(7.0) * (vc - vu)
+        dt = np.float32(t - sch[i + 1]) if i + 1 < len(sch) else np.float32(t)
+        x = x - v * dt
+    m = metrics(dev, x)
+    assert np.isfinite(dev).all()
+    assert m["rel_l2"] <= 50 * REASSOC, m      # 50 guided steps amplify the per-step re-association noise; parity tolerance is 2e-2
+
+
+# ---------------------------------------------------------------- configs[3]: VAE decode of one 600 s clip
+
+@pytest.fixture(scope="module")
+def clip600(br):
+    br.load_vae(full_vae_dir())
+    lat = fx.vae_latents(fx.VAE_FULL, 15000, seed=7)
+    audio = br.vae_decode_tfirst(lat)
+    assert audio.shape == (15000 * 1920, 2) and np.isfinite(audio).all()
+    return lat, audio
+
+
+@pytest.mark.parametrize("c0,c1", [(0, 1875), (1875, 3750), (7493, 7621), (13125, 15000)])
+def test_config3_window_with_halo_equals_whole_clip(br, clip600, c0, c1):
+    """core frames [c0, c1) decoded inside a window with a 16-frame halo (clip ends keep the decoder's own zero padding) equal the same
+    samples of the un-split 600 s decode: the 8-GPU time split of configs[3] and the reference's chunk/overlap policy."""
+    lat, audio = clip600
+    br.load_vae(full_vae_dir())
+    w0, w1 = max(0, c0 - 16), min(15000, c1 + 16)
+    win = br.vae_decode_tfirst(lat[w0:w1])
+    core = win[(c0 - w0) * 1920:(c1 - w0) * 1920]
+    ref = audio[c0 * 1920:c1 * 1920]
+    assert np.abs(core - ref).max() <= 1e-6 * max(1.0, float(np.abs(ref).max())), metrics(core, ref)
+
+
+def test_config3_short_halo_is_detected(br, clip600):
+    """the same comparison with a 4-frame halo (inside the 9.5-frame receptive field) must FAIL — the test above can see a wrong halo"""
+    lat, audio = clip600
+    br.load_vae(full_vae_dir())
+    c0, c1 = 7493, 7621
+    win = br.vae_decode_tfirst(lat[c0 - 4:c1 + 4])
+    core = win[4 * 1920:(4 + c1 - c0) * 1920]
+    assert np.abs(core - audio[c0 * 1920:c1 * 1920]).max() > 1e-4
+
+
+def test_vae_240s_batch_members_are_independent_and_routes_agree(br, monkeypatch):
+    """two 240 s clips decoded in one batched call equal their single decodes bit for bit, and the fused residual-unit kernel equals
+    the two-launch route at full length (6000 frames: 45 000 / 90 000 row tiles on the two 128-channel levels)."""
+    br.load_vae(full_vae_dir())
+    lat = np.stack([fx.vae_latents(fx.VAE_FULL, 6000, seed=s) for s in (3, 4)])
+    both = br.vae_decode_batched(lat)
+    assert np.isfinite(both).all()
+    for b in range(2):
+        assert np.array_equal(both[b], br.vae_decode_tfirst(lat[b])), b
+    monkeypatch.setenv("ACE_B200_VAE_FUSE", "0")
+    plain = br.vae_decode_tfirst(lat[1])
+    assert np.array_equal(plain, both[1]), metrics(plain, both[1])

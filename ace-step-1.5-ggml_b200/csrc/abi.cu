@@ -11,6 +11,7 @@
 #include <cstdlib>
 #include <cstring>
 #include <string>
+#include <thread>
 #include <vector>
 
 namespace ace {
@@ -19,11 +20,40 @@ std::atomic<uint64_t> g_kernel_launches{0};
 
 namespace ace_abi {
 
+// memcmp == 0 over large host buffers on several threads (a 67 MB batch of encoder states takes ~6 ms on one core, longer than
+// uploading it): 4 MB pieces dealt round-robin, every thread stops at the first difference anyone finds
+bool host_bytes_equal(const void* a, const void* b, size_t n) {
+    constexpr size_t PIECE = 4u << 20;
+    if (n < 2 * PIECE) return std::memcmp(a, b, n) == 0;
+    const size_t pieces = (n + PIECE - 1) / PIECE;
+    const unsigned hw = std::max(1u, std::thread::hardware_concurrency());
+    const unsigned nt = (unsigned)std::min<size_t>(std::min(8u, hw), pieces);
+    std::atomic<bool> differ{false};
+    auto work = [&](unsigned t) {
+        for (size_t i = t; i < pieces && !differ.load(std::memory_order_relaxed); i += nt) {
+            const size_t off = i * PIECE, len = std::min(PIECE, n - off);
+            if (std::memcmp(static_cast<const char*>(a) + off, static_cast<const char*>(b) + off, len) != 0) differ.store(true, std::memory_order_relaxed);
+        }
+    };
+    std::vector<std::thread> pool;
+    try {
+        for (unsigned t = 1; t < nt; ++t) pool.emplace_back(work, t);
+    } catch (...) {  // no threads to be had: the calling thread covers what was not started
+        for (auto& th : pool) th.join();
+        return std::memcmp(a, b, n) == 0;
+    }
+    work(0);
+    for (auto& th : pool) th.join();
+    return !differ.load();
+}
+
+ace_ggml_status stage_dit_conditioning(ace_ggml_context* ctx, const float* enc, const int32_t* enc_mask, int B, int E);
+
 // H2D copies of one batched forward's inputs into the workspace
 ace_ggml_status stage_dit_inputs(ace_ggml_context* ctx, const float* hidden, const float* context, const float* enc,
                                  const int32_t* mask, const int32_t* enc_mask, int B, int T, int E) {
     const DitConfig& c = ctx->dit.cfg;
-    const int A = c.audio_acoustic_hidden_dim, cd = c.in_channels - A, H = c.hidden_size;
+    const int A = c.audio_acoustic_hidden_dim, cd = c.in_channels - A;
     DitWorkspace& ws = ctx->dws;
     cudaStream_t st = ctx->stream;
     cudaError_t e = cudaSuccess;
@@ -34,12 +64,17 @@ ace_ggml_status stage_dit_inputs(ace_ggml_context* ctx, const float* hidden, con
     else if (e == cudaSuccess) e = cudaMemsetAsync(ws.d_hidden, 0, (size_t)B * T * A * 4, st);
     if (context) h2d(ws.d_context, context, (size_t)B * T * cd * 4);
     else if (e == cudaSuccess) e = cudaMemsetAsync(ws.d_context, 0, (size_t)B * T * cd * 4, st);
-    if (E > 0) {
-        if (enc) h2d(ws.d_enc, enc, (size_t)B * E * H * 4);
-        else if (e == cudaSuccess) e = cudaMemsetAsync(ws.d_enc, 0, (size_t)B * E * H * 4, st);
-    }
     if (mask) h2d(ws.d_mask, mask, (size_t)B * T * 4);
-    if (enc_mask && E > 0) h2d(ws.d_enc_mask, enc_mask, (size_t)B * E * 4);
+    if (e != cudaSuccess) return cuda_fail(ctx, "input upload failed", e);
+    return E > 0 ? stage_dit_conditioning(ctx, enc, enc_mask, B, E) : ACE_GGML_OK;
+}
+
+// the step-invariant part of the inputs: encoder states (zeros when absent) and their mask
+ace_ggml_status stage_dit_conditioning(ace_ggml_context* ctx, const float* enc, const int32_t* enc_mask, int B, int E) {
+    const size_t n = (size_t)B * E * ctx->dit.cfg.hidden_size * 4;
+    DitWorkspace& ws = ctx->dws;
+    cudaError_t e = enc ? cudaMemcpyAsync(ws.d_enc, enc, n, cudaMemcpyHostToDevice, ctx->stream) : cudaMemsetAsync(ws.d_enc, 0, n, ctx->stream);
+    if (e == cudaSuccess && enc_mask) e = cudaMemcpyAsync(ws.d_enc_mask, enc_mask, (size_t)B * E * 4, cudaMemcpyHostToDevice, ctx->stream);
     if (e != cudaSuccess) return cuda_fail(ctx, "input upload failed", e);
     return ACE_GGML_OK;
 }
@@ -70,8 +105,11 @@ ace_ggml_status dit_forward_impl(ace_ggml_context* ctx, const float* hidden, con
     bool same_cond = E > 0 && enc != nullptr && ctx->dws.cross_kv_valid && ctx->enc_cache_B == B && ctx->enc_cache_E == E &&
                      ctx->enc_cache_layers == o.max_layers && ctx->enc_cache.size() == enc_n && ctx->enc_cache_has_mask == (enc_mask != nullptr) &&
                      !env_on("ACE_B200_NO_COND_CACHE");
-    if (same_cond) same_cond = std::memcmp(ctx->enc_cache.data(), enc, enc_n * 4) == 0;
-    if (same_cond && enc_mask) same_cond = std::memcmp(ctx->enc_mask_cache.data(), enc_mask, (size_t)B * E * 4) == 0;
+    // the per-step inputs go first: their (asynchronous, when the caller's memory is pinned) upload runs under the host-side compare
+    ace_ggml_status s = stage_dit_inputs(ctx, hidden, context, nullptr, mask, nullptr, B, T, 0);
+    if (s != ACE_GGML_OK) return s;
+    if (same_cond) same_cond = host_bytes_equal(ctx->enc_cache.data(), enc, enc_n * 4);
+    if (same_cond && enc_mask) same_cond = host_bytes_equal(ctx->enc_mask_cache.data(), enc_mask, (size_t)B * E * 4);
     if (!same_cond) {
         ctx->dws.cross_kv_valid = false;
         ctx->enc_cache_B = 0;
@@ -84,8 +122,10 @@ ace_ggml_status dit_forward_impl(ace_ggml_context* ctx, const float* hidden, con
             ctx->enc_cache_layers = o.max_layers;
         }
     }
-    ace_ggml_status s = stage_dit_inputs(ctx, hidden, context, same_cond ? nullptr : enc, mask, same_cond ? nullptr : enc_mask, B, T, same_cond ? 0 : E);
-    if (s != ACE_GGML_OK) return s;
+    if (!same_cond && E > 0) {
+        s = stage_dit_conditioning(ctx, enc, enc_mask, B, E);
+        if (s != ACE_GGML_OK) return s;
+    }
     std::vector<float> tt((size_t)2 * B);
     for (int b = 0; b < B; ++b) {
         tt[(size_t)b] = t[b];

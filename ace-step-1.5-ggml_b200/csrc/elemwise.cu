@@ -2,7 +2,9 @@
 // All are HBM-bound: vectorised 16-byte accesses, warp-shuffle reductions, one pass over the data.
 #include "kernels.h"
 
+#include <algorithm>
 #include <cmath>
+#include <cstdlib>
 #include <cstdio>
 
 namespace ace {
@@ -108,16 +110,20 @@ __global__ void build_modulation_kernel(const float* __restrict__ tables, const 
     }
 }
 
-// ---------------------------------------------------------------- RMSNorm (+ AdaLN modulate): one 128-thread CTA per row
-// (rows x 4 warps keeps every SM busy at S = 375..3000; the row stays in registers between the two passes)
+// ---------------------------------------------------------------- RMSNorm (+ AdaLN modulate): a 128-thread CTA per group of rows
+// grid (row groups of one sample, samples).  The norm weight and the AdaLN scale / shift of the sample are fetched ONCE per CTA and
+// stay in registers while the CTA walks `rows_per_cta` consecutive rows (each row lives in registers between its two passes).
+// One row per CTA read 24 KB of tables from L2 for every 8 KB row from HBM: at M = 48 000 that is 12 TB/s of L2 -> SM traffic,
+// the chip's delivery limit, and the kernel sat at 0.72 of the HBM copy bandwidth (profiles/r2_ncu_config2_n.md).  The launcher keeps
+// one row per CTA where rows are scarce (M = 375..1500: rows x 4 warps is what keeps every SM busy there).
 __global__ void __launch_bounds__(128)
 rmsnorm_mod_kernel(const float* __restrict__ x, const float* __restrict__ w, const float* __restrict__ scale1,
-                   const float* __restrict__ shift, long mod_bstride, __half* __restrict__ y, long rows, int rows_per_b,
+                   const float* __restrict__ shift, long mod_bstride, __half* __restrict__ y, int rows_per_cta, int rows_per_b,
                    int H, float eps, float* __restrict__ y32, int early_mod) {
-    __shared__ float red[4];
-    const long row = blockIdx.x;
+    __shared__ float red[2][4];
     const int tid = threadIdx.x;
-    const int b = (int)(row / rows_per_b);
+    const int b = blockIdx.y;
+    const int r_lo = blockIdx.x * rows_per_cta, r_hi = min(r_lo + rows_per_cta, rows_per_b);
     const float* s1 = scale1 ? scale1 + (long)b * mod_bstride : nullptr;
     const float* sh = shift ? shift + (long)b * mod_bstride : nullptr;
     constexpr int MAXV = 4;  // up to H = 2048 held in registers; wider rows re-read from L1/L2
@@ -150,52 +156,56 @@ rmsnorm_mod_kernel(const float* __restrict__ x, const float* __restrict__ w, con
             }
         }
     }
-    const float* xr = x + row * H;
-    float4 v[MAXV];
-    float ss = 0.f;
+    for (int r = r_lo; r < r_hi; ++r) {
+        const long row = (long)b * rows_per_b + r;
+        const float* xr = x + row * H;
+        float4 v[MAXV];
+        float ss = 0.f;
 #pragma unroll
-    for (int i = 0; i < MAXV; ++i) {
-        const int c = (i * 128 + tid) * 4;
-        if (c < H) {
-            v[i] = *reinterpret_cast<const float4*>(xr + c);
-            ss += v[i].x * v[i].x + v[i].y * v[i].y + v[i].z * v[i].z + v[i].w * v[i].w;
+        for (int i = 0; i < MAXV; ++i) {
+            const int c = (i * 128 + tid) * 4;
+            if (c < H) {
+                v[i] = *reinterpret_cast<const float4*>(xr + c);
+                ss += v[i].x * v[i].x + v[i].y * v[i].y + v[i].z * v[i].z + v[i].w * v[i].w;
+            }
         }
-    }
-    for (int c = (MAXV * 128 + tid) * 4; c < H; c += 512) {
-        const float4 t = *reinterpret_cast<const float4*>(xr + c);
-        ss += t.x * t.x + t.y * t.y + t.z * t.z + t.w * t.w;
-    }
-    ss = warp_sum(ss);
-    if ((tid & 31) == 0) red[tid >> 5] = ss;
-    __syncthreads();
-    ss = red[0] + red[1] + red[2] + red[3];
-    const float inv = 1.0f / sqrtf(ss / (float)H + eps);
-    __half* yr = y + row * H;
-    auto emit = [&](int c, float4 t, float4 wv, float4 a1, float4 a2) {
-        float o0 = t.x * inv * wv.x, o1 = t.y * inv * wv.y, o2 = t.z * inv * wv.z, o3 = t.w * inv * wv.w;
-        if (s1) {
-            o0 *= a1.x; o1 *= a1.y; o2 *= a1.z; o3 *= a1.w;
+        for (int c = (MAXV * 128 + tid) * 4; c < H; c += 512) {
+            const float4 t = *reinterpret_cast<const float4*>(xr + c);
+            ss += t.x * t.x + t.y * t.y + t.z * t.z + t.w * t.w;
         }
-        if (sh) {
-            o0 += a2.x; o1 += a2.y; o2 += a2.z; o3 += a2.w;
-        }
-        if (y32) *reinterpret_cast<float4*>(y32 + row * H + c) = make_float4(o0, o1, o2, o3);
-        if (!y) return;
-        __half2 h0 = __floats2half2_rn(o0, o1), h1 = __floats2half2_rn(o2, o3);
-        uint2 o;
-        o.x = *reinterpret_cast<uint32_t*>(&h0);
-        o.y = *reinterpret_cast<uint32_t*>(&h1);
-        *reinterpret_cast<uint2*>(yr + c) = o;
-    };
+        ss = warp_sum(ss);
+        float* rd = red[(r - r_lo) & 1];  // two buffers: row r + 1 writes the other one while stragglers still read this one
+        if ((tid & 31) == 0) rd[tid >> 5] = ss;
+        __syncthreads();
+        ss = rd[0] + rd[1] + rd[2] + rd[3];
+        const float inv = 1.0f / sqrtf(ss / (float)H + eps);
+        __half* yr = y + row * H;
+        auto emit = [&](int c, float4 t, float4 wv, float4 a1, float4 a2) {
+            float o0 = t.x * inv * wv.x, o1 = t.y * inv * wv.y, o2 = t.z * inv * wv.z, o3 = t.w * inv * wv.w;
+            if (s1) {
+                o0 *= a1.x; o1 *= a1.y; o2 *= a1.z; o3 *= a1.w;
+            }
+            if (sh) {
+                o0 += a2.x; o1 += a2.y; o2 += a2.z; o3 += a2.w;
+            }
+            if (y32) *reinterpret_cast<float4*>(y32 + row * H + c) = make_float4(o0, o1, o2, o3);
+            if (!y) return;
+            __half2 h0 = __floats2half2_rn(o0, o1), h1 = __floats2half2_rn(o2, o3);
+            uint2 o;
+            o.x = *reinterpret_cast<uint32_t*>(&h0);
+            o.y = *reinterpret_cast<uint32_t*>(&h1);
+            *reinterpret_cast<uint2*>(yr + c) = o;
+        };
 #pragma unroll
-    for (int i = 0; i < MAXV; ++i) {
-        const int c = (i * 128 + tid) * 4;
-        if (c < H) emit(c, v[i], ww[i], sc[i], sf[i]);
-    }
-    for (int c = (MAXV * 128 + tid) * 4; c < H; c += 512) {
-        const float4 z = make_float4(0.f, 0.f, 0.f, 0.f);
-        emit(c, *reinterpret_cast<const float4*>(xr + c), *reinterpret_cast<const float4*>(w + c),
-             s1 ? *reinterpret_cast<const float4*>(s1 + c) : z, sh ? *reinterpret_cast<const float4*>(sh + c) : z);
+        for (int i = 0; i < MAXV; ++i) {
+            const int c = (i * 128 + tid) * 4;
+            if (c < H) emit(c, v[i], ww[i], sc[i], sf[i]);
+        }
+        for (int c = (MAXV * 128 + tid) * 4; c < H; c += 512) {
+            const float4 z = make_float4(0.f, 0.f, 0.f, 0.f);
+            emit(c, *reinterpret_cast<const float4*>(xr + c), *reinterpret_cast<const float4*>(w + c),
+                 s1 ? *reinterpret_cast<const float4*>(s1 + c) : z, sh ? *reinterpret_cast<const float4*>(sh + c) : z);
+        }
     }
 }
 
@@ -418,8 +428,12 @@ void launch_rmsnorm_mod(const float* x, const float* w, const float* scale1, con
     note_launch();
     const long rows = (long)B * rows_per_b;
     ProfScope prof_scope(PROF_ELEM, 0.0, (double)rows * H * (4.0 + (y ? 2.0 : 0.0) + (y32 ? 4.0 : 0.0)), st);  // weight / scale / shift are L2-resident vectors
-    launch_pdl(rmsnorm_mod_kernel, dim3((unsigned)rows), dim3(128), 0, st, x, w, scale1, shift, mod_bstride, y, rows, rows_per_b, H, eps, y32,
-               early_mod ? 1 : 0);
+    // rows per CTA: as many as still leave ~16 CTAs per SM (8 at M = 48 000, 1 below M ~ 4700); ACE_B200_NORM_ROWS overrides
+    int rpc = (int)std::max(1L, std::min(8L, rows / (16L * 148L)));
+    if (const char* e = std::getenv("ACE_B200_NORM_ROWS")) rpc = std::max(1, std::atoi(e));
+    rpc = std::min(rpc, rows_per_b);
+    launch_pdl(rmsnorm_mod_kernel, dim3((unsigned)((rows_per_b + rpc - 1) / rpc), (unsigned)B), dim3(128), 0, st, x, w, scale1, shift, mod_bstride, y,
+               rpc, rows_per_b, H, eps, y32, early_mod ? 1 : 0);
 }
 void launch_headnorm_rope(__half* buf, long row_stride, int col0, int n_heads, const float* w, const float2* rope_tab,
                           int B, int rows_per_b, float eps, cudaStream_t st) {

@@ -27,6 +27,7 @@
 #include "tmap.h"
 
 #include <cuda.h>
+#include <algorithm>
 #include <cstdio>
 #include <cstdlib>
 #include <vector>
@@ -72,6 +73,8 @@ struct RuParams {
     const __half* x_in;      // residual stream [B, L, 128]
     int B, L, m_tiles_per_b, dilation, slab_rows, store_x;
     long long* trace;        // debug (ACE_B200_RU_TRACE=1): clock64 stamps of one steady-state tile per CTA, else null
+    int stall_ns;            // test hook (ACE_B200_RU_STALL_NS): the producer sleeps this long before every W2 load, so the second MMA
+                             // of an item is issued late and the epilogue warps run ahead of the issuer (see h_ready below)
 };
 
 constexpr int RU_TR_N = 32, RU_TR_TILE = 4;   // stamps per CTA; the CTA's 5th work item is the one traced
@@ -109,8 +112,13 @@ vae_resunit128_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_cons
     uint64_t* peer_slab = bars + 16;    // [2] leader only
     uint64_t* acc1_full = bars + 18;    // [2]
     uint64_t* acc1_empty = bars + 20;   // [2] leader only in a pair: the epilogue warps of both CTAs
-    uint64_t* h_ready = bars + 22;      //     8 local epilogue warps: h of the tile is in shared memory
-    uint64_t* peer_h = bars + 23;       //     leader only: CTA 1's h
+    // h_ready / peer_h are indexed by item parity and waited on with parity (item >> 1) & 1.  In a pair, pass 1 of item j + 1 does not
+    // depend on the second MMA of item j, so the epilogue warps can finish it while the issuer still waits for item j's W2 slot; a single
+    // barrier waited on with parity j & 1 would then be TWO phases ahead of the issuer, the wait would never succeed and the kernel hung
+    // (seen once in ~20 decodes of a 240 s clip).  Per-parity barriers cannot lead by more than one phase: pass 1 of item j + 2 needs the
+    // first MMA of item j + 2, which the issuer starts after the second MMA of item j.
+    uint64_t* h_ready = bars + 36;      // [2] 8 local epilogue warps: h of the item is in shared / tensor memory
+    uint64_t* peer_h = bars + 38;       // [2] leader only: CTA 1's h
     uint64_t* acc2_full = bars + 24;
     uint64_t* acc2_empty = bars + 25;   //     leader only in a pair
     uint64_t* r_full = bars + 26;       // [8] PAIR: the residual box of epilogue warp w has landed in its staging slice
@@ -140,8 +148,10 @@ vae_resunit128_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_cons
             ptx::mbar_init(&acc1_full[a], 1);
             ptx::mbar_init(&acc1_empty[a], EPI_ARRIVALS);
         }
-        ptx::mbar_init(h_ready, 8);
-        ptx::mbar_init(peer_h, 1);
+        for (int a = 0; a < 2; ++a) {
+            ptx::mbar_init(&h_ready[a], 8);
+            ptx::mbar_init(&peer_h[a], 1);
+        }
         ptx::mbar_init(acc2_full, 1);
         ptx::mbar_init(acc2_empty, EPI_ARRIVALS);
         for (int w = 0; w < 8; ++w) ptx::mbar_init(&r_full[w], 1);
@@ -213,9 +223,15 @@ vae_resunit128_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_cons
                 ring_load(p.W1 + (size_t)tap * (2 * RU_WTILE));
                 if (tap == NSLOT && t + stride < total_tiles) slab_load(it + 1, t + stride);
             }
-            if (it > 0) ring_load(p.W2);   // consumed by MMA2 of the previous tile, issued after this tile's MMA1
+            if (it > 0) {   // consumed by MMA2 of the previous tile, issued after this tile's MMA1
+                if (p.stall_ns) __nanosleep((unsigned)p.stall_ns);
+                ring_load(p.W2);
+            }
         }
-        if (it > 0) ring_load(p.W2);
+        if (it > 0) {
+            if (p.stall_ns) __nanosleep((unsigned)p.stall_ns);
+            ring_load(p.W2);
+        }
     } else if (warp == 9 && rank == 0) {
         // ===================== MMA issuer (leader; whole warp on uniform values, one elected lane issues) =====================
         constexpr uint32_t idesc = ptx::umma_idesc_f16(PAIR ? 2 * RU_BM : RU_BM, RU_C);
@@ -242,8 +258,8 @@ vae_resunit128_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_cons
             ptx::mbar_wait(&full[s], ph);
             if (PAIR) ptx::mbar_wait(&peer_full[s], ph);
             if (lane == 0) ru_stamp(p, j + 1, 4);
-            ptx::mbar_wait(h_ready, (uint32_t)(j & 1));
-            if (PAIR) ptx::mbar_wait(peer_h, (uint32_t)(j & 1));
+            ptx::mbar_wait(&h_ready[j & 1], (uint32_t)((j >> 1) & 1));
+            if (PAIR) ptx::mbar_wait(&peer_h[j & 1], (uint32_t)((j >> 1) & 1));
             if (lane == 0) ru_stamp(p, j + 1, 5);
             ptx::mbar_wait(acc2_empty, (uint32_t)((j & 1) ^ 1));
             ptx::tc_fence_after();
@@ -318,8 +334,8 @@ vae_resunit128_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_cons
             };
             auto relay_h = [&](int j) {
                 relay_slot();   // the W2 slot
-                ptx::mbar_wait(h_ready, (uint32_t)(j & 1));
-                ptx::mbar_arrive_cluster(ptx::mapa(peer_h, 0));
+                ptx::mbar_wait(&h_ready[j & 1], (uint32_t)((j >> 1) & 1));
+                ptx::mbar_arrive_cluster(ptx::mapa(&peer_h[j & 1], 0));
             };
             int it = 0;
             for (int t = first; t < total_tiles; t += stride, ++it) {
@@ -489,7 +505,7 @@ vae_resunit128_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_cons
             __syncwarp();
             if (lane == 0) {
                 arrive_leader(&acc1_empty[a]);
-                ptx::mbar_arrive(h_ready);   // local: the leader's issuer waits on it directly, CTA 1's relay forwards it
+                ptx::mbar_arrive(&h_ready[a]);   // local: the leader's issuer waits on it directly, CTA 1's relay forwards it
             }
             if (tr) ru_stamp(p, i, 18);
         };
@@ -554,7 +570,7 @@ bool vae_resunit128_supported(const VaeResUnit& ru) {
 
 cudaError_t launch_vae_resunit128(const __half* xs_in, const __half* x_in, __half* x_out, __half* xs_out, int B, long L,
                                   const VaeResUnit& ru, const VaeSnake& next, cudaStream_t st) {
-    if (!vae_resunit128_supported(ru) || !next.alpha || !next.inv_beta || L <= 0 || L > 0x7fffffffL / RU_C || xs_in == xs_out)
+    if (!vae_resunit128_supported(ru) || !next.alpha || !next.inv_beta || L <= 0 || L > 0x7fffffffL - 4 * RU_BM || (long)B * ((L + RU_BM - 1) / RU_BM) > 0x7fffffffL || xs_in == xs_out)
         return cudaErrorInvalidValue;
     note_launch();
     const double elems = (double)B * (double)L * RU_C;
@@ -615,6 +631,8 @@ cudaError_t launch_vae_resunit128(const __half* xs_in, const __half* x_in, __hal
     const char* fe = std::getenv("ACE_B200_VAE_FUSE");
     const bool pair = !(fe && fe[0] == '1') && max_pairs >= 8 && tiles >= 2;
     p.trace = nullptr;
+    p.stall_ns = 0;
+    if (const char* es = std::getenv("ACE_B200_RU_STALL_NS")) p.stall_ns = std::max(0, std::min(1000000, std::atoi(es)));
     struct TraceDump {   // debug aid: synchronous, prints the mean timeline of one work item of the leader CTAs
         long long* buf = nullptr; int ctas = 0, step = 1; cudaStream_t st = nullptr; long L = 0; int d = 0, sx = 0, pair = 0;
         ~TraceDump() {

@@ -1,0 +1,73 @@
+#!/usr/bin/env python
+"""Run-to-run determinism of one full DiT evaluation (turbo dims, T = 6000) under the route switches: N identical calls, how many
+distinct outputs?   python scripts/probes/determinism.py [reps]"""
+import hashlib
+import os
+import sys
+from collections import Counter
+
+import numpy as np
+
+ROOT = os.path.dirname(os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
+sys.path[:0] = [ROOT, os.path.join(ROOT, "ace-step-1.5-ggml_b200"), os.path.join(ROOT, "tests")]
+from tools import fixtures as fx  # noqa: E402
+from acestep_b200.bridge import B200Bridge  # noqa: E402
+from parity_common import metrics, turbo_dit_dir  # noqa: E402
+
+reps = int(sys.argv[1]) if len(sys.argv) > 1 else 40
+T = 6000
+inp = fx.dit_inputs(fx.TURBO, T, 512, seed=1236)
+
+
+def trial(quant, env, label):
+    for k in [k for k in os.environ if k.startswith("ACE_B200_") and k != "ACE_B200_DEVICE"]:
+        del os.environ[k]
+    os.environ.update(env)
+    br = B200Bridge()
+    br.load_dit(turbo_dit_dir(quant))
+    outs, hashes = {}, []
+    for _ in range(reps):
+        v = br.dit_forward_tfirst(inp["hidden_states"], inp["context_latents"], inp["encoder_hidden_states"], None, None, 0.3, 0.3)
+        hsh = hashlib.md5(v.tobytes()).hexdigest()
+        hashes.append(hsh)
+        outs.setdefault(hsh, v)
+    cnt = Counter(hashes)
+    mode = cnt.most_common(1)[0][0]
+    worst = max((metrics(v, outs[mode])["rel_l2"] for h, v in outs.items() if h != mode), default=0.0)
+    print(f"[{quant:5s}] {label:34s} {len(cnt):3d} distinct outputs in {reps} calls (mode x{cnt[mode]}), worst rel_l2 to the mode {worst:.2e}", flush=True)
+    br.close()
+
+
+if len(sys.argv) > 2 and sys.argv[2].startswith("dbg="):
+    for d in sys.argv[2][4:].split(","):
+        trial("Q4_K", {"ACE_B200_GEMM_DBG": d}, f"ACE_B200_GEMM_DBG={d}")
+    sys.exit(0)
+if len(sys.argv) > 2 and sys.argv[2] == "fix":
+    trial("Q4_K", {}, "default (fence.proxy.async)")
+    trial("Q4_K", {"ACE_B200_GEMM_DBG": "16"}, "fence.proxy.async.shared::cluster")
+    trial("Q4_K", {"ACE_B200_GEMM_DBG": "1"}, "fence.proxy.async.shared::cta (old)")
+    sys.exit(0)
+if len(sys.argv) > 2 and sys.argv[2] == "bisect":
+    trial("Q4_K", {}, "default")
+    trial("Q4_K", {"ACE_B200_GEMM_QNS": "4"}, "4-stage ring")
+    trial("Q4_K", {"ACE_B200_GEMM_DBG": "1"}, "decoders: fence.proxy.async (all spaces)")
+    trial("Q4_K", {"ACE_B200_GEMM_DBG": "2"}, "relay: fence.acq_rel.cluster")
+    trial("Q4_K", {"ACE_B200_GEMM_DBG": "64"}, "leader: acquire.cluster wait on peer_full")
+    trial("Q4_K", {"ACE_B200_GEMM_DBG": "4"}, "epilogue: wait_group.read after every reduce")
+    trial("Q4_K", {"ACE_B200_GEMM_DBG": "8"}, "epilogue: wait_group after every reduce")
+    trial("Q6_K", {}, "Q6_K default")
+    sys.exit(0)
+trial("Q4_K", {}, "default")
+trial("Q4_K", {"ACE_B200_GEMM_2CTA": "0"}, "single-CTA GEMMs")
+trial("Q4_K", {"ACE_B200_PREDECODE": "1"}, "F16 twin through the pair kernel")
+trial("Q4_K", {"ACE_B200_ATTN": "tc4"}, "attention: smem-P kernel")
+trial("Q4_K", {"ACE_B200_ATTN": "mma"}, "attention: mma.sync kernel")
+trial("Q4_K", {"ACE_B200_GEMM_TMARED": "0"}, "red.add instead of TMA reduce")
+trial("Q4_K", {"ACE_B200_GEMM_WARM": "0"}, "no epilogue warm-up pass")
+trial("Q4_K", {"ACE_B200_GEMM_QDEC": "1"}, "one decoder group")
+trial("Q4_K", {"ACE_B200_GEMM_QEPI": "4"}, "4 epilogue warps everywhere")
+trial("Q4_K", {"ACE_B200_GEMM_BAND_MB": "0"}, "no rasterisation bands")
+trial("Q4_K", {"ACE_B200_NO_SCHED_TEMB": "1", "ACE_B200_NO_COND_CACHE": "1"}, "no conditioning cache")
+trial("F16", {}, "F16 weights, default")
+trial("F16", {"ACE_B200_GEMM_2CTA": "0"}, "F16 weights, single-CTA GEMMs")
+trial("Q8_0", {}, "Q8_0 weights, default")

@@ -170,3 +170,22 @@ def test_vae_fused_residual_units_equal_the_two_launch_route(br, n_frames, batch
     assert np.isfinite(pair).all()
     assert np.array_equal(single, plain), metrics(single, plain)
     assert np.array_equal(pair, plain), metrics(pair, plain)
+
+
+@pytest.mark.timeout(180, method="thread")
+def test_vae_fused_residual_units_survive_a_late_second_mma(br, monkeypatch):
+    """Regression test of a hang (1 in ~20 decodes of a 240 s clip).  In the CTA-pair kernel pass 1 of item j + 1 does not depend on the
+    second MMA of item j, so when that MMA's W2 weights land late the epilogue warps finish pass 1 of item j + 1 before the issuer has
+    looked at item j's "h ready" barrier; with ONE barrier and a 1-bit phase the issuer then waited for a phase that had already gone by.
+    ACE_B200_RU_STALL_NS makes the producer sleep before every W2 load (20 us: several times MMA1 + pass 1), which turned the old
+    kernel's rare hang into a certain one (scripts/probes/ru_stall_ab.py, profiles/r2_ru_stall_ab.log); the barriers are now per
+    item parity.  The stalled decode must finish and equal the un-stalled one bit for bit."""
+    br.load_vae(full_vae_dir())
+    lat = np.stack([fx.vae_latents(fx.VAE_FULL, 40, seed=5), fx.vae_latents(fx.VAE_FULL, 40, seed=6)])
+    want = br.vae_decode_batched(lat)
+    monkeypatch.setenv("ACE_B200_RU_STALL_NS", "20000")
+    got = br.vae_decode_batched(lat)
+    assert np.array_equal(got, want)
+    monkeypatch.delenv("ACE_B200_RU_STALL_NS")
+    for _ in range(6):   # and a few plain repetitions at a length with tens of items per CTA
+        assert np.array_equal(br.vae_decode_batched(lat), want)

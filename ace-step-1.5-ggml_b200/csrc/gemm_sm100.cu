@@ -49,7 +49,7 @@ struct KParams {
     int  warm_epi;               // epilogue warps run the epilogue once as a dry run (stores predicated off) while the first tile's MMAs are in flight
     int  epi_variant;            // EPI_STORE fast path chosen on the host (store_variant()); 0 = generic code
     long long* trace;            // debug (ACE_B200_GEMM_TRACE=1): per-CTA clock64 stamps of the pipeline phases, else null
-    int  dbg;                    // bisecting aid (ACE_B200_GEMM_DBG, bit mask; see gemm_tc2_kernel)
+    int  dbg;                    // A/B aid (ACE_B200_GEMM_DBG): bit 1 = CTA-scoped proxy fence in the pair kernel's decoders (the racy one)
 };
 
 // trace slots per CTA
@@ -453,8 +453,6 @@ __device__ __forceinline__ bool epilogue_store_staged(const KParams& p, const CU
         if (lane == 0 && !(W && dry)) {
             ptx::tma_reduce_add_3d(tmOut, stg, n0, l_base, b);
             ptx::bulk_commit();
-            if (p.dbg & 4) ptx::bulk_wait_read0();
-            if (p.dbg & 8) ptx::bulk_wait0();
         }
         return true;
     }
@@ -1247,9 +1245,7 @@ gemm_tc2_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__
                 uint32_t acc_flag = 0;
                 for (int kb = kb0; kb < kb1; ++kb) {
                     ptx::mbar_wait(&full[s], ph);
-                    if (p.dbg & 64) ptx::mbar_wait_cluster(&peer_full[s], ph);
-                    else ptx::mbar_wait(&peer_full[s], ph);
-                    if (p.dbg & 256) asm volatile("fence.proxy.async;" ::: "memory");
+                    ptx::mbar_wait(&peer_full[s], ph);
                     ptx::tc_fence_after();
                     const uint64_t da = desc_a0 + (uint64_t)(s * (A_STAGE_BYTES >> 4)), db = desc_b0 + (uint64_t)(s * (W_SUB_BYTES >> 4));
                     if (ptx::elect_one()) {
@@ -1277,9 +1273,6 @@ gemm_tc2_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__
                     k_range(sp, kb0, kb1);
                     for (int kb = kb0; kb < kb1; ++kb) {
                         ptx::mbar_wait(&full[s], ph);
-                        if (p.dbg & 2) asm volatile("fence.acq_rel.cluster;" ::: "memory");
-                        if (p.dbg & 512) asm volatile("mbarrier.arrive.release.cluster.shared::cluster.b64 _, [%0];" ::"r"(ptx::mapa(&peer_full[s], 0)) : "memory");
-                        else
                         ptx::mbar_arrive_cluster(ptx::mapa(&peer_full[s], 0));
                         if (++s == (uint32_t)NS) {
                             s = 0;
@@ -1307,12 +1300,17 @@ gemm_tc2_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__
                 ptx::mbar_wait(&raw_full[s], ph);
                 ptx::mbar_wait(&empty[s], ph ^ 1);
                 decode_tile(p.wtype, sR + s * raw_stride, sB + s * W_SUB_BYTES, row);
-                if (p.dbg & 1) asm volatile("fence.proxy.async;" ::: "memory");
-                else if (p.dbg & 16) asm volatile("fence.proxy.async.shared::cluster;" ::: "memory");
-                else ptx::fence_proxy_async_smem();
+                // The decoded sub-tile is read by BOTH tensor cores of the pair (each CTA stages half of the 256-row weight tile): the peer's
+                // reads come through the shared::cluster window, so the writers' proxy fence must cover that window.  With the CTA-scoped
+                // fence (fence.proxy.async.shared::cta = MEMBAR.ALL.CTA + FENCE.VIEW.ASYNC.S) a tensor core occasionally consumed a
+                // sub-tile that was not completely visible yet: one 256-row tile off by ~1e-3, 8 distinct results in 12 identical
+                // calls at M = 48 000 (scripts/probes/determinism.py, profiles/r2_determinism_*.log).  The cluster-scoped fence compiles to
+                // MEMBAR.ALL.GPU + FENCE.VIEW.ASYNC.S and costs ~25 % of the kernel's throughput (profiles/r2_quant_sweep_fence_s8.log);
+                // no cheaper placement was found (one lane per warp, the relay, the leader: same cost).
+                // ACE_B200_GEMM_DBG bit 1 restores the CTA-scoped fence for A/B measurements.
+                if (p.dbg & 1) ptx::fence_proxy_async_smem();
+                else asm volatile("fence.proxy.async.shared::cluster;" ::: "memory");
                 __syncwarp();
-                if (lane == 0 && (p.dbg & 32)) asm volatile("fence.proxy.async;" ::: "memory");
-                if (lane == 0 && (p.dbg & 128)) asm volatile("fence.acq_rel.cluster;" ::: "memory");
                 if (lane == 0) {
                     ptx::mbar_arrive(&full[s]);
                     ptx::mbar_arrive(&raw_empty[s]);
@@ -1610,7 +1608,10 @@ cudaError_t launch_tc2(const CUtensorMap& tm, const CUtensorMap& tmo, const KPar
     if (const char* e = std::getenv("ACE_B200_GEMM_QEPI")) epi_warps = std::atoi(e) == 8 ? 8 : 4;
     if (dec_groups == 1) epi_warps = 8;
     int ns = quant && smem2q_bytes(5, epi_warps, kp.tile_bytes) <= 227 * 1024 ? 5 : 4;
-    if (const char* e = std::getenv("ACE_B200_GEMM_QNS")) if (std::atoi(e) == 4) ns = 4;
+    if (const char* e = std::getenv("ACE_B200_GEMM_QNS")) {
+        if (std::atoi(e) == 4) ns = 4;
+        if (std::atoi(e) == 5 && quant && smem2q_bytes(5, epi_warps, kp.tile_bytes) <= 227 * 1024) ns = 5;
+    }
     cfg.blockDim = dim3(NUM_THREADS);
     cfg.dynamicSmemBytes = quant ? smem2q_bytes(ns, epi_warps, kp.tile_bytes) : SMEM2_BYTES;
     cfg.stream = stream;

@@ -38,6 +38,41 @@ def trial(quant, env, label):
     br.close()
 
 
+def trial_batched(quant, B, n, env, label):
+    for k in [k for k in os.environ if k.startswith("ACE_B200_") and k != "ACE_B200_DEVICE"]:
+        del os.environ[k]
+    os.environ.update(env)
+    br = B200Bridge()
+    br.load_dit(turbo_dit_dir(quant))
+    ins = [fx.dit_inputs(fx.TURBO, T, 512, seed=1234 + i) for i in range(B)]
+    h = np.stack([i["hidden_states"] for i in ins]); c = np.stack([i["context_latents"] for i in ins]); e = np.stack([i["encoder_hidden_states"] for i in ins])
+    ts = [0.3 + 0.04 * i for i in range(B)]
+    outs, hashes = {}, []
+    for _ in range(n):
+        v = br.dit_forward_batched(h, c, e, None, None, ts, ts)
+        hsh = hashlib.md5(v.tobytes()).hexdigest()
+        hashes.append(hsh)
+        outs.setdefault(hsh, v.copy())
+    cnt = Counter(hashes)
+    mode = cnt.most_common(1)[0][0]
+    worst = max((metrics(v, outs[mode])["rel_l2"] for hh, v in outs.items() if hh != mode), default=0.0)
+    print(f"[{quant:5s}] {label:28s} batch {B:2d} (M = {B * 3000:5d}): {len(cnt):3d} distinct outputs in {n} calls = {n * B} evaluations, "
+          f"worst rel_l2 to the mode {worst:.2e}", flush=True)
+    br.close()
+
+
+if len(sys.argv) > 2 and sys.argv[2].startswith("big="):
+    for d in sys.argv[2][4:].split(","):
+        trial_batched("Q4_K", 16, max(4, reps // 12), {"ACE_B200_GEMM_DBG": d}, f"ACE_B200_GEMM_DBG={d}")
+        trial_batched("Q4_K", 1, reps, {"ACE_B200_GEMM_DBG": d}, f"ACE_B200_GEMM_DBG={d}")
+    sys.exit(0)
+if len(sys.argv) > 2 and sys.argv[2] == "sizes":
+    for q in ("Q4_K", "Q6_K", "Q8_0"):
+        trial_batched(q, 1, reps, {}, "default")
+        trial_batched(q, 2, reps // 2, {}, "default")
+    trial_batched("Q4_K", 16, max(4, reps // 12), {}, "default")
+    trial_batched("Q4_K", 1, reps, {"ACE_B200_GEMM_QNS": "5"}, "5-stage ring forced")
+    sys.exit(0)
 if len(sys.argv) > 2 and sys.argv[2].startswith("dbg="):
     for d in sys.argv[2][4:].split(","):
         trial("Q4_K", {"ACE_B200_GEMM_DBG": d}, f"ACE_B200_GEMM_DBG={d}")

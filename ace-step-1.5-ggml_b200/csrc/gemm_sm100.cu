@@ -50,6 +50,7 @@ struct KParams {
     int  epi_variant;            // EPI_STORE fast path chosen on the host (store_variant()); 0 = generic code
     long long* trace;            // debug (ACE_B200_GEMM_TRACE=1): per-CTA clock64 stamps of the pipeline phases, else null
     int  dbg;                    // A/B aid (ACE_B200_GEMM_DBG): bit 1 = CTA-scoped proxy fence in the pair kernel's decoders (the racy one)
+    int  qpub;                   // pair kernel, packed tiles: decoders publish their rows with a shared->shared bulk copy (see gemm_tc2_kernel)
 };
 
 // trace slots per CTA
@@ -101,7 +102,7 @@ __device__ __forceinline__ uint32_t h2u(__half2 h) { return *reinterpret_cast<ui
 __device__ __forceinline__ __half2 u2h(uint32_t u) { return *reinterpret_cast<__half2*>(&u); }
 
 // Q8_0 tile: codes [4][128][16] int8, scales [128][2] fp16 at +8192
-__device__ __forceinline__ void decode_q8_0(const uint8_t* raw, uint8_t* btile, int row) {
+__device__ __forceinline__ void decode_q8_0(const uint8_t* raw, int row, uint4 (&out)[8]) {
     const __half2 sc2 = *reinterpret_cast<const __half2*>(raw + 8192 + row * 4);
     const __half2 kOff = __floats2half2_rn(1152.f, 1152.f);
 #pragma unroll
@@ -119,13 +120,13 @@ __device__ __forceinline__ void decode_q8_0(const uint8_t* raw, uint8_t* btile, 
             o[2 * i]     = h2u(__hmul2(__hsub2(u2h(lo), kOff), s2));
             o[2 * i + 1] = h2u(__hmul2(__hsub2(u2h(hi), kOff), s2));
         }
-        st_chunk(btile, row, 2 * j, make_uint4(o[0], o[1], o[2], o[3]));
-        st_chunk(btile, row, 2 * j + 1, make_uint4(o[4], o[5], o[6], o[7]));
+        out[2 * j] = make_uint4(o[0], o[1], o[2], o[3]);
+        out[2 * j + 1] = make_uint4(o[4], o[5], o[6], o[7]);
     }
 }
 
 // Q4_K tile: nibble words [2][128][16], (d*sc, dmin*m) fp16 pairs [128][2] at +4096
-__device__ __forceinline__ void decode_q4_k(const uint8_t* raw, uint8_t* btile, int row) {
+__device__ __forceinline__ void decode_q4_k(const uint8_t* raw, int row, uint4 (&out)[8]) {
     const uint2 sm = *reinterpret_cast<const uint2*>(raw + 4096 + row * 8);
     const __half2 k1024 = __floats2half2_rn(1024.f, 1024.f);
 #pragma unroll
@@ -143,13 +144,13 @@ __device__ __forceinline__ void decode_q4_k(const uint8_t* raw, uint8_t* btile, 
                 const uint32_t t = ((w[wi] >> (4 * i)) & 0x000F000Fu) | 0x64006400u;
                 o[i] = h2u(__hfma2(__hsub2(u2h(t), k1024), ds, dm));
             }
-            st_chunk(btile, row, 4 * j + wi, make_uint4(o[0], o[1], o[2], o[3]));
+            out[4 * j + wi] = make_uint4(o[0], o[1], o[2], o[3]);
         }
     }
 }
 
 // Q6_K tile: low nibble words [2][128][16], 2-bit plane [128][16] at +4096, fp16 d*sc [128][4] at +6144
-__device__ __forceinline__ void decode_q6_k(const uint8_t* raw, uint8_t* btile, int row) {
+__device__ __forceinline__ void decode_q6_k(const uint8_t* raw, int row, uint4 (&out)[8]) {
     const uint4 hp = *reinterpret_cast<const uint4*>(raw + 4096 + row * 16);
     const uint2 sc = *reinterpret_cast<const uint2*>(raw + 6144 + row * 8);
     const uint32_t P[4] = {hp.x, hp.y, hp.z, hp.w};
@@ -171,15 +172,26 @@ __device__ __forceinline__ void decode_q6_k(const uint8_t* raw, uint8_t* btile, 
                 const uint32_t t = ((w[wi] >> (4 * i)) & 0x000F000Fu) | ((Hs >> (2 * i)) & 0x00300030u) | 0x64006400u;
                 o[i] = h2u(__hmul2(__hsub2(u2h(t), k1056), s2));
             }
-            st_chunk(btile, row, g, make_uint4(o[0], o[1], o[2], o[3]));
+            out[g] = make_uint4(o[0], o[1], o[2], o[3]);
         }
     }
 }
 
+// one row of a packed tile -> its 64 fp16 weights as eight 16-byte chunks (registers)
+__device__ __forceinline__ void decode_row(int wtype, const uint8_t* raw, int row, uint4 (&out)[8]) {
+    if (wtype == W_Q8_0) decode_q8_0(raw, row, out);
+    else if (wtype == W_Q4_K) decode_q4_k(raw, row, out);
+    else decode_q6_k(raw, row, out);
+}
+// ... and into the 128-byte-swizzle K-major image of the tile
+__device__ __forceinline__ void store_row(uint8_t* btile, int row, const uint4 (&out)[8]) {
+#pragma unroll
+    for (int c = 0; c < 8; ++c) st_chunk(btile, row, c, out[c]);
+}
 __device__ __forceinline__ void decode_tile(int wtype, const uint8_t* raw, uint8_t* btile, int row) {
-    if (wtype == W_Q8_0) decode_q8_0(raw, btile, row);
-    else if (wtype == W_Q4_K) decode_q4_k(raw, btile, row);
-    else decode_q6_k(raw, btile, row);
+    uint4 out[8];
+    decode_row(wtype, raw, row, out);
+    store_row(btile, row, out);
 }
 
 // ---------------------------------------------------------------- fused epilogue for 32 consecutive columns of one row
@@ -1098,8 +1110,8 @@ constexpr int SMEM2_BYTES = STAGES2 * STAGE2_BYTES + 8 * STG_WARP_BYTES + 2 * 25
 // (Q4_K 5120 B, Q6_K 7168 B, Q8_0 8704 B), so Q4_K affords 5 stages next to 8 transpose buffers, the others 4.
 inline __host__ __device__ int raw2_stride(int tile_bytes) { return (tile_bytes + 127) & ~127; }
 inline __host__ __device__ int raw2_total(int ns, int tile_bytes) { return (ns * raw2_stride(tile_bytes) + 1023) / 1024 * 1024; }
-inline int smem2q_bytes(int ns, int epi_warps, int tile_bytes) {
-    return ns * STAGE2_BYTES + raw2_total(ns, tile_bytes) + epi_warps * STG_WARP_BYTES + 2 * 256 * 4 + 512;
+inline int smem2q_bytes(int ns, int epi_warps, int tile_bytes, bool pub = false) {
+    return ns * STAGE2_BYTES + raw2_total(ns, tile_bytes) + epi_warps * STG_WARP_BYTES + 2 * 256 * 4 + 512 + (pub ? 2 * W_SUB_BYTES : 0);
 }
 // EPIW = 8 with two decoder groups makes 18 warps (576 threads, 112 registers per thread: the epilogue spills a little more, but
 // twice as many warps share it — the K = 2048 shapes with heavy epilogues (QKV head-norm, SwiGLU) were epilogue-bound with 4)
@@ -1134,6 +1146,8 @@ gemm_tc2_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__
     uint64_t* acc_full = bars + 5 * NS;  // [2] local (multicast commit)
     uint64_t* acc_empty = acc_full + 2;  // [2] leader only: the epilogue warps of the pair
     uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(acc_empty + 2);
+    uint8_t* sDec = reinterpret_cast<uint8_t*>(bars) + 512;   // QUANT + qpub: [DEC_GROUPS][16 KB] decoded rows on their way to sB
+    const bool pub = QUANT && p.qpub != 0;
 
     const int warp = threadIdx.x >> 5;
     const int lane = threadIdx.x & 31;
@@ -1148,7 +1162,7 @@ gemm_tc2_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__
 
     if (threadIdx.x == 0) {
         for (int s = 0; s < NS; ++s) {
-            ptx::mbar_init(&full[s], QUANT ? 1 + 4 : 1);
+            ptx::mbar_init(&full[s], (QUANT && !pub) ? 1 + 4 : 1);
             ptx::mbar_init(&empty[s], 1);
             ptx::mbar_init(&peer_full[s], 1);
             ptx::mbar_init(&raw_full[s], 1);
@@ -1200,7 +1214,7 @@ gemm_tc2_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__
                     if (QUANT) {
                         ptx::mbar_wait(&raw_empty[s], ph ^ 1);
                         if (ptx::elect_one()) {
-                            ptx::mbar_expect_tx(&full[s], A_STAGE_BYTES);
+                            ptx::mbar_expect_tx(&full[s], pub ? A_STAGE_BYTES + W_SUB_BYTES : A_STAGE_BYTES);
                             ptx::tma_load_3d(sA + s * A_STAGE_BYTES, &tmA, &full[s], kc * BK, row, b);
                             ptx::mbar_expect_tx(&raw_full[s], (uint32_t)p.tile_bytes);
                             ptx::bulk_load(sR + s * raw_stride, wptr, p.tile_bytes, &raw_full[s]);
@@ -1289,6 +1303,16 @@ gemm_tc2_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__
         const int grp = (warp - DEC0) >> 2;
         const int row = (int)threadIdx.x - DEC0 * 32 - grp * 128;  // 0..127
         uint32_t g = 0;
+        // PUBLISH mode (p.qpub; even ring depth): the rows are decoded into a staging buffer of the group and each warp hands its 4 KB
+        // (32 rows of the 128-byte-swizzle image, contiguous) to the bulk-copy engine, which writes them into sB[s] and counts the bytes
+        // on full[s] (complete_tx) next to the TMA's A box.  sB is then written by the async proxy only, exactly like the F16 kernel's
+        // weight tiles, so "full[s] completed" means "every byte is in shared memory" for BOTH tensor cores of the pair, and the
+        // writers' fence only has to cover the CTA's own copy engine (fence.proxy.async.shared::cta).  The staging buffer is free again
+        // when the copy out of it has completed = the previous stage of this group is full.
+        uint8_t* myDec = sDec + grp * W_SUB_BYTES;
+        const int wq = (warp - DEC0) & 3;
+        bool have_prev = false;
+        uint32_t prev_s = 0, prev_ph = 0;
         for (int t = cluster_id; t < total_tiles; t += n_clusters) {
             int nt, sp, b, l0, kb0, kb1;
             decode_tile_index(t, nt, sp, b, l0);
@@ -1298,6 +1322,24 @@ gemm_tc2_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__
                 const uint32_t s = g % (uint32_t)NS;
                 const uint32_t ph = (g / (uint32_t)NS) & 1u;
                 ptx::mbar_wait(&raw_full[s], ph);
+                if (pub) {
+                    uint4 out[8];   // the row is decoded into registers while the previous copy still reads the staging buffer
+                    decode_row(p.wtype, sR + s * raw_stride, row, out);
+                    if (have_prev) ptx::mbar_wait(&full[prev_s], prev_ph);
+                    store_row(myDec, row, out);
+                    ptx::fence_proxy_async_smem();
+                    __syncwarp();
+                    if (lane == 0) {
+                        ptx::mbar_arrive(&raw_empty[s]);
+                        ptx::mbar_wait(&empty[s], ph ^ 1);   // only the copy INTO sB[s] has to wait for the MMAs that read its old contents
+                        ptx::bulk_copy_s2s(sB + s * W_SUB_BYTES + wq * 4096, myDec + wq * 4096, 4096, &full[s]);
+                    }
+                    __syncwarp();
+                    have_prev = true;
+                    prev_s = s;
+                    prev_ph = ph;
+                    continue;
+                }
                 ptx::mbar_wait(&empty[s], ph ^ 1);
                 decode_tile(p.wtype, sR + s * raw_stride, sB + s * W_SUB_BYTES, row);
                 // The decoded sub-tile is read by BOTH tensor cores of the pair (each CTA stages half of the 256-row weight tile): the peer's
@@ -1612,8 +1654,18 @@ cudaError_t launch_tc2(const CUtensorMap& tm, const CUtensorMap& tmo, const KPar
         if (std::atoi(e) == 4) ns = 4;
         if (std::atoi(e) == 5 && quant && smem2q_bytes(5, epi_warps, kp.tile_bytes) <= 227 * 1024) ns = 5;
     }
+    // publish mode (decoded rows reach sB through the bulk-copy engine): two decoder groups, 4-stage ring (a slot must always be
+    // decoded by the same group), 32 KB of staging; 8 epilogue warps only where that still fits (not Q8_0's 8.5 KB code slots)
+    bool pub = quant && dec_groups == 2 && kp.qpub != 0;
+    if (pub) {
+        ns = 4;
+        if (smem2q_bytes(4, epi_warps, kp.tile_bytes, true) > 227 * 1024) epi_warps = 4;
+        if (smem2q_bytes(4, epi_warps, kp.tile_bytes, true) > 227 * 1024) pub = false;
+    }
+    KParams kq = kp;
+    kq.qpub = pub ? 1 : 0;
     cfg.blockDim = dim3(NUM_THREADS);
-    cfg.dynamicSmemBytes = quant ? smem2q_bytes(ns, epi_warps, kp.tile_bytes) : SMEM2_BYTES;
+    cfg.dynamicSmemBytes = quant ? smem2q_bytes(ns, epi_warps, kp.tile_bytes, pub) : SMEM2_BYTES;
     cfg.stream = stream;
     cudaLaunchAttribute at[2];
     at[0].id = cudaLaunchAttributeClusterDimension;
@@ -1625,9 +1677,9 @@ cudaError_t launch_tc2(const CUtensorMap& tm, const CUtensorMap& tmo, const KPar
     cfg.attrs = at;
     cfg.numAttrs = pdl_enabled() ? 2 : 1;
     if (quant) {
-        if (dec_groups == 1) return ns == 5 ? launch_tc2q<5, 1, 8>(cfg, tm, tmo, kp) : launch_tc2q<4, 1, 8>(cfg, tm, tmo, kp);
-        if (epi_warps == 8) return ns == 5 ? launch_tc2q<5, 2, 8>(cfg, tm, tmo, kp) : launch_tc2q<4, 2, 8>(cfg, tm, tmo, kp);
-        return ns == 5 ? launch_tc2q<5, 2, 4>(cfg, tm, tmo, kp) : launch_tc2q<4, 2, 4>(cfg, tm, tmo, kp);
+        if (dec_groups == 1) return ns == 5 ? launch_tc2q<5, 1, 8>(cfg, tm, tmo, kq) : launch_tc2q<4, 1, 8>(cfg, tm, tmo, kq);
+        if (epi_warps == 8) return ns == 5 ? launch_tc2q<5, 2, 8>(cfg, tm, tmo, kq) : launch_tc2q<4, 2, 8>(cfg, tm, tmo, kq);
+        return ns == 5 ? launch_tc2q<5, 2, 4>(cfg, tm, tmo, kq) : launch_tc2q<4, 2, 4>(cfg, tm, tmo, kq);
     }
     return kp.warm_epi ? cudaLaunchKernelEx(&cfg, gemm_tc2_kernel<true, false>, tm, tmo, kp) : cudaLaunchKernelEx(&cfg, gemm_tc2_kernel<false, false>, tm, tmo, kp);
 }
@@ -1718,6 +1770,8 @@ cudaError_t gemm_launch(const GemmProblem& g, cudaStream_t stream, bool simt) {
     kp.trace = nullptr;
     kp.dbg = 0;
     if (const char* ed = std::getenv("ACE_B200_GEMM_DBG")) kp.dbg = std::atoi(ed);
+    kp.qpub = 0;
+    if (const char* ep = std::getenv("ACE_B200_GEMM_QPUB")) kp.qpub = std::atoi(ep) != 0;
     kp.W = static_cast<const uint8_t*>(w.dev);
     kp.wtype = w.wtype;
     kp.tile_bytes = w.tile_bytes;

@@ -95,6 +95,12 @@ __device__ __forceinline__ void tma_store_3d(const void* tmap, const void* src, 
 __device__ __forceinline__ void bulk_commit() { asm volatile("cp.async.bulk.commit_group;" ::: "memory"); }
 __device__ __forceinline__ void bulk_wait_read0() { asm volatile("cp.async.bulk.wait_group.read 0;" ::: "memory"); }
 __device__ __forceinline__ void bulk_wait0() { asm volatile("cp.async.bulk.wait_group 0;" ::: "memory"); }
+// 1-D bulk copy shared::cta -> shared (this CTA's own buffers here), completion counted on an mbarrier like a load
+__device__ __forceinline__ void bulk_copy_s2s(void* dst, const void* src, uint32_t bytes, uint64_t* bar) {
+    asm volatile("cp.async.bulk.shared::cluster.shared::cta.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];" ::"r"(smem_u32(dst)), "r"(smem_u32(src)),
+                 "r"(bytes), "r"(smem_u32(bar))
+                 : "memory");
+}
 // 1-D bulk copy global -> shared (16-byte aligned src/dst, size multiple of 16)
 __device__ __forceinline__ void bulk_load(void* dst, const void* src, uint32_t bytes, uint64_t* bar) {
     asm volatile(

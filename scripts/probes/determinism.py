@@ -66,6 +66,11 @@ if len(sys.argv) > 2 and sys.argv[2].startswith("big="):
         trial_batched("Q4_K", 16, max(4, reps // 12), {"ACE_B200_GEMM_DBG": d}, f"ACE_B200_GEMM_DBG={d}")
         trial_batched("Q4_K", 1, reps, {"ACE_B200_GEMM_DBG": d}, f"ACE_B200_GEMM_DBG={d}")
     sys.exit(0)
+if len(sys.argv) > 2 and sys.argv[2] == "pub":
+    for q in ("Q4_K", "Q6_K", "Q8_0"):
+        trial_batched(q, 16, max(4, reps // 12), {"ACE_B200_GEMM_QPUB": "1"}, "publish mode")
+        trial_batched(q, 1, reps // 2, {"ACE_B200_GEMM_QPUB": "1"}, "publish mode")
+    sys.exit(0)
 if len(sys.argv) > 2 and sys.argv[2] == "sizes":
     for q in ("Q4_K", "Q6_K", "Q8_0"):
         trial_batched(q, 1, reps, {}, "default")

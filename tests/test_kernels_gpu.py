@@ -252,6 +252,12 @@ def test_gemm_quantised_routes_agree(br, gt, shape, monkeypatch):
     single = br.debug_gemm(A, rows, w_type=gt, N=N)
     monkeypatch.delenv("ACE_B200_GEMM_2CTA")
     default = br.debug_gemm(A, rows, w_type=gt, N=N)
+    # publish mode of the pair kernel (ACE_B200_GEMM_QPUB=1): the decoded rows reach the operand tile through the bulk-copy engine
+    # instead of generic stores + a cluster-scoped fence; same MMAs in the same order -> bit-identical to the default
+    monkeypatch.setenv("ACE_B200_GEMM_QPUB", "1")
+    published = br.debug_gemm(A, rows, w_type=gt, N=N)
+    monkeypatch.delenv("ACE_B200_GEMM_QPUB")
+    assert np.array_equal(published, default)
     monkeypatch.setenv("ACE_B200_PREDECODE", "1")
     monkeypatch.setenv("ACE_B200_PREDECODE_MIN_M", "1")
     monkeypatch.setenv("ACE_B200_GEMM_2CTA", "0")

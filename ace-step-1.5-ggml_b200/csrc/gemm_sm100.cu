@@ -1110,8 +1110,11 @@ constexpr int SMEM2_BYTES = STAGES2 * STAGE2_BYTES + 8 * STG_WARP_BYTES + 2 * 25
 // (Q4_K 5120 B, Q6_K 7168 B, Q8_0 8704 B), so Q4_K affords 5 stages next to 8 transpose buffers, the others 4.
 inline __host__ __device__ int raw2_stride(int tile_bytes) { return (tile_bytes + 127) & ~127; }
 inline __host__ __device__ int raw2_total(int ns, int tile_bytes) { return (ns * raw2_stride(tile_bytes) + 1023) / 1024 * 1024; }
-inline int smem2q_bytes(int ns, int epi_warps, int tile_bytes, bool pub = false) {
-    return ns * STAGE2_BYTES + raw2_total(ns, tile_bytes) + epi_warps * STG_WARP_BYTES + 2 * 256 * 4 + 512 + (pub ? 2 * W_SUB_BYTES : 0);
+// pub: 0 = decoders write the operand tile themselves (cluster-scoped fence); 1 = publish through ONE 16 KB staging buffer per decoder group,
+// packed-code ring as deep as the stage ring; 2 = TWO staging buffers per group, packed-code ring of 3 (see gemm_tc2_kernel)
+inline __host__ __device__ int raw2_slots(int ns, int pub) { return pub == 2 ? 3 : ns; }
+inline int smem2q_bytes(int ns, int epi_warps, int tile_bytes, int pub = 0) {
+    return ns * STAGE2_BYTES + raw2_total(raw2_slots(ns, pub), tile_bytes) + epi_warps * STG_WARP_BYTES + 2 * 256 * 4 + 512 + pub * 2 * W_SUB_BYTES;
 }
 // EPIW = 8 with two decoder groups makes 18 warps (576 threads, 112 registers per thread: the epilogue spills a little more, but
 // twice as many warps share it — the K = 2048 shapes with heavy epilogues (QKV head-norm, SwiGLU) were epilogue-bound with 4)
@@ -1134,7 +1137,8 @@ gemm_tc2_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__
     uint8_t* sA = smem;                       // [NS][16 KB]
     uint8_t* sB = sA + NS * A_STAGE_BYTES;    // [NS][16 KB]  this CTA's half of the weight tile (fp16 UMMA image)
     uint8_t* sR = sB + NS * W_SUB_BYTES;      // QUANT: [NS][raw_stride] packed codes as they land
-    float* sStg = reinterpret_cast<float*>(sR + (QUANT ? raw2_total(NS, p.tile_bytes) : 0));  // [EPI_WARPS][32 x 32 fp32] epilogue transpose buffers (1 KB aligned:
+    const int nraw = QUANT ? raw2_slots(NS, p.qpub) : 1;   // depth of the packed-code ring
+    float* sStg = reinterpret_cast<float*>(sR + (QUANT ? raw2_total(nraw, p.tile_bytes) : 0));  // [EPI_WARPS][32 x 32 fp32] epilogue transpose buffers (1 KB aligned:
                                                                           // they are the 128-byte-swizzle source image of the TMA reduce-add boxes)
     float* sCol = sStg + EPI_WARPS * (STG_WARP_BYTES / 4);  // [2][256]: bias, gate of the current tile
     uint64_t* bars = reinterpret_cast<uint64_t*>(sCol + 2 * 256);
@@ -1146,7 +1150,7 @@ gemm_tc2_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__
     uint64_t* acc_full = bars + 5 * NS;  // [2] local (multicast commit)
     uint64_t* acc_empty = acc_full + 2;  // [2] leader only: the epilogue warps of the pair
     uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(acc_empty + 2);
-    uint8_t* sDec = reinterpret_cast<uint8_t*>(bars) + 512;   // QUANT + qpub: [DEC_GROUPS][16 KB] decoded rows on their way to sB
+    uint8_t* sDec = reinterpret_cast<uint8_t*>(bars) + 512;   // QUANT + qpub: [DEC_GROUPS][qpub][16 KB] decoded rows on their way to sB
     const bool pub = QUANT && p.qpub != 0;
 
     const int warp = threadIdx.x >> 5;
@@ -1199,6 +1203,7 @@ gemm_tc2_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__
         // ===================== TMA producer (both CTAs): whole warp, elected lane issues =====================
         {
             uint32_t s = 0, ph = 0;
+            uint32_t rs = 0, rph = 0;   // packed-code ring (QUANT)
             const size_t w_tile = QUANT ? (size_t)p.tile_bytes : (size_t)W_SUB_BYTES;
             const size_t sub_stride = (size_t)p.kb_total * w_tile;
             for (int t = cluster_id; t < total_tiles; t += n_clusters) {
@@ -1212,12 +1217,16 @@ gemm_tc2_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__
                 for (int kb = kb0; kb < kb1; ++kb) {
                     ptx::mbar_wait(&empty[s], ph ^ 1);
                     if (QUANT) {
-                        ptx::mbar_wait(&raw_empty[s], ph ^ 1);
+                        ptx::mbar_wait(&raw_empty[rs], rph ^ 1);
                         if (ptx::elect_one()) {
                             ptx::mbar_expect_tx(&full[s], pub ? A_STAGE_BYTES + W_SUB_BYTES : A_STAGE_BYTES);
                             ptx::tma_load_3d(sA + s * A_STAGE_BYTES, &tmA, &full[s], kc * BK, row, b);
-                            ptx::mbar_expect_tx(&raw_full[s], (uint32_t)p.tile_bytes);
-                            ptx::bulk_load(sR + s * raw_stride, wptr, p.tile_bytes, &raw_full[s]);
+                            ptx::mbar_expect_tx(&raw_full[rs], (uint32_t)p.tile_bytes);
+                            ptx::bulk_load(sR + rs * raw_stride, wptr, p.tile_bytes, &raw_full[rs]);
+                        }
+                        if (++rs == (uint32_t)nraw) {
+                            rs = 0;
+                            rph ^= 1;
                         }
                     } else {
                         if (ptx::elect_one()) {
@@ -1309,10 +1318,14 @@ gemm_tc2_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__
         // weight tiles, so "full[s] completed" means "every byte is in shared memory" for BOTH tensor cores of the pair, and the
         // writers' fence only has to cover the CTA's own copy engine (fence.proxy.async.shared::cta).  The staging buffer is free again
         // when the copy out of it has completed = the previous stage of this group is full.
-        uint8_t* myDec = sDec + grp * W_SUB_BYTES;
+        // qpub = 2: two staging buffers per group, so a group decodes and stores its next rows while the copy of the previous ones is in
+        // flight; a buffer was last used two visits = one full turn of the 4-stage ring ago, for the SAME stage, so it is free when that
+        // stage's previous phase is full.  The packed codes then live in their own ring of 3 (a slot is released as soon as its rows are
+        // in registers), which is what makes room for the second pair of buffers.
+        uint8_t* myDec = sDec + grp * p.qpub * W_SUB_BYTES;
         const int wq = (warp - DEC0) & 3;
         bool have_prev = false;
-        uint32_t prev_s = 0, prev_ph = 0;
+        uint32_t prev_s = 0, prev_ph = 0, visit = 0;
         for (int t = cluster_id; t < total_tiles; t += n_clusters) {
             int nt, sp, b, l0, kb0, kb1;
             decode_tile_index(t, nt, sp, b, l0);
@@ -1321,27 +1334,36 @@ gemm_tc2_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__
                 if (DEC_GROUPS == 2 && (int)(g & 1u) != grp) continue;
                 const uint32_t s = g % (uint32_t)NS;
                 const uint32_t ph = (g / (uint32_t)NS) & 1u;
-                ptx::mbar_wait(&raw_full[s], ph);
+                const uint32_t rs = g % (uint32_t)nraw;
+                const uint32_t rph = (g / (uint32_t)nraw) & 1u;
+                ptx::mbar_wait(&raw_full[rs], rph);
                 if (pub) {
                     uint4 out[8];   // the row is decoded into registers while the previous copy still reads the staging buffer
-                    decode_row(p.wtype, sR + s * raw_stride, row, out);
-                    if (have_prev) ptx::mbar_wait(&full[prev_s], prev_ph);
-                    store_row(myDec, row, out);
+                    decode_row(p.wtype, sR + rs * raw_stride, row, out);
+                    uint8_t* dec = myDec;
+                    if (p.qpub == 2) {
+                        dec += (visit & 1u) * W_SUB_BYTES;
+                        ptx::mbar_wait(&full[s], ph ^ 1);
+                    } else if (have_prev) {
+                        ptx::mbar_wait(&full[prev_s], prev_ph);
+                    }
+                    store_row(dec, row, out);
                     ptx::fence_proxy_async_smem();
                     __syncwarp();
                     if (lane == 0) {
-                        ptx::mbar_arrive(&raw_empty[s]);
+                        ptx::mbar_arrive(&raw_empty[rs]);
                         ptx::mbar_wait(&empty[s], ph ^ 1);   // only the copy INTO sB[s] has to wait for the MMAs that read its old contents
-                        ptx::bulk_copy_s2s(sB + s * W_SUB_BYTES + wq * 4096, myDec + wq * 4096, 4096, &full[s]);
+                        ptx::bulk_copy_s2s(sB + s * W_SUB_BYTES + wq * 4096, dec + wq * 4096, 4096, &full[s]);
                     }
                     __syncwarp();
                     have_prev = true;
                     prev_s = s;
                     prev_ph = ph;
+                    ++visit;
                     continue;
                 }
                 ptx::mbar_wait(&empty[s], ph ^ 1);
-                decode_tile(p.wtype, sR + s * raw_stride, sB + s * W_SUB_BYTES, row);
+                decode_tile(p.wtype, sR + rs * raw_stride, sB + s * W_SUB_BYTES, row);
                 // The decoded sub-tile is read by BOTH tensor cores of the pair (each CTA stages half of the 256-row weight tile): the peer's
                 // reads come through the shared::cluster window, so the writers' proxy fence must cover that window.  With the CTA-scoped
                 // fence (fence.proxy.async.shared::cta = MEMBAR.ALL.CTA + FENCE.VIEW.ASYNC.S) a tensor core occasionally consumed a
@@ -1355,7 +1377,7 @@ gemm_tc2_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__
                 __syncwarp();
                 if (lane == 0) {
                     ptx::mbar_arrive(&full[s]);
-                    ptx::mbar_arrive(&raw_empty[s]);
+                    ptx::mbar_arrive(&raw_empty[rs]);
                 }
             }
         }
@@ -1656,14 +1678,16 @@ cudaError_t launch_tc2(const CUtensorMap& tm, const CUtensorMap& tmo, const KPar
     }
     // publish mode (decoded rows reach sB through the bulk-copy engine): two decoder groups, 4-stage ring (a slot must always be
     // decoded by the same group), 32 KB of staging; 8 epilogue warps only where that still fits (not Q8_0's 8.5 KB code slots)
-    bool pub = quant && dec_groups == 2 && kp.qpub != 0;
+    int pub = (quant && dec_groups == 2) ? kp.qpub : 0;
     if (pub) {
         ns = 4;
-        if (smem2q_bytes(4, epi_warps, kp.tile_bytes, true) > 227 * 1024) epi_warps = 4;
-        if (smem2q_bytes(4, epi_warps, kp.tile_bytes, true) > 227 * 1024) pub = false;
+        if (pub == 2 && smem2q_bytes(4, 4, kp.tile_bytes, 2) > 227 * 1024) pub = 1;   // two buffers per group: Q4_K's 5 KB code slots only
+        if (pub == 2) epi_warps = 4;
+        if (smem2q_bytes(4, epi_warps, kp.tile_bytes, pub) > 227 * 1024) epi_warps = 4;
+        if (smem2q_bytes(4, epi_warps, kp.tile_bytes, pub) > 227 * 1024) pub = 0;
     }
     KParams kq = kp;
-    kq.qpub = pub ? 1 : 0;
+    kq.qpub = pub;
     cfg.blockDim = dim3(NUM_THREADS);
     cfg.dynamicSmemBytes = quant ? smem2q_bytes(ns, epi_warps, kp.tile_bytes, pub) : SMEM2_BYTES;
     cfg.stream = stream;
@@ -1771,7 +1795,7 @@ cudaError_t gemm_launch(const GemmProblem& g, cudaStream_t stream, bool simt) {
     kp.dbg = 0;
     if (const char* ed = std::getenv("ACE_B200_GEMM_DBG")) kp.dbg = std::atoi(ed);
     kp.qpub = 0;
-    if (const char* ep = std::getenv("ACE_B200_GEMM_QPUB")) kp.qpub = std::atoi(ep) != 0;
+    if (const char* ep = std::getenv("ACE_B200_GEMM_QPUB")) kp.qpub = std::max(0, std::min(2, std::atoi(ep)));
     kp.W = static_cast<const uint8_t*>(w.dev);
     kp.wtype = w.wtype;
     kp.tile_bytes = w.tile_bytes;

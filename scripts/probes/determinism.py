@@ -68,8 +68,9 @@ if len(sys.argv) > 2 and sys.argv[2].startswith("big="):
     sys.exit(0)
 if len(sys.argv) > 2 and sys.argv[2] == "pub":
     for q in ("Q4_K", "Q6_K", "Q8_0"):
-        trial_batched(q, 16, max(4, reps // 12), {"ACE_B200_GEMM_QPUB": "1"}, "publish mode")
-        trial_batched(q, 1, reps // 2, {"ACE_B200_GEMM_QPUB": "1"}, "publish mode")
+        mode = sys.argv[3] if len(sys.argv) > 3 else "1"
+        trial_batched(q, 16, max(4, reps // 12), {"ACE_B200_GEMM_QPUB": mode}, f"publish mode {mode}")
+        trial_batched(q, 1, reps // 2, {"ACE_B200_GEMM_QPUB": mode}, f"publish mode {mode}")
     sys.exit(0)
 if len(sys.argv) > 2 and sys.argv[2] == "sizes":
     for q in ("Q4_K", "Q6_K", "Q8_0"):

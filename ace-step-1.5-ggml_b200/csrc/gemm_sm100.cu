@@ -17,6 +17,7 @@
 #include <cstdlib>
 #include <algorithm>
 #include <mutex>
+#include <unordered_map>
 #include <vector>
 
 namespace ace {
@@ -1110,11 +1111,9 @@ constexpr int SMEM2_BYTES = STAGES2 * STAGE2_BYTES + 8 * STG_WARP_BYTES + 2 * 25
 // (Q4_K 5120 B, Q6_K 7168 B, Q8_0 8704 B), so Q4_K affords 5 stages next to 8 transpose buffers, the others 4.
 inline __host__ __device__ int raw2_stride(int tile_bytes) { return (tile_bytes + 127) & ~127; }
 inline __host__ __device__ int raw2_total(int ns, int tile_bytes) { return (ns * raw2_stride(tile_bytes) + 1023) / 1024 * 1024; }
-// pub: 0 = decoders write the operand tile themselves (cluster-scoped fence); 1 = publish through ONE 16 KB staging buffer per decoder group,
-// packed-code ring as deep as the stage ring; 2 = TWO staging buffers per group, packed-code ring of 3 (see gemm_tc2_kernel)
-inline __host__ __device__ int raw2_slots(int ns, int pub) { return pub == 2 ? 3 : ns; }
-inline int smem2q_bytes(int ns, int epi_warps, int tile_bytes, int pub = 0) {
-    return ns * STAGE2_BYTES + raw2_total(raw2_slots(ns, pub), tile_bytes) + epi_warps * STG_WARP_BYTES + 2 * 256 * 4 + 512 + pub * 2 * W_SUB_BYTES;
+// pub: decoders publish their rows through one 16 KB staging buffer per decoder group and the bulk-copy engine (see gemm_tc2_kernel)
+inline int smem2q_bytes(int ns, int epi_warps, int tile_bytes, bool pub = false) {
+    return ns * STAGE2_BYTES + raw2_total(ns, tile_bytes) + epi_warps * STG_WARP_BYTES + 2 * 256 * 4 + 512 + (pub ? 2 * W_SUB_BYTES : 0);
 }
 // EPIW = 8 with two decoder groups makes 18 warps (576 threads, 112 registers per thread: the epilogue spills a little more, but
 // twice as many warps share it — the K = 2048 shapes with heavy epilogues (QKV head-norm, SwiGLU) were epilogue-bound with 4)
@@ -1137,7 +1136,7 @@ gemm_tc2_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__
     uint8_t* sA = smem;                       // [NS][16 KB]
     uint8_t* sB = sA + NS * A_STAGE_BYTES;    // [NS][16 KB]  this CTA's half of the weight tile (fp16 UMMA image)
     uint8_t* sR = sB + NS * W_SUB_BYTES;      // QUANT: [NS][raw_stride] packed codes as they land
-    const int nraw = QUANT ? raw2_slots(NS, p.qpub) : 1;   // depth of the packed-code ring
+    constexpr int nraw = NS;   // the packed-code ring is as deep as the stage ring
     float* sStg = reinterpret_cast<float*>(sR + (QUANT ? raw2_total(nraw, p.tile_bytes) : 0));  // [EPI_WARPS][32 x 32 fp32] epilogue transpose buffers (1 KB aligned:
                                                                           // they are the 128-byte-swizzle source image of the TMA reduce-add boxes)
     float* sCol = sStg + EPI_WARPS * (STG_WARP_BYTES / 4);  // [2][256]: bias, gate of the current tile
@@ -1150,7 +1149,7 @@ gemm_tc2_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__
     uint64_t* acc_full = bars + 5 * NS;  // [2] local (multicast commit)
     uint64_t* acc_empty = acc_full + 2;  // [2] leader only: the epilogue warps of the pair
     uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(acc_empty + 2);
-    uint8_t* sDec = reinterpret_cast<uint8_t*>(bars) + 512;   // QUANT + qpub: [DEC_GROUPS][qpub][16 KB] decoded rows on their way to sB
+    uint8_t* sDec = reinterpret_cast<uint8_t*>(bars) + 512;   // QUANT + qpub: [DEC_GROUPS][16 KB] decoded rows on their way to sB
     const bool pub = QUANT && p.qpub != 0;
 
     const int warp = threadIdx.x >> 5;
@@ -1318,14 +1317,10 @@ gemm_tc2_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__
         // weight tiles, so "full[s] completed" means "every byte is in shared memory" for BOTH tensor cores of the pair, and the
         // writers' fence only has to cover the CTA's own copy engine (fence.proxy.async.shared::cta).  The staging buffer is free again
         // when the copy out of it has completed = the previous stage of this group is full.
-        // qpub = 2: two staging buffers per group, so a group decodes and stores its next rows while the copy of the previous ones is in
-        // flight; a buffer was last used two visits = one full turn of the 4-stage ring ago, for the SAME stage, so it is free when that
-        // stage's previous phase is full.  The packed codes then live in their own ring of 3 (a slot is released as soon as its rows are
-        // in registers), which is what makes room for the second pair of buffers.
-        uint8_t* myDec = sDec + grp * p.qpub * W_SUB_BYTES;
+        uint8_t* myDec = sDec + grp * W_SUB_BYTES;
         const int wq = (warp - DEC0) & 3;
         bool have_prev = false;
-        uint32_t prev_s = 0, prev_ph = 0, visit = 0;
+        uint32_t prev_s = 0, prev_ph = 0;
         for (int t = cluster_id; t < total_tiles; t += n_clusters) {
             int nt, sp, b, l0, kb0, kb1;
             decode_tile_index(t, nt, sp, b, l0);
@@ -1341,12 +1336,7 @@ gemm_tc2_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__
                     uint4 out[8];   // the row is decoded into registers while the previous copy still reads the staging buffer
                     decode_row(p.wtype, sR + rs * raw_stride, row, out);
                     uint8_t* dec = myDec;
-                    if (p.qpub == 2) {
-                        dec += (visit & 1u) * W_SUB_BYTES;
-                        ptx::mbar_wait(&full[s], ph ^ 1);
-                    } else if (have_prev) {
-                        ptx::mbar_wait(&full[prev_s], prev_ph);
-                    }
+                    if (have_prev) ptx::mbar_wait(&full[prev_s], prev_ph);   // the previous copy has read the staging buffer
                     store_row(dec, row, out);
                     ptx::fence_proxy_async_smem();
                     __syncwarp();
@@ -1359,7 +1349,6 @@ gemm_tc2_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__
                     have_prev = true;
                     prev_s = s;
                     prev_ph = ph;
-                    ++visit;
                     continue;
                 }
                 ptx::mbar_wait(&empty[s], ph ^ 1);
@@ -1553,6 +1542,44 @@ cudaError_t gemm_predecode(const PackedWeight& w, void* dst, cudaStream_t stream
     return cudaGetLastError();
 }
 
+// Decode pass: a packed matrix is decoded ONCE per launch into a scratch buffer of the calling stream (<= 50 MB: the largest matrix of
+// the DiT), stream-ordered in front of the GEMM, which then runs on F16 tiles.  The weights stay packed in HBM (0.94 GB for the Q4_K
+// turbo DiT, no resident twin); the decoded image is written and immediately re-read through the 126 MB L2.  This is the route for
+// launches of many rows since the in-kernel decoders of the CTA-pair kernel need a cluster-scoped proxy fence per k-block (see
+// gemm_tc2_kernel): gate_up at M = 48 000 runs 941 TFLOP/s with in-kernel decode, the decode pass + F16 kernel costs one ~20 us launch in
+// front of a 1.7 ms GEMM.  ACE_B200_DECODE_PASS=0 forbids it (in-kernel decode everywhere), ACE_B200_DECODE_PASS_MIN_M=n moves the row
+// threshold (default 2048 rows; below, the GEMMs are weight-stream / latency bound and the in-kernel decode reads 3.6x fewer bytes).
+int decode_pass_min_rows() {
+    if (const char* e = std::getenv("ACE_B200_DECODE_PASS")) if (e[0] == '0') return 0;   // read per call: tests flip it
+    if (const char* e = std::getenv("ACE_B200_DECODE_PASS_MIN_M")) if (e[0]) return std::max(1, std::atoi(e));
+    return 2048;
+}
+namespace {
+struct DecodeScratch { void* ptr = nullptr; size_t bytes = 0; };
+std::mutex g_scratch_mu;
+std::unordered_map<cudaStream_t, DecodeScratch> g_scratch;   // one per stream = per context (contexts never share a stream)
+}  // namespace
+// scratch of at least `bytes` for launches on `stream` (grown with a synchronising free; lives until process exit)
+void* decode_scratch(cudaStream_t stream, size_t bytes) {
+    std::lock_guard<std::mutex> lk(g_scratch_mu);
+    DecodeScratch& sc = g_scratch[stream];
+    if (sc.bytes < bytes) {
+        if (sc.ptr) {
+            cudaStreamSynchronize(stream);
+            cudaFree(sc.ptr);
+        }
+        sc.ptr = nullptr;
+        sc.bytes = 0;
+        if (cudaMalloc(&sc.ptr, bytes) != cudaSuccess) {
+            cudaGetLastError();
+            sc.ptr = nullptr;
+            return nullptr;
+        }
+        sc.bytes = bytes;
+    }
+    return sc.ptr;
+}
+
 bool predecode_enabled() {  // opt-in since the CTA-pair kernel decodes in shared memory at full speed (read per call: tests flip it)
     const char* e = std::getenv("ACE_B200_PREDECODE");
     return e && e[0] && e[0] != '0';
@@ -1678,16 +1705,14 @@ cudaError_t launch_tc2(const CUtensorMap& tm, const CUtensorMap& tmo, const KPar
     }
     // publish mode (decoded rows reach sB through the bulk-copy engine): two decoder groups, 4-stage ring (a slot must always be
     // decoded by the same group), 32 KB of staging; 8 epilogue warps only where that still fits (not Q8_0's 8.5 KB code slots)
-    int pub = (quant && dec_groups == 2) ? kp.qpub : 0;
+    bool pub = quant && dec_groups == 2 && kp.qpub != 0;
     if (pub) {
         ns = 4;
-        if (pub == 2 && smem2q_bytes(4, 4, kp.tile_bytes, 2) > 227 * 1024) pub = 1;   // two buffers per group: Q4_K's 5 KB code slots only
-        if (pub == 2) epi_warps = 4;
-        if (smem2q_bytes(4, epi_warps, kp.tile_bytes, pub) > 227 * 1024) epi_warps = 4;
-        if (smem2q_bytes(4, epi_warps, kp.tile_bytes, pub) > 227 * 1024) pub = 0;
+        if (smem2q_bytes(4, epi_warps, kp.tile_bytes, true) > 227 * 1024) epi_warps = 4;
+        if (smem2q_bytes(4, epi_warps, kp.tile_bytes, true) > 227 * 1024) pub = false;
     }
     KParams kq = kp;
-    kq.qpub = pub;
+    kq.qpub = pub ? 1 : 0;
     cfg.blockDim = dim3(NUM_THREADS);
     cfg.dynamicSmemBytes = quant ? smem2q_bytes(ns, epi_warps, kp.tile_bytes, pub) : SMEM2_BYTES;
     cfg.stream = stream;
@@ -1795,7 +1820,7 @@ cudaError_t gemm_launch(const GemmProblem& g, cudaStream_t stream, bool simt) {
     kp.dbg = 0;
     if (const char* ed = std::getenv("ACE_B200_GEMM_DBG")) kp.dbg = std::atoi(ed);
     kp.qpub = 0;
-    if (const char* ep = std::getenv("ACE_B200_GEMM_QPUB")) kp.qpub = std::max(0, std::min(2, std::atoi(ep)));
+    if (const char* ep = std::getenv("ACE_B200_GEMM_QPUB")) kp.qpub = std::atoi(ep) != 0;
     kp.W = static_cast<const uint8_t*>(w.dev);
     kp.wtype = w.wtype;
     kp.tile_bytes = w.tile_bytes;
@@ -1803,6 +1828,16 @@ cudaError_t gemm_launch(const GemmProblem& g, cudaStream_t stream, bool simt) {
         kp.W = static_cast<const uint8_t*>(w.dev_f16);  // compute-bound: decoded twin through the F16 kernel
         kp.wtype = W_F16;
         kp.tile_bytes = W_SUB_BYTES;
+    } else if (w.wtype != W_F16 && !simt && !gemm_force_simt() && decode_pass_min_rows() > 0 && (long)g.B * g.l_out >= decode_pass_min_rows() &&
+               w.taps == 1) {
+        // decode pass (see decode_pass_min_rows): packed -> F16 image in this stream's scratch, then the F16 kernels
+        if (void* sc = decode_scratch(stream, gemm_predecode_bytes(w))) {
+            const cudaError_t de = gemm_predecode(w, sc, stream);   // inside this launch's ProfScope: its time counts as GEMM time
+            if (de != cudaSuccess) return de;
+            kp.W = static_cast<const uint8_t*>(sc);
+            kp.wtype = W_F16;
+            kp.tile_bytes = W_SUB_BYTES;
+        }
     }
     kp.N = w.N;
     kp.n_tiles128 = w.n_tiles;

@@ -40,7 +40,7 @@ def vae_gold():
 
 
 @pytest.mark.parametrize("q", ["f32", "F16", "Q8_0", "Q4_K", "Q6_K"])
-@pytest.mark.parametrize("route", ["in_kernel_decode", "single_cta_decode", "f16_twin"])
+@pytest.mark.parametrize("route", ["in_kernel_decode", "single_cta_decode", "f16_twin", "decode_pass"])
 def test_dit_forward_vs_golden(br, root, dit_gold, q, route, monkeypatch):
     if q in ("Q4_K", "Q6_K") and not refbridge.ref_available():
         pytest.fail("K-quant GGUF export needs ggml_quantize_chunk from oracle/_ref")
@@ -51,6 +51,10 @@ def test_dit_forward_vs_golden(br, root, dit_gold, q, route, monkeypatch):
         monkeypatch.setenv("ACE_B200_PREDECODE_MIN_M", "1")
     elif route == "single_cta_decode":
         monkeypatch.setenv("ACE_B200_GEMM_2CTA", "0")
+    elif route == "decode_pass":  # per-launch decode into the stream's scratch + F16 kernels: the default from 2048 rows, forced here
+        monkeypatch.setenv("ACE_B200_DECODE_PASS_MIN_M", "1")
+    if route == "in_kernel_decode":
+        monkeypatch.setenv("ACE_B200_DECODE_PASS", "0")
     d = make_dit_dir(root, fx.TOY, 0, None if q == "f32" else q)
     inp = fx.dit_inputs(fx.TOY, 33, 7, seed=1234)
     br.load_dit(d)

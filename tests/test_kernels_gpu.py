@@ -251,6 +251,8 @@ def test_gemm_quantised_routes_agree(br, gt, shape, monkeypatch):
     monkeypatch.setenv("ACE_B200_GEMM_2CTA", "0")
     single = br.debug_gemm(A, rows, w_type=gt, N=N)
     monkeypatch.delenv("ACE_B200_GEMM_2CTA")
+    by_default = br.debug_gemm(A, rows, w_type=gt, N=N)   # >= 2048 rows: decode pass + F16 kernels, else in-kernel decode
+    monkeypatch.setenv("ACE_B200_DECODE_PASS", "0")      # in-kernel decode at every size for the rest of the test
     default = br.debug_gemm(A, rows, w_type=gt, N=N)
     # publish mode of the pair kernel (ACE_B200_GEMM_QPUB=1): the decoded rows reach the operand tile through the bulk-copy engine
     # instead of generic stores + a cluster-scoped fence; same MMAs in the same order -> bit-identical to the default
@@ -266,6 +268,7 @@ def test_gemm_quantised_routes_agree(br, gt, shape, monkeypatch):
     ref = tap_gemm_ref(h16(A), dequant_ref(rows, gt, N, K).astype(np.float64)[:, None, :], 1, 0, 0, L)
     assert rel_err(twin, ref) < 2e-3
     assert np.isfinite(default).all() and np.abs(default - single).max() <= 1e-5 * np.abs(ref).max(), np.abs(default - single).max()
+    assert np.abs(by_default - single).max() <= 1e-5 * np.abs(ref).max(), np.abs(by_default - single).max()
 
 
 @pytest.mark.parametrize("route", ["single", "pair"])

@@ -212,7 +212,7 @@ def test_vae_240s_batch_members_are_independent_and_routes_agree(br, monkeypatch
 
 # ---------------------------------------------------------------- run-to-run determinism of the quantised path at configs[2] sizes
 
-def test_config2_evaluations_are_bit_reproducible(br, q4k):
+def test_config2_evaluations_are_bit_reproducible(br, q4k, monkeypatch):
     """Identical calls give identical bits.  Before the decoders of the CTA-pair GEMM fenced their decoded sub-tile for the peer's tensor
     core (fence.proxy.async.shared::cluster; gemm_sm100.cu), a tensor core occasionally read a sub-tile that was not completely visible:
     13 distinct results in 60 single evaluations at M = 3000 and 8 in 12 calls of the 16-evaluation batch at M = 48 000, each off by
@@ -229,3 +229,12 @@ def test_config2_evaluations_are_bit_reproducible(br, q4k):
     assert np.isfinite(outs[0]).all()
     for o in outs[1:]:
         assert np.array_equal(o, outs[0]), metrics(o, outs[0])
+    # the same with in-kernel decode at every size (ACE_B200_DECODE_PASS=0: the fenced CTA-pair decoders, the route of < 2048 rows)
+    monkeypatch.setenv("ACE_B200_DECODE_PASS", "0")
+    seen = {hashlib.md5(br.dit_forward_tfirst(h[0], c[0], e[0], None, None, 0.3, 0.3).tobytes()).hexdigest() for _ in range(30)}
+    assert len(seen) == 1, f"in-kernel decode: {len(seen)} distinct outputs in 30 identical single evaluations"
+    inner = [br.dit_forward_batched(hb, cb, eb, None, None, ts, ts) for _ in range(4)]
+    for o in inner[1:]:
+        assert np.array_equal(o, inner[0]), metrics(o, inner[0])
+    m = metrics(inner[0], outs[0])   # the two routes feed the tensor cores the same fp16 operands
+    assert m["rel_l2"] <= NOISE, m

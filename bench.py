@@ -376,7 +376,7 @@ def run_dit_workload(a, wl, world, rank, local, dist):
             traffic = json.load(open(os.path.join(ROOT, "profiles", "roofline_traffic.json"))).get(f"gemm_bytes_per_launch_{a.workload}")
         except Exception:
             pass
-        roofline = {"bound": "tensor", "kernel": "gemm_tc2_kernel / gemm_tc_kernel (tcgen05 tap-GEMM family)", "achieved": ach, "peak": peak, "unit": "TFLOP/s",
+        roofline = {"bound": "tensor", "kernel": "gemm_tc2_kernel / gemm_tc_kernel (tcgen05 tap-GEMM family; packed weights of launches >= 2048 rows are decoded per launch by predecode_kernel, whose time is inside the family)", "achieved": ach, "peak": peak, "unit": "TFLOP/s",
                     "frac": ach / peak, "traffic": traffic, "peak_source": f"{peak_kind}: bf16_tflops_sustained (kernel timed inside a long step)",
                     "avg_launch_us": 1e3 * gm["ms"] / max(gm["launches"], 1), "launches": gm["launches"],
                     "flops_per_launch": gm["flops"] / max(gm["launches"], 1),

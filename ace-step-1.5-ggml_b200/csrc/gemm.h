@@ -69,16 +69,21 @@ struct GemmProblem {
 // (same operands, same epilogue) that the tensor-core kernel is unit-tested against.
 cudaError_t gemm_launch(const GemmProblem& p, cudaStream_t stream, bool simt = false);
 
-// Quantised weights are decoded IN THE GEMM: packed codes land in shared memory by TMA bulk copy, decoder warps expand them to
-// the fp16 UMMA tile, tcgen05 consumes it (single-CTA kernel for one row tile, CTA-pair kernel — one sub-tile decoded per CTA
-// per k-block — beyond).  The decoded F16 twin of round 1 survives as an opt-in A/B route: ACE_B200_PREDECODE=1 decodes every
-// quantised weight once at load (gemm_predecode, same decoder code, +3.15 GB for the turbo DiT) and GEMMs with
-// >= predecode_min_rows() rows (ACE_B200_PREDECODE_MIN_M, default 256) read it through the F16 kernels.  Both routes feed the
-// tensor cores bit-identical operands (tests/test_kernels_gpu.py).
+// Quantised weights stay packed in HBM.  Three routes feed the tensor cores bit-identical fp16 operands (tests/test_kernels_gpu.py,
+// test_golden_gpu.py, test_y_full_size_properties_gpu.py):
+//   * launches of < decode_pass_min_rows() rows (default 2048): decoded IN THE GEMM — packed codes land in shared memory by TMA bulk copy,
+//     decoder warps expand them to the fp16 UMMA tile, tcgen05 consumes it (single-CTA kernel for one row tile, CTA-pair kernel beyond;
+//     the pair's decoders need a cluster-scoped proxy fence because the peer's tensor core reads their tile: gemm_sm100.cu);
+//   * launches of >= decode_pass_min_rows() rows: DECODE PASS — the matrix of this launch is decoded by predecode_kernel into a <= 50 MB
+//     scratch of the calling stream, stream-ordered in front of the GEMM, which runs the F16 CTA-pair kernel (ACE_B200_DECODE_PASS=0
+//     forbids it, ACE_B200_DECODE_PASS_MIN_M moves the threshold);
+//   * opt-in A/B route of round 1: ACE_B200_PREDECODE=1 decodes every quantised weight once at load (a resident F16 twin, +3.15 GB for the
+//     turbo DiT) and GEMMs with >= predecode_min_rows() rows (ACE_B200_PREDECODE_MIN_M, default 256) read it through the F16 kernels.
 size_t      gemm_predecode_bytes(const PackedWeight& w);
 cudaError_t gemm_predecode(const PackedWeight& w, void* dst, cudaStream_t stream);
 bool        predecode_enabled();
 int         predecode_min_rows();
+int         decode_pass_min_rows();   // 0 = decode pass forbidden
 
 // true when ACE_B200_GEMM=simt is set (debug bisecting aid; never the default)
 bool gemm_force_simt();

@@ -11,15 +11,18 @@
 // traffic plus the k7 kernel's store) disappears and the remaining three streams ride under the k7 MMAs.
 // The arithmetic is the unfused kernels' to the bit: same MMA order, h rounded to fp16 before the second MMA, (acc + bias) + x in fp32.
 //
-// CTA = 10 warps, persistent over 128-row tiles, one CTA per SM:
+// CTA = 10 warps, persistent; by default a CLUSTER OF TWO CTAs (cta_group::2, M = 256) works on 256-row items, CTA r owning rows 128 r..
+// (template PAIR; the single-CTA variant on 128-row tiles is kept behind ACE_B200_VAE_FUSE=1):
 //   warps 0-7  epilogue: warp w owns TMEM lanes 32 (w & 3).. and the 64-column half (w >> 2) of both accumulators
-//   warp  8    TMA producer: activation slab per tile (double-buffered), weight ring (slot = the two 64-channel k-blocks of a tap;
-//              the k1 weights travel through the same ring, one slot per tile)
-//   warp  9    TMEM allocator + tcgen05.mma issuer.  Issue order  MMA1(0) | MMA1(1) MMA2(0) | MMA1(2) MMA2(1) | ... : the second
-//              MMA of a tile is issued one tile late, so the tensor pipe never waits for the epilogue pass that produces h.
-// Epilogue order per iteration i:  pass 2 of tile i-1 (acc2 -> x', xs -> TMA stores), residual prefetch of tile i (registers),
-// pass 1 of tile i (acc1 -> h in shared memory).  A warp's 32 x 64 block of h is one contiguous 4 KB piece of the K-major
-// SWIZZLE_128B operand image AND exactly a {64, 32} TMA store box, so the same 4 KB stages x' and xs on their way out.
+//   warp  8    TMA producer: activation slab per item (double-buffered), weight ring (slot = the two 64-channel k-blocks of a tap, a pair
+//              CTA stages half of each; the k1 weights travel through the same ring, one slot per item)
+//   warp  9    TMEM allocator + tcgen05.mma issuer (leader CTA; CTA 1's warp 9 relays its "landed" barriers to the leader).  Issue order
+//              MMA1(0) | MMA1(1) MMA2(0) | MMA1(2) MMA2(1) | ... : the second MMA of an item is issued one item late, so the tensor pipe
+//              never waits for the epilogue pass that produces h.
+// h: pair — pass 1 writes it as fp16 pairs into TENSOR MEMORY (columns 384.., double-buffered by item parity) and the second MMA takes its
+// A operand from there; single CTA — a K-major SWIZZLE_128B image in shared memory, whose 4 KB per warp doubles as the staging slice of
+// the {64, 32} TMA store boxes that carry x' and xs out.  Epilogue order per iteration i (pair): pass 1 of item i, then pass 2 of item
+// i - 1 (its second MMA was issued an iteration ago); the "h ready" barriers are therefore per item parity (see below).
 #include "vae.h"
 #include "gemm.h"
 #include "kernels.h"

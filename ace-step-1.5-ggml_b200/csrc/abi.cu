@@ -368,7 +368,10 @@ void ace_ggml_destroy(ace_ggml_context* ctx) {
         for (void* p : ctx->dbg_allocs) cudaFree(p);
         if (ctx->ev0) cudaEventDestroy(ctx->ev0);
         if (ctx->ev1) cudaEventDestroy(ctx->ev1);
-        if (ctx->stream) cudaStreamDestroy(ctx->stream);
+        if (ctx->stream) {
+            ace::decode_scratch_release(ctx->stream);
+            cudaStreamDestroy(ctx->stream);
+        }
     }
     delete ctx;
 }

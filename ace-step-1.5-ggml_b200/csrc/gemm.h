@@ -84,6 +84,7 @@ cudaError_t gemm_predecode(const PackedWeight& w, void* dst, cudaStream_t stream
 bool        predecode_enabled();
 int         predecode_min_rows();
 int         decode_pass_min_rows();   // 0 = decode pass forbidden
+void        decode_scratch_release(cudaStream_t stream);   // frees the decode-pass scratch of a stream about to be destroyed
 
 // true when ACE_B200_GEMM=simt is set (debug bisecting aid; never the default)
 bool gemm_force_simt();

@@ -1559,7 +1559,18 @@ struct DecodeScratch { void* ptr = nullptr; size_t bytes = 0; };
 std::mutex g_scratch_mu;
 std::unordered_map<cudaStream_t, DecodeScratch> g_scratch;   // one per stream = per context (contexts never share a stream)
 }  // namespace
-// scratch of at least `bytes` for launches on `stream` (grown with a synchronising free; lives until process exit)
+// called by the owner of `stream` before it destroys the stream (a later stream may reuse the handle value, possibly on another device)
+void decode_scratch_release(cudaStream_t stream) {
+    std::lock_guard<std::mutex> lk(g_scratch_mu);
+    auto it = g_scratch.find(stream);
+    if (it == g_scratch.end()) return;
+    if (it->second.ptr) {
+        cudaStreamSynchronize(stream);
+        cudaFree(it->second.ptr);
+    }
+    g_scratch.erase(it);
+}
+// scratch of at least `bytes` for launches on `stream` (grown with a synchronising free; released with the stream's context)
 void* decode_scratch(cudaStream_t stream, size_t bytes) {
     std::lock_guard<std::mutex> lk(g_scratch_mu);
     DecodeScratch& sc = g_scratch[stream];

@@ -1,6 +1,15 @@
 #!/usr/bin/env python
-"""Run-to-run determinism of one full DiT evaluation (turbo dims, T = 6000) under the route switches: N identical calls, how many
-distinct outputs?   python scripts/probes/determinism.py [reps]"""
+"""Run-to-run determinism of full DiT evaluations (turbo dims, T = 6000): N identical calls, how many distinct outputs?
+
+    python scripts/probes/determinism.py [reps]            one evaluation (M = 3000) under the route switches, Q4_K / F16 / Q8_0
+    python scripts/probes/determinism.py [reps] sizes      batches of 1 / 2 / 16 evaluations (M = 3000 / 6000 / 48 000), Q4_K / Q6_K / Q8_0
+    python scripts/probes/determinism.py [reps] pub        the publish mode of the pair kernel (ACE_B200_GEMM_QPUB=1)
+    python scripts/probes/determinism.py [reps] fix        in-kernel decode (ACE_B200_DECODE_PASS=0): cluster-scoped decoder fence vs the
+                                                           CTA-scoped one (ACE_B200_GEMM_DBG=1) that let a tensor core read a stale sub-tile
+
+This is the probe that found and bisected the visibility race of the CTA-pair kernel's in-kernel decoders (DESIGN.md 4.1,
+profiles/r2_determinism_investigation.log; the investigation build had more ACE_B200_GEMM_DBG bits — fence placements in the relay / the
+leader / one lane per warp — than the library keeps)."""
 import hashlib
 import os
 import sys
@@ -61,45 +70,27 @@ def trial_batched(quant, B, n, env, label):
     br.close()
 
 
-if len(sys.argv) > 2 and sys.argv[2].startswith("big="):
-    for d in sys.argv[2][4:].split(","):
-        trial_batched("Q4_K", 16, max(4, reps // 12), {"ACE_B200_GEMM_DBG": d}, f"ACE_B200_GEMM_DBG={d}")
-        trial_batched("Q4_K", 1, reps, {"ACE_B200_GEMM_DBG": d}, f"ACE_B200_GEMM_DBG={d}")
-    sys.exit(0)
 if len(sys.argv) > 2 and sys.argv[2] == "pub":
     for q in ("Q4_K", "Q6_K", "Q8_0"):
-        mode = sys.argv[3] if len(sys.argv) > 3 else "1"
-        trial_batched(q, 16, max(4, reps // 12), {"ACE_B200_GEMM_QPUB": mode}, f"publish mode {mode}")
-        trial_batched(q, 1, reps // 2, {"ACE_B200_GEMM_QPUB": mode}, f"publish mode {mode}")
+        env = {"ACE_B200_GEMM_QPUB": "1", "ACE_B200_DECODE_PASS": "0"}
+        trial_batched(q, 16, max(4, reps // 12), env, "publish mode")
+        trial_batched(q, 1, reps // 2, env, "publish mode")
     sys.exit(0)
 if len(sys.argv) > 2 and sys.argv[2] == "sizes":
     for q in ("Q4_K", "Q6_K", "Q8_0"):
         trial_batched(q, 1, reps, {}, "default")
         trial_batched(q, 2, reps // 2, {}, "default")
     trial_batched("Q4_K", 16, max(4, reps // 12), {}, "default")
-    trial_batched("Q4_K", 1, reps, {"ACE_B200_GEMM_QNS": "5"}, "5-stage ring forced")
-    sys.exit(0)
-if len(sys.argv) > 2 and sys.argv[2].startswith("dbg="):
-    for d in sys.argv[2][4:].split(","):
-        trial("Q4_K", {"ACE_B200_GEMM_DBG": d}, f"ACE_B200_GEMM_DBG={d}")
     sys.exit(0)
 if len(sys.argv) > 2 and sys.argv[2] == "fix":
-    trial("Q4_K", {}, "default (fence.proxy.async)")
-    trial("Q4_K", {"ACE_B200_GEMM_DBG": "16"}, "fence.proxy.async.shared::cluster")
-    trial("Q4_K", {"ACE_B200_GEMM_DBG": "1"}, "fence.proxy.async.shared::cta (old)")
+    trial("Q4_K", {"ACE_B200_DECODE_PASS": "0"}, "in-kernel decode, cluster-scoped fence")
+    trial("Q4_K", {"ACE_B200_DECODE_PASS": "0", "ACE_B200_GEMM_DBG": "1"}, "in-kernel decode, CTA-scoped fence (racy)")
+    trial_batched("Q4_K", 16, max(4, reps // 12), {"ACE_B200_DECODE_PASS": "0"}, "in-kernel, cluster fence")
+    trial_batched("Q4_K", 16, max(4, reps // 12), {"ACE_B200_DECODE_PASS": "0", "ACE_B200_GEMM_DBG": "1"}, "in-kernel, CTA fence (racy)")
     sys.exit(0)
-if len(sys.argv) > 2 and sys.argv[2] == "bisect":
-    trial("Q4_K", {}, "default")
-    trial("Q4_K", {"ACE_B200_GEMM_QNS": "4"}, "4-stage ring")
-    trial("Q4_K", {"ACE_B200_GEMM_DBG": "1"}, "decoders: fence.proxy.async (all spaces)")
-    trial("Q4_K", {"ACE_B200_GEMM_DBG": "2"}, "relay: fence.acq_rel.cluster")
-    trial("Q4_K", {"ACE_B200_GEMM_DBG": "64"}, "leader: acquire.cluster wait on peer_full")
-    trial("Q4_K", {"ACE_B200_GEMM_DBG": "4"}, "epilogue: wait_group.read after every reduce")
-    trial("Q4_K", {"ACE_B200_GEMM_DBG": "8"}, "epilogue: wait_group after every reduce")
-    trial("Q6_K", {}, "Q6_K default")
-    sys.exit(0)
-trial("Q4_K", {}, "default")
-trial("Q4_K", {"ACE_B200_GEMM_2CTA": "0"}, "single-CTA GEMMs")
+trial("Q4_K", {}, "default (decode pass from 2048 rows)")
+trial("Q4_K", {"ACE_B200_DECODE_PASS": "0"}, "in-kernel decode everywhere")
+trial("Q4_K", {"ACE_B200_DECODE_PASS": "0", "ACE_B200_GEMM_2CTA": "0"}, "single-CTA GEMMs, in-kernel decode")
 trial("Q4_K", {"ACE_B200_PREDECODE": "1"}, "F16 twin through the pair kernel")
 trial("Q4_K", {"ACE_B200_ATTN": "tc4"}, "attention: smem-P kernel")
 trial("Q4_K", {"ACE_B200_ATTN": "mma"}, "attention: mma.sync kernel")
